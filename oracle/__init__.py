@@ -1,0 +1,248 @@
+"""ctypes binding of the CPU oracle (oracle/orb_oracle.cpp).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs.  The product package
+(vi_slam_b200) never imports this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_build", "liborb_oracle.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+
+def build(force: bool = False) -> str:
+    src = os.path.join(_HERE, "orb_oracle.cpp")
+    if force or not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < os.path.getmtime(src):
+        subprocess.run(["make", "-C", _HERE, "-s"] + (["-B"] if force else []), check=True)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            build()
+        L = C.CDLL(LIB_PATH)
+        u8p, i32p, f32p = C.POINTER(C.c_uint8), C.POINTER(C.c_int32), C.POINTER(C.c_float)
+        L.orc_extractor_create.restype = C.c_void_p
+        L.orc_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orc_extractor_destroy.argtypes = [C.c_void_p]
+        L.orc_tables.argtypes = [C.c_void_p, f32p, f32p, f32p, f32p, i32p, i32p]
+        L.orc_extract.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                  C.c_void_p, u8p, C.c_int, i32p]
+        L.orc_level_size.argtypes = [C.c_void_p, C.c_int, i32p, i32p]
+        L.orc_level_image.argtypes = [C.c_void_p, C.c_int, u8p]
+        L.orc_level_blurred.argtypes = [C.c_void_p, C.c_int, u8p]
+        L.orc_level_candidates.argtypes = [C.c_void_p, C.c_int, i32p, C.c_int]
+        L.orc_level_keypoints.argtypes = [C.c_void_p, C.c_int, i32p, f32p, C.c_int]
+        L.orc_tie_events.restype = C.c_long
+        L.orc_tie_events.argtypes = [C.c_void_p]
+        L.orc_resize_linear.argtypes = [u8p, C.c_int, C.c_int, C.c_int, u8p, C.c_int, C.c_int, C.c_int]
+        L.orc_gaussian7.argtypes = [u8p, C.c_int, C.c_int, C.c_int, u8p, C.c_int]
+        L.orc_fast.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, i32p, C.c_int]
+        L.orc_fast_atan2.restype = C.c_float
+        L.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
+        L.orc_fast_atan2_array.argtypes = [f32p, f32p, f32p, C.c_int]
+        L.orc_sincos_deg.argtypes = [f32p, f32p, f32p, C.c_int]
+        L.orc_descriptor_distance.argtypes = [u8p, u8p]
+        L.orc_knn2.argtypes = [u8p, C.c_int, u8p, C.c_int, i32p, i32p, C.c_int]
+        L.orc_ratio_filter.argtypes = [i32p, i32p, C.c_int, C.c_double, C.c_int, i32p]
+        L.orc_dedup_by_train.argtypes = [i32p, C.c_int]
+        L.orc_stereo_match.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, u8p, C.c_int, C.c_void_p, u8p, C.c_int,
+                                       C.c_float, C.c_float, f32p, f32p, i32p, i32p]
+        L.orc_bench_frames.restype = C.c_long
+        L.orc_bench_frames.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, u8p, C.c_int, C.c_int, C.c_int,
+                                       C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.POINTER(C.c_long)]
+        _lib = L
+    return _lib
+
+
+def _u8(a):
+    return a.ctypes.data_as(C.POINTER(C.c_uint8))
+
+
+def _i32(a):
+    return a.ctypes.data_as(C.POINTER(C.c_int32))
+
+
+def _f32(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+class OracleExtractor:
+    """CPU restatement of FExtractor (reference include/vi_slam/geometry/fextractor.h:26-64)."""
+
+    def __init__(self, nfeatures=2000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.nfeatures, self.nlevels = nfeatures, nlevels
+        self._h = lib().orc_extractor_create(nfeatures, scale_factor, nlevels, ini_th, min_th)
+        n = nlevels
+        self.scale = np.zeros(n, np.float32)
+        self.inv_scale = np.zeros(n, np.float32)
+        self.sigma2 = np.zeros(n, np.float32)
+        self.inv_sigma2 = np.zeros(n, np.float32)
+        self.features_per_level = np.zeros(n, np.int32)
+        self.umax = np.zeros(16, np.int32)
+        lib().orc_tables(self._h, _f32(self.scale), _f32(self.inv_scale), _f32(self.sigma2), _f32(self.inv_sigma2),
+                         _i32(self.features_per_level), _i32(self.umax))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_extractor_destroy(self._h)
+            self._h = None
+
+    def compute(self, image: np.ndarray, lapping=(0, 0)):
+        """-> (mono_index, keypoints[KP_DTYPE], descriptors uint8[n,32]); mono_index -1 on empty image."""
+        if image is None or image.size == 0:
+            return -1, np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        assert image.dtype == np.uint8 and image.ndim == 2
+        h, w = image.shape
+        step = image.strides[0]
+        assert image.strides[1] == 1
+        cap = self.nfeatures + 64
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        mono = C.c_int32(0)
+        n = lib().orc_extract(self._h, _u8(image), w, h, step, int(lapping[0]), int(lapping[1]),
+                              kps.ctypes.data, _u8(desc), cap, C.byref(mono))
+        if n < 0:
+            return -1, kps[:0], desc[:0]
+        assert n <= cap
+        return mono.value, kps[:n].copy(), desc[:n].copy()
+
+    def level_image(self, l):
+        w, h = C.c_int32(), C.c_int32()
+        lib().orc_level_size(self._h, l, C.byref(w), C.byref(h))
+        out = np.zeros((h.value, w.value), np.uint8)
+        lib().orc_level_image(self._h, l, _u8(out))
+        return out
+
+    def level_blurred(self, l):
+        w, h = C.c_int32(), C.c_int32()
+        lib().orc_level_size(self._h, l, C.byref(w), C.byref(h))
+        out = np.zeros((h.value, w.value), np.uint8)
+        if lib().orc_level_blurred(self._h, l, _u8(out)) != 0:
+            return None
+        return out
+
+    def level_candidates(self, l):
+        cap = 1 << 20
+        buf = np.zeros((cap, 3), np.int32)
+        n = lib().orc_level_candidates(self._h, l, _i32(buf), cap)
+        return buf[:n].copy()
+
+    def level_keypoints(self, l):
+        cap = self.nfeatures + 64
+        buf = np.zeros((cap, 3), np.int32)
+        ang = np.zeros(cap, np.float32)
+        n = lib().orc_level_keypoints(self._h, l, _i32(buf), _f32(ang), cap)
+        return buf[:n].copy(), ang[:n].copy()
+
+    @property
+    def tie_events(self):
+        return lib().orc_tie_events(self._h)
+
+
+def resize_linear(src: np.ndarray, dw: int, dh: int) -> np.ndarray:
+    src = np.ascontiguousarray(src)
+    dst = np.zeros((dh, dw), np.uint8)
+    lib().orc_resize_linear(_u8(src), src.shape[1], src.shape[0], src.shape[1], _u8(dst), dw, dh, dw)
+    return dst
+
+
+def gaussian7(src: np.ndarray) -> np.ndarray:
+    src = np.ascontiguousarray(src)
+    dst = np.zeros_like(src)
+    lib().orc_gaussian7(_u8(src), src.shape[1], src.shape[0], src.shape[1], _u8(dst), src.shape[1])
+    return dst
+
+
+def fast(img: np.ndarray, threshold: int) -> np.ndarray:
+    img = np.ascontiguousarray(img)
+    cap = img.size
+    buf = np.zeros((cap, 3), np.int32)
+    n = lib().orc_fast(_u8(img), img.shape[1], img.shape[0], img.shape[1], threshold, _i32(buf), cap)
+    return buf[:n].copy()
+
+
+def fast_atan2(y: np.ndarray, x: np.ndarray) -> np.ndarray:
+    y = np.ascontiguousarray(y, np.float32)
+    x = np.ascontiguousarray(x, np.float32)
+    out = np.zeros_like(y)
+    lib().orc_fast_atan2_array(_f32(y), _f32(x), _f32(out), y.size)
+    return out
+
+
+def sincos_deg(deg: np.ndarray):
+    deg = np.ascontiguousarray(deg, np.float32)
+    c = np.zeros_like(deg)
+    s = np.zeros_like(deg)
+    lib().orc_sincos_deg(_f32(deg), _f32(c), _f32(s), deg.size)
+    return c, s
+
+
+def descriptor_distance(a: np.ndarray, b: np.ndarray) -> int:
+    a = np.ascontiguousarray(a, np.uint8)
+    b = np.ascontiguousarray(b, np.uint8)
+    return lib().orc_descriptor_distance(_u8(a), _u8(b))
+
+
+def knn2(q: np.ndarray, t: np.ndarray, nthreads: int = 1):
+    q = np.ascontiguousarray(q, np.uint8)
+    t = np.ascontiguousarray(t, np.uint8)
+    idx = np.full((q.shape[0], 2), -1, np.int32)
+    dist = np.full((q.shape[0], 2), -1, np.int32)
+    lib().orc_knn2(_u8(q), q.shape[0], _u8(t), t.shape[0], _i32(idx), _i32(dist), nthreads)
+    return idx, dist
+
+
+def ratio_filter(idx, dist, ratio: float, rule: int) -> np.ndarray:
+    idx = np.ascontiguousarray(idx, np.int32)
+    dist = np.ascontiguousarray(dist, np.int32)
+    out = np.zeros((idx.shape[0], 3), np.int32)
+    n = lib().orc_ratio_filter(_i32(idx), _i32(dist), idx.shape[0], ratio, rule, _i32(out))
+    return out[:n].copy()
+
+
+def dedup_by_train(m: np.ndarray) -> np.ndarray:
+    m = np.ascontiguousarray(m, np.int32).copy()
+    n = lib().orc_dedup_by_train(_i32(m), m.shape[0])
+    return m[:n].copy()
+
+
+def stereo_match(ex_l: OracleExtractor, ex_r: OracleExtractor, kl, dl, kr, dr, bf: float, b: float):
+    kl = np.ascontiguousarray(kl)
+    kr = np.ascontiguousarray(kr)
+    dl = np.ascontiguousarray(dl)
+    dr = np.ascontiguousarray(dr)
+    n = kl.shape[0]
+    u_right = np.zeros(n, np.float32)
+    depth = np.zeros(n, np.float32)
+    bidx = np.zeros(n, np.int32)
+    bdist = np.zeros(n, np.int32)
+    lib().orc_stereo_match(ex_l._h, ex_r._h, kl.ctypes.data, _u8(dl), n, kr.ctypes.data, _u8(dr), kr.shape[0],
+                           bf, b, _f32(u_right), _f32(depth), _i32(bidx), _i32(bdist))
+    return u_right, depth, bidx, bdist
+
+
+def bench_frames(frames: np.ndarray, nfeatures=2000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7,
+                 lapping=(0, 0), stereo=False, bf=386.1448, b=0.5371657, nthreads=1):
+    """Timed CPU baseline body: returns (total keypoints, matches)."""
+    frames = np.ascontiguousarray(frames)
+    n, h, w = frames.shape
+    nm = C.c_long(0)
+    tot = lib().orc_bench_frames(nfeatures, scale_factor, nlevels, ini_th, min_th, _u8(frames), n, w, h,
+                                 int(lapping[0]), int(lapping[1]), int(stereo), bf, b, nthreads, C.byref(nm))
+    return tot, nm.value
