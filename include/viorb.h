@@ -1,0 +1,160 @@
+/* viorb.h — C ABI of the B200-native ORB front-end (libviorb.so).
+ *
+ * Drop-in boundary for the feature path of KMS-TEAM/vi_slam.  Every entry point
+ * names the reference interface it replaces (paths relative to the reference
+ * repository).  Plain pointers and sizes only; no C++/torch types; no exceptions
+ * cross this boundary.  All functions return VIORB_OK (0) or a negative
+ * viorb_status; viorb_last_error() gives a thread-local message.
+ *
+ * Threading contract (reference src/datastructures/frame.cpp:107-111): one
+ * extractor handle per camera; different handles may be driven concurrently
+ * from different host threads (each owns its CUDA stream and arenas); a single
+ * handle must not be entered concurrently.
+ */
+#ifndef VIORB_H_
+#define VIORB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum viorb_status {
+    VIORB_OK = 0,
+    VIORB_E_EMPTY = -1,        /* empty image: FExtractor::compute returns -1 (fextractor.cpp:1037) */
+    VIORB_E_ARG = -2,
+    VIORB_E_CUDA = -3,
+    VIORB_E_CAPACITY = -4,     /* caller buffer / handle arena too small; sizes are reported */
+    VIORB_E_NO_DEVICE = -5
+} viorb_status;
+
+/* cv::KeyPoint, 28-byte POD (what FExtractor::compute fills, fextractor.cpp:1108-1129):
+ * pt in level-0 pixels, size = int(31*scale[octave]), angle in degrees [0,360),
+ * response = FAST score, class_id = -1. */
+typedef struct viorb_keypoint {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} viorb_keypoint;
+
+/* cv::DMatch-shaped result row (queryIdx, trainIdx, distance as integer Hamming). */
+typedef struct viorb_match {
+    int32_t query_idx, train_idx, distance;
+} viorb_match;
+
+/* FExtractor ctor arguments (include/vi_slam/geometry/fextractor.h:30-31, values from
+ * Tracking::ParseORBParamFile, src/core/tracking.cpp:1020-1100) plus arena sizing. */
+typedef struct viorb_params {
+    int32_t nfeatures;      /* ORBextractor.nFeatures (2000; 5x for the mono initialiser) */
+    float scale_factor;     /* ORBextractor.scaleFactor (1.2) */
+    int32_t nlevels;        /* ORBextractor.nLevels (8), <= 16 */
+    int32_t ini_th_fast;    /* ORBextractor.iniThFAST (20) */
+    int32_t min_th_fast;    /* ORBextractor.minThFAST (7) */
+    int32_t max_width;      /* largest image this handle will see */
+    int32_t max_height;
+    int32_t max_batch;      /* frames per extract_batch call (>= 1) */
+    int32_t device;         /* CUDA device ordinal */
+} viorb_params;
+
+typedef struct viorb_extractor viorb_extractor;
+
+const char* viorb_last_error(void);
+const char* viorb_version(void);
+
+/* ---- extractor: replaces class FExtractor (fextractor.h:26-64) ------------------------- */
+
+/* FExtractor::FExtractor (fextractor.cpp:401-461). */
+int viorb_extractor_create(const viorb_params* params, viorb_extractor** out);
+void viorb_extractor_destroy(viorb_extractor* ex);
+
+/* GetLevels/GetScaleFactor(s)/GetInverseScaleFactors/GetScaleSigmaSquares/
+ * GetInverseScaleSigmaSquares (fextractor.h:40-62) and mnFeaturesPerLevel. Any pointer may be NULL. */
+int viorb_extractor_tables(const viorb_extractor* ex, int32_t* nlevels, float* scale, float* inv_scale,
+                           float* sigma2, float* inv_sigma2, int32_t* features_per_level);
+
+/* Upper bound of keypoints one frame can produce (sum over levels of N_l + slack). */
+int viorb_extractor_capacity(const viorb_extractor* ex);
+
+/* FExtractor::compute (fextractor.cpp:1034-1133) for one host image (CV_8UC1, row step `step`).
+ * lap0/lap1 = vLappingArea.  Writes up to `cap` keypoints/descriptors (row i of desc belongs to
+ * keypoint i), *n_out = keypoint count, *mono_index_out = compute()'s return value.
+ * Returns VIORB_E_EMPTY for an empty image (the reference returns -1). */
+int viorb_extract(viorb_extractor* ex, const uint8_t* img, int width, int height, int step,
+                  int lap0, int lap1, viorb_keypoint* kps, uint8_t* desc, int cap,
+                  int* n_out, int* mono_index_out);
+
+/* The same for n host images of one size (frame-batch path of BASELINE.json config 4).
+ * imgs[i] points to image i; outputs are [n][cap] / [n][cap][32] / [n]. */
+int viorb_extract_batch(viorb_extractor* ex, const uint8_t* const* imgs, int n, int width, int height, int step,
+                        int lap0, int lap1, viorb_keypoint* kps, uint8_t* desc, int cap,
+                        int* n_out, int* mono_index_out);
+
+/* Device-resident variant: n images already in HBM at d_imgs + i*frame_stride, row step `step`
+ * (step % 16 == 0 and 16-byte aligned base).  Results stay on the device inside the handle until the
+ * next extract call; fetch them with viorb_fetch / use them with the *_resident matchers.
+ * The image buffer must stay valid while the results are used (it is pyramid level 0). */
+int viorb_extract_device(viorb_extractor* ex, const uint8_t* d_imgs, int n, int width, int height, int step,
+                         size_t frame_stride, int lap0, int lap1);
+/* Copies the resident results of frame `frame` to host buffers. */
+int viorb_fetch(viorb_extractor* ex, int frame, viorb_keypoint* kps, uint8_t* desc, int cap,
+                int* n_out, int* mono_index_out);
+/* Waits for all work queued on the handle's stream. */
+int viorb_extractor_sync(viorb_extractor* ex);
+
+/* mvImagePyramid[level] of the last compute (fextractor.h:64; read by Frame::ComputeStereoMatches,
+ * frame.cpp:830,920,937).  Copies the level image (without the 19-px border, which this path never
+ * reads) into dst (row step dst_step); reports its size. dst may be NULL to query the size. */
+int viorb_pyramid_level(viorb_extractor* ex, int frame, int level, uint8_t* dst, int dst_step,
+                        int* width, int* height);
+
+/* Stage inspection for parity tests (not used by the reference-facing path):
+ * FAST candidates of one level = vToDistributeKeys (fextractor.cpp:756-820), as (x, y, score)
+ * triples relative to the 16-px border, sorted in the reference's cell-major raster order;
+ * retained keypoints after DistributeOctTree + IC_Angle = (x, y, score) in level pixels + angle. */
+int viorb_debug_candidates(viorb_extractor* ex, int frame, int level, int32_t* xys, int cap, int* n_out);
+int viorb_debug_kept(viorb_extractor* ex, int frame, int level, int32_t* xys, float* angle, int cap, int* n_out);
+int viorb_debug_blurred(viorb_extractor* ex, int frame, int level, uint8_t* dst, int dst_step);
+
+/* ---- matching ---------------------------------------------------------------------------- */
+
+/* FMatcher::DescriptorDistance (src/geometry/fmatcher.cpp:2859-2875) for n row pairs (host buffers). */
+int viorb_descriptor_distance(const uint8_t* a, const uint8_t* b, int n, int32_t* dist, int device);
+
+/* cv::BFMatcher(NORM_HAMMING).knnMatch(q, t, matches, 2) (frame.cpp:1167, fmatcher.cpp:214):
+ * idx[nq][2], dist[nq][2]; ascending distance, ties -> lower train index; -1 where nt < 2. Host buffers. */
+int viorb_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx, int32_t* dist, int device);
+/* Same with device buffers, asynchronous on `stream` (a cudaStream_t cast to void*; NULL = default). */
+int viorb_knn2_device(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int32_t* d_idx, int32_t* d_dist,
+                      void* stream);
+
+/* kNN-2 followed by the ratio test, accepted matches in query order.
+ * rule 0: frame.cpp:1170   d0 < d1 * ratio (float * double; ratio 0.7 there);
+ * rule 1: fmatcher.cpp:220-223 (matchFeatures method 2) (double)d0 < ratio * d1, then with
+ *         dedup != 0 removeDuplicatedMatches (fmatcher.cpp:247-266; stable, first of each trainIdx). */
+int viorb_match_ratio(const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int rule, int dedup,
+                      viorb_match* out, int cap, int* n_out, int device);
+
+/* Frame::ComputeStereoMatches (src/datastructures/frame.cpp:823-997) for frame `frame` of two
+ * extractors holding the left/right results of the same extract call index.  bf = mbf, b = mb.
+ * u_right/depth: [n_left] (= mvuRight / mvDepth, -1 where unmatched). best_idx/best_dist may be NULL
+ * (coarse row-band Hamming winner per left keypoint, -1 if none < TH_HIGH). Host output buffers. */
+int viorb_stereo_match(viorb_extractor* left, viorb_extractor* right, int frame, float bf, float b,
+                       float* u_right, float* depth, int32_t* best_idx, int32_t* best_dist, int cap, int* n_left);
+
+/* Batched, device-resident stereo front-end for frames [0, n) of the last extract calls:
+ * ComputeStereoMatches + ComputeStereoFishEyeMatches' kNN-2/ratio (frame.cpp:1167-1170) left->right.
+ * Results stay on the device; *_fetch copies one frame's rows out. */
+int viorb_stereo_batch(viorb_extractor* left, viorb_extractor* right, int n, float bf, float b, double ratio);
+int viorb_stereo_fetch(viorb_extractor* left, int frame, float* u_right, float* depth, int32_t* lr_match,
+                       int cap, int* n_left, int* n_stereo, int* n_ratio);
+
+/* Frame-to-frame brute-force kNN-2 + ratio between the resident descriptors of two extractors'
+ * frames (cur.frame_q -> prev.frame_t); result rows in query order. */
+int viorb_match_resident(viorb_extractor* cur, int frame_q, viorb_extractor* prev, int frame_t, double ratio,
+                         int rule, viorb_match* out, int cap, int* n_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VIORB_H_ */

@@ -1,0 +1,764 @@
+// kernels_extract.cuh — sm_100a kernels of the ORB extraction path.
+//
+// Stage map (reference src/geometry/fextractor.cpp):
+//   k_resize    ComputePyramid              :1135-1160  (cv::resize INTER_LINEAR, fixed point)
+//   k_fast      ComputeKeyPointsOctTree     :756-820    (per-cell cv::FAST ini/min threshold + NMS)
+//   k_octree    DistributeOctTree           :530-754    (quadtree culling, list order preserved)
+//   k_orient    IC_Angle / fastAtan2        :68-95
+//   k_emit      compute() output ordering   :1074-1129  (scale, mono / lapping split)
+//   k_blur      GaussianBlur 7x7 s=2        :1086       (8-bit fixed point, reflect-101)
+//   k_describe  computeOrbDescriptor        :99-138     (steered BRIEF-256)
+#pragma once
+#include "viorb_common.cuh"
+
+static __device__ const int8_t d_orb_pattern[1024] = {
+#include "orb_pattern.inc"
+};
+
+__device__ __forceinline__ int reflect101_dev(int p, int n) {
+    if (n == 1) return 0;
+    while (p < 0 || p >= n) p = p < 0 ? -p : 2 * (n - 1) - p;
+    return p;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Pyramid level l from level l-1.  One thread = 4 adjacent output pixels of one row.
+// Coefficient tables (11-bit, built on the host exactly like cv::resize does) live in global memory.
+// grid (ceil(w/4/64), ceil(h/4), B), block (64,4).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int l, const int* __restrict__ xofs,
+                                                const short2* __restrict__ xalpha, const int* __restrict__ yofs,
+                                                const short2* __restrict__ ybeta) {
+    const LevelGeom& L = g.lv[l];
+    const LevelGeom& S = g.lv[l - 1];
+    const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const int dy = blockIdx.y * blockDim.y + threadIdx.y;
+    const int f = blockIdx.z;
+    if (x4 >= L.w || dy >= L.h) return;
+    int sp;
+    const uint8_t* src = level_ptr(g, fs, l - 1, f, sp);
+    uint8_t* dst = fs.pyr + (size_t)f * g.arenaStride + L.off + (size_t)dy * L.pitch;
+    uint32_t packed = 0;
+    if (L.areaHalf) {
+        const uint8_t* a = src + (size_t)(2 * dy) * sp;
+        const uint8_t* b = a + sp;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int x = x4 + i;
+            if (x < L.w) {
+                int v = (a[2 * x] + a[2 * x + 1] + b[2 * x] + b[2 * x + 1] + 2) >> 2;
+                packed |= (uint32_t)v << (8 * i);
+            }
+        }
+    } else {
+        const int sy = __ldg(yofs + L.yTab + dy);
+        const short2 bt = __ldg(ybeta + L.yTab + dy);
+        const int sy0 = min(max(sy, 0), S.h - 1), sy1 = min(max(sy + 1, 0), S.h - 1);
+        const uint8_t* r0 = src + (size_t)sy0 * sp;
+        const uint8_t* r1 = src + (size_t)sy1 * sp;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int x = x4 + i;
+            if (x < L.w) {
+                const int sx = __ldg(xofs + L.xTab + x);
+                const short2 al = __ldg(xalpha + L.xTab + x);
+                const int sx1 = min(sx + 1, S.w - 1);
+                const int h0 = r0[sx] * al.x + r0[sx1] * al.y;
+                const int h1 = r1[sx] * al.x + r1[sx1] * al.y;
+                const int v = ((((int)bt.x * (h0 >> 4)) >> 16) + (((int)bt.y * (h1 >> 4)) >> 16) + 2) >> 2;
+                packed |= (uint32_t)(v & 0xFF) << (8 * i);
+            }
+        }
+    }
+    if (x4 + 3 < L.w) {
+        *reinterpret_cast<uint32_t*>(dst + x4) = packed;
+    } else {
+        for (int i = 0; i < 4 && x4 + i < L.w; ++i) dst[x4 + i] = (uint8_t)(packed >> (8 * i));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// FAST-9 + cell-local 3x3 NMS + per-cell ini/min threshold.  One CTA = one cell of one frame.
+//   phase 0  stage the cell region + 3-px halo in shared memory with aligned 32-bit loads
+//   phase A  opposite-pair pre-test per pixel -> warp-ballot compaction into a queue
+//   phase B  dense corner score (cornerScore<16>) on the queue -> 8-bit score tile
+//   phase C  strict 3x3 NMS inside the cell (outside = 0), survivors to shared
+//   phase D  keep score >= iniTh if any survivor reaches it, else all (>= minTh); append to the
+//            (frame, level) candidate list with one global atomic per warp
+// Candidate word: x | y << 12 | score << 24, x/y relative to the 16-px border (as vToDistributeKeys).
+// grid (totalCells, B), block 128.
+// ---------------------------------------------------------------------------------------------
+#define VIORB_FAST_THREADS 128
+
+__device__ __forceinline__ int fast_score16(const uint8_t* p, const int* o) {
+    const int v = p[0];
+    int d[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) d[k] = v - (int)p[o[k]];
+    int t[16], u[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        t[k] = __vimin3_s32(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+        u[k] = __vimax3_s32(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+    }
+    int a = -256, b = 256;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        a = max(a, __vimin3_s32(t[k], t[(k + 3) & 15], t[(k + 6) & 15]));
+        b = min(b, __vimax3_s32(u[k], u[(k + 3) & 15], u[(k + 6) & 15]));
+    }
+    return max(a, -b) - 1;
+}
+
+__global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, FrameSrc fs, const CellDesc* __restrict__ cells,
+                                                             uint32_t* __restrict__ cand, int* __restrict__ candCount,
+                                                             int* __restrict__ status) {
+    VIORB_DYN_SMEM(smem);
+    __shared__ int qCount, sCount, hasIni;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int f = blockIdx.y;
+    const CellDesc c = cells[blockIdx.x];
+    const int l = c.level;
+    int pitch;
+    const uint8_t* img = level_ptr(g, fs, l, f, pitch);
+    const int rw = c.x1 - c.x0, rh = c.y1 - c.y0, npx = rw * rh;
+    const int TP = (g.tileW + 3 + 3) & ~3;          // tile pitch (bytes), room for the alignment shift
+    const int SP = g.tileW - 4;                     // score pitch: region + 1-px ring
+    uint8_t* T = smem;
+    uint8_t* S = T + g.tileH * TP;
+    uint16_t* Q = reinterpret_cast<uint16_t*>(S + (((g.tileH - 4) * SP + 3) & ~3));
+    uint32_t* surv = reinterpret_cast<uint32_t*>(Q);
+    if (tid == 0) { qCount = 0; sCount = 0; hasIni = 0; }
+
+    // phase 0
+    const int ox = c.x0 - 3, oy = c.y0 - 3;
+    const int ax = ox & ~3, shift = ox - ax;
+    const int nW = (shift + rw + 6 + 3) >> 2, nR = rh + 6;
+    for (int i = tid; i < nW * nR; i += VIORB_FAST_THREADS) {
+        const int r = i / nW, k = i - r * nW;
+        reinterpret_cast<uint32_t*>(T + r * TP)[k] =
+            __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)(oy + r) * pitch + ax) + k);
+    }
+    for (int i = tid; i < (((rh + 2) * SP + 3) >> 2); i += VIORB_FAST_THREADS) reinterpret_cast<uint32_t*>(S)[i] = 0;
+    __syncthreads();
+
+    const int th = g.minTh;
+    const unsigned inv = (1u << 20) / (unsigned)rw + 1;     // p / rw == (p * inv) >> 20 for p < 16384
+    const uint8_t* T0 = T + 3 * TP + shift + 3;             // region pixel (0,0)
+
+    // phase A
+    for (int base = 0; base < npx; base += VIORB_FAST_THREADS) {
+        const int p = base + tid;
+        bool pass = false;
+        if (p < npx) {
+            const int py = (int)(((unsigned)p * inv) >> 20), px = p - py * rw;
+            const uint8_t* q = T0 + py * TP + px;
+            const int v = q[0], lo = v - th, hi = v + th;
+            int a = q[3 * TP], b = q[-3 * TP];
+            bool dark = (a < lo) | (b < lo), bright = (a > hi) | (b > hi);
+            if (dark | bright) {
+                a = q[3]; b = q[-3];
+                dark &= (a < lo) | (b < lo); bright &= (a > hi) | (b > hi);
+                if (dark | bright) {
+                    a = q[2 * TP + 2]; b = q[-2 * TP - 2];
+                    dark &= (a < lo) | (b < lo); bright &= (a > hi) | (b > hi);
+                    a = q[-2 * TP + 2]; b = q[2 * TP - 2];
+                    dark &= (a < lo) | (b < lo); bright &= (a > hi) | (b > hi);
+                    pass = dark | bright;
+                }
+            }
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, pass);
+        if (m) {
+            const int leader = __ffs(m) - 1;
+            int qb = 0;
+            if (lane == leader) qb = atomicAdd(&qCount, __popc(m));
+            qb = __shfl_sync(0xffffffffu, qb, leader);
+            if (pass) Q[qb + __popc(m & ((1u << lane) - 1))] = (uint16_t)p;
+        }
+    }
+    __syncthreads();
+
+    // phase B
+    {
+        const int o[16] = {3 * TP, 3 * TP + 1, 2 * TP + 2, TP + 3, 3, -TP + 3, -2 * TP + 2, -3 * TP + 1,
+                           -3 * TP, -3 * TP - 1, -2 * TP - 2, -TP - 3, -3, TP - 3, 2 * TP - 2, 3 * TP - 1};
+        const int nq = qCount;
+        for (int i = tid; i < nq; i += VIORB_FAST_THREADS) {
+            const int p = Q[i];
+            const int py = (int)(((unsigned)p * inv) >> 20), px = p - py * rw;
+            const int sc = fast_score16(T0 + py * TP + px, o);
+            if (sc >= th) S[(py + 1) * SP + px + 1] = (uint8_t)sc;
+        }
+    }
+    __syncthreads();
+
+    // phase C
+    for (int p = tid; p < npx; p += VIORB_FAST_THREADS) {
+        const int py = (int)(((unsigned)p * inv) >> 20), px = p - py * rw;
+        const uint8_t* s = S + (py + 1) * SP + px + 1;
+        const int v = s[0];
+        if (v) {
+            const bool keep = v > s[-1] && v > s[1] && v > s[-SP - 1] && v > s[-SP] && v > s[-SP + 1] &&
+                              v > s[SP - 1] && v > s[SP] && v > s[SP + 1];
+            if (keep) {
+                const int i = atomicAdd(&sCount, 1);
+                surv[i] = (uint32_t)(c.x0 + px - VIORB_MINB) | ((uint32_t)(c.y0 + py - VIORB_MINB) << 12) | ((uint32_t)v << 24);
+                if (v >= g.iniTh) hasIni = 1;
+            }
+        }
+    }
+    __syncthreads();
+
+    // phase D
+    const int ns = sCount, needIni = hasIni ? g.iniTh : 0;
+    const LevelGeom& L = g.lv[l];
+    uint32_t* out = cand + (size_t)f * g.candPerFrame + L.candOff;
+    int* cnt = candCount + f * g.nlevels + l;
+    for (int base = 0; base < ns; base += VIORB_FAST_THREADS) {
+        const int i = base + tid;
+        uint32_t e = 0;
+        bool keep = false;
+        if (i < ns) { e = surv[i]; keep = (int)(e >> 24) >= needIni; }
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (m) {
+            const int leader = __ffs(m) - 1;
+            int gb = 0;
+            if (lane == leader) gb = atomicAdd(cnt, __popc(m));
+            gb = __shfl_sync(0xffffffffu, gb, leader);
+            if (keep) {
+                const int pos = gb + __popc(m & ((1u << lane) - 1));
+                if (pos < L.candCap) out[pos] = e;
+                else atomicOr(status, 1);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Quadtree culling.  One CTA per (level, frame).  The std::list of the reference becomes an index
+// order: position 0 = list front.  Every round splits a set of nodes "in push order"; children are
+// pushed to the front (so they appear reversed), unsplit nodes keep their relative order behind.
+//   full round    : every node with > 1 key, in list order                       (:614-662)
+//   careful round : nodes of the last round, biggest first, until N is reached   (:664-728)
+// The reference breaks (size) ties by heap pointer; here, as in the oracle, by creation order
+// (later created first), which for nodes of one round equals "smaller list index first".
+// Final pick per node: max response, first in cell-major raster order wins ties          (:735-751).
+// grid (nlevels, B), block 512, dynamic smem = octree_smem_bytes(maxNodes).
+// ---------------------------------------------------------------------------------------------
+#define VIORB_OCT_THREADS 512
+
+struct OctBounds { short ulx, uly, brx, bry; };
+
+__host__ __device__ inline size_t octree_smem_bytes(int nc) {
+    // bounds[2][nc] (8 B) + cnt[2][nc] + child[4 nc] + rank[nc] + aux0[nc] + aux1[nc] + newIdx[nc]
+    return (size_t)nc * (16 + 8 + 16 + 4 + 4 + 4 + 4) + 64;
+}
+
+// exclusive scan of a[0..m) in place by the whole CTA; returns the total (all threads).
+__device__ __forceinline__ int block_excl_scan(int* a, int m, int* warpSums /* >= 17 ints */) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nth = blockDim.x;
+    const int chunk = (m + nth - 1) / nth;
+    const int st = min(tid * chunk, m), en = min(st + chunk, m);
+    int sum = 0;
+    for (int i = st; i < en; ++i) sum += a[i];
+    int inc = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += t;
+    }
+    if (lane == 31) warpSums[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        int v = lane < (nth >> 5) ? warpSums[lane] : 0;
+        int vi = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, vi, d);
+            if (lane >= d) vi += t;
+        }
+        if (lane < (nth >> 5)) warpSums[lane] = vi - v;
+        if (lane == 31) warpSums[16] = vi;
+    }
+    __syncthreads();
+    int run = warpSums[wid] + inc - sum;
+    for (int i = st; i < en; ++i) { int t = a[i]; a[i] = run; run += t; }
+    const int total = warpSums[16];
+    __syncthreads();
+    return total;
+}
+
+__global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, const uint32_t* __restrict__ cand,
+                                                              const int* __restrict__ candCount, uint16_t* __restrict__ keyNode,
+                                                              KeptKp* __restrict__ kept, int* __restrict__ keptCount,
+                                                              int* __restrict__ status) {
+    VIORB_DYN_SMEM(smem);
+    __shared__ int warpSums[20];
+    __shared__ int sh_live, sh_nExp, sh_cut, sh_remap[64];
+    const int tid = threadIdx.x, nth = VIORB_OCT_THREADS;
+    const int l = blockIdx.x, f = blockIdx.y;
+    const LevelGeom& L = g.lv[l];
+    const int NC = g.maxNodes;
+    const int n = min(candCount[f * g.nlevels + l], L.candCap);
+    const uint32_t* keys = cand + (size_t)f * g.candPerFrame + L.candOff;
+    uint16_t* kn = keyNode + (size_t)f * g.candPerFrame + L.candOff;
+    KeptKp* out = kept + (size_t)f * g.keptPerFrame + L.keptOff;
+    if (n == 0) {
+        if (tid == 0) keptCount[f * g.nlevels + l] = 0;
+        return;
+    }
+    OctBounds* bnd[2];
+    int* cnt[2];
+    bnd[0] = reinterpret_cast<OctBounds*>(smem);
+    bnd[1] = bnd[0] + NC;
+    cnt[0] = reinterpret_cast<int*>(bnd[1] + NC);
+    cnt[1] = cnt[0] + NC;
+    int* child = cnt[1] + NC;          // [4 NC] child key counts, later child new index
+    int* rankv = child + 4 * NC;       // push rank of a split node, -1 otherwise
+    int* aux0 = rankv + NC;            // scans
+    int* aux1 = aux0 + NC;
+    int* newIdx = aux1 + NC;           // new index of an unsplit node
+    const int N = L.nWant;
+
+    // ---- roots (:535-578)
+    const int nIni = L.nIni;
+    const float hX = L.hX;
+    for (int i = tid; i < nIni; i += nth) {
+        OctBounds b;
+        b.ulx = (short)(int)__fmul_rn(hX, (float)i);
+        b.brx = (short)(int)__fmul_rn(hX, (float)(i + 1));
+        b.uly = 0;
+        b.bry = (short)(L.maxBY - VIORB_MINB);
+        bnd[0][i] = b;
+        cnt[0][i] = 0;
+    }
+    __syncthreads();
+    for (int k = tid; k < n; k += nth) {
+        const int x = keys[k] & 0xFFF;
+        int r = (int)__fdiv_rn((float)x, hX);
+        r = min(r, nIni - 1);
+        kn[k] = (uint16_t)r;
+        atomicAdd(&cnt[0][r], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int m = 0;
+        for (int i = 0; i < nIni; ++i) {
+            if (cnt[0][i] > 0) { sh_remap[i] = m; bnd[1][m] = bnd[0][i]; cnt[1][m] = cnt[0][i]; ++m; }
+            else sh_remap[i] = -1;
+        }
+        sh_live = m;
+    }
+    __syncthreads();
+    for (int k = tid; k < n; k += nth) kn[k] = (uint16_t)sh_remap[kn[k]];
+    int cur = 1;
+    int live = sh_live;
+    bool careful = false;
+    __syncthreads();
+
+    for (int round = 0; round < 64; ++round) {
+        const OctBounds* B = bnd[cur];
+        const int* Cn = cnt[cur];
+        OctBounds* B2 = bnd[cur ^ 1];
+        int* Cn2 = cnt[cur ^ 1];
+        const int prevSize = live;
+        // 1. child key counts of every expandable node
+        for (int i = tid; i < 4 * live; i += nth) child[i] = 0;
+        __syncthreads();
+        for (int k = tid; k < n; k += nth) {
+            const int nd = kn[k];
+            if (Cn[nd] > 1) {
+                const uint32_t e = keys[k];
+                const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
+                const OctBounds b = B[nd];
+                const int mx = b.ulx + ((b.brx - b.ulx + 1) >> 1), my = b.uly + ((b.bry - b.uly + 1) >> 1);
+                atomicAdd(&child[nd * 4 + (x < mx ? 0 : 1) + (y < my ? 0 : 2)], 1);
+            }
+        }
+        __syncthreads();
+        // 2. push rank of the nodes to split
+        int nSplit;
+        if (!careful) {
+            for (int i = tid; i < live; i += nth) aux0[i] = Cn[i] > 1 ? 1 : 0;
+            __syncthreads();
+            nSplit = block_excl_scan(aux0, live, warpSums);
+            for (int i = tid; i < live; i += nth) rankv[i] = Cn[i] > 1 ? aux0[i] : -1;
+            __syncthreads();
+        } else {
+            // rank by (key count desc, list index asc); gains in rank order -> cut where N is reached
+            for (int i = tid; i < live; i += nth) {
+                int r = -1;
+                const int ci = Cn[i];
+                if (ci > 1) {
+                    r = 0;
+                    for (int j = 0; j < live; ++j) {
+                        const int cj = Cn[j];
+                        r += (cj > ci) || (cj == ci && j < i);
+                    }
+                }
+                rankv[i] = r;
+            }
+            for (int i = tid; i < live; i += nth) aux0[i] = 0;
+            if (tid == 0) sh_cut = 0x7fffffff;
+            __syncthreads();
+            for (int i = tid; i < live; i += nth)
+                if (rankv[i] >= 0) {
+                    const int* ch = child + 4 * i;
+                    aux0[rankv[i]] = (ch[0] > 0) + (ch[1] > 0) + (ch[2] > 0) + (ch[3] > 0) - 1;
+                }
+            __syncthreads();
+            int nE = 0;
+            for (int i = tid; i < live; i += nth) nE += rankv[i] >= 0;
+            nE = __syncthreads_count(0) * 0 + nE;   // (keeps all threads converged; nE reduced below)
+            // reduce nE over the block
+            aux1[tid < NC ? tid : 0] = 0;
+            __syncthreads();
+            if (tid == 0) sh_nExp = 0;
+            __syncthreads();
+            if (nE) atomicAdd(&sh_nExp, nE);
+            __syncthreads();
+            nE = sh_nExp;
+            block_excl_scan(aux0, nE, warpSums);    // aux0[r] = gain of ranks < r
+            for (int r = tid; r < nE; r += nth) {
+                // inclusive gain after splitting rank r = aux0[r+1] (or total); recompute from neighbours
+                const int before = live + aux0[r];
+                // gain of rank r itself: find via next exclusive value
+                int after;
+                if (r + 1 < nE) after = live + aux0[r + 1];
+                else after = 0x7ffffffe;   // last rank: everything is split if no earlier cut
+                if (before < N && after >= N) atomicMin(&sh_cut, r);
+            }
+            __syncthreads();
+            const int cut = sh_cut;     // ranks <= cut are split (cut >= nE-1 means all)
+            for (int i = tid; i < live; i += nth)
+                if (rankv[i] > cut) rankv[i] = -1;
+            __syncthreads();
+            nSplit = min(nE, cut == 0x7fffffff ? nE : cut + 1);
+        }
+        if (nSplit == 0) break;            // nothing to split: size == prevSize (:655, :724)
+        // 3. pushes: nonempty children in rank order
+        for (int i = tid; i < nSplit; i += nth) aux0[i] = 0;
+        __syncthreads();
+        for (int i = tid; i < live; i += nth)
+            if (rankv[i] >= 0) {
+                const int* ch = child + 4 * i;
+                aux0[rankv[i]] = (ch[0] > 0) + (ch[1] > 0) + (ch[2] > 0) + (ch[3] > 0);
+            }
+        __syncthreads();
+        const int P = block_excl_scan(aux0, nSplit, warpSums);      // aux0[rank] = first push position
+        for (int i = tid; i < live; i += nth) aux1[i] = rankv[i] < 0 ? 1 : 0;
+        __syncthreads();
+        const int nKeep = block_excl_scan(aux1, live, warpSums);    // aux1[i] = #unsplit before i
+        const int newLive = P + nKeep;
+        if (newLive > NC) {                 // cannot happen for maxNodes = max(N+3, 4 nIni); guard anyway
+            if (tid == 0) atomicOr(status, 2);
+            break;
+        }
+        if (tid == 0) sh_nExp = 0;
+        __syncthreads();
+        int myExp = 0;
+        for (int i = tid; i < live; i += nth) {
+            if (rankv[i] >= 0) {
+                const OctBounds b = B[i];
+                const int mx = b.ulx + ((b.brx - b.ulx + 1) >> 1), my = b.uly + ((b.bry - b.uly + 1) >> 1);
+                int pp = aux0[rankv[i]];
+                int* ch = child + 4 * i;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int c = ch[q];
+                    if (c > 0) {
+                        const int ni = P - 1 - pp;
+                        ++pp;
+                        OctBounds nb;
+                        nb.ulx = (q & 1) ? (short)mx : b.ulx;
+                        nb.brx = (q & 1) ? b.brx : (short)mx;
+                        nb.uly = (q & 2) ? (short)my : b.uly;
+                        nb.bry = (q & 2) ? b.bry : (short)my;
+                        B2[ni] = nb;
+                        Cn2[ni] = c;
+                        myExp += c > 1;
+                        ch[q] = ni;
+                    }
+                }
+            } else {
+                const int ni = P + aux1[i];
+                B2[ni] = B[i];
+                Cn2[ni] = Cn[i];
+                newIdx[i] = ni;
+            }
+        }
+        if (myExp) atomicAdd(&sh_nExp, myExp);
+        __syncthreads();
+        // 4. move the keys
+        for (int k = tid; k < n; k += nth) {
+            const int nd = kn[k];
+            if (rankv[nd] >= 0) {
+                const uint32_t e = keys[k];
+                const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
+                const OctBounds b = B[nd];
+                const int mx = b.ulx + ((b.brx - b.ulx + 1) >> 1), my = b.uly + ((b.bry - b.uly + 1) >> 1);
+                kn[k] = (uint16_t)child[nd * 4 + (x < mx ? 0 : 1) + (y < my ? 0 : 2)];
+            } else {
+                kn[k] = (uint16_t)newIdx[nd];
+            }
+        }
+        const int nToExpand = sh_nExp;
+        __syncthreads();
+        cur ^= 1;
+        live = newLive;
+        // 5. termination (:655-662, :724-725)
+        if (live >= N || live == prevSize) break;
+        if (!careful && live + 3 * nToExpand > N) careful = true;
+    }
+
+    // ---- best key per node (:735-751): max score, ties -> first in (cell row, cell col, y, x) order
+    unsigned long long* best = reinterpret_cast<unsigned long long*>(child);
+    for (int i = tid; i < live; i += nth) best[i] = 0ull;
+    __syncthreads();
+    const unsigned long long OMASK = (1ull << 40) - 1;
+    for (int k = tid; k < n; k += nth) {
+        const uint32_t e = keys[k];
+        const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
+        const unsigned long long sc = e >> 24;
+        const int cj = min(max(x - 3, 0) / L.wCell, L.lastCol);
+        const int ci = min(max(y - 3, 0) / L.hCell, L.lastRow);
+        const unsigned long long okey = ((unsigned long long)ci << 32) | ((unsigned long long)cj << 24) |
+                                        ((unsigned long long)y << 12) | (unsigned long long)x;
+        atomicMax(&best[kn[k]], (sc << 40) | (OMASK - okey));
+    }
+    __syncthreads();
+    for (int i = tid; i < live; i += nth) {
+        const unsigned long long v = best[i];
+        const unsigned long long okey = OMASK - (v & OMASK);
+        KeptKp kp;
+        kp.x = (short)((int)(okey & 0xFFF) + VIORB_MINB);
+        kp.y = (short)((int)((okey >> 12) & 0xFFF) + VIORB_MINB);
+        kp.score = (int)(v >> 40) | (l << 16);
+        kp.angle = -1.f; kp.c = 1.f; kp.s = 0.f;
+        if (i < L.keptCap) out[i] = kp;
+    }
+    if (tid == 0) {
+        if (live > L.keptCap) atomicOr(status, 4);
+        keptCount[f * g.nlevels + l] = min(live, L.keptCap);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Intensity-centroid orientation.  One warp per retained keypoint: lane = column u+15, loop over
+// the 31 rows of the radius-15 disc (coalesced row segments), integer moments reduced exactly with
+// __reduce_add_sync; cv::fastAtan2's float32 polynomial evaluated without FMA contraction.
+// Also stores cos/sin of the angle for k_describe: double-precision sincos rounded to float.
+// grid (ceil(keptPerFrame/8), B), block 256.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+    const float sc = (float)(180.0 / 3.14159265358979323846);
+    const float p1 = __fmul_rn(0.9997878412794807f, sc), p3 = __fmul_rn(-0.3258083974640975f, sc);
+    const float p5 = __fmul_rn(0.1555786518463281f, sc), p7 = __fmul_rn(-0.04432655554792128f, sc);
+    const float ax = fabsf(x), ay = fabsf(y);
+    const float eps = 2.220446049250313e-16f;     // (float)DBL_EPSILON
+    float a;
+    if (ax >= ay) {
+        const float c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+        const float c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        const float c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+        const float c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+struct UmaxTable { int v[16]; };
+
+__global__ void __launch_bounds__(256) k_orient(ExtractGeom g, FrameSrc fs, UmaxTable um, KeptKp* __restrict__ kept,
+                                                const int* __restrict__ keptCount) {
+    const int lane = threadIdx.x & 31;
+    const int slot = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int f = blockIdx.y;
+    if (slot >= g.keptPerFrame) return;
+    int l = -1;
+    for (int i = 0; i < g.nlevels; ++i) {
+        const int o = g.lv[i].keptOff;
+        if (slot >= o && slot < o + keptCount[f * g.nlevels + i]) l = i;
+    }
+    if (l < 0) return;
+    KeptKp* kp = kept + (size_t)f * g.keptPerFrame + slot;
+    int pitch;
+    const uint8_t* img = level_ptr(g, fs, l, f, pitch);
+    const int x = kp->x, y = kp->y;
+    const int u = lane - VIORB_HALF_PATCH;
+    int colSum = 0, m01 = 0;
+    if (lane < 31) {
+        const int au = u < 0 ? -u : u;
+        const uint8_t* c = img + (size_t)y * pitch + x + u;
+        for (int v = -VIORB_HALF_PATCH; v <= VIORB_HALF_PATCH; ++v) {
+            const int av = v < 0 ? -v : v;
+            if (au <= um.v[av]) {
+                const int val = c[v * pitch];
+                colSum += val;
+                m01 += v * val;
+            }
+        }
+    }
+    int m10 = u * colSum;
+    m10 = __reduce_add_sync(0xffffffffu, m10);
+    m01 = __reduce_add_sync(0xffffffffu, m01);
+    if (lane == 0) {
+        const float ang = fast_atan2_deg((float)m01, (float)m10);
+        const float factorPI = (float)(3.14159265358979323846 / 180.0);
+        const float rad = __fmul_rn(ang, factorPI);
+        double sn, cs;
+        sincos((double)rad, &sn, &cs);
+        kp->angle = ang;
+        kp->c = (float)cs;
+        kp->s = (float)sn;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Output ordering (:1074-1129).  One CTA per frame walks the retained keypoints level by level in
+// list order; a keypoint whose scaled x lies in [lap0, lap1] goes to the back (reverse order), the
+// others to the front.  Writes cv::KeyPoint records and the slot -> kept-index map for k_describe.
+// grid (B), block 256.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_emit(ExtractGeom g, const KeptKp* __restrict__ kept, const int* __restrict__ keptCount,
+                                              int lap0, int lap1, viorb_keypoint* __restrict__ kps, int* __restrict__ slot2kept,
+                                              int* __restrict__ nOut, int* __restrict__ monoOut) {
+    __shared__ int warpCnt[8];
+    __shared__ int sh_mono, sh_lap;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int f = blockIdx.x;
+    int total = 0;
+    for (int l = 0; l < g.nlevels; ++l) total += keptCount[f * g.nlevels + l];
+    if (tid == 0) { sh_mono = 0; sh_lap = 0; }
+    __syncthreads();
+    viorb_keypoint* okp = kps + (size_t)f * g.outCap;
+    int* s2k = slot2kept + (size_t)f * g.outCap;
+    for (int l = 0; l < g.nlevels; ++l) {
+        const LevelGeom& L = g.lv[l];
+        const int cnt = keptCount[f * g.nlevels + l];
+        const KeptKp* src = kept + (size_t)f * g.keptPerFrame + L.keptOff;
+        for (int base = 0; base < cnt; base += 256) {
+            const int i = base + tid;
+            const bool valid = i < cnt;
+            viorb_keypoint kp;
+            bool lap = false;
+            if (valid) {
+                const KeptKp k = src[i];
+                kp.x = (float)k.x; kp.y = (float)k.y;
+                if (l != 0) { kp.x = __fmul_rn(kp.x, L.scale); kp.y = __fmul_rn(kp.y, L.scale); }
+                kp.size = L.kpSize;
+                kp.angle = k.angle;
+                kp.response = (float)(k.score & 0xFFFF);
+                kp.octave = l;
+                kp.class_id = -1;
+                lap = kp.x >= (float)lap0 && kp.x <= (float)lap1;
+            }
+            const unsigned mLap = __ballot_sync(0xffffffffu, valid && lap);
+            const unsigned mMono = __ballot_sync(0xffffffffu, valid && !lap);
+            if (lane == 0) warpCnt[wid] = (__popc(mLap) << 16) | __popc(mMono);
+            __syncthreads();
+            int lapBefore = sh_lap, monoBefore = sh_mono;
+            for (int w = 0; w < wid; ++w) { lapBefore += warpCnt[w] >> 16; monoBefore += warpCnt[w] & 0xFFFF; }
+            if (valid) {
+                const unsigned lt = (1u << lane) - 1;
+                const int slot = lap ? total - 1 - (lapBefore + __popc(mLap & lt)) : monoBefore + __popc(mMono & lt);
+                okp[slot] = kp;
+                s2k[slot] = L.keptOff + i;
+            }
+            __syncthreads();
+            if (tid == 0) {
+                int a = 0, b = 0;
+                for (int w = 0; w < 8; ++w) { a += warpCnt[w] >> 16; b += warpCnt[w] & 0xFFFF; }
+                sh_lap += a; sh_mono += b;
+            }
+            __syncthreads();
+        }
+    }
+    if (tid == 0) { nOut[f] = total; monoOut[f] = sh_mono; }
+}
+
+// ---------------------------------------------------------------------------------------------
+// 7x7 sigma-2 Gaussian, 8-bit fixed point: taps {18,34,48,56,48,34,18}/256, row pass Q8.8, column
+// pass Q16.16, +0.5, >>16; BORDER_REFLECT_101 from the level image itself.  All levels in one launch:
+// grid (totalBlurTiles, B), block 256; tile = 64 x 16 output pixels, halo 3 staged in shared memory.
+// ---------------------------------------------------------------------------------------------
+struct BlurTiles { int base[VIORB_MAX_LEVELS + 1]; int tilesX[VIORB_MAX_LEVELS]; };
+
+__global__ void __launch_bounds__(256) k_blur(ExtractGeom g, FrameSrc fs, BlurTiles bt) {
+    __shared__ uint8_t sIn[22 * 72];
+    __shared__ uint16_t sH[22 * 64];
+    const int tid = threadIdx.x, f = blockIdx.y;
+    int l = 0;
+    while (l + 1 < g.nlevels && (int)blockIdx.x >= bt.base[l + 1]) ++l;
+    const LevelGeom& L = g.lv[l];
+    const int t = blockIdx.x - bt.base[l];
+    const int tx0 = (t % bt.tilesX[l]) * 64, ty0 = (t / bt.tilesX[l]) * 16;
+    int pitch;
+    const uint8_t* img = level_ptr(g, fs, l, f, pitch);
+    uint8_t* dst = fs.blur + (size_t)f * g.arenaStride + L.off;
+    const bool interior = tx0 >= 3 && ty0 >= 3 && tx0 + 67 <= L.w && ty0 + 19 <= L.h;
+    for (int i = tid; i < 22 * 70; i += 256) {
+        const int r = i / 70, c = i - r * 70;
+        int sy = ty0 - 3 + r, sx = tx0 - 3 + c;
+        if (!interior) { sy = reflect101_dev(sy, L.h); sx = reflect101_dev(sx, L.w); }
+        sIn[r * 72 + c] = img[(size_t)sy * pitch + sx];
+    }
+    __syncthreads();
+    for (int i = tid; i < 22 * 64; i += 256) {
+        const int r = i >> 6, c = i & 63;
+        const uint8_t* p = sIn + r * 72 + c;
+        sH[i] = (uint16_t)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
+    }
+    __syncthreads();
+    for (int i = tid; i < 16 * 64; i += 256) {
+        const int r = i >> 6, c = i & 63;
+        const int x = tx0 + c, y = ty0 + r;
+        if (x < L.w && y < L.h) {
+            const uint16_t* p = sH + r * 64 + c;
+            const uint32_t acc = 18u * (p[0] + p[6 * 64]) + 34u * (p[64] + p[5 * 64]) + 48u * (p[2 * 64] + p[4 * 64]) + 56u * p[3 * 64];
+            dst[(size_t)y * L.pitch + x] = (uint8_t)((acc + 32768u) >> 16);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Steered BRIEF-256.  One warp per output slot, lane = descriptor byte (8 tests, 16 samples).
+// Sample offset = cvRound(x*b + y*a), cvRound(x*a - y*b): float32 products and sums rounded
+// separately (no FMA), round-half-even.  grid (ceil(outCap/8), B), block 256.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_describe(ExtractGeom g, FrameSrc fs, const KeptKp* __restrict__ kept,
+                                                  const int* __restrict__ slot2kept, const int* __restrict__ nOut,
+                                                  uint8_t* __restrict__ desc) {
+    __shared__ int8_t pat[1024];
+    for (int i = threadIdx.x; i < 256; i += 256)
+        reinterpret_cast<uint32_t*>(pat)[i] = reinterpret_cast<const uint32_t*>(d_orb_pattern)[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int slot = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int f = blockIdx.y;
+    if (slot >= nOut[f]) return;
+    const KeptKp k = kept[(size_t)f * g.keptPerFrame + slot2kept[(size_t)f * g.outCap + slot]];
+    const int l = k.score >> 16;
+    const LevelGeom& L = g.lv[l];
+    const uint8_t* img = fs.blur + (size_t)f * g.arenaStride + L.off;
+    const uint8_t* ctr = img + (size_t)k.y * L.pitch + k.x;
+    const float a = k.c, b = k.s;
+    int val = 0;
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+        const int8_t* p = pat + (lane * 16 + 2 * t) * 2;
+        const float x0 = (float)p[0], y0 = (float)p[1], x1 = (float)p[2], y1 = (float)p[3];
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
+        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
+        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+        const int t0 = ctr[r0 * L.pitch + c0], t1 = ctr[r1 * L.pitch + c1];
+        val |= (t0 < t1) << t;
+    }
+    desc[((size_t)f * g.outCap + slot) * 32 + lane] = (uint8_t)val;
+}

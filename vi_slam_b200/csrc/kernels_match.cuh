@@ -1,0 +1,388 @@
+// kernels_match.cuh — sm_100a kernels of the descriptor matching path.
+//
+//   k_knn2            cv::BFMatcher(NORM_HAMMING).knnMatch(k=2)   frame.cpp:1167, fmatcher.cpp:214
+//   k_ratio           Lowe ratio rules                             frame.cpp:1170, fmatcher.cpp:220-223
+//   k_dedup_*         removeDuplicatedMatches                      fmatcher.cpp:247-266
+//   k_stereo_coarse   ComputeStereoMatches row-band Hamming        frame.cpp:833-906
+//   k_stereo_refine   11x11 SAD slide + parabola sub-pixel         frame.cpp:909-979
+//   k_stereo_cut      median-based outlier cut                     frame.cpp:983-996
+//   k_desc_dist       FMatcher::DescriptorDistance                 fmatcher.cpp:2859-2875
+#pragma once
+#include "viorb_common.cuh"
+
+#define VIORB_KNN_THREADS 128
+#define VIORB_KNN_IDX_BITS 22          // train index bits in the packed (distance, index) key
+#define VIORB_TH_HIGH 100              // FMatcher::TH_HIGH (fmatcher.cpp:313)
+#define VIORB_TH_LOW 50                // FMatcher::TH_LOW  (fmatcher.cpp:314)
+
+// A batch of descriptor sets: set p lives at base + p*stride, its row count is n[p] (device array) or
+// nFixed when n == nullptr.
+struct DescSet {
+    const uint8_t* base;
+    size_t stride;
+    const int* n;
+    int nFixed;
+};
+__device__ __forceinline__ int descset_count(const DescSet& s, int p) { return s.n ? s.n[p] : s.nFixed; }
+
+__device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) {
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Brute-force Hamming 2-NN.  One thread = one query row (256 bits in 8 registers); train rows are
+// staged 128 at a time in shared memory and read as warp-wide broadcasts (2 x LDS.128 per row).
+// Per pair: 8 LOP3(xor) + 8 POPC + adds, then a 3-instruction running top-2 on the packed key
+// (distance << 22 | train index), which also yields cv::BFMatcher's tie rule (lower index first).
+// grid (ceil(maxNq/128), nSets), block 128.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(VIORB_KNN_THREADS) k_knn2(DescSet Q, DescSet T, int32_t* __restrict__ idx,
+                                                            int32_t* __restrict__ dist, size_t outStride) {
+    __shared__ uint4 tile[VIORB_KNN_THREADS * 2];
+    const int tid = threadIdx.x, p = blockIdx.y;
+    const int nq = descset_count(Q, p), nt = descset_count(T, p);
+    const int q0 = blockIdx.x * VIORB_KNN_THREADS;
+    if (q0 >= nq) return;
+    const int qi = q0 + tid;
+    const bool valid = qi < nq;
+    const uint4* qrow = reinterpret_cast<const uint4*>(Q.base + (size_t)p * Q.stride) + (size_t)(valid ? qi : q0) * 2;
+    const uint4 a0 = __ldg(qrow), a1 = __ldg(qrow + 1);
+    const uint4* tb = reinterpret_cast<const uint4*>(T.base + (size_t)p * T.stride);
+    unsigned best0 = 0xFFFFFFFFu, best1 = 0xFFFFFFFFu;
+    for (int t0 = 0; t0 < nt; t0 += VIORB_KNN_THREADS) {
+        const int m = min(VIORB_KNN_THREADS, nt - t0);
+        __syncthreads();
+        if (tid < m) {
+            tile[tid * 2] = __ldg(tb + (size_t)(t0 + tid) * 2);
+            tile[tid * 2 + 1] = __ldg(tb + (size_t)(t0 + tid) * 2 + 1);
+        }
+        __syncthreads();
+        const unsigned kb = (unsigned)t0;
+#pragma unroll 4
+        for (int j = 0; j < m; ++j) {
+            const uint4 b0 = tile[2 * j], b1 = tile[2 * j + 1];
+            const unsigned key = ((unsigned)hamming256(a0, a1, b0, b1) << VIORB_KNN_IDX_BITS) | (kb + j);
+            const unsigned lo = min(key, best0);
+            best1 = min(best1, max(key, best0));
+            best0 = lo;
+        }
+    }
+    if (valid) {
+        const unsigned mask = (1u << VIORB_KNN_IDX_BITS) - 1;
+        int32_t* oi = idx + (size_t)p * outStride * 2 + (size_t)qi * 2;
+        int32_t* od = dist + (size_t)p * outStride * 2 + (size_t)qi * 2;
+        oi[0] = best0 == 0xFFFFFFFFu ? -1 : (int)(best0 & mask);
+        od[0] = best0 == 0xFFFFFFFFu ? -1 : (int)(best0 >> VIORB_KNN_IDX_BITS);
+        oi[1] = best1 == 0xFFFFFFFFu ? -1 : (int)(best1 & mask);
+        od[1] = best1 == 0xFFFFFFFFu ? -1 : (int)(best1 >> VIORB_KNN_IDX_BITS);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Ratio test + ordered compaction.  One CTA per set; accepted matches are written in query order.
+// rule 0: d0 < d1 * ratio with d as float, product in double (frame.cpp:1170).
+// rule 1: (double)d0 < ratio * d1 (fmatcher.cpp:220-223).
+// lrMatch (optional): per query the accepted train index or -1.
+// grid (nSets), block 256.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_ratio(DescSet Q, const int32_t* __restrict__ idx, const int32_t* __restrict__ dist,
+                                               size_t knnStride, double ratio, int rule, viorb_match* __restrict__ out,
+                                               size_t outStride, int* __restrict__ nOut, int32_t* __restrict__ lrMatch) {
+    __shared__ int warpCnt[8];
+    __shared__ int sh_base;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, p = blockIdx.x;
+    const int nq = descset_count(Q, p);
+    const int32_t* I = idx + (size_t)p * knnStride * 2;
+    const int32_t* D = dist + (size_t)p * knnStride * 2;
+    viorb_match* o = out + (size_t)p * outStride;
+    if (tid == 0) sh_base = 0;
+    __syncthreads();
+    for (int base = 0; base < nq; base += 256) {
+        const int i = base + tid;
+        bool ok = false;
+        int i0 = -1, d0i = 0;
+        if (i < nq) {
+            i0 = I[2 * i];
+            const int i1 = I[2 * i + 1];
+            d0i = D[2 * i];
+            if (i0 >= 0 && i1 >= 0) {
+                const double d0 = (double)(float)d0i, d1 = (double)(float)D[2 * i + 1];
+                ok = rule == 0 ? (d0 < d1 * ratio) : (d0 < ratio * d1);
+            }
+            if (lrMatch) lrMatch[(size_t)p * knnStride + i] = ok ? i0 : -1;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        if (lane == 0) warpCnt[wid] = __popc(m);
+        __syncthreads();
+        int before = sh_base;
+        for (int w = 0; w < wid; ++w) before += warpCnt[w];
+        if (ok) {
+            viorb_match mm;
+            mm.query_idx = i; mm.train_idx = i0; mm.distance = d0i;
+            const int pos = before + __popc(m & ((1u << lane) - 1));
+            if ((size_t)pos < outStride) o[pos] = mm;
+        }
+        __syncthreads();
+        if (tid == 0) { int s = 0; for (int w = 0; w < 8; ++w) s += warpCnt[w]; sh_base += s; }
+        __syncthreads();
+    }
+    if (tid == 0) nOut[p] = sh_base;
+}
+
+// removeDuplicatedMatches, deterministic form: per train index keep the accepted match with the
+// smallest query index; output ordered by train index.  Single set.
+__global__ void k_dedup_mark(const viorb_match* __restrict__ m, int n, int* __restrict__ firstQ) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) atomicMin(&firstQ[m[i].train_idx], m[i].query_idx);
+}
+__global__ void __launch_bounds__(256) k_dedup_emit(const int* __restrict__ firstQ, int nt, const int32_t* __restrict__ dist,
+                                                    viorb_match* __restrict__ out, int* __restrict__ nOut) {
+    __shared__ int warpCnt[8];
+    __shared__ int sh_base;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) sh_base = 0;
+    __syncthreads();
+    for (int base = 0; base < nt; base += 256) {
+        const int t = base + tid;
+        const int q = t < nt ? firstQ[t] : 0x7fffffff;
+        const bool ok = q != 0x7fffffff;
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        if (lane == 0) warpCnt[wid] = __popc(m);
+        __syncthreads();
+        int before = sh_base;
+        for (int w = 0; w < wid; ++w) before += warpCnt[w];
+        if (ok) {
+            viorb_match mm;
+            mm.query_idx = q; mm.train_idx = t; mm.distance = dist[2 * q];
+            out[before + __popc(m & ((1u << lane) - 1))] = mm;
+        }
+        __syncthreads();
+        if (tid == 0) { int s = 0; for (int w = 0; w < 8; ++w) s += warpCnt[w]; sh_base += s; }
+        __syncthreads();
+    }
+    if (tid == 0) *nOut = sh_base;
+}
+
+__global__ void k_desc_dist(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, int n, int32_t* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4* pa = reinterpret_cast<const uint4*>(a) + (size_t)i * 2;
+    const uint4* pb = reinterpret_cast<const uint4*>(b) + (size_t)i * 2;
+    out[i] = hamming256(pa[0], pa[1], pb[0], pb[1]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Rectified stereo, coarse stage.  One warp per left keypoint; the right keypoints' row band
+// [floor(y - 2 s), ceil(y + 2 s)], octave and x are staged 256 at a time in shared memory, lanes
+// stride over them, and only candidates passing the row / octave / disparity predicate pay for the
+// 256-bit Hamming distance.  Winner = min (distance, right index) with distance < TH_HIGH, which is
+// the reference's "first strictly smaller wins" over its ascending-index row lists.
+// grid (ceil(outCap/8), nFrames), block 256.
+// ---------------------------------------------------------------------------------------------
+struct StereoParams {
+    float bf, maxD;                         // mbf, mbf / mb
+    float scale[VIORB_MAX_LEVELS];
+    float invScale[VIORB_MAX_LEVELS];
+    int nlevels, outCap;
+};
+
+__global__ void __launch_bounds__(256) k_stereo_coarse(StereoParams sp, const viorb_keypoint* __restrict__ kl,
+                                                       const uint8_t* __restrict__ dl, const int* __restrict__ nL,
+                                                       const viorb_keypoint* __restrict__ kr, const uint8_t* __restrict__ dr,
+                                                       const int* __restrict__ nR, int32_t* __restrict__ bestIdx,
+                                                       int32_t* __restrict__ bestDist) {
+    __shared__ short sMin[256], sMax[256];
+    __shared__ float sU[256];
+    __shared__ int8_t sOct[256];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, f = blockIdx.y;
+    const int nl = nL[f], nr = nR[f];
+    const int iL = blockIdx.x * 8 + wid;
+    if (blockIdx.x * 8 >= nl) return;
+    const bool active = iL < nl;
+    const viorb_keypoint* KL = kl + (size_t)f * sp.outCap;
+    const viorb_keypoint* KR = kr + (size_t)f * sp.outCap;
+    const uint4* DL = reinterpret_cast<const uint4*>(dl + (size_t)f * sp.outCap * 32);
+    const uint4* DR = reinterpret_cast<const uint4*>(dr + (size_t)f * sp.outCap * 32);
+    float uL = 0.f, minU = 0.f;
+    int row = 0, levelL = 0;
+    uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+    bool search = false;
+    if (active) {
+        const viorb_keypoint k = KL[iL];
+        uL = k.x; row = (int)k.y; levelL = k.octave;
+        minU = __fsub_rn(uL, sp.maxD);
+        search = !(uL < 0.f);                   // maxU = uL - minD, minD = 0
+        a0 = DL[(size_t)iL * 2]; a1 = DL[(size_t)iL * 2 + 1];
+    }
+    int best = VIORB_TH_HIGH << 20;
+    for (int r0 = 0; r0 < nr; r0 += 256) {
+        __syncthreads();
+        if (r0 + tid < nr) {
+            const viorb_keypoint k = KR[r0 + tid];
+            const float r = __fmul_rn(2.0f, sp.scale[k.octave]);
+            sMax[tid] = (short)__float2int_ru(__fadd_rn(k.y, r));
+            sMin[tid] = (short)__float2int_rd(__fsub_rn(k.y, r));
+            sU[tid] = k.x;
+            sOct[tid] = (int8_t)k.octave;
+        }
+        __syncthreads();
+        if (search) {
+            const int m = min(256, nr - r0);
+            for (int j = lane; j < m; j += 32) {
+                const int oc = sOct[j];
+                const float uR = sU[j];
+                if (row >= sMin[j] && row <= sMax[j] && oc >= levelL - 1 && oc <= levelL + 1 && uR >= minU && uR <= uL) {
+                    const int iR = r0 + j;
+                    const int d = hamming256(a0, a1, DR[(size_t)iR * 2], DR[(size_t)iR * 2 + 1]);
+                    best = min(best, (d << 20) | iR);
+                }
+            }
+        }
+    }
+    best = __reduce_min_sync(0xffffffffu, best);
+    if (active && lane == 0) {
+        const bool found = best < (VIORB_TH_HIGH << 20);
+        bestIdx[(size_t)f * sp.outCap + iL] = found ? (best & 0xFFFFF) : -1;
+        bestDist[(size_t)f * sp.outCap + iL] = found ? (best >> 20) : -1;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Stereo refinement.  One warp per left keypoint whose coarse distance is < (TH_HIGH+TH_LOW)/2:
+// 11x11 centre-subtracted L1 over 11 horizontal shifts on pyramid level octave(left) of both images
+// (integer arithmetic: identical to the reference's float sums, which are exact below 2^24), then
+// the parabola fit and the disparity / depth arithmetic in float32 without FMA contraction.
+// grid (ceil(outCap/8), nFrames), block 256.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_stereo_refine(StereoParams sp, ExtractGeom g, FrameSrc fsL, FrameSrc fsR,
+                                                       const viorb_keypoint* __restrict__ kl, const int* __restrict__ nL,
+                                                       const viorb_keypoint* __restrict__ kr, const int32_t* __restrict__ bestIdx,
+                                                       const int32_t* __restrict__ bestDist, float* __restrict__ uRight,
+                                                       float* __restrict__ depth, int32_t* __restrict__ sad) {
+    const int lane = threadIdx.x & 31, f = blockIdx.y;
+    const int iL = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (iL >= nL[f]) return;
+    const size_t o = (size_t)f * sp.outCap + iL;
+    float outU = -1.f, outD = -1.f;
+    int outS = -1;
+    const int bd = bestDist[o];
+    if (bd >= 0 && bd < (VIORB_TH_HIGH + VIORB_TH_LOW) / 2) {
+        const viorb_keypoint kpL = kl[o];
+        const int lv = kpL.octave;
+        const float uR0 = kr[(size_t)f * sp.outCap + bestIdx[o]].x;
+        const float sf = sp.invScale[lv];
+        const float su = roundf(__fmul_rn(kpL.x, sf)), sv = roundf(__fmul_rn(kpL.y, sf)), sr = roundf(__fmul_rn(uR0, sf));
+        const int cu = (int)su, cv = (int)sv, cr = (int)sr;
+        const LevelGeom& L = g.lv[lv];
+        const float endu = __fadd_rn(__fadd_rn(__fadd_rn(sr, 5.f), 5.f), 1.f);
+        if (!(sr < 0.f) && !(endu >= (float)L.w)) {
+            int pl, pr;
+            const uint8_t* imL = level_ptr(g, fsL, lv, f, pl);
+            const uint8_t* imR = level_ptr(g, fsR, lv, f, pr);
+            const int cL = imL[(size_t)cv * pl + cu];
+            int cR[11], acc[11];
+#pragma unroll
+            for (int k = 0; k < 11; ++k) { cR[k] = imR[(size_t)cv * pr + cr + k - 5]; acc[k] = 0; }
+            for (int p = lane; p < 121; p += 32) {
+                const int dy = p / 11 - 5, dx = p % 11 - 5;
+                const int a = (int)imL[(size_t)(cv + dy) * pl + cu + dx] - cL;
+                const uint8_t* rr = imR + (size_t)(cv + dy) * pr + cr + dx - 5;
+#pragma unroll
+                for (int k = 0; k < 11; ++k) {
+                    const int b = (int)rr[k] - cR[k];
+                    const int d = a - b;
+                    acc[k] += d < 0 ? -d : d;
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 11; ++k) acc[k] = __reduce_add_sync(0xffffffffu, acc[k]);
+            int bestS = 0x7fffffff, bestInc = 0;
+#pragma unroll
+            for (int k = 0; k < 11; ++k)
+                if (acc[k] < bestS) { bestS = acc[k]; bestInc = k - 5; }
+            if (bestInc != -5 && bestInc != 5) {
+                float d1 = 0.f, d2 = 0.f, d3 = 0.f;
+#pragma unroll
+                for (int k = 1; k < 10; ++k)
+                    if (k - 5 == bestInc) { d1 = (float)acc[k - 1]; d2 = (float)acc[k]; d3 = (float)acc[k + 1]; }
+                const float deltaR = __fdiv_rn(__fsub_rn(d1, d3),
+                                               __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
+                if (!(deltaR < -1.f) && !(deltaR > 1.f)) {
+                    float bestuR = __fmul_rn(sp.scale[lv], __fadd_rn(__fadd_rn(sr, (float)bestInc), deltaR));
+                    float disparity = __fsub_rn(kpL.x, bestuR);
+                    if (disparity >= 0.f && disparity < sp.maxD) {
+                        if (disparity <= 0.f) {
+                            disparity = 0.01f;
+                            bestuR = (float)((double)kpL.x - 0.01);
+                        }
+                        outD = __fdiv_rn(sp.bf, disparity);
+                        outU = bestuR;
+                        outS = bestS;
+                    }
+                }
+            }
+        }
+    }
+    if (lane == 0) { uRight[o] = outU; depth[o] = outD; sad[o] = outS; }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Outlier cut: median of the accepted SAD values (element size/2 of the ascending list), reject
+// everything with sad >= 1.5 * 1.4 * median.  16-bit radix select (SAD <= 121 * 510 < 2^16) with
+// two 256-bin shared histograms.  grid (nFrames), block 256.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_stereo_cut(int outCap, const int* __restrict__ nL, const int32_t* __restrict__ sad,
+                                                    float* __restrict__ uRight, float* __restrict__ depth, int* __restrict__ nStereo) {
+    __shared__ int hist[256];
+    __shared__ int sh_cnt, sh_bin, sh_k, sh_kept;
+    const int tid = threadIdx.x, f = blockIdx.x;
+    const int n = nL[f];
+    const int32_t* S = sad + (size_t)f * outCap;
+    hist[tid] = 0;
+    if (tid == 0) { sh_cnt = 0; sh_kept = 0; }
+    __syncthreads();
+    int loc = 0;
+    for (int i = tid; i < n; i += 256) {
+        const int v = S[i];
+        if (v >= 0) { atomicAdd(&hist[(v >> 8) & 0xFF], 1); ++loc; }
+    }
+    if (loc) atomicAdd(&sh_cnt, loc);
+    __syncthreads();
+    const int cnt = sh_cnt;
+    if (cnt == 0) { if (tid == 0) nStereo[f] = 0; return; }
+    if (tid == 0) {
+        int k = cnt / 2, b = 0;
+        while (k >= hist[b]) { k -= hist[b]; ++b; }
+        sh_bin = b; sh_k = k;
+    }
+    __syncthreads();
+    const int hiBin = sh_bin;
+    __syncthreads();
+    hist[tid] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += 256) {
+        const int v = S[i];
+        if (v >= 0 && ((v >> 8) & 0xFF) == hiBin) atomicAdd(&hist[v & 0xFF], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int k = sh_k, b = 0;
+        while (k >= hist[b]) { k -= hist[b]; ++b; }
+        sh_bin = (hiBin << 8) | b;
+    }
+    __syncthreads();
+    const float median = (float)sh_bin;
+    const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), median);
+    int kept = 0;
+    for (int i = tid; i < n; i += 256) {
+        const int v = S[i];
+        if (v >= 0) {
+            if ((float)v >= thDist) { uRight[(size_t)f * outCap + i] = -1.f; depth[(size_t)f * outCap + i] = -1.f; }
+            else ++kept;
+        }
+    }
+    if (kept) atomicAdd(&sh_kept, kept);
+    __syncthreads();
+    if (tid == 0) nStereo[f] = sh_kept;
+}

@@ -1,0 +1,928 @@
+// viorb_api.cu — host side of libviorb.so: handles, arenas, geometry tables, launches, and the C ABI
+// declared in include/viorb.h.  No OpenCV, no torch; CUDA runtime only.
+//
+// There is deliberately NO CPU fallback: every entry point that computes launches the sm_100a
+// kernels in kernels_extract.cuh / kernels_match.cuh and fails with VIORB_E_CUDA / VIORB_E_NO_DEVICE
+// if that is impossible.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels_extract.cuh"
+#include "kernels_match.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(VIORB_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));         \
+    } while (0)
+
+inline int round_up(int v, int a) { return (v + a - 1) / a * a; }
+inline int cv_round_f(float v) { return (int)lrintf(v); }
+inline short sat_short(float v) { return (short)std::min(std::max(cv_round_f(v), -32768), 32767); }
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t alloc(size_t count) {
+        release();
+        n = count;
+        return cudaMalloc((void**)&p, std::max<size_t>(count, 1) * sizeof(T));
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+};
+template <class T>
+struct PinBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t alloc(size_t count) {
+        release();
+        n = count;
+        return cudaMallocHost((void**)&p, std::max<size_t>(count, 1) * sizeof(T));
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; n = 0; }
+};
+
+}  // namespace
+
+struct viorb_extractor {
+    viorb_params prm;
+    // FExtractor ctor tables (fextractor.cpp:401-461)
+    float scale[VIORB_MAX_LEVELS], invScale[VIORB_MAX_LEVELS], sigma2[VIORB_MAX_LEVELS], invSigma2[VIORB_MAX_LEVELS];
+    int featPerLevel[VIORB_MAX_LEVELS];
+    UmaxTable umax;
+    // geometry of the current image size
+    ExtractGeom g;
+    BlurTiles blurTiles;
+    int totalBlurTiles = 0;
+    std::vector<CellDesc> cells;
+    size_t fastSmem = 0, octSmem = 0;
+    // limits the arenas were sized for
+    size_t capArena = 0, capCand = 0, capKept = 0, capCells = 0, capXTab = 0, capYTab = 0;
+    int capOut = 0;
+    // device state
+    cudaStream_t stream = nullptr;
+    bool ownStream = false;
+    DevBuf<uint8_t> dIn, dPyr, dBlur, dDesc;
+    DevBuf<uint32_t> dCand;
+    DevBuf<uint16_t> dKeyNode;
+    DevBuf<int> dCandCount, dKeptCount, dSlot2Kept, dNOut, dMono, dStatus, dXofs, dYofs;
+    DevBuf<short2> dXalpha, dYbeta;
+    DevBuf<KeptKp> dKept;
+    DevBuf<viorb_keypoint> dKps;
+    DevBuf<CellDesc> dCells;
+    // stereo / matching results of the last viorb_stereo_batch on this (left) handle
+    DevBuf<int32_t> dBestIdx, dBestDist, dSad, dKnnIdx, dKnnDist, dLrMatch;
+    DevBuf<float> dURight, dDepth;
+    DevBuf<int> dNStereo, dNRatio;
+    DevBuf<viorb_match> dMatches;
+    // pinned staging
+    PinBuf<uint8_t> hIn, hDesc;
+    PinBuf<viorb_keypoint> hKps;
+    PinBuf<int> hCounts;
+    // last run
+    FrameSrc src{};
+    int lastN = 0;
+    int inPitch = 0;
+};
+
+namespace {
+
+// ---- FExtractor::FExtractor tables ----------------------------------------------------------
+void build_tables(viorb_extractor* ex) {
+    const viorb_params& p = ex->prm;
+    const int nl = p.nlevels;
+    ex->scale[0] = 1.0f;
+    ex->sigma2[0] = 1.0f;
+    for (int i = 1; i < nl; ++i) {
+        ex->scale[i] = ex->scale[i - 1] * p.scale_factor;
+        ex->sigma2[i] = ex->scale[i] * ex->scale[i];
+    }
+    for (int i = 0; i < nl; ++i) {
+        ex->invScale[i] = 1.0f / ex->scale[i];
+        ex->invSigma2[i] = 1.0f / ex->sigma2[i];
+    }
+    const float factor = 1.0f / p.scale_factor;
+    float want = p.nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; ++l) {
+        ex->featPerLevel[l] = cv_round_f(want);
+        sum += ex->featPerLevel[l];
+        want *= factor;
+    }
+    ex->featPerLevel[nl - 1] = std::max(p.nfeatures - sum, 0);
+    // umax: end of each row of the radius-15 disc, made symmetric (fextractor.cpp:444-460)
+    int* um = ex->umax.v;
+    const int hp = VIORB_HALF_PATCH;
+    const int vmax = (int)std::floor(hp * std::sqrt(2.f) / 2 + 1);
+    const int vmin = (int)std::ceil(hp * std::sqrt(2.f) / 2);
+    for (int v = 0; v <= vmax; ++v) um[v] = (int)lrint(std::sqrt((double)hp * hp - v * v));
+    for (int v = hp, v0 = 0; v >= vmin; --v) {
+        while (um[v0] == um[v0 + 1]) ++v0;
+        um[v] = v0;
+        ++v0;
+    }
+}
+
+// ---- geometry for one image size ------------------------------------------------------------
+struct ResizeTabs {
+    std::vector<int> xofs, yofs;
+    std::vector<short2> xalpha, ybeta;
+};
+
+// cv::resize INTER_LINEAR coefficient tables (OpenCV resize.cpp, linear 8U path).
+void build_resize_tables(int sw, int sh, int dw, int dh, ResizeTabs& t) {
+    const double scale_x = 1.0 / ((double)dw / sw), scale_y = 1.0 / ((double)dh / sh);
+    for (int dx = 0; dx < dw; ++dx) {
+        float fx = (float)((dx + 0.5) * scale_x - 0.5);
+        int sx = (int)std::floor(fx);
+        fx -= sx;
+        if (sx < 0) { fx = 0; sx = 0; }
+        if (sx >= sw - 1) { fx = 0; sx = sw - 1; }
+        t.xofs.push_back(sx);
+        t.xalpha.push_back(make_short2(sat_short((1.f - fx) * 2048), sat_short(fx * 2048)));
+    }
+    for (int dy = 0; dy < dh; ++dy) {
+        float fy = (float)((dy + 0.5) * scale_y - 0.5);
+        int sy = (int)std::floor(fy);
+        fy -= sy;
+        t.yofs.push_back(sy);
+        t.ybeta.push_back(make_short2(sat_short((1.f - fy) * 2048), sat_short(fy * 2048)));
+    }
+}
+
+int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
+    ExtractGeom& g = ex->g;
+    std::memset(&g, 0, sizeof(g));
+    const int nl = ex->prm.nlevels;
+    g.nlevels = nl; g.W = W; g.H = H;
+    g.iniTh = std::min(std::max(ex->prm.ini_th_fast, 0), 255);
+    g.minTh = std::min(std::max(ex->prm.min_th_fast, 0), 255);
+    ex->cells.clear();
+    tabs = ResizeTabs();
+    size_t off = 0;
+    int candOff = 0, keptOff = 0, maxRW = 1, maxRH = 1, maxNodes = 8, blurBase = 0;
+    for (int l = 0; l < nl; ++l) {
+        LevelGeom& L = g.lv[l];
+        L.w = cv_round_f((float)W * ex->invScale[l]);           // fextractor.cpp:1139-1140
+        L.h = cv_round_f((float)H * ex->invScale[l]);
+        if (L.w < 1 || L.h < 1) return fail(VIORB_E_ARG, "image too small for the configured number of levels");
+        if (L.w > 4096 + 32 || L.h > 4096 + 32) return fail(VIORB_E_ARG, "image larger than 4128 px is not supported");
+        L.pitch = round_up(L.w, 64);
+        L.off = (int)off;
+        off += (size_t)round_up(L.pitch * L.h, 256);
+        L.scale = ex->scale[l];
+        L.kpSize = (float)(int)(31 * ex->scale[l]);             // fextractor.cpp:828,837
+        L.maxBX = L.w - VIORB_EDGE + 3;
+        L.maxBY = L.h - VIORB_EDGE + 3;
+        L.xTab = (int)tabs.xofs.size();
+        L.yTab = (int)tabs.yofs.size();
+        if (l > 0) {
+            const LevelGeom& S = g.lv[l - 1];
+            L.areaHalf = (S.w == 2 * L.w && S.h == 2 * L.h) ? 1 : 0;
+            build_resize_tables(S.w, S.h, L.w, L.h, tabs);
+        }
+        // FAST cell grid (fextractor.cpp:769-806)
+        const float width = (float)(L.maxBX - VIORB_MINB), height = (float)(L.maxBY - VIORB_MINB);
+        L.nCols = (int)(width / 30.f);
+        L.nRows = (int)(height / 30.f);
+        L.cellBase = (int)ex->cells.size();
+        L.lastCol = L.lastRow = 0;
+        if (L.nCols > 0 && L.nRows > 0 && width > 0 && height > 0) {
+            L.wCell = (int)std::ceil(width / L.nCols);
+            L.hCell = (int)std::ceil(height / L.nRows);
+            for (int i = 0; i < L.nRows; ++i) {
+                const float iniY = (float)(VIORB_MINB + i * L.hCell);
+                float maxY = iniY + L.hCell + 6;
+                if (iniY >= L.maxBY - 3) continue;
+                if (maxY > L.maxBY) maxY = (float)L.maxBY;
+                for (int j = 0; j < L.nCols; ++j) {
+                    const float iniX = (float)(VIORB_MINB + j * L.wCell);
+                    float maxX = iniX + L.wCell + 6;
+                    if (iniX >= L.maxBX - 6) continue;
+                    if (maxX > L.maxBX) maxX = (float)L.maxBX;
+                    CellDesc c;
+                    c.level = (short)l; c.pad = 0;
+                    c.x0 = (short)((int)iniX + 3); c.x1 = (short)((int)maxX - 3);
+                    c.y0 = (short)((int)iniY + 3); c.y1 = (short)((int)maxY - 3);
+                    if (c.x1 <= c.x0 || c.y1 <= c.y0) continue;    // ROI narrower than 7: cv::FAST finds nothing
+                    ex->cells.push_back(c);
+                    L.lastCol = std::max(L.lastCol, j);
+                    L.lastRow = std::max(L.lastRow, i);
+                    maxRW = std::max(maxRW, c.x1 - c.x0);
+                    maxRH = std::max(maxRH, c.y1 - c.y0);
+                }
+            }
+        } else {
+            L.wCell = L.hCell = 1;
+        }
+        L.nCells = (int)ex->cells.size() - L.cellBase;
+        // NMS leaves at most one corner per 2x2 block
+        L.candOff = candOff;
+        L.candCap = std::max(0, (L.maxBX - VIORB_MINB)) * std::max(0, (L.maxBY - VIORB_MINB)) / 4 + 64;
+        candOff += round_up(L.candCap, 8);
+        // DistributeOctTree roots (fextractor.cpp:533-536)
+        L.nWant = ex->featPerLevel[l];
+        const int dx = L.maxBX - VIORB_MINB, dy = L.maxBY - VIORB_MINB;
+        L.nIni = dy > 0 ? (int)std::round((float)dx / dy) : 1;
+        if (L.nIni < 1) L.nIni = 1;
+        if (L.nIni > 64) return fail(VIORB_E_ARG, "aspect ratio above 64:1 is not supported");
+        L.hX = (float)dx / L.nIni;
+        L.keptOff = keptOff;
+        L.keptCap = std::max(L.nWant + 3, 4 * L.nIni) + 1;
+        keptOff += L.keptCap;
+        maxNodes = std::max(maxNodes, L.keptCap + 4);
+        ex->blurTiles.base[l] = blurBase;
+        ex->blurTiles.tilesX[l] = (L.w + 63) / 64;
+        blurBase += ex->blurTiles.tilesX[l] * ((L.h + 15) / 16);
+    }
+    ex->blurTiles.base[nl] = blurBase;
+    ex->totalBlurTiles = blurBase;
+    if (maxNodes > 65535) return fail(VIORB_E_ARG, "nfeatures too large for 16-bit node ids");
+    g.totalCells = (int)ex->cells.size();
+    g.candPerFrame = candOff;
+    g.keptPerFrame = keptOff;
+    g.outCap = keptOff;
+    g.tileW = maxRW + 6;
+    g.tileH = maxRH + 6;
+    g.maxNodes = maxNodes;
+    g.arenaStride = off;
+    const int TP = (g.tileW + 3 + 3) & ~3, SP = g.tileW - 4;
+    ex->fastSmem = (size_t)g.tileH * TP + (size_t)(((g.tileH - 4) * SP + 3) & ~3) + (size_t)2 * maxRW * maxRH + 16;
+    ex->octSmem = octree_smem_bytes(maxNodes);
+    if (ex->octSmem > 220 * 1024) return fail(VIORB_E_ARG, "nfeatures too large for the quadtree's shared memory");
+    if (maxRW * maxRH >= 16384) return fail(VIORB_E_ARG, "FAST cell larger than supported");
+    return VIORB_OK;
+}
+
+int upload_geometry(viorb_extractor* ex, const ResizeTabs& tabs) {
+    if (ex->cells.size() > ex->capCells || tabs.xofs.size() > ex->capXTab || tabs.yofs.size() > ex->capYTab)
+        return fail(VIORB_E_CAPACITY, "image size exceeds the max_width/max_height the handle was created with");
+    CU(cudaMemcpyAsync(ex->dCells.p, ex->cells.data(), ex->cells.size() * sizeof(CellDesc), cudaMemcpyHostToDevice, ex->stream));
+    CU(cudaMemcpyAsync(ex->dXofs.p, tabs.xofs.data(), tabs.xofs.size() * sizeof(int), cudaMemcpyHostToDevice, ex->stream));
+    CU(cudaMemcpyAsync(ex->dXalpha.p, tabs.xalpha.data(), tabs.xalpha.size() * sizeof(short2), cudaMemcpyHostToDevice, ex->stream));
+    CU(cudaMemcpyAsync(ex->dYofs.p, tabs.yofs.data(), tabs.yofs.size() * sizeof(int), cudaMemcpyHostToDevice, ex->stream));
+    CU(cudaMemcpyAsync(ex->dYbeta.p, tabs.ybeta.data(), tabs.ybeta.size() * sizeof(short2), cudaMemcpyHostToDevice, ex->stream));
+    CU(cudaStreamSynchronize(ex->stream));      // the host vectors go out of scope
+    return VIORB_OK;
+}
+
+int set_size(viorb_extractor* ex, int W, int H) {
+    if (ex->g.W == W && ex->g.H == H) return VIORB_OK;
+    if (W > ex->prm.max_width || H > ex->prm.max_height)
+        return fail(VIORB_E_CAPACITY, "image larger than max_width x max_height of this handle");
+    ResizeTabs tabs;
+    int rc = build_geometry(ex, W, H, tabs);
+    if (rc) { ex->g.W = ex->g.H = 0; return rc; }
+    if (ex->g.arenaStride > ex->capArena || (size_t)ex->g.candPerFrame > ex->capCand ||
+        (size_t)ex->g.keptPerFrame > ex->capKept || ex->g.outCap > ex->capOut) {
+        ex->g.W = ex->g.H = 0;
+        return fail(VIORB_E_CAPACITY, "image size exceeds the arenas sized at create time");
+    }
+    rc = upload_geometry(ex, tabs);
+    if (rc) { ex->g.W = ex->g.H = 0; return rc; }
+#ifndef VIORB_EMU
+    CU(cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->fastSmem));
+    CU(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->octSmem));
+#endif
+    return VIORB_OK;
+}
+
+// ---- the extraction pipeline on n frames already on the device ------------------------------
+int run_pipeline(viorb_extractor* ex, int n, int lap0, int lap1) {
+    const ExtractGeom& g = ex->g;
+    const FrameSrc& fs = ex->src;
+    cudaStream_t st = ex->stream;
+    CU(cudaMemsetAsync(ex->dCandCount.p, 0, sizeof(int) * (size_t)n * g.nlevels, st));
+    for (int l = 1; l < g.nlevels; ++l) {
+        const LevelGeom& L = g.lv[l];
+        dim3 grid((L.w + 255) / 256, (L.h + 3) / 4, n), block(64, 4);
+        VIORB_LAUNCH(k_resize, grid, block, 0, st, g, fs, l, ex->dXofs.p, ex->dXalpha.p, ex->dYofs.p, ex->dYbeta.p);
+    }
+    if (g.totalCells > 0) {
+        VIORB_LAUNCH(k_fast, dim3(g.totalCells, n), dim3(VIORB_FAST_THREADS), ex->fastSmem, st, g, fs, ex->dCells.p,
+                     ex->dCand.p, ex->dCandCount.p, ex->dStatus.p);
+    }
+    VIORB_LAUNCH(k_octree, dim3(g.nlevels, n), dim3(VIORB_OCT_THREADS), ex->octSmem, st, g, ex->dCand.p, ex->dCandCount.p,
+                 ex->dKeyNode.p, ex->dKept.p, ex->dKeptCount.p, ex->dStatus.p);
+    VIORB_LAUNCH(k_orient, dim3((g.keptPerFrame + 7) / 8, n), dim3(256), 0, st, g, fs, ex->umax, ex->dKept.p, ex->dKeptCount.p);
+    VIORB_LAUNCH(k_emit, dim3(n), dim3(256), 0, st, g, ex->dKept.p, ex->dKeptCount.p, lap0, lap1, ex->dKps.p,
+                 ex->dSlot2Kept.p, ex->dNOut.p, ex->dMono.p);
+    VIORB_LAUNCH(k_blur, dim3(ex->totalBlurTiles, n), dim3(256), 0, st, g, fs, ex->blurTiles);
+    VIORB_LAUNCH(k_describe, dim3((g.outCap + 7) / 8, n), dim3(256), 0, st, g, fs, ex->dKept.p, ex->dSlot2Kept.p,
+                 ex->dNOut.p, ex->dDesc.p);
+    CU(cudaGetLastError());
+    ex->lastN = n;
+    return VIORB_OK;
+}
+
+int check_status(viorb_extractor* ex) {
+    int st = 0;
+    CU(cudaMemcpyAsync(&st, ex->dStatus.p, sizeof(int), cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaStreamSynchronize(ex->stream));
+    if (st) {
+        CU(cudaMemsetAsync(ex->dStatus.p, 0, sizeof(int), ex->stream));
+        char buf[96];
+        std::snprintf(buf, sizeof buf, "device arena overflow (status bits 0x%x)", st);
+        return fail(VIORB_E_CAPACITY, buf);
+    }
+    return VIORB_OK;
+}
+
+int ensure_match_buffers(viorb_extractor* ex) {
+    const size_t need = (size_t)ex->prm.max_batch * ex->capOut;
+    if (ex->dBestIdx.n >= need) return VIORB_OK;
+    CU(ex->dBestIdx.alloc(need)); CU(ex->dBestDist.alloc(need)); CU(ex->dSad.alloc(need));
+    CU(ex->dURight.alloc(need)); CU(ex->dDepth.alloc(need)); CU(ex->dLrMatch.alloc(need));
+    CU(ex->dKnnIdx.alloc(need * 2)); CU(ex->dKnnDist.alloc(need * 2));
+    CU(ex->dMatches.alloc(need));
+    CU(ex->dNStereo.alloc(ex->prm.max_batch)); CU(ex->dNRatio.alloc(ex->prm.max_batch));
+    return VIORB_OK;
+}
+
+bool same_geometry(const viorb_extractor* a, const viorb_extractor* b) {
+    return a->g.W == b->g.W && a->g.H == b->g.H && a->g.nlevels == b->g.nlevels && a->g.outCap == b->g.outCap &&
+           a->prm.scale_factor == b->prm.scale_factor && a->g.W > 0;
+}
+
+StereoParams make_stereo_params(const viorb_extractor* ex, float bf, float b) {
+    StereoParams sp;
+    std::memset(&sp, 0, sizeof sp);
+    sp.bf = bf;
+    sp.maxD = bf / b;                       // maxD = mbf / minZ, minZ = mb (frame.cpp:853-855)
+    sp.nlevels = ex->g.nlevels;
+    sp.outCap = ex->g.outCap;
+    for (int l = 0; l < ex->g.nlevels; ++l) { sp.scale[l] = ex->scale[l]; sp.invScale[l] = ex->invScale[l]; }
+    return sp;
+}
+
+int launch_stereo(viorb_extractor* L, viorb_extractor* R, int n, float bf, float b) {
+    const StereoParams sp = make_stereo_params(L, bf, b);
+    cudaStream_t st = L->stream;
+    const int gx = (L->g.outCap + 7) / 8;
+    VIORB_LAUNCH(k_stereo_coarse, dim3(gx, n), dim3(256), 0, st, sp, L->dKps.p, L->dDesc.p, L->dNOut.p, R->dKps.p, R->dDesc.p,
+                 R->dNOut.p, L->dBestIdx.p, L->dBestDist.p);
+    VIORB_LAUNCH(k_stereo_refine, dim3(gx, n), dim3(256), 0, st, sp, L->g, L->src, R->src, L->dKps.p, L->dNOut.p, R->dKps.p,
+                 L->dBestIdx.p, L->dBestDist.p, L->dURight.p, L->dDepth.p, L->dSad.p);
+    VIORB_LAUNCH(k_stereo_cut, dim3(n), dim3(256), 0, st, sp.outCap, L->dNOut.p, L->dSad.p, L->dURight.p, L->dDepth.p,
+                 L->dNStereo.p);
+    CU(cudaGetLastError());
+    return VIORB_OK;
+}
+
+// both handles must be quiescent w.r.t. each other: wait for the right handle's stream
+int join_streams(viorb_extractor* L, viorb_extractor* R) {
+    if (L->stream != R->stream) CU(cudaStreamSynchronize(R->stream));
+    return VIORB_OK;
+}
+
+}  // namespace
+
+// =================================================================================================
+// C ABI
+// =================================================================================================
+extern "C" {
+
+const char* viorb_last_error(void) { return g_err.c_str(); }
+const char* viorb_version(void) {
+#ifdef VIORB_EMU
+    return "viorb 0.1 (cpu emulation build: tests only)";
+#else
+    return "viorb 0.1 (sm_100a)";
+#endif
+}
+
+int viorb_extractor_create(const viorb_params* params, viorb_extractor** out) {
+    if (!params || !out) return fail(VIORB_E_ARG, "null argument");
+    *out = nullptr;
+    const viorb_params& p = *params;
+    if (p.nlevels < 1 || p.nlevels > VIORB_MAX_LEVELS || p.nfeatures < 1 || !(p.scale_factor > 1.0f) || p.max_batch < 1 ||
+        p.max_width < 1 || p.max_height < 1)
+        return fail(VIORB_E_ARG, "invalid viorb_params");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= p.device)
+        return fail(VIORB_E_NO_DEVICE, "no CUDA device: libviorb has no CPU path");
+    CU(cudaSetDevice(p.device));
+    viorb_extractor* ex = new viorb_extractor();
+    ex->prm = p;
+    std::memset(&ex->g, 0, sizeof(ex->g));
+    build_tables(ex);
+    ResizeTabs tabs;
+    int rc = build_geometry(ex, p.max_width, p.max_height, tabs);
+    if (rc) { delete ex; return rc; }
+    const ExtractGeom g = ex->g;
+    const size_t B = (size_t)p.max_batch;
+    ex->capArena = g.arenaStride + 4096;
+    ex->capCand = (size_t)g.candPerFrame + 1024;
+    ex->capKept = (size_t)g.keptPerFrame + 64;
+    ex->capOut = g.outCap + 64;
+    ex->capCells = ex->cells.size() + 256;
+    ex->capXTab = tabs.xofs.size() + 64 * VIORB_MAX_LEVELS;
+    ex->capYTab = tabs.yofs.size() + 64 * VIORB_MAX_LEVELS;
+    ex->inPitch = round_up(p.max_width, 64);
+    cudaError_t e = cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking);
+    ex->ownStream = true;
+    auto ok = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+    ok(ex->dIn.alloc(B * ex->inPitch * p.max_height));
+    ok(ex->dPyr.alloc(B * ex->capArena));
+    ok(ex->dBlur.alloc(B * ex->capArena));
+    ok(ex->dCand.alloc(B * ex->capCand));
+    ok(ex->dKeyNode.alloc(B * ex->capCand));
+    ok(ex->dCandCount.alloc(B * VIORB_MAX_LEVELS));
+    ok(ex->dKeptCount.alloc(B * VIORB_MAX_LEVELS));
+    ok(ex->dKept.alloc(B * ex->capKept));
+    ok(ex->dKps.alloc(B * ex->capOut));
+    ok(ex->dDesc.alloc(B * ex->capOut * 32));
+    ok(ex->dSlot2Kept.alloc(B * ex->capOut));
+    ok(ex->dNOut.alloc(B));
+    ok(ex->dMono.alloc(B));
+    ok(ex->dStatus.alloc(1));
+    ok(ex->dCells.alloc(ex->capCells));
+    ok(ex->dXofs.alloc(ex->capXTab));
+    ok(ex->dXalpha.alloc(ex->capXTab));
+    ok(ex->dYofs.alloc(ex->capYTab));
+    ok(ex->dYbeta.alloc(ex->capYTab));
+    ok(ex->hIn.alloc(B * ex->inPitch * p.max_height));
+    ok(ex->hKps.alloc(B * ex->capOut));
+    ok(ex->hDesc.alloc(B * ex->capOut * 32));
+    ok(ex->hCounts.alloc(B * 2 + 8));
+    if (e == cudaSuccess) e = cudaMemset(ex->dStatus.p, 0, sizeof(int));
+    if (e != cudaSuccess) {
+        std::string msg = std::string("allocation failed: ") + cudaGetErrorString(e);
+        viorb_extractor_destroy(ex);
+        return fail(VIORB_E_CUDA, msg);
+    }
+    ex->g.W = ex->g.H = 0;      // force the geometry upload on first use
+    *out = ex;
+    return VIORB_OK;
+}
+
+void viorb_extractor_destroy(viorb_extractor* ex) {
+    if (!ex) return;
+    cudaSetDevice(ex->prm.device);
+    if (ex->stream || ex->ownStream) cudaStreamSynchronize(ex->stream);
+    ex->dIn.release(); ex->dPyr.release(); ex->dBlur.release(); ex->dDesc.release(); ex->dCand.release();
+    ex->dKeyNode.release(); ex->dCandCount.release(); ex->dKeptCount.release(); ex->dSlot2Kept.release();
+    ex->dNOut.release(); ex->dMono.release(); ex->dStatus.release(); ex->dXofs.release(); ex->dYofs.release();
+    ex->dXalpha.release(); ex->dYbeta.release(); ex->dKept.release(); ex->dKps.release(); ex->dCells.release();
+    ex->dBestIdx.release(); ex->dBestDist.release(); ex->dSad.release(); ex->dKnnIdx.release(); ex->dKnnDist.release();
+    ex->dLrMatch.release(); ex->dURight.release(); ex->dDepth.release(); ex->dNStereo.release(); ex->dNRatio.release();
+    ex->dMatches.release();
+    ex->hIn.release(); ex->hDesc.release(); ex->hKps.release(); ex->hCounts.release();
+    if (ex->ownStream && ex->stream) cudaStreamDestroy(ex->stream);
+    delete ex;
+}
+
+int viorb_extractor_tables(const viorb_extractor* ex, int32_t* nlevels, float* scale, float* inv_scale, float* sigma2,
+                           float* inv_sigma2, int32_t* features_per_level) {
+    if (!ex) return fail(VIORB_E_ARG, "null handle");
+    const int nl = ex->prm.nlevels;
+    if (nlevels) *nlevels = nl;
+    for (int l = 0; l < nl; ++l) {
+        if (scale) scale[l] = ex->scale[l];
+        if (inv_scale) inv_scale[l] = ex->invScale[l];
+        if (sigma2) sigma2[l] = ex->sigma2[l];
+        if (inv_sigma2) inv_sigma2[l] = ex->invSigma2[l];
+        if (features_per_level) features_per_level[l] = ex->featPerLevel[l];
+    }
+    return VIORB_OK;
+}
+
+int viorb_extractor_capacity(const viorb_extractor* ex) { return ex ? ex->capOut : 0; }
+
+void* viorb_extractor_stream(viorb_extractor* ex) { return ex ? (void*)ex->stream : nullptr; }
+
+/* Run this handle's work on a caller-owned stream (e.g. the framework's current stream). */
+int viorb_extractor_set_stream(viorb_extractor* ex, void* stream) {
+    if (!ex) return fail(VIORB_E_ARG, "null handle");
+    CU(cudaSetDevice(ex->prm.device));
+    CU(cudaStreamSynchronize(ex->stream));
+    if (ex->ownStream && ex->stream) cudaStreamDestroy(ex->stream);
+    ex->stream = (cudaStream_t)stream;
+    ex->ownStream = false;
+    return VIORB_OK;
+}
+
+int viorb_extractor_sync(viorb_extractor* ex) {
+    if (!ex) return fail(VIORB_E_ARG, "null handle");
+    CU(cudaSetDevice(ex->prm.device));
+    CU(cudaStreamSynchronize(ex->stream));
+    return VIORB_OK;
+}
+
+int viorb_extract_device(viorb_extractor* ex, const uint8_t* d_imgs, int n, int width, int height, int step,
+                         size_t frame_stride, int lap0, int lap1) {
+    if (!ex || !d_imgs) return fail(VIORB_E_ARG, "null argument");
+    if (width <= 0 || height <= 0 || n <= 0) return fail(VIORB_E_EMPTY, "empty image");
+    if (n > ex->prm.max_batch) return fail(VIORB_E_CAPACITY, "batch larger than max_batch");
+    if (step % 16 != 0 || ((uintptr_t)d_imgs & 15) || frame_stride % 16 != 0 || step < width)
+        return fail(VIORB_E_ARG, "device images need a 16-byte aligned base, step and frame stride");
+    CU(cudaSetDevice(ex->prm.device));
+    int rc = set_size(ex, width, height);
+    if (rc) return rc;
+    ex->src.l0 = d_imgs;
+    ex->src.l0Pitch = step;
+    ex->src.l0Stride = frame_stride;
+    ex->src.pyr = ex->dPyr.p;
+    ex->src.blur = ex->dBlur.p;
+    return run_pipeline(ex, n, lap0, lap1);
+}
+
+int viorb_extract_batch(viorb_extractor* ex, const uint8_t* const* imgs, int n, int width, int height, int step, int lap0,
+                        int lap1, viorb_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_index_out) {
+    if (!ex) return fail(VIORB_E_ARG, "null handle");
+    if (!imgs || n <= 0 || width <= 0 || height <= 0) {
+        if (mono_index_out) for (int i = 0; i < std::max(n, 1); ++i) mono_index_out[i] = -1;
+        if (n_out) for (int i = 0; i < std::max(n, 1); ++i) n_out[i] = 0;
+        return fail(VIORB_E_EMPTY, "empty image");
+    }
+    if (n > ex->prm.max_batch) return fail(VIORB_E_CAPACITY, "batch larger than max_batch");
+    if (width > ex->prm.max_width || height > ex->prm.max_height)
+        return fail(VIORB_E_CAPACITY, "image larger than max_width x max_height of this handle");
+    CU(cudaSetDevice(ex->prm.device));
+    const int pitch = ex->inPitch;
+    const size_t fstride = (size_t)pitch * height;
+    for (int i = 0; i < n; ++i) {
+        if (!imgs[i]) return fail(VIORB_E_EMPTY, "empty image");
+        for (int y = 0; y < height; ++y)
+            std::memcpy(ex->hIn.p + i * fstride + (size_t)y * pitch, imgs[i] + (size_t)y * step, width);
+    }
+    CU(cudaMemcpyAsync(ex->dIn.p, ex->hIn.p, fstride * n, cudaMemcpyHostToDevice, ex->stream));
+    int rc = viorb_extract_device(ex, ex->dIn.p, n, width, height, pitch, fstride, lap0, lap1);
+    if (rc) return rc;
+    const size_t oc = ex->g.outCap;
+    CU(cudaMemcpyAsync(ex->hCounts.p, ex->dNOut.p, sizeof(int) * n, cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaMemcpyAsync(ex->hCounts.p + n, ex->dMono.p, sizeof(int) * n, cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaMemcpyAsync(ex->hKps.p, ex->dKps.p, sizeof(viorb_keypoint) * oc * n, cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaMemcpyAsync(ex->hDesc.p, ex->dDesc.p, 32 * oc * n, cudaMemcpyDeviceToHost, ex->stream));
+    rc = check_status(ex);          // synchronises the stream
+    if (rc) return rc;
+    int worst = VIORB_OK;
+    for (int i = 0; i < n; ++i) {
+        const int cnt = ex->hCounts.p[i];
+        if (n_out) n_out[i] = cnt;
+        if (mono_index_out) mono_index_out[i] = ex->hCounts.p[n + i];
+        const int m = std::min(cnt, cap);
+        if (cnt > cap) worst = VIORB_E_CAPACITY;
+        if (kps && m > 0) std::memcpy(kps + (size_t)i * cap, ex->hKps.p + i * oc, sizeof(viorb_keypoint) * m);
+        if (desc && m > 0) std::memcpy(desc + (size_t)i * cap * 32, ex->hDesc.p + i * oc * 32, (size_t)32 * m);
+    }
+    if (worst) return fail(worst, "output buffer smaller than the number of keypoints (n_out holds the count)");
+    return VIORB_OK;
+}
+
+int viorb_extract(viorb_extractor* ex, const uint8_t* img, int width, int height, int step, int lap0, int lap1,
+                  viorb_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_index_out) {
+    const uint8_t* one[1] = {img};
+    if (!img) {
+        if (n_out) *n_out = 0;
+        if (mono_index_out) *mono_index_out = -1;
+        return fail(VIORB_E_EMPTY, "empty image");
+    }
+    return viorb_extract_batch(ex, one, 1, width, height, step, lap0, lap1, kps, desc, cap, n_out, mono_index_out);
+}
+
+int viorb_fetch(viorb_extractor* ex, int frame, viorb_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_index_out) {
+    if (!ex || frame < 0 || frame >= ex->lastN) return fail(VIORB_E_ARG, "bad handle or frame index");
+    CU(cudaSetDevice(ex->prm.device));
+    int rc = check_status(ex);
+    if (rc) return rc;
+    int cnt[2];
+    CU(cudaMemcpyAsync(&cnt[0], ex->dNOut.p + frame, sizeof(int), cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaMemcpyAsync(&cnt[1], ex->dMono.p + frame, sizeof(int), cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaStreamSynchronize(ex->stream));
+    if (n_out) *n_out = cnt[0];
+    if (mono_index_out) *mono_index_out = cnt[1];
+    const int m = std::min(cnt[0], cap);
+    const size_t oc = ex->g.outCap;
+    if (kps && m > 0) CU(cudaMemcpyAsync(kps, ex->dKps.p + frame * oc, sizeof(viorb_keypoint) * m, cudaMemcpyDeviceToHost, ex->stream));
+    if (desc && m > 0) CU(cudaMemcpyAsync(desc, ex->dDesc.p + frame * oc * 32, (size_t)32 * m, cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaStreamSynchronize(ex->stream));
+    if (cnt[0] > cap && (kps || desc)) return fail(VIORB_E_CAPACITY, "output buffer smaller than the number of keypoints");
+    return VIORB_OK;
+}
+
+int viorb_pyramid_level(viorb_extractor* ex, int frame, int level, uint8_t* dst, int dst_step, int* width, int* height) {
+    if (!ex || frame < 0 || frame >= ex->lastN || level < 0 || level >= ex->g.nlevels)
+        return fail(VIORB_E_ARG, "bad handle, frame or level");
+    CU(cudaSetDevice(ex->prm.device));
+    const LevelGeom& L = ex->g.lv[level];
+    if (width) *width = L.w;
+    if (height) *height = L.h;
+    if (!dst) return VIORB_OK;
+    const uint8_t* p;
+    int pitch;
+    if (level == 0) { p = ex->src.l0 + (size_t)frame * ex->src.l0Stride; pitch = ex->src.l0Pitch; }
+    else { p = ex->src.pyr + (size_t)frame * ex->g.arenaStride + L.off; pitch = L.pitch; }
+    CU(cudaMemcpy2DAsync(dst, dst_step, p, pitch, L.w, L.h, cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaStreamSynchronize(ex->stream));
+    return VIORB_OK;
+}
+
+int viorb_debug_blurred(viorb_extractor* ex, int frame, int level, uint8_t* dst, int dst_step) {
+    if (!ex || frame < 0 || frame >= ex->lastN || level < 0 || level >= ex->g.nlevels || !dst)
+        return fail(VIORB_E_ARG, "bad handle, frame or level");
+    CU(cudaSetDevice(ex->prm.device));
+    const LevelGeom& L = ex->g.lv[level];
+    CU(cudaMemcpy2DAsync(dst, dst_step, ex->src.blur + (size_t)frame * ex->g.arenaStride + L.off, L.pitch, L.w, L.h,
+                         cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaStreamSynchronize(ex->stream));
+    return VIORB_OK;
+}
+
+int viorb_debug_candidates(viorb_extractor* ex, int frame, int level, int32_t* xys, int cap, int* n_out) {
+    if (!ex || frame < 0 || frame >= ex->lastN || level < 0 || level >= ex->g.nlevels)
+        return fail(VIORB_E_ARG, "bad handle, frame or level");
+    CU(cudaSetDevice(ex->prm.device));
+    const LevelGeom& L = ex->g.lv[level];
+    int n = 0;
+    CU(cudaMemcpyAsync(&n, ex->dCandCount.p + frame * ex->g.nlevels + level, sizeof(int), cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaStreamSynchronize(ex->stream));
+    n = std::min(n, L.candCap);
+    if (n_out) *n_out = n;
+    if (!xys || n == 0) return VIORB_OK;
+    std::vector<uint32_t> raw(n);
+    CU(cudaMemcpyAsync(raw.data(), ex->dCand.p + (size_t)frame * ex->g.candPerFrame + L.candOff, sizeof(uint32_t) * n,
+                       cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaStreamSynchronize(ex->stream));
+    // presentation only: put the (unordered) device list into the reference's cell-major raster order
+    struct E { long long key; uint32_t e; };
+    std::vector<E> v(n);
+    for (int i = 0; i < n; ++i) {
+        const int x = raw[i] & 0xFFF, y = (raw[i] >> 12) & 0xFFF;
+        const long long cj = std::min(std::max(x - 3, 0) / L.wCell, L.lastCol), ci = std::min(std::max(y - 3, 0) / L.hCell, L.lastRow);
+        v[i] = {(ci << 32) | (cj << 24) | ((long long)y << 12) | x, raw[i]};
+    }
+    std::sort(v.begin(), v.end(), [](const E& a, const E& b) { return a.key < b.key; });
+    for (int i = 0; i < std::min(n, cap); ++i) {
+        xys[3 * i] = v[i].e & 0xFFF; xys[3 * i + 1] = (v[i].e >> 12) & 0xFFF; xys[3 * i + 2] = v[i].e >> 24;
+    }
+    return VIORB_OK;
+}
+
+int viorb_debug_kept(viorb_extractor* ex, int frame, int level, int32_t* xys, float* angle, int cap, int* n_out) {
+    if (!ex || frame < 0 || frame >= ex->lastN || level < 0 || level >= ex->g.nlevels)
+        return fail(VIORB_E_ARG, "bad handle, frame or level");
+    CU(cudaSetDevice(ex->prm.device));
+    const LevelGeom& L = ex->g.lv[level];
+    int n = 0;
+    CU(cudaMemcpyAsync(&n, ex->dKeptCount.p + frame * ex->g.nlevels + level, sizeof(int), cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaStreamSynchronize(ex->stream));
+    if (n_out) *n_out = n;
+    if (n == 0) return VIORB_OK;
+    std::vector<KeptKp> raw(n);
+    CU(cudaMemcpyAsync(raw.data(), ex->dKept.p + (size_t)frame * ex->g.keptPerFrame + L.keptOff, sizeof(KeptKp) * n,
+                       cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaStreamSynchronize(ex->stream));
+    for (int i = 0; i < std::min(n, cap); ++i) {
+        if (xys) { xys[3 * i] = raw[i].x; xys[3 * i + 1] = raw[i].y; xys[3 * i + 2] = raw[i].score & 0xFFFF; }
+        if (angle) angle[i] = raw[i].angle;
+    }
+    return VIORB_OK;
+}
+
+// ---- matching ------------------------------------------------------------------------------------
+
+int viorb_knn2_device(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int32_t* d_idx, int32_t* d_dist, void* stream) {
+    if (nq < 0 || nt < 0 || (nq > 0 && (!d_q || !d_idx || !d_dist))) return fail(VIORB_E_ARG, "bad argument");
+    if (nt >= (1 << VIORB_KNN_IDX_BITS)) return fail(VIORB_E_ARG, "train set larger than 2^22 rows");
+    if (((uintptr_t)d_q & 15) || ((uintptr_t)d_t & 15)) return fail(VIORB_E_ARG, "descriptor buffers must be 16-byte aligned");
+    if (nq == 0) return VIORB_OK;
+    DescSet Q{d_q, 0, nullptr, nq}, T{d_t, 0, nullptr, nt};
+    VIORB_LAUNCH(k_knn2, dim3((nq + VIORB_KNN_THREADS - 1) / VIORB_KNN_THREADS, 1), dim3(VIORB_KNN_THREADS), 0,
+                 (cudaStream_t)stream, Q, T, d_idx, d_dist, (size_t)nq);
+    CU(cudaGetLastError());
+    return VIORB_OK;
+}
+
+int viorb_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx, int32_t* dist, int device) {
+    if (nq < 0 || nt < 0 || (nq > 0 && (!q || !idx || !dist)) || (nt > 0 && !t)) return fail(VIORB_E_ARG, "bad argument");
+    if (nq == 0) return VIORB_OK;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= device) return fail(VIORB_E_NO_DEVICE, "no CUDA device: libviorb has no CPU path");
+    CU(cudaSetDevice(device));
+    DevBuf<uint8_t> dq, dt;
+    DevBuf<int32_t> di, dd;
+    int rc = VIORB_OK;
+    cudaError_t e = dq.alloc((size_t)nq * 32);
+    if (e == cudaSuccess) e = dt.alloc((size_t)std::max(nt, 1) * 32);
+    if (e == cudaSuccess) e = di.alloc((size_t)nq * 2);
+    if (e == cudaSuccess) e = dd.alloc((size_t)nq * 2);
+    if (e == cudaSuccess) e = cudaMemcpy(dq.p, q, (size_t)nq * 32, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && nt > 0) e = cudaMemcpy(dt.p, t, (size_t)nt * 32, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    if (!rc) rc = viorb_knn2_device(dq.p, nq, dt.p, nt, di.p, dd.p, nullptr);
+    if (!rc) {
+        e = cudaMemcpy(idx, di.p, sizeof(int32_t) * 2 * nq, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(dist, dd.p, sizeof(int32_t) * 2 * nq, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    }
+    dq.release(); dt.release(); di.release(); dd.release();
+    return rc;
+}
+
+int viorb_descriptor_distance(const uint8_t* a, const uint8_t* b, int n, int32_t* dist, int device) {
+    if (n < 0 || (n > 0 && (!a || !b || !dist))) return fail(VIORB_E_ARG, "bad argument");
+    if (n == 0) return VIORB_OK;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= device) return fail(VIORB_E_NO_DEVICE, "no CUDA device: libviorb has no CPU path");
+    CU(cudaSetDevice(device));
+    DevBuf<uint8_t> da, db;
+    DevBuf<int32_t> dd;
+    cudaError_t e = da.alloc((size_t)n * 32);
+    if (e == cudaSuccess) e = db.alloc((size_t)n * 32);
+    if (e == cudaSuccess) e = dd.alloc(n);
+    if (e == cudaSuccess) e = cudaMemcpy(da.p, a, (size_t)n * 32, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(db.p, b, (size_t)n * 32, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        VIORB_LAUNCH(k_desc_dist, dim3((n + 255) / 256), dim3(256), 0, (cudaStream_t)0, da.p, db.p, n, dd.p);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(dist, dd.p, sizeof(int32_t) * n, cudaMemcpyDeviceToHost);
+    da.release(); db.release(); dd.release();
+    if (e != cudaSuccess) return fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    return VIORB_OK;
+}
+
+// kNN-2 + ratio (+ dedup) on device buffers of one set; result rows to host.
+static int ratio_on_device(const uint8_t* dq, int nq, const uint8_t* dt, int nt, double ratio, int rule, int dedup,
+                           viorb_match* out, int cap, int* n_out, cudaStream_t st) {
+    if (n_out) *n_out = 0;
+    if (nq == 0) return VIORB_OK;
+    DevBuf<int32_t> di, dd;
+    DevBuf<viorb_match> dm, dm2;
+    DevBuf<int> dn, dFirst;
+    cudaError_t e = di.alloc((size_t)nq * 2);
+    if (e == cudaSuccess) e = dd.alloc((size_t)nq * 2);
+    if (e == cudaSuccess) e = dm.alloc(nq);
+    if (e == cudaSuccess) e = dn.alloc(2);
+    int rc = VIORB_OK;
+    if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    if (!rc) rc = viorb_knn2_device(dq, nq, dt, nt, di.p, dd.p, (void*)st);
+    int cnt = 0;
+    if (!rc) {
+        DescSet Q{dq, 0, nullptr, nq};
+        VIORB_LAUNCH(k_ratio, dim3(1), dim3(256), 0, st, Q, di.p, dd.p, (size_t)nq, ratio, rule, dm.p, (size_t)nq, dn.p,
+                     (int32_t*)nullptr);
+        e = cudaMemcpyAsync(&cnt, dn.p, sizeof(int), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    }
+    const viorb_match* res = dm.p;
+    if (!rc && dedup && cnt > 0) {
+        e = dFirst.alloc(std::max(nt, 1));
+        if (e == cudaSuccess) e = dm2.alloc(cnt);
+        if (e == cudaSuccess) e = cudaMemsetAsync(dFirst.p, 0x7f, sizeof(int) * (size_t)nt, st);   // 0x7f7f7f7f > any index
+        if (e == cudaSuccess) {
+            // sentinel must be exactly INT_MAX for k_dedup_emit: overwrite with a fill kernel-free trick
+            std::vector<int> init(nt, 0x7fffffff);
+            e = cudaMemcpyAsync(dFirst.p, init.data(), sizeof(int) * (size_t)nt, cudaMemcpyHostToDevice, st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        }
+        if (e == cudaSuccess) {
+            VIORB_LAUNCH(k_dedup_mark, dim3((cnt + 255) / 256), dim3(256), 0, st, dm.p, cnt, dFirst.p);
+            VIORB_LAUNCH(k_dedup_emit, dim3(1), dim3(256), 0, st, dFirst.p, nt, dd.p, dm2.p, dn.p + 1);
+            e = cudaMemcpyAsync(&cnt, dn.p + 1, sizeof(int), cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        }
+        if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+        res = dm2.p;
+    }
+    if (!rc) {
+        if (n_out) *n_out = cnt;
+        const int m = std::min(cnt, cap);
+        if (out && m > 0) {
+            e = cudaMemcpyAsync(out, res, sizeof(viorb_match) * m, cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+            if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+        }
+        if (!rc && cnt > cap && out) rc = fail(VIORB_E_CAPACITY, "match buffer too small (n_out holds the count)");
+    }
+    di.release(); dd.release(); dm.release(); dm2.release(); dn.release(); dFirst.release();
+    return rc;
+}
+
+int viorb_match_ratio(const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int rule, int dedup, viorb_match* out,
+                      int cap, int* n_out, int device) {
+    if (nq < 0 || nt < 0 || (nq > 0 && !q) || (nt > 0 && !t)) return fail(VIORB_E_ARG, "bad argument");
+    if (n_out) *n_out = 0;
+    if (nq == 0) return VIORB_OK;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= device) return fail(VIORB_E_NO_DEVICE, "no CUDA device: libviorb has no CPU path");
+    CU(cudaSetDevice(device));
+    DevBuf<uint8_t> dq, dt;
+    cudaError_t e = dq.alloc((size_t)nq * 32);
+    if (e == cudaSuccess) e = dt.alloc((size_t)std::max(nt, 1) * 32);
+    if (e == cudaSuccess) e = cudaMemcpy(dq.p, q, (size_t)nq * 32, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && nt > 0) e = cudaMemcpy(dt.p, t, (size_t)nt * 32, cudaMemcpyHostToDevice);
+    int rc = e == cudaSuccess ? VIORB_OK : fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    if (!rc) rc = ratio_on_device(dq.p, nq, dt.p, nt, ratio, rule, dedup, out, cap, n_out, (cudaStream_t)0);
+    dq.release(); dt.release();
+    return rc;
+}
+
+int viorb_match_resident(viorb_extractor* cur, int frame_q, viorb_extractor* prev, int frame_t, double ratio, int rule,
+                         viorb_match* out, int cap, int* n_out) {
+    if (!cur || !prev || frame_q < 0 || frame_q >= cur->lastN || frame_t < 0 || frame_t >= prev->lastN)
+        return fail(VIORB_E_ARG, "bad handle or frame index");
+    CU(cudaSetDevice(cur->prm.device));
+    int rc = join_streams(cur, prev);
+    if (rc) return rc;
+    int nq = 0, nt = 0;
+    CU(cudaMemcpyAsync(&nq, cur->dNOut.p + frame_q, sizeof(int), cudaMemcpyDeviceToHost, cur->stream));
+    CU(cudaMemcpyAsync(&nt, prev->dNOut.p + frame_t, sizeof(int), cudaMemcpyDeviceToHost, cur->stream));
+    CU(cudaStreamSynchronize(cur->stream));
+    return ratio_on_device(cur->dDesc.p + (size_t)frame_q * cur->g.outCap * 32, nq,
+                           prev->dDesc.p + (size_t)frame_t * prev->g.outCap * 32, nt, ratio, rule, 0, out, cap, n_out,
+                           cur->stream);
+}
+
+int viorb_stereo_batch(viorb_extractor* L, viorb_extractor* R, int n, float bf, float b, double ratio) {
+    if (!L || !R || n <= 0 || n > L->lastN || n > R->lastN) return fail(VIORB_E_ARG, "bad handle or frame count");
+    if (!same_geometry(L, R)) return fail(VIORB_E_ARG, "left and right extractor must share parameters and image size");
+    CU(cudaSetDevice(L->prm.device));
+    int rc = ensure_match_buffers(L);
+    if (rc) return rc;
+    rc = join_streams(L, R);
+    if (rc) return rc;
+    rc = launch_stereo(L, R, n, bf, b);
+    if (rc) return rc;
+    // fisheye-style brute force kNN-2 + ratio, left -> right (frame.cpp:1167-1170)
+    const size_t oc = L->g.outCap;
+    DescSet Q{L->dDesc.p, oc * 32, L->dNOut.p, 0}, T{R->dDesc.p, oc * 32, R->dNOut.p, 0};
+    VIORB_LAUNCH(k_knn2, dim3((L->g.outCap + VIORB_KNN_THREADS - 1) / VIORB_KNN_THREADS, n), dim3(VIORB_KNN_THREADS), 0, L->stream,
+                 Q, T, L->dKnnIdx.p, L->dKnnDist.p, oc);
+    VIORB_LAUNCH(k_ratio, dim3(n), dim3(256), 0, L->stream, Q, L->dKnnIdx.p, L->dKnnDist.p, oc, ratio, 0, L->dMatches.p, oc,
+                 L->dNRatio.p, L->dLrMatch.p);
+    CU(cudaGetLastError());
+    return VIORB_OK;
+}
+
+int viorb_stereo_fetch(viorb_extractor* L, int frame, float* u_right, float* depth, int32_t* lr_match, int cap, int* n_left,
+                       int* n_stereo, int* n_ratio) {
+    if (!L || frame < 0 || frame >= L->lastN || !L->dURight.p) return fail(VIORB_E_ARG, "bad handle or frame index");
+    CU(cudaSetDevice(L->prm.device));
+    int c[3];
+    CU(cudaMemcpyAsync(&c[0], L->dNOut.p + frame, sizeof(int), cudaMemcpyDeviceToHost, L->stream));
+    CU(cudaMemcpyAsync(&c[1], L->dNStereo.p + frame, sizeof(int), cudaMemcpyDeviceToHost, L->stream));
+    CU(cudaMemcpyAsync(&c[2], L->dNRatio.p + frame, sizeof(int), cudaMemcpyDeviceToHost, L->stream));
+    CU(cudaStreamSynchronize(L->stream));
+    if (n_left) *n_left = c[0];
+    if (n_stereo) *n_stereo = c[1];
+    if (n_ratio) *n_ratio = c[2];
+    const int m = std::min(c[0], cap);
+    const size_t o = (size_t)frame * L->g.outCap;
+    if (m > 0) {
+        if (u_right) CU(cudaMemcpyAsync(u_right, L->dURight.p + o, sizeof(float) * m, cudaMemcpyDeviceToHost, L->stream));
+        if (depth) CU(cudaMemcpyAsync(depth, L->dDepth.p + o, sizeof(float) * m, cudaMemcpyDeviceToHost, L->stream));
+        if (lr_match) CU(cudaMemcpyAsync(lr_match, L->dLrMatch.p + o, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, L->stream));
+        CU(cudaStreamSynchronize(L->stream));
+    }
+    return VIORB_OK;
+}
+
+int viorb_stereo_match(viorb_extractor* L, viorb_extractor* R, int frame, float bf, float b, float* u_right, float* depth,
+                       int32_t* best_idx, int32_t* best_dist, int cap, int* n_left) {
+    if (!L || !R || frame < 0 || frame >= L->lastN || frame >= R->lastN) return fail(VIORB_E_ARG, "bad handle or frame index");
+    if (!same_geometry(L, R)) return fail(VIORB_E_ARG, "left and right extractor must share parameters and image size");
+    CU(cudaSetDevice(L->prm.device));
+    int rc = ensure_match_buffers(L);
+    if (rc) return rc;
+    rc = join_streams(L, R);
+    if (rc) return rc;
+    // the kernels are batched over frames [0, n): run up to and including `frame`
+    rc = launch_stereo(L, R, frame + 1, bf, b);
+    if (rc) return rc;
+    int nl = 0;
+    CU(cudaMemcpyAsync(&nl, L->dNOut.p + frame, sizeof(int), cudaMemcpyDeviceToHost, L->stream));
+    CU(cudaStreamSynchronize(L->stream));
+    if (n_left) *n_left = nl;
+    const int m = std::min(nl, cap);
+    const size_t o = (size_t)frame * L->g.outCap;
+    if (m > 0) {
+        if (u_right) CU(cudaMemcpyAsync(u_right, L->dURight.p + o, sizeof(float) * m, cudaMemcpyDeviceToHost, L->stream));
+        if (depth) CU(cudaMemcpyAsync(depth, L->dDepth.p + o, sizeof(float) * m, cudaMemcpyDeviceToHost, L->stream));
+        if (best_idx) CU(cudaMemcpyAsync(best_idx, L->dBestIdx.p + o, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, L->stream));
+        if (best_dist) CU(cudaMemcpyAsync(best_dist, L->dBestDist.p + o, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, L->stream));
+        CU(cudaStreamSynchronize(L->stream));
+    }
+    if (nl > cap) return fail(VIORB_E_CAPACITY, "output buffer smaller than the number of left keypoints");
+    return VIORB_OK;
+}
+
+}  // extern "C"

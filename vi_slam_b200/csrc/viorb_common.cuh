@@ -1,0 +1,83 @@
+// viorb_common.cuh — shared declarations for the sm_100a ORB front-end kernels.
+#pragma once
+
+#ifdef VIORB_EMU
+// g++ build of the same sources for CPU logic tests (tests/cuda_emu); never shipped.
+#include "cuda_emu.h"
+#define VIORB_LAUNCH(kernel, grid, block, smem, stream, ...) \
+    cuda_emu::launch((grid), (block), (smem), [&]() { kernel(__VA_ARGS__); })
+#define VIORB_DYN_SMEM(name) unsigned char* name = (unsigned char*)EMU_DYN_SMEM_PTR
+#else
+#include <cuda_runtime.h>
+#define VIORB_LAUNCH(kernel, grid, block, smem, stream, ...) \
+    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+#define VIORB_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
+#endif
+
+#include <stdint.h>
+
+#include "../../include/viorb.h"
+
+#define VIORB_MAX_LEVELS 16
+#define VIORB_EDGE 19          // EDGE_THRESHOLD (fextractor.cpp:66)
+#define VIORB_HALF_PATCH 15    // HALF_PATCH_SIZE (fextractor.cpp:65)
+#define VIORB_MINB 16          // EDGE_THRESHOLD - 3 (fextractor.cpp:764)
+
+// Geometry of one pyramid level for a given input size (host-computed once per size).
+struct LevelGeom {
+    int w, h, pitch;       // level image; pitch is a multiple of 16
+    int off;               // byte offset inside one frame's pyramid / blur arena
+    int maxBX, maxBY;      // w - 16, h - 16 (fextractor.cpp:766-767)
+    int nCols, nRows, wCell, hCell, lastCol, lastRow;   // FAST cell grid (fextractor.cpp:775-778)
+    int cellBase, nCells;  // slice of the cell table
+    int candOff, candCap;  // slice of one frame's candidate arena (entries)
+    int nWant, nIni;       // DistributeOctTree N and root count
+    float hX;              // root width
+    int keptOff, keptCap;  // slice of one frame's kept-keypoint arena
+    int xTab, yTab;        // offsets into the resize coefficient tables (entries)
+    int areaHalf;          // 1: exact 2x decimation (INTER_AREA fast path)
+    float scale;           // mvScaleFactor[l]
+    float kpSize;          // (float)(int)(31 * scale)
+};
+
+struct ExtractGeom {
+    int nlevels, W, H;
+    int iniTh, minTh;
+    int totalCells;
+    int candPerFrame, keptPerFrame;
+    int outCap;            // per-frame output capacity (keypoints)
+    int tileW, tileH;      // FAST smem tile (max cell region + 6)
+    int maxNodes;          // octree node capacity in shared memory
+    size_t arenaStride;    // bytes per frame in the pyramid and blur arenas
+    LevelGeom lv[VIORB_MAX_LEVELS];
+};
+
+// One FAST cell: the pixels [x0,x1) x [y0,y1) of level `level` on which cv::FAST would evaluate the
+// corner test for this cell's ROI (ROI inset by 3), fextractor.cpp:780-806.
+struct CellDesc {
+    short level, pad;
+    short x0, y0, x1, y1;
+};
+
+// Where the images of a batch live.
+struct FrameSrc {
+    const uint8_t* l0;     // level 0 = the input images
+    int l0Pitch;
+    size_t l0Stride;
+    uint8_t* pyr;          // levels >= 1 (arena; level 0 slot unused)
+    uint8_t* blur;         // blurred levels (arena, all levels)
+};
+
+// Keypoint retained by the quadtree, before output ordering.
+struct KeptKp {
+    short x, y;            // level pixels
+    int score;
+    float angle;           // degrees
+    float c, s;            // cos / sin of the angle (float32-rounded)
+};
+
+__device__ __forceinline__ const uint8_t* level_ptr(const ExtractGeom& g, const FrameSrc& fs, int l, int f, int& pitch) {
+    if (l == 0) { pitch = fs.l0Pitch; return fs.l0 + (size_t)f * fs.l0Stride; }
+    pitch = g.lv[l].pitch;
+    return fs.pyr + (size_t)f * g.arenaStride + g.lv[l].off;
+}
