@@ -101,6 +101,10 @@ int viorb_fetch(viorb_extractor* ex, int frame, viorb_keypoint* kps, uint8_t* de
                 int* n_out, int* mono_index_out);
 /* Waits for all work queued on the handle's stream. */
 int viorb_extractor_sync(viorb_extractor* ex);
+/* The handle's CUDA stream (a cudaStream_t as void*), and a way to run the handle on a caller-owned
+ * stream instead (so that a host framework can time or order the work with its own events). */
+void* viorb_extractor_stream(viorb_extractor* ex);
+int viorb_extractor_set_stream(viorb_extractor* ex, void* stream);
 
 /* mvImagePyramid[level] of the last compute (fextractor.h:64; read by Frame::ComputeStereoMatches,
  * frame.cpp:830,920,937).  Copies the level image (without the 19-px border, which this path never

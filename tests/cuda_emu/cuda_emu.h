@@ -16,6 +16,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <climits>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -404,6 +405,5 @@ static inline unsigned __vimax3_u32(unsigned a, unsigned b, unsigned c) { return
 static inline int __sad(int a, int b, unsigned c) { return (int)(c + (unsigned)std::abs(a - b)); }
 using std::max;
 using std::min;
-static inline void sincos(double a, double* s, double* c) { *s = std::sin(a); *c = std::cos(a); }
 
 #define EMU_DYN_SMEM_PTR ((void*)cuda_emu::C().dyn_smem)

@@ -1,0 +1,60 @@
+"""Logic parity on CPU: the CUDA sources compiled by g++ on the execution shim (tests/cuda_emu) must
+reproduce the oracle.  This checks index math, barriers and host orchestration without a GPU; the
+real parity tests (-m gpu, tests/test_gpu_parity.py) run the nvcc build on the B200."""
+import numpy as np
+import pytest
+
+import __graft_entry__ as ge
+from tests import parity
+from vi_slam_b200 import synthetic
+
+
+@pytest.fixture(scope="module")
+def emu(oracle_mod):
+    return ge.build_emu()
+
+
+@pytest.mark.parametrize("w,h,nf,lap,seed", [(320, 240, 500, (0, 0), 1), (400, 200, 700, (100, 250), 2),
+                                             (640, 360, 3000, (0, 1000), 3)])
+def test_extract_stages(emu, w, h, nf, lap, seed):
+    parity.check_extract(synthetic.make_frame(seed, w, h), nf, lap, lib_path=emu)
+
+
+def test_extract_edge_cases(emu):
+    from vi_slam_b200 import FExtractor
+    ex = FExtractor(500, 1.2, 8, 20, 7, max_size=(320, 240), lib_path=emu)
+    mono, kps, desc = ex.compute(np.zeros((0, 0), np.uint8))
+    assert mono == -1 and len(kps) == 0
+    parity.check_extract(np.zeros((120, 160), np.uint8), 500, (0, 0), lib_path=emu, ex=ex)          # no keypoints
+    rng = np.random.default_rng(1)
+    parity.check_extract(rng.integers(0, 256, (120, 160), dtype=np.uint8), 500, (0, 0), lib_path=emu, ex=ex)
+    parity.check_extract(synthetic.make_frame(4, 320, 240), 500, (0, 0), lib_path=emu, ex=ex)       # size change
+    big = np.zeros((120, 200), np.uint8)
+    big[:, :160] = rng.integers(0, 256, (120, 160), dtype=np.uint8)
+    parity.check_extract(big[:, :160], 500, (0, 0), lib_path=emu, ex=ex)                            # strided input
+    with pytest.raises(Exception):
+        ex.compute(np.zeros((300, 400), np.uint8))                                                  # above max_size
+
+
+def test_knn_and_ratio(emu):
+    q, t = synthetic.make_descriptors(300, 257, seed=3)
+    parity.check_knn(q, t, emu)
+    assert parity.check_ratio(q, t, emu) > 10
+    parity.check_knn(q[:5], t[:1], emu)                 # second neighbour missing
+    parity.check_knn(q[:130], t[:129], emu)             # tile boundary
+
+
+def test_stereo(emu):
+    left, right = synthetic.make_stereo_pair(5, 480, 270)
+    n_stereo, n_ratio, _ = parity.check_stereo(left, right, 1000, emu)
+    assert n_stereo > 50 and n_ratio > 50
+
+
+def test_batch_matches_single(emu):
+    from vi_slam_b200 import FExtractor
+    frames = [synthetic.make_frame(10 + i, 320, 240) for i in range(3)]
+    ex = FExtractor(500, 1.2, 8, 20, 7, max_size=(320, 240), max_batch=3, lib_path=emu)
+    mono, kps, desc = ex.compute_batch(frames, (0, 0))
+    for i, f in enumerate(frames):
+        _, _, (m1, k1, d1), _ = parity.check_extract(f, 500, (0, 0), lib_path=emu, stages=False)
+        assert m1 == mono[i] and np.array_equal(k1, kps[i]) and np.array_equal(d1, desc[i])

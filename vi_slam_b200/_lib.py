@@ -1,0 +1,79 @@
+"""Loader for libviorb.so (the C ABI of include/viorb.h).
+
+The product has no CPU path: if the CUDA library is missing this raises.  Tests
+may point ``VIORB_LIBRARY`` at another build of the same ABI (the g++ emulation
+build under tests/cuda_emu) to check host logic without a GPU; nothing in the
+package, bench.py or __graft_entry__.py sets that variable.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+DEFAULT_LIB = os.path.join(_HERE, "libviorb.so")
+
+u8p = C.POINTER(C.c_uint8)
+i32p = C.POINTER(C.c_int32)
+f32p = C.POINTER(C.c_float)
+
+
+class ViorbParams(C.Structure):
+    _fields_ = [("nfeatures", C.c_int32), ("scale_factor", C.c_float), ("nlevels", C.c_int32),
+                ("ini_th_fast", C.c_int32), ("min_th_fast", C.c_int32), ("max_width", C.c_int32),
+                ("max_height", C.c_int32), ("max_batch", C.c_int32), ("device", C.c_int32)]
+
+
+SYMBOLS = {
+    # name: (restype, argtypes)
+    "viorb_last_error": (C.c_char_p, []),
+    "viorb_version": (C.c_char_p, []),
+    "viorb_extractor_create": (C.c_int, [C.POINTER(ViorbParams), C.POINTER(C.c_void_p)]),
+    "viorb_extractor_destroy": (None, [C.c_void_p]),
+    "viorb_extractor_tables": (C.c_int, [C.c_void_p, i32p, f32p, f32p, f32p, f32p, i32p]),
+    "viorb_extractor_capacity": (C.c_int, [C.c_void_p]),
+    "viorb_extractor_stream": (C.c_void_p, [C.c_void_p]),
+    "viorb_extractor_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "viorb_extractor_sync": (C.c_int, [C.c_void_p]),
+    "viorb_extract": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                C.c_void_p, C.c_void_p, C.c_int, i32p, i32p]),
+    "viorb_extract_batch": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_int,
+                                      C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, i32p, i32p]),
+    "viorb_extract_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t,
+                                       C.c_int, C.c_int]),
+    "viorb_fetch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, i32p, i32p]),
+    "viorb_pyramid_level": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, i32p, i32p]),
+    "viorb_debug_candidates": (C.c_int, [C.c_void_p, C.c_int, C.c_int, i32p, C.c_int, i32p]),
+    "viorb_debug_kept": (C.c_int, [C.c_void_p, C.c_int, C.c_int, i32p, f32p, C.c_int, i32p]),
+    "viorb_debug_blurred": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]),
+    "viorb_descriptor_distance": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, i32p, C.c_int]),
+    "viorb_knn2": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, i32p, i32p, C.c_int]),
+    "viorb_knn2_device": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "viorb_match_ratio": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_int,
+                                    C.c_void_p, C.c_int, i32p, C.c_int]),
+    "viorb_stereo_match": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, f32p, f32p, i32p, i32p,
+                                     C.c_int, i32p]),
+    "viorb_stereo_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_double]),
+    "viorb_stereo_fetch": (C.c_int, [C.c_void_p, C.c_int, f32p, f32p, i32p, C.c_int, i32p, i32p, i32p]),
+    "viorb_match_resident": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_void_p,
+                                       C.c_int, i32p]),
+}
+
+_cache = {}
+
+
+def load(path: str | None = None):
+    path = path or os.environ.get("VIORB_LIBRARY") or DEFAULT_LIB
+    if path in _cache:
+        return _cache[path]
+    if not os.path.exists(path):
+        raise ImportError(
+            f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). vi_slam_b200 has no CPU fallback.")
+    lib = C.CDLL(path)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)          # AttributeError if the ABI is incomplete
+        fn.restype = res
+        fn.argtypes = args
+    _cache[path] = lib
+    return lib

@@ -11,7 +11,7 @@
 #pragma once
 #include "viorb_common.cuh"
 
-static __device__ const int8_t d_orb_pattern[1024] = {
+static __device__ __align__(16) const int8_t d_orb_pattern[1024] = {
 #include "orb_pattern.inc"
 };
 
@@ -410,15 +410,12 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
             __syncthreads();
             int nE = 0;
             for (int i = tid; i < live; i += nth) nE += rankv[i] >= 0;
-            nE = __syncthreads_count(0) * 0 + nE;   // (keeps all threads converged; nE reduced below)
-            // reduce nE over the block
-            aux1[tid < NC ? tid : 0] = 0;
-            __syncthreads();
             if (tid == 0) sh_nExp = 0;
             __syncthreads();
             if (nE) atomicAdd(&sh_nExp, nE);
             __syncthreads();
-            nE = sh_nExp;
+            nE = sh_nExp;                           // number of expandable nodes
+            __syncthreads();
             block_excl_scan(aux0, nE, warpSums);    // aux0[r] = gain of ranks < r
             for (int r = tid; r < nE; r += nth) {
                 // inclusive gain after splitting rank r = aux0[r+1] (or total); recompute from neighbours

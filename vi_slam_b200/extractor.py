@@ -1,0 +1,180 @@
+"""Host-side mirror of the reference's extractor interface over the C ABI.
+
+``FExtractor`` keeps the names and argument meaning of
+reference include/vi_slam/geometry/fextractor.h:26-64 (the reference is C++;
+its toolchain dependencies are absent here, so this mirror is what the parity
+tests drive; the C++ shim with the identical signature is include/viorb_fextractor.hpp).
+All compute happens in libviorb.so (CUDA, sm_100a); there is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+MATCH_DTYPE = np.dtype([("query_idx", "<i4"), ("train_idx", "<i4"), ("distance", "<i4")])
+
+
+class ViorbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"viorb error {code}: {msg}")
+        self.code = code
+
+
+def _check(lib, rc):
+    if rc != 0:
+        raise ViorbError(rc, lib.viorb_last_error().decode())
+
+
+class FExtractor:
+    """FExtractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST) — fextractor.cpp:401-461.
+
+    Extra keyword arguments size the device arenas: ``max_size=(w, h)``, ``max_batch``, ``device``.
+    """
+
+    def __init__(self, nfeatures=2000, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7, *,
+                 max_size=(1280, 720), max_batch=1, device=0, lib_path=None):
+        self._lib = _lib.load(lib_path)
+        self._h = C.c_void_p()
+        p = _lib.ViorbParams(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, max_size[0], max_size[1],
+                             max_batch, device)
+        _check(self._lib, self._lib.viorb_extractor_create(C.byref(p), C.byref(self._h)))
+        self.nfeatures, self.nlevels, self.scaleFactor = nfeatures, nlevels, scaleFactor
+        self.max_batch = max_batch
+        self.capacity = self._lib.viorb_extractor_capacity(self._h)
+        nl = C.c_int32()
+        t = [np.zeros(nlevels, np.float32) for _ in range(4)]
+        self.mnFeaturesPerLevel = np.zeros(nlevels, np.int32)
+        _check(self._lib, self._lib.viorb_extractor_tables(
+            self._h, C.byref(nl), *[a.ctypes.data_as(_lib.f32p) for a in t],
+            self.mnFeaturesPerLevel.ctypes.data_as(_lib.i32p)))
+        self.mvScaleFactor, self.mvInvScaleFactor, self.mvLevelSigma2, self.mvInvLevelSigma2 = t
+        self._last_n = 0
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.viorb_extractor_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # --- getters (fextractor.h:40-62)
+    def GetLevels(self):
+        return self.nlevels
+
+    def GetScaleFactor(self):
+        return self.scaleFactor
+
+    def GetScaleFactors(self):
+        return self.mvScaleFactor.copy()
+
+    def GetInverseScaleFactors(self):
+        return self.mvInvScaleFactor.copy()
+
+    def GetScaleSigmaSquares(self):
+        return self.mvLevelSigma2.copy()
+
+    def GetInverseScaleSigmaSquares(self):
+        return self.mvInvLevelSigma2.copy()
+
+    # --- compute (fextractor.cpp:1034-1133)
+    def compute(self, image, mask=None, vLappingArea=(0, 0)):
+        """-> (monoIndex, keypoints[KP_DTYPE], descriptors uint8[n,32]); monoIndex == -1 for an empty image.
+        ``mask`` is ignored like in the reference."""
+        if image is None or getattr(image, "size", 0) == 0:
+            return -1, np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        mono, kps, desc = self.compute_batch([image], vLappingArea)
+        return mono[0], kps[0], desc[0]
+
+    def compute_batch(self, images, vLappingArea=(0, 0)):
+        n = len(images)
+        h, w = images[0].shape
+        step = images[0].strides[0]
+        keep = []
+        ptrs = (C.c_void_p * n)()
+        for i, im in enumerate(images):
+            assert im.dtype == np.uint8 and im.ndim == 2 and im.shape == (h, w)   # CV_8UC1 (fextractor.cpp:1041)
+            if im.strides[1] != 1 or im.strides[0] != step:
+                im = np.ascontiguousarray(im)
+                assert im.strides[0] == step or n == 1
+                step = im.strides[0]
+            keep.append(im)
+            ptrs[i] = im.ctypes.data
+        cap = self.capacity
+        kps = np.zeros((n, cap), KP_DTYPE)
+        desc = np.zeros((n, cap, 32), np.uint8)
+        cnt = np.zeros(n, np.int32)
+        mono = np.zeros(n, np.int32)
+        _check(self._lib, self._lib.viorb_extract_batch(
+            self._h, ptrs, n, w, h, step, int(vLappingArea[0]), int(vLappingArea[1]), kps.ctypes.data,
+            desc.ctypes.data, cap, cnt.ctypes.data_as(_lib.i32p), mono.ctypes.data_as(_lib.i32p)))
+        self._last_n = n
+        return ([int(m) for m in mono], [kps[i, :cnt[i]].copy() for i in range(n)],
+                [desc[i, :cnt[i]].copy() for i in range(n)])
+
+    # --- device-resident path
+    def extract_device(self, ptr, n, width, height, step, frame_stride, vLappingArea=(0, 0)):
+        _check(self._lib, self._lib.viorb_extract_device(self._h, ptr, n, width, height, step, frame_stride,
+                                                         int(vLappingArea[0]), int(vLappingArea[1])))
+        self._last_n = n
+
+    def fetch(self, frame):
+        cap = self.capacity
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        cnt, mono = C.c_int32(), C.c_int32()
+        _check(self._lib, self._lib.viorb_fetch(self._h, frame, kps.ctypes.data, desc.ctypes.data, cap,
+                                                C.byref(cnt), C.byref(mono)))
+        return mono.value, kps[:cnt.value].copy(), desc[:cnt.value].copy()
+
+    def sync(self):
+        _check(self._lib, self._lib.viorb_extractor_sync(self._h))
+
+    def set_stream(self, stream_ptr):
+        _check(self._lib, self._lib.viorb_extractor_set_stream(self._h, stream_ptr))
+
+    # --- mvImagePyramid (fextractor.h:64)
+    def pyramid_level(self, level, frame=0):
+        w, h = C.c_int32(), C.c_int32()
+        _check(self._lib, self._lib.viorb_pyramid_level(self._h, frame, level, None, 0, C.byref(w), C.byref(h)))
+        out = np.zeros((h.value, w.value), np.uint8)
+        _check(self._lib, self._lib.viorb_pyramid_level(self._h, frame, level, out.ctypes.data, w.value,
+                                                        C.byref(w), C.byref(h)))
+        return out
+
+    @property
+    def mvImagePyramid(self):
+        return [self.pyramid_level(l) for l in range(self.nlevels)]
+
+    # --- stage inspection (parity tests)
+    def debug_candidates(self, level, frame=0):
+        n = C.c_int32()
+        _check(self._lib, self._lib.viorb_debug_candidates(self._h, frame, level, None, 0, C.byref(n)))
+        buf = np.zeros((max(n.value, 1), 3), np.int32)
+        _check(self._lib, self._lib.viorb_debug_candidates(self._h, frame, level, buf.ctypes.data_as(_lib.i32p),
+                                                           n.value, C.byref(n)))
+        return buf[:n.value]
+
+    def debug_kept(self, level, frame=0):
+        cap = self.capacity
+        buf = np.zeros((cap, 3), np.int32)
+        ang = np.zeros(cap, np.float32)
+        n = C.c_int32()
+        _check(self._lib, self._lib.viorb_debug_kept(self._h, frame, level, buf.ctypes.data_as(_lib.i32p),
+                                                     ang.ctypes.data_as(_lib.f32p), cap, C.byref(n)))
+        return buf[:n.value], ang[:n.value]
+
+    def debug_blurred(self, level, frame=0):
+        w, h = C.c_int32(), C.c_int32()
+        _check(self._lib, self._lib.viorb_pyramid_level(self._h, frame, level, None, 0, C.byref(w), C.byref(h)))
+        out = np.zeros((h.value, w.value), np.uint8)
+        _check(self._lib, self._lib.viorb_debug_blurred(self._h, frame, level, out.ctypes.data, w.value))
+        return out

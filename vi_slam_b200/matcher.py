@@ -1,0 +1,111 @@
+"""Host-side mirror of the reference's descriptor matching calls over the C ABI.
+
+* ``descriptor_distance``      FMatcher::DescriptorDistance   (src/geometry/fmatcher.cpp:2859-2875)
+* ``knn_match``                cv::BFMatcher(NORM_HAMMING).knnMatch(q, t, 2)  (frame.cpp:1167)
+* ``match_features``           matchFeatures(..., method_index=2)             (fmatcher.cpp:204-229,247-266)
+* ``fisheye_ratio_match``      the 0.7 ratio rule of ComputeStereoFishEyeMatches (frame.cpp:1170)
+* ``compute_stereo_matches``   Frame::ComputeStereoMatches                    (frame.cpp:823-997)
+* ``stereo_batch``             both stereo matchers on a resident batch
+All compute happens in libviorb.so (CUDA); no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .extractor import MATCH_DTYPE, FExtractor, _check
+
+TH_HIGH, TH_LOW, HISTO_LENGTH = 100, 50, 30      # fmatcher.cpp:313-315
+
+
+def _desc(a):
+    a = np.ascontiguousarray(a, np.uint8)
+    assert a.ndim == 2 and a.shape[1] == 32
+    return a
+
+
+def descriptor_distance(a, b, device=0, lib_path=None):
+    lib = _lib.load(lib_path)
+    a, b = _desc(np.atleast_2d(a)), _desc(np.atleast_2d(b))
+    out = np.zeros(a.shape[0], np.int32)
+    _check(lib, lib.viorb_descriptor_distance(a.ctypes.data, b.ctypes.data, a.shape[0], out.ctypes.data_as(_lib.i32p), device))
+    return out
+
+
+def knn_match(query, train, device=0, lib_path=None):
+    """-> (idx int32[nq,2], dist int32[nq,2]); ascending distance, ties to the lower train index, -1 if absent."""
+    lib = _lib.load(lib_path)
+    q, t = _desc(query), _desc(train)
+    idx = np.full((q.shape[0], 2), -1, np.int32)
+    dist = np.full((q.shape[0], 2), -1, np.int32)
+    _check(lib, lib.viorb_knn2(q.ctypes.data, q.shape[0], t.ctypes.data, t.shape[0], idx.ctypes.data_as(_lib.i32p),
+                               dist.ctypes.data_as(_lib.i32p), device))
+    return idx, dist
+
+
+def _ratio(query, train, ratio, rule, dedup, device, lib_path):
+    lib = _lib.load(lib_path)
+    q, t = _desc(query), _desc(train)
+    out = np.zeros(max(q.shape[0], 1), MATCH_DTYPE)
+    n = C.c_int32()
+    _check(lib, lib.viorb_match_ratio(q.ctypes.data, q.shape[0], t.ctypes.data, t.shape[0], float(ratio), rule, dedup,
+                                      out.ctypes.data, out.shape[0], C.byref(n), device))
+    return out[:n.value].copy()
+
+
+def match_features(descriptors_1, descriptors_2, method_index=2, lowe_method_dist_ratio=0.8, device=0, lib_path=None):
+    """matchFeatures method 2: kNN-2, Lowe ratio, removeDuplicatedMatches.  Other method indices raise like the
+    reference's std::runtime_error (methods 1/3 are FLANN-LSH based and out of scope)."""
+    if method_index != 2:
+        raise RuntimeError("feature_match.cpp::matchFeatures: wrong method index.")
+    return _ratio(descriptors_1, descriptors_2, lowe_method_dist_ratio, 1, 1, device, lib_path)
+
+
+def fisheye_ratio_match(desc_left, desc_right, ratio=0.7, device=0, lib_path=None):
+    return _ratio(desc_left, desc_right, ratio, 0, 0, device, lib_path)
+
+
+def compute_stereo_matches(left: FExtractor, right: FExtractor, bf: float, b: float, frame=0):
+    """-> (mvuRight, mvDepth, bestIdx, bestDist) for the frames last extracted by ``left`` / ``right``."""
+    lib = left._lib
+    cap = left.capacity
+    ur = np.zeros(cap, np.float32)
+    dp = np.zeros(cap, np.float32)
+    bi = np.zeros(cap, np.int32)
+    bd = np.zeros(cap, np.int32)
+    n = C.c_int32()
+    _check(lib, lib.viorb_stereo_match(left._h, right._h, frame, bf, b, ur.ctypes.data_as(_lib.f32p),
+                                       dp.ctypes.data_as(_lib.f32p), bi.ctypes.data_as(_lib.i32p),
+                                       bd.ctypes.data_as(_lib.i32p), cap, C.byref(n)))
+    k = n.value
+    return ur[:k].copy(), dp[:k].copy(), bi[:k].copy(), bd[:k].copy()
+
+
+def stereo_batch(left: FExtractor, right: FExtractor, n: int, bf: float, b: float, ratio=0.7):
+    _check(left._lib, left._lib.viorb_stereo_batch(left._h, right._h, n, bf, b, float(ratio)))
+
+
+def stereo_fetch(left: FExtractor, frame: int):
+    """-> dict(u_right, depth, lr_match, n_stereo, n_ratio) of one frame after ``stereo_batch``."""
+    lib = left._lib
+    cap = left.capacity
+    ur = np.zeros(cap, np.float32)
+    dp = np.zeros(cap, np.float32)
+    lr = np.zeros(cap, np.int32)
+    nl, ns, nr = C.c_int32(), C.c_int32(), C.c_int32()
+    _check(lib, lib.viorb_stereo_fetch(left._h, frame, ur.ctypes.data_as(_lib.f32p), dp.ctypes.data_as(_lib.f32p),
+                                       lr.ctypes.data_as(_lib.i32p), cap, C.byref(nl), C.byref(ns), C.byref(nr)))
+    k = nl.value
+    return {"u_right": ur[:k].copy(), "depth": dp[:k].copy(), "lr_match": lr[:k].copy(), "n_stereo": ns.value,
+            "n_ratio": nr.value}
+
+
+def match_resident(cur: FExtractor, frame_q: int, prev: FExtractor, frame_t: int, ratio=0.7, rule=0):
+    lib = cur._lib
+    out = np.zeros(cur.capacity, MATCH_DTYPE)
+    n = C.c_int32()
+    _check(lib, lib.viorb_match_resident(cur._h, frame_q, prev._h, frame_t, float(ratio), rule, out.ctypes.data,
+                                         out.shape[0], C.byref(n)))
+    return out[:n.value].copy()
