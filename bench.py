@@ -1,0 +1,332 @@
+#!/usr/bin/env python3
+"""bench.py — ORB extract+match throughput on synthetic KITTI-shaped stereo frames.
+
+Contract (see the task statement): `python bench.py --gpus N --steps K --warmup W` prints ONE JSON line.
+
+Workload (BASELINE.json configs[1], KITTI00-Stereo.yaml): one step = B stereo frames per GPU;
+each frame = left + right ORB extraction (1241x376, 8 levels x1.2, 2000 kp, FAST 20/7) +
+Frame::ComputeStereoMatches (row-band Hamming, SAD refinement, outlier cut) + brute-force kNN-2 with the
+0.7 ratio test left->right.  `value` = stereo frames/s with the images already resident in HBM;
+`e2e` = the same through the host-buffer C ABI calls (H2D of the images and D2H of every result inside
+the timed region).  `--impl reference` times the CPU oracle (the restated reference path) instead.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H, PITCH = 1241, 376, 1280
+NFEAT, NLEVELS, SCALE, INI_TH, MIN_TH = 2000, 8, 1.2, 20, 7
+BF, FX = 386.1448, 718.856
+B_BASELINE = float(np.float32(BF) / np.float32(FX))
+METRIC = "ORB extract+match frames/s (KITTI 1241x376, 2k kp)"
+UNIT = "stereo frames/s"
+# algorithmic bytes: W*H + 2*sum_{l>=1} w_l*h_l + N*60 per image
+LEVEL_PIXELS = [1241 * 376, 1034 * 313, 862 * 261, 718 * 218, 598 * 181, 499 * 151, 416 * 126, 346 * 105]
+BYTES_EXTRACT_PER_IMAGE = LEVEL_PIXELS[0] + 2 * sum(LEVEL_PIXELS[1:]) + NFEAT * 60
+BYTES_FAST_PER_IMAGE = sum(LEVEL_PIXELS)          # k_fast reads every level pixel once (+ 4 B per candidate)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--pairs", type=int, default=160, help="stereo frames per GPU per step")
+    ap.add_argument("--distinct", type=int, default=8, help="distinct synthetic stereo pairs generated (tiled to --pairs)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def make_pairs(n, distinct, seed0=1000):
+    from vi_slam_b200 import synthetic
+    base = [synthetic.make_stereo_pair(seed0 + i) for i in range(min(distinct, n))]
+    left = np.zeros((n, H, PITCH), np.uint8)
+    right = np.zeros((n, H, PITCH), np.uint8)
+    for i in range(n):
+        l, r = base[i % len(base)]
+        k = i // len(base)
+        if k:       # shift rows together so pairs stay rectified but no two frames are byte-identical
+            l, r = np.roll(l, 2 * k, axis=0), np.roll(r, 2 * k, axis=0)
+        left[i, :, :W], right[i, :, :W] = l, r
+    return left, right
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            pass
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out = self.proc.communicate(timeout=5)[0]
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            p = [t.strip() for t in line.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                sm.append(float(p[0]))
+                mx = max(mx, float(p[1]))
+            except ValueError:
+                continue
+            for nme, v in zip(names, p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        # under-load median: ignore idle samples taken before the first launch
+        load = [v for v in sm if v >= 0.5 * max(sm)] if sm else []
+        return {"sm_mhz": float(np.median(load)) if load else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline(nthreads, pairs):
+    """The CPU oracle (restated reference path) on `pairs` stereo frames with `nthreads` host threads."""
+    import oracle
+    oracle.build()
+    left, right = make_pairs(pairs, 4, seed0=5000)
+    frames = np.empty((2 * pairs, H, W), np.uint8)
+    frames[0::2] = left[:, :, :W]
+    frames[1::2] = right[:, :, :W]
+    t0 = time.perf_counter()
+    tot, nm = oracle.bench_frames(frames, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, (0, 0), True, BF, B_BASELINE, nthreads)
+    dt = time.perf_counter() - t0
+    return pairs / dt, dt, tot, nm
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def run_reference(args, rank):
+    """--impl reference: the reference's CPU path (restated: oracle/) on all host threads."""
+    if rank != 0:
+        return
+    cores = host_threads()
+    pairs = max(2 * cores, 8)
+    for _ in range(args.warmup):
+        cpu_baseline(cores, pairs)
+    t = []
+    for _ in range(args.steps):
+        v, dt, _, _ = cpu_baseline(cores, pairs)
+        t.append(dt)
+    total = sum(t)
+    value = pairs * args.steps / total
+    sample = f"{pairs} synthetic KITTI stereo frames per step, {cores} threads, oracle/orb_oracle.cpp (-O3, no -march)"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "kitti_stereo_1241x376_2000kp_extract+stereo_match+knn2_ratio", "frames_per_step": pairs,
+                   "device": "cpu"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    from vi_slam_b200 import FExtractor, matcher
+
+    os.environ.pop("VIORB_LIBRARY", None)            # the product library only
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    B, K, Wm = args.pairs, args.steps, args.warmup
+    left, right = make_pairs(B, args.distinct, seed0=1000 + 100 * rank)
+    dl = torch.from_numpy(left).pin_memory().cuda(non_blocking=True)
+    dr = torch.from_numpy(right).pin_memory().cuda(non_blocking=True)
+    torch.cuda.synchronize()
+    stream = torch.cuda.Stream()
+    exl = FExtractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, max_size=(W, H), max_batch=B, device=local_rank)
+    exr = FExtractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, max_size=(W, H), max_batch=B, device=local_rank)
+    exl.set_stream(stream.cuda_stream)
+    exr.set_stream(stream.cuda_stream)
+
+    def step():
+        exl.extract_device(dl.data_ptr(), B, W, H, PITCH, H * PITCH, (0, 0))
+        exr.extract_device(dr.data_ptr(), B, W, H, PITCH, H * PITCH, (0, 0))
+        matcher.stereo_batch(exl, exr, B, BF, B_BASELINE, 0.7)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    with torch.cuda.stream(stream):
+        for _ in range(Wm):
+            step()
+        stream.synchronize()
+        exl.set_timing(True)
+        exr.set_timing(True)
+        stages = {}
+        barrier()
+        torch.cuda.synchronize()
+        clocks = ClockSampler(local_rank)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for _ in range(K):
+            step()
+            # per-stage CUDA-event times of this step (waits for the step; one small bubble per step)
+            for d in (exl.stage_ms(), exr.stage_ms(), matcher.stereo_stage_ms(exl)):
+                for k, v in d.items():
+                    stages[k] = stages.get(k, 0.0) + v
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        barrier()
+        clk = clocks.stop()
+        ms = ev0.elapsed_time(ev1)
+    exl.set_timing(False)
+    exr.set_timing(False)
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = world * B * K / (ms * 1e-3)
+
+    # results of the last step (sanity + matches/s)
+    res = matcher.stereo_fetch_all(exl, B)
+    n_kp = int(res["n_left"].sum())
+    n_stereo, n_ratio = int(res["n_stereo"].sum()), int(res["n_ratio"].sum())
+
+    # ---- end to end through the host-buffer C ABI
+    e2e = None
+    if not args.no_e2e:
+        del exl, exr
+        hl = [left[i, :, :W] for i in range(B)]
+        hr = [right[i, :, :W] for i in range(B)]
+        el = FExtractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, max_size=(W, H), max_batch=B, device=local_rank)
+        er = FExtractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, max_size=(W, H), max_batch=B, device=local_rank)
+        out = [None, None]
+        buf = None
+
+        def e2e_step():
+            nonlocal buf
+            th = [threading.Thread(target=lambda i=i, e=e, im=im: out.__setitem__(i, e.compute_batch(im, (0, 0))))
+                  for i, (e, im) in enumerate(((el, hl), (er, hr)))]
+            [t.start() for t in th]
+            [t.join() for t in th]
+            matcher.stereo_batch(el, er, B, BF, B_BASELINE, 0.7)
+            buf = matcher.stereo_fetch_all(el, B, buf)
+
+        for _ in range(max(1, min(Wm, 2))):
+            e2e_step()
+        Ke = K
+        barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(Ke):
+            e2e_step()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([dt], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        cap = el.capacity
+        h2d = 2 * B * 1280 * H
+        d2h = 2 * B * (el._lib.viorb_extractor_capacity(el._h) - 64) * 60 + 2 * B * 8 + B * cap * 12 + 3 * B * 4
+        e2e = {"value": world * B * Ke / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "ms_per_step": 1e3 * dt / Ke}
+
+    if rank != 0:
+        return
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    mean = {k: v / K for k, v in stages.items()}           # ms per step (left + right extract summed)
+    dom = max(mean, key=mean.get)
+    px = LEVEL_PIXELS
+    alg = {"fast": sum(px), "blur": 2 * sum(px), "resize": sum(px[:-1]) + sum(px[1:])}
+    launches_per_step = {"resize": 2 * (NLEVELS - 1)}.get(dom, 1 if dom in matcher.STEREO_STAGES else 2)
+    if dom in alg:
+        bytes_per_step = 2 * B * alg[dom]
+        bound = "hbm"
+    else:
+        bytes_per_step = 2 * B * BYTES_EXTRACT_PER_IMAGE
+        bound = "hbm"
+    achieved = bytes_per_step / (mean[dom] * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get(dom)
+    roofline = {"bound": bound, "kernel": "k_" + dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "bytes_per_launch": bytes_per_step / launches_per_step, "ms_per_launch": mean[dom] / launches_per_step,
+                "path_hbm_frac": 2 * B * K * BYTES_EXTRACT_PER_IMAGE / (ms * 1e-3) / 1e9 / peak}
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {"workload": "kitti_stereo_1241x376_2000kp_extract+stereo_match+knn2_ratio",
+                   "stereo_frames_per_gpu_per_step": B, "images_per_s": 2 * value, "l2_policy": "inputs_and_intermediates_larger_than_L2",
+                   "input_bytes_per_step": 2 * B * PITCH * H, "parallelism": f"frame-batch x{world}, no collective",
+                   "keypoints_per_frame": n_kp / B, "stereo_matches_per_s": n_stereo / B * value,
+                   "ratio_matches_per_s": n_ratio / B * value},
+        "clocks": clk, "e2e": e2e, "gpu_launches": K * (2 * (NLEVELS - 1 + 6) + 5),
+        "stages_ms_per_step": mean, "roofline": roofline,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cores = host_threads()
+        pairs = max(2 * cores, 8)
+        cpu_baseline(cores, min(pairs, 8))          # warm
+        v, dt, _, _ = cpu_baseline(cores, pairs)
+        reps = max(1, int(10.0 / max(dt, 1e-3)))
+        if reps > 1:
+            tt = [cpu_baseline(cores, pairs)[1] for _ in range(min(reps, 6))]
+            v = pairs * len(tt) / sum(tt)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"{pairs} synthetic KITTI stereo frames per pass, oracle/orb_oracle.cpp on {cores} threads"}
+    print(json.dumps(line))
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    run_ours(args, rank, world, local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -105,6 +105,13 @@ int viorb_extractor_sync(viorb_extractor* ex);
  * stream instead (so that a host framework can time or order the work with its own events). */
 void* viorb_extractor_stream(viorb_extractor* ex);
 int viorb_extractor_set_stream(viorb_extractor* ex, void* stream);
+/* Stage timing with CUDA events on the handle's stream (the reference's REGISTER_TIMES spans,
+ * frame.cpp:103-116,124-132).  stage_ms: ms[7] = resize, fast, octree, orient, emit, blur, describe of
+ * the last extract; viorb_stereo_stage_ms: ms[5] = coarse, refine, cut, knn2, ratio of the last
+ * viorb_stereo_batch (left handle). */
+int viorb_extractor_set_timing(viorb_extractor* ex, int enable);
+int viorb_extractor_stage_ms(viorb_extractor* ex, float* ms);
+int viorb_stereo_stage_ms(viorb_extractor* left, float* ms);
 
 /* mvImagePyramid[level] of the last compute (fextractor.h:64; read by Frame::ComputeStereoMatches,
  * frame.cpp:830,920,937).  Copies the level image (without the 19-px border, which this path never
@@ -152,6 +159,9 @@ int viorb_stereo_match(viorb_extractor* left, viorb_extractor* right, int frame,
 int viorb_stereo_batch(viorb_extractor* left, viorb_extractor* right, int n, float bf, float b, double ratio);
 int viorb_stereo_fetch(viorb_extractor* left, int frame, float* u_right, float* depth, int32_t* lr_match,
                        int cap, int* n_left, int* n_stereo, int* n_ratio);
+/* Whole-batch read-back: arrays are [n][cap] / [n], cap >= viorb_extractor_capacity(). */
+int viorb_stereo_fetch_all(viorb_extractor* left, int n, float* u_right, float* depth, int32_t* lr_match,
+                           int cap, int* n_left, int* n_stereo, int* n_ratio);
 
 /* Frame-to-frame brute-force kNN-2 + ratio between the resident descriptors of two extractors'
  * frames (cur.frame_q -> prev.frame_t); result rows in query order. */

@@ -35,6 +35,10 @@ SYMBOLS = {
     "viorb_extractor_stream": (C.c_void_p, [C.c_void_p]),
     "viorb_extractor_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "viorb_extractor_sync": (C.c_int, [C.c_void_p]),
+    "viorb_extractor_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
+    "viorb_extractor_stage_ms": (C.c_int, [C.c_void_p, f32p]),
+    "viorb_stereo_stage_ms": (C.c_int, [C.c_void_p, f32p]),
+    "viorb_stereo_fetch_all": (C.c_int, [C.c_void_p, C.c_int, f32p, f32p, i32p, C.c_int, i32p, i32p, i32p]),
     "viorb_extract": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                 C.c_void_p, C.c_void_p, C.c_int, i32p, i32p]),
     "viorb_extract_batch": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_int,

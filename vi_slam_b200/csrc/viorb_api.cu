@@ -95,6 +95,10 @@ struct viorb_extractor {
     PinBuf<uint8_t> hIn, hDesc;
     PinBuf<viorb_keypoint> hKps;
     PinBuf<int> hCounts;
+    // stage timing (CUDA events on the handle's stream; read back with viorb_*_stage_ms)
+    cudaEvent_t evX[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t evS[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool timing = false, haveX = false, haveS = false;
     // last run
     FrameSrc src{};
     int lastN = 0;
@@ -309,23 +313,32 @@ int run_pipeline(viorb_extractor* ex, int n, int lap0, int lap1) {
     const FrameSrc& fs = ex->src;
     cudaStream_t st = ex->stream;
     CU(cudaMemsetAsync(ex->dCandCount.p, 0, sizeof(int) * (size_t)n * g.nlevels, st));
+    const bool tm = ex->timing;
+    if (tm) CU(cudaEventRecord(ex->evX[0], st));
     for (int l = 1; l < g.nlevels; ++l) {
         const LevelGeom& L = g.lv[l];
         dim3 grid((L.w + 255) / 256, (L.h + 3) / 4, n), block(64, 4);
         VIORB_LAUNCH(k_resize, grid, block, 0, st, g, fs, l, ex->dXofs.p, ex->dXalpha.p, ex->dYofs.p, ex->dYbeta.p);
     }
+    if (tm) CU(cudaEventRecord(ex->evX[1], st));
     if (g.totalCells > 0) {
         VIORB_LAUNCH(k_fast, dim3(g.totalCells, n), dim3(VIORB_FAST_THREADS), ex->fastSmem, st, g, fs, ex->dCells.p,
                      ex->dCand.p, ex->dCandCount.p, ex->dStatus.p);
     }
+    if (tm) CU(cudaEventRecord(ex->evX[2], st));
     VIORB_LAUNCH(k_octree, dim3(g.nlevels, n), dim3(VIORB_OCT_THREADS), ex->octSmem, st, g, ex->dCand.p, ex->dCandCount.p,
                  ex->dKeyNode.p, ex->dKept.p, ex->dKeptCount.p, ex->dStatus.p);
+    if (tm) CU(cudaEventRecord(ex->evX[3], st));
     VIORB_LAUNCH(k_orient, dim3((g.keptPerFrame + 7) / 8, n), dim3(256), 0, st, g, fs, ex->umax, ex->dKept.p, ex->dKeptCount.p);
+    if (tm) CU(cudaEventRecord(ex->evX[4], st));
     VIORB_LAUNCH(k_emit, dim3(n), dim3(256), 0, st, g, ex->dKept.p, ex->dKeptCount.p, lap0, lap1, ex->dKps.p,
                  ex->dSlot2Kept.p, ex->dNOut.p, ex->dMono.p);
+    if (tm) CU(cudaEventRecord(ex->evX[5], st));
     VIORB_LAUNCH(k_blur, dim3(ex->totalBlurTiles, n), dim3(256), 0, st, g, fs, ex->blurTiles);
+    if (tm) CU(cudaEventRecord(ex->evX[6], st));
     VIORB_LAUNCH(k_describe, dim3((g.outCap + 7) / 8, n), dim3(256), 0, st, g, fs, ex->dKept.p, ex->dSlot2Kept.p,
                  ex->dNOut.p, ex->dDesc.p);
+    if (tm) { CU(cudaEventRecord(ex->evX[7], st)); ex->haveX = true; }
     CU(cudaGetLastError());
     ex->lastN = n;
     return VIORB_OK;
@@ -375,12 +388,17 @@ int launch_stereo(viorb_extractor* L, viorb_extractor* R, int n, float bf, float
     const StereoParams sp = make_stereo_params(L, bf, b);
     cudaStream_t st = L->stream;
     const int gx = (L->g.outCap + 7) / 8;
+    const bool tm = L->timing;
+    if (tm) CU(cudaEventRecord(L->evS[0], st));
     VIORB_LAUNCH(k_stereo_coarse, dim3(gx, n), dim3(256), 0, st, sp, L->dKps.p, L->dDesc.p, L->dNOut.p, R->dKps.p, R->dDesc.p,
                  R->dNOut.p, L->dBestIdx.p, L->dBestDist.p);
+    if (tm) CU(cudaEventRecord(L->evS[1], st));
     VIORB_LAUNCH(k_stereo_refine, dim3(gx, n), dim3(256), 0, st, sp, L->g, L->src, R->src, L->dKps.p, L->dNOut.p, R->dKps.p,
                  L->dBestIdx.p, L->dBestDist.p, L->dURight.p, L->dDepth.p, L->dSad.p);
+    if (tm) CU(cudaEventRecord(L->evS[2], st));
     VIORB_LAUNCH(k_stereo_cut, dim3(n), dim3(256), 0, st, sp.outCap, L->dNOut.p, L->dSad.p, L->dURight.p, L->dDepth.p,
                  L->dNStereo.p);
+    if (tm) CU(cudaEventRecord(L->evS[3], st));
     CU(cudaGetLastError());
     return VIORB_OK;
 }
@@ -461,6 +479,8 @@ int viorb_extractor_create(const viorb_params* params, viorb_extractor** out) {
     ok(ex->hKps.alloc(B * ex->capOut));
     ok(ex->hDesc.alloc(B * ex->capOut * 32));
     ok(ex->hCounts.alloc(B * 2 + 8));
+    for (int i = 0; i < 8; ++i) ok(cudaEventCreate(&ex->evX[i]));
+    for (int i = 0; i < 6; ++i) ok(cudaEventCreate(&ex->evS[i]));
     if (e == cudaSuccess) e = cudaMemset(ex->dStatus.p, 0, sizeof(int));
     if (e != cudaSuccess) {
         std::string msg = std::string("allocation failed: ") + cudaGetErrorString(e);
@@ -484,6 +504,8 @@ void viorb_extractor_destroy(viorb_extractor* ex) {
     ex->dLrMatch.release(); ex->dURight.release(); ex->dDepth.release(); ex->dNStereo.release(); ex->dNRatio.release();
     ex->dMatches.release();
     ex->hIn.release(); ex->hDesc.release(); ex->hKps.release(); ex->hCounts.release();
+    for (int i = 0; i < 8; ++i) if (ex->evX[i]) cudaEventDestroy(ex->evX[i]);
+    for (int i = 0; i < 6; ++i) if (ex->evS[i]) cudaEventDestroy(ex->evS[i]);
     if (ex->ownStream && ex->stream) cudaStreamDestroy(ex->stream);
     delete ex;
 }
@@ -515,6 +537,33 @@ int viorb_extractor_set_stream(viorb_extractor* ex, void* stream) {
     if (ex->ownStream && ex->stream) cudaStreamDestroy(ex->stream);
     ex->stream = (cudaStream_t)stream;
     ex->ownStream = false;
+    return VIORB_OK;
+}
+
+int viorb_extractor_set_timing(viorb_extractor* ex, int enable) {
+    if (!ex) return fail(VIORB_E_ARG, "null handle");
+    ex->timing = enable != 0;
+    ex->haveX = ex->haveS = false;
+    return VIORB_OK;
+}
+
+/* ms[7]: resize, fast, octree, orient, emit, blur, describe of the last extract (waits for it). */
+int viorb_extractor_stage_ms(viorb_extractor* ex, float* ms) {
+    if (!ex || !ms) return fail(VIORB_E_ARG, "null argument");
+    if (!ex->haveX) return fail(VIORB_E_ARG, "no timed extract: call viorb_extractor_set_timing(ex, 1) first");
+    CU(cudaSetDevice(ex->prm.device));
+    CU(cudaEventSynchronize(ex->evX[7]));
+    for (int i = 0; i < 7; ++i) CU(cudaEventElapsedTime(&ms[i], ex->evX[i], ex->evX[i + 1]));
+    return VIORB_OK;
+}
+
+/* ms[5]: stereo coarse, refine, cut, knn2, ratio of the last viorb_stereo_batch on this (left) handle. */
+int viorb_stereo_stage_ms(viorb_extractor* ex, float* ms) {
+    if (!ex || !ms) return fail(VIORB_E_ARG, "null argument");
+    if (!ex->haveS) return fail(VIORB_E_ARG, "no timed stereo batch");
+    CU(cudaSetDevice(ex->prm.device));
+    CU(cudaEventSynchronize(ex->evS[5]));
+    for (int i = 0; i < 5; ++i) CU(cudaEventElapsedTime(&ms[i], ex->evS[i], ex->evS[i + 1]));
     return VIORB_OK;
 }
 
@@ -867,8 +916,10 @@ int viorb_stereo_batch(viorb_extractor* L, viorb_extractor* R, int n, float bf, 
     DescSet Q{L->dDesc.p, oc * 32, L->dNOut.p, 0}, T{R->dDesc.p, oc * 32, R->dNOut.p, 0};
     VIORB_LAUNCH(k_knn2, dim3((L->g.outCap + VIORB_KNN_THREADS - 1) / VIORB_KNN_THREADS, n), dim3(VIORB_KNN_THREADS), 0, L->stream,
                  Q, T, L->dKnnIdx.p, L->dKnnDist.p, oc);
+    if (L->timing) CU(cudaEventRecord(L->evS[4], L->stream));
     VIORB_LAUNCH(k_ratio, dim3(n), dim3(256), 0, L->stream, Q, L->dKnnIdx.p, L->dKnnDist.p, oc, ratio, 0, L->dMatches.p, oc,
                  L->dNRatio.p, L->dLrMatch.p);
+    if (L->timing) { CU(cudaEventRecord(L->evS[5], L->stream)); L->haveS = true; }
     CU(cudaGetLastError());
     return VIORB_OK;
 }
@@ -893,6 +944,24 @@ int viorb_stereo_fetch(viorb_extractor* L, int frame, float* u_right, float* dep
         if (lr_match) CU(cudaMemcpyAsync(lr_match, L->dLrMatch.p + o, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, L->stream));
         CU(cudaStreamSynchronize(L->stream));
     }
+    return VIORB_OK;
+}
+
+/* Whole-batch read-back of the stereo results: arrays are [n][cap] / [n]. One pinned-free D2H per array. */
+int viorb_stereo_fetch_all(viorb_extractor* L, int n, float* u_right, float* depth, int32_t* lr_match, int cap, int* n_left,
+                           int* n_stereo, int* n_ratio) {
+    if (!L || n <= 0 || n > L->lastN || !L->dURight.p) return fail(VIORB_E_ARG, "bad handle or frame count");
+    if (cap < L->g.outCap) return fail(VIORB_E_CAPACITY, "cap must be at least viorb_extractor_capacity()");
+    CU(cudaSetDevice(L->prm.device));
+    const size_t oc = L->g.outCap;
+    cudaStream_t st = L->stream;
+    if (n_left) CU(cudaMemcpyAsync(n_left, L->dNOut.p, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+    if (n_stereo) CU(cudaMemcpyAsync(n_stereo, L->dNStereo.p, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+    if (n_ratio) CU(cudaMemcpyAsync(n_ratio, L->dNRatio.p, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
+    if (u_right) CU(cudaMemcpy2DAsync(u_right, sizeof(float) * cap, L->dURight.p, sizeof(float) * oc, sizeof(float) * oc, n, cudaMemcpyDeviceToHost, st));
+    if (depth) CU(cudaMemcpy2DAsync(depth, sizeof(float) * cap, L->dDepth.p, sizeof(float) * oc, sizeof(float) * oc, n, cudaMemcpyDeviceToHost, st));
+    if (lr_match) CU(cudaMemcpy2DAsync(lr_match, sizeof(int32_t) * cap, L->dLrMatch.p, sizeof(int32_t) * oc, sizeof(int32_t) * oc, n, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
     return VIORB_OK;
 }
 

@@ -138,6 +138,16 @@ class FExtractor:
     def sync(self):
         _check(self._lib, self._lib.viorb_extractor_sync(self._h))
 
+    STAGES = ("resize", "fast", "octree", "orient", "emit", "blur", "describe")
+
+    def set_timing(self, enable=True):
+        _check(self._lib, self._lib.viorb_extractor_set_timing(self._h, int(enable)))
+
+    def stage_ms(self):
+        ms = np.zeros(7, np.float32)
+        _check(self._lib, self._lib.viorb_extractor_stage_ms(self._h, ms.ctypes.data_as(_lib.f32p)))
+        return dict(zip(self.STAGES, ms.tolist()))
+
     def set_stream(self, stream_ptr):
         _check(self._lib, self._lib.viorb_extractor_set_stream(self._h, stream_ptr))
 

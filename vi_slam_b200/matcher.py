@@ -109,3 +109,27 @@ def match_resident(cur: FExtractor, frame_q: int, prev: FExtractor, frame_t: int
     _check(lib, lib.viorb_match_resident(cur._h, frame_q, prev._h, frame_t, float(ratio), rule, out.ctypes.data,
                                          out.shape[0], C.byref(n)))
     return out[:n.value].copy()
+
+
+STEREO_STAGES = ("stereo_coarse", "stereo_refine", "stereo_cut", "knn2", "ratio")
+
+
+def stereo_stage_ms(left: FExtractor):
+    ms = np.zeros(5, np.float32)
+    _check(left._lib, left._lib.viorb_stereo_stage_ms(left._h, ms.ctypes.data_as(_lib.f32p)))
+    return dict(zip(STEREO_STAGES, ms.tolist()))
+
+
+def stereo_fetch_all(left: FExtractor, n: int, out=None):
+    """Whole-batch read-back after ``stereo_batch``: dict of [n, cap] arrays and [n] counts."""
+    lib = left._lib
+    cap = left.capacity
+    if out is None:
+        out = {"u_right": np.zeros((n, cap), np.float32), "depth": np.zeros((n, cap), np.float32),
+               "lr_match": np.zeros((n, cap), np.int32), "n_left": np.zeros(n, np.int32),
+               "n_stereo": np.zeros(n, np.int32), "n_ratio": np.zeros(n, np.int32)}
+    _check(lib, lib.viorb_stereo_fetch_all(left._h, n, out["u_right"].ctypes.data_as(_lib.f32p),
+                                           out["depth"].ctypes.data_as(_lib.f32p), out["lr_match"].ctypes.data_as(_lib.i32p),
+                                           cap, out["n_left"].ctypes.data_as(_lib.i32p),
+                                           out["n_stereo"].ctypes.data_as(_lib.i32p), out["n_ratio"].ctypes.data_as(_lib.i32p)))
+    return out
