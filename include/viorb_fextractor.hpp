@@ -1,0 +1,124 @@
+// viorb_fextractor.hpp — header-only C++ shim with the reference's extractor interface
+// (reference include/vi_slam/geometry/fextractor.h:26-64) forwarding to the C ABI in viorb.h.
+//
+// In the reference tree: replace the body of src/geometry/fextractor.cpp by
+//     #include "viorb_fextractor.hpp"
+// with VIORB_WITH_OPENCV defined, link libviorb.so, and Frame / Tracking compile unchanged
+// (see INTEGRATION.md).  Without OpenCV (this repository's own builds) the same class is
+// available over the tiny POD stand-ins below, which is what tests/test_cpp_shim.py compiles.
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "viorb.h"
+
+#ifdef VIORB_WITH_OPENCV
+#include <opencv2/core.hpp>
+namespace viorb_cv = cv;
+#else
+namespace viorb_cv {
+struct Point2f { float x, y; };
+struct KeyPoint {                 // cv::KeyPoint layout (28 bytes)
+    Point2f pt; float size, angle, response; int octave, class_id;
+};
+struct Mat {                      // minimal CV_8UC1 view / owner
+    int rows = 0, cols = 0; size_t step = 0; uint8_t* data = nullptr; std::vector<uint8_t> own;
+    Mat() {}
+    Mat(int r, int c, uint8_t* d, size_t s) : rows(r), cols(c), step(s), data(d) {}
+    void create(int r, int c) { rows = r; cols = c; step = (size_t)c; own.assign((size_t)r * c, 0); data = own.data(); }
+    void release() { rows = cols = 0; step = 0; own.clear(); data = nullptr; }
+    bool empty() const { return rows == 0 || cols == 0 || data == nullptr; }
+};
+}  // namespace viorb_cv
+#endif
+
+namespace vi_slam {
+namespace geometry {
+
+static_assert(sizeof(viorb_cv::KeyPoint) == sizeof(viorb_keypoint), "cv::KeyPoint must be the 28-byte POD");
+
+class FExtractor {
+public:
+    enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
+
+    // fextractor.cpp:401-461.  max_width / max_height size the device arenas (the reference allocates per call).
+    FExtractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST,
+               int max_width = 1280, int max_height = 720, int device = 0)
+        : nlevels_(nlevels), scaleFactor_(scaleFactor) {
+        viorb_params p{nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, max_width, max_height, 1, device};
+        if (viorb_extractor_create(&p, &h_) != VIORB_OK) throw std::runtime_error(viorb_last_error());
+        mvScaleFactor.resize(nlevels); mvInvScaleFactor.resize(nlevels);
+        mvLevelSigma2.resize(nlevels); mvInvLevelSigma2.resize(nlevels);
+        viorb_extractor_tables(h_, nullptr, mvScaleFactor.data(), mvInvScaleFactor.data(), mvLevelSigma2.data(),
+                               mvInvLevelSigma2.data(), nullptr);
+        mvImagePyramid.resize(nlevels);
+        cap_ = viorb_extractor_capacity(h_);
+    }
+    ~FExtractor() { viorb_extractor_destroy(h_); }
+    FExtractor(const FExtractor&) = delete;
+    FExtractor& operator=(const FExtractor&) = delete;
+
+    // fextractor.cpp:1034-1133.  `mask` is ignored like in the reference.  Returns monoIndex, -1 on an empty image.
+    int compute(const viorb_cv::Mat& image, const viorb_cv::Mat& /*mask*/, std::vector<viorb_cv::KeyPoint>& keypoints,
+                viorb_cv::Mat& descriptors, std::vector<int>& vLappingArea) {
+        if (image.empty()) return -1;
+        kp_.resize(cap_); desc_.resize((size_t)cap_ * 32);
+        int n = 0, mono = -1;
+        int rc = viorb_extract(h_, image.data, image.cols, image.rows, (int)image.step, vLappingArea[0], vLappingArea[1],
+                               kp_.data(), desc_.data(), cap_, &n, &mono);
+        if (rc == VIORB_E_EMPTY) return -1;
+        if (rc != VIORB_OK) throw std::runtime_error(viorb_last_error());
+        keypoints.resize(n);
+        static_assert(sizeof(viorb_cv::KeyPoint) == 28, "");
+        if (n) std::memcpy((void*)keypoints.data(), kp_.data(), sizeof(viorb_keypoint) * (size_t)n);
+        if (n == 0) descriptors.release();
+        else {
+#ifdef VIORB_WITH_OPENCV
+            descriptors.create(n, 32, CV_8U);
+#else
+            descriptors.create(n, 32);
+#endif
+            for (int i = 0; i < n; ++i) std::memcpy(descriptors.data + (size_t)i * descriptors.step, &desc_[(size_t)i * 32], 32);
+        }
+        // mvImagePyramid stays valid until the next compute (read by Frame::ComputeStereoMatches, frame.cpp:830,920,937)
+        for (int l = 0; l < nlevels_; ++l) {
+            int w = 0, hgt = 0;
+            viorb_pyramid_level(h_, 0, l, nullptr, 0, &w, &hgt);
+#ifdef VIORB_WITH_OPENCV
+            mvImagePyramid[l].create(hgt, w, CV_8U);
+#else
+            mvImagePyramid[l].create(hgt, w);
+#endif
+            viorb_pyramid_level(h_, 0, l, mvImagePyramid[l].data, (int)mvImagePyramid[l].step, &w, &hgt);
+        }
+        return mono;
+    }
+
+    int GetLevels() { return nlevels_; }
+    float GetScaleFactor() { return scaleFactor_; }
+    std::vector<float> GetScaleFactors() { return mvScaleFactor; }
+    std::vector<float> GetInverseScaleFactors() { return mvInvScaleFactor; }
+    std::vector<float> GetScaleSigmaSquares() { return mvLevelSigma2; }
+    std::vector<float> GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
+    viorb_extractor* handle() { return h_; }
+
+    std::vector<viorb_cv::Mat> mvImagePyramid;
+
+protected:
+    viorb_extractor* h_ = nullptr;
+    int nlevels_, cap_ = 0;
+    float scaleFactor_;
+    std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
+    std::vector<viorb_keypoint> kp_;
+    std::vector<uint8_t> desc_;
+};
+
+// FMatcher::DescriptorDistance keeps its scalar host form in the reference's windowed matchers (it is called
+// per candidate pair inside host loops, fmatcher.cpp:2859); bulk distance / kNN work goes through viorb_knn2,
+// viorb_match_ratio and viorb_stereo_match.
+
+}  // namespace geometry
+}  // namespace vi_slam
