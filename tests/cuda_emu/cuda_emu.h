@@ -402,6 +402,20 @@ static inline int __vimin3_s32(int a, int b, int c) { return std::min(a, std::mi
 static inline int __vimax3_s32(int a, int b, int c) { return std::max(a, std::max(b, c)); }
 static inline unsigned __vimin3_u32(unsigned a, unsigned b, unsigned c) { return std::min(a, std::min(b, c)); }
 static inline unsigned __vimax3_u32(unsigned a, unsigned b, unsigned c) { return std::max(a, std::max(b, c)); }
+// packed 16x2 (DPX-style) intrinsics
+static inline unsigned emu_pack16(int lo, int hi) { return ((unsigned)lo & 0xFFFFu) | ((unsigned)hi << 16); }
+static inline int emu_lo16(unsigned v) { return (short)(v & 0xFFFF); }
+static inline int emu_hi16(unsigned v) { return (short)(v >> 16); }
+static inline unsigned __vadd2(unsigned a, unsigned b) { return emu_pack16(emu_lo16(a) + emu_lo16(b), emu_hi16(a) + emu_hi16(b)); }
+static inline unsigned __vsub2(unsigned a, unsigned b) { return emu_pack16(emu_lo16(a) - emu_lo16(b), emu_hi16(a) - emu_hi16(b)); }
+static inline unsigned __vmaxs2(unsigned a, unsigned b) { return emu_pack16(std::max(emu_lo16(a), emu_lo16(b)), std::max(emu_hi16(a), emu_hi16(b))); }
+static inline unsigned __vmins2(unsigned a, unsigned b) { return emu_pack16(std::min(emu_lo16(a), emu_lo16(b)), std::min(emu_hi16(a), emu_hi16(b))); }
+static inline unsigned __vimax3_s16x2(unsigned a, unsigned b, unsigned c) { return __vmaxs2(__vmaxs2(a, b), c); }
+static inline unsigned __vimin3_s16x2(unsigned a, unsigned b, unsigned c) { return __vmins2(__vmins2(a, b), c); }
+static inline unsigned __dp4a(unsigned a, unsigned b, unsigned c) {
+    for (int i = 0; i < 4; ++i) c += ((a >> (8 * i)) & 0xFF) * ((b >> (8 * i)) & 0xFF);
+    return c;
+}
 static inline int __sad(int a, int b, unsigned c) { return (int)(c + (unsigned)std::abs(a - b)); }
 using std::max;
 using std::min;

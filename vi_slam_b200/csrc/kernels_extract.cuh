@@ -110,6 +110,32 @@ __device__ __forceinline__ int fast_score16(const uint8_t* p, const int* o) {
     return max(a, -b) - 1;
 }
 
+// shared-memory layout of one k_fast CTA (all sizes from ExtractGeom::tileW/tileH = max region + 6)
+__host__ __device__ inline int fast_tile_pitch(int tileW) { return (((tileW + 6) >> 2) << 2) + 8; }   // bytes, incl. pad words
+__host__ __device__ inline int fast_score_pitch(int tileW) { return (tileW - 4 + 3) & ~3; }             // region + ring
+__host__ __device__ inline size_t fast_smem_bytes(int tileW, int tileH) {
+    return (size_t)tileH * fast_tile_pitch(tileW) + (size_t)(tileH - 4) * fast_score_pitch(tileW) +
+           (size_t)2 * (tileW - 6) * (tileH - 6) + 16;
+}
+
+// bytes 0,1 (resp. 2,3) of w zero-extended into the two 16-bit lanes
+__device__ __forceinline__ unsigned lo16x2(unsigned w) { return __byte_perm(w, 0, 0x4140); }
+__device__ __forceinline__ unsigned hi16x2(unsigned w) { return __byte_perm(w, 0, 0x4342); }
+
+// opposite-pair pre-test of 2 pixels packed as s16x2: a 9-arc brighter (darker) than centre +/- th
+// contains one pixel of each opposite pair, so min over pairs of max(pair) > c + th (resp. max over
+// pairs of min(pair) < c - th) is necessary.  Returns 0x8000 per lane that may be a corner.
+__device__ __forceinline__ unsigned fast_pretest2(unsigned c, unsigned up, unsigned dn, unsigned lf, unsigned rt,
+                                                  unsigned d22, unsigned dm2m2, unsigned d2m2, unsigned dm22,
+                                                  unsigned nthp1, unsigned th) {
+    const unsigned nc = __vadd2(~c, 0x00010001u);                                  // -c per lane
+    const unsigned mb = __vmins2(__vimin3_s16x2(__vmaxs2(up, dn), __vmaxs2(lf, rt), __vmaxs2(d22, dm2m2)), __vmaxs2(d2m2, dm22));
+    const unsigned md = __vmaxs2(__vimax3_s16x2(__vmins2(up, dn), __vmins2(lf, rt), __vmins2(d22, dm2m2)), __vmins2(d2m2, dm22));
+    const unsigned xb = __vadd2(__vadd2(mb, nc), nthp1);                           // mb - c - (th+1): >= 0 <=> bright possible
+    const unsigned yd = __vadd2(__vadd2(md, nc), th);                              // md - c + th: < 0 <=> dark possible
+    return (~xb | yd) & 0x80008000u;
+}
+
 __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, FrameSrc fs, const CellDesc* __restrict__ cells,
                                                              uint32_t* __restrict__ cand, int* __restrict__ candCount,
                                                              int* __restrict__ status) {
@@ -122,64 +148,88 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
     int pitch;
     const uint8_t* img = level_ptr(g, fs, l, f, pitch);
     const int rw = c.x1 - c.x0, rh = c.y1 - c.y0, npx = rw * rh;
-    const int TP = (g.tileW + 3 + 3) & ~3;          // tile pitch (bytes), room for the alignment shift
-    const int SP = g.tileW - 4;                     // score pitch: region + 1-px ring
+    const int TP = fast_tile_pitch(g.tileW), TPW = TP >> 2;
+    const int SP = fast_score_pitch(g.tileW);
     uint8_t* T = smem;
     uint8_t* S = T + g.tileH * TP;
-    uint16_t* Q = reinterpret_cast<uint16_t*>(S + (((g.tileH - 4) * SP + 3) & ~3));
+    uint16_t* Q = reinterpret_cast<uint16_t*>(S + (g.tileH - 4) * SP);
     uint32_t* surv = reinterpret_cast<uint32_t*>(Q);
     if (tid == 0) { qCount = 0; sCount = 0; hasIni = 0; }
 
-    // phase 0
+    // phase 0: tile column 0 <-> image x = ax (4-byte aligned, one pad word left of the halo)
     const int ox = c.x0 - 3, oy = c.y0 - 3;
-    const int ax = ox & ~3, shift = ox - ax;
-    const int nW = (shift + rw + 6 + 3) >> 2, nR = rh + 6;
+    const int ax = (ox & ~3) - 4, shift = ox - ax;          // shift in [4,7]
+    const int nW = ((shift + rw + 9) >> 2) + 1, nR = rh + 6;
     for (int i = tid; i < nW * nR; i += VIORB_FAST_THREADS) {
         const int r = i / nW, k = i - r * nW;
         reinterpret_cast<uint32_t*>(T + r * TP)[k] =
             __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)(oy + r) * pitch + ax) + k);
     }
-    for (int i = tid; i < (((rh + 2) * SP + 3) >> 2); i += VIORB_FAST_THREADS) reinterpret_cast<uint32_t*>(S)[i] = 0;
+    for (int i = tid; i < (((rh + 2) * SP) >> 2); i += VIORB_FAST_THREADS) reinterpret_cast<uint32_t*>(S)[i] = 0;
     __syncthreads();
 
     const int th = g.minTh;
     const unsigned inv = (1u << 20) / (unsigned)rw + 1;     // p / rw == (p * inv) >> 20 for p < 16384
-    const uint8_t* T0 = T + 3 * TP + shift + 3;             // region pixel (0,0)
+    const int col0 = shift + 3;                             // tile column of region pixel 0
+    const uint8_t* T0 = T + 3 * TP + col0;                  // region pixel (0,0)
 
-    // phase A
-    for (int base = 0; base < npx; base += VIORB_FAST_THREADS) {
-        const int p = base + tid;
-        bool pass = false;
-        if (p < npx) {
-            const int py = (int)(((unsigned)p * inv) >> 20), px = p - py * rw;
-            const uint8_t* q = T0 + py * TP + px;
-            const int v = q[0], lo = v - th, hi = v + th;
-            int a = q[3 * TP], b = q[-3 * TP];
-            bool dark = (a < lo) | (b < lo), bright = (a > hi) | (b > hi);
-            if (dark | bright) {
-                a = q[3]; b = q[-3];
-                dark &= (a < lo) | (b < lo); bright &= (a > hi) | (b > hi);
-                if (dark | bright) {
-                    a = q[2 * TP + 2]; b = q[-2 * TP - 2];
-                    dark &= (a < lo) | (b < lo); bright &= (a > hi) | (b > hi);
-                    a = q[-2 * TP + 2]; b = q[2 * TP - 2];
-                    dark &= (a < lo) | (b < lo); bright &= (a > hi) | (b > hi);
-                    pass = dark | bright;
-                }
+    // phase A: 4 horizontally adjacent pixels (one aligned tile word) per thread, packed 16x2 pre-test
+    {
+        const int g0 = col0 >> 2, g1 = (col0 + rw - 1) >> 2, ng = g1 - g0 + 1;
+        const unsigned ginv = (1u << 20) / (unsigned)ng + 1;
+        const unsigned thp = (unsigned)th | ((unsigned)th << 16);
+        const unsigned nthp1 = ((0x10000u - (unsigned)(th + 1)) & 0xFFFFu) * 0x10001u;     // -(th+1) in both lanes
+        const int total = ng * rh;
+        for (int base = 0; base < total; base += VIORB_FAST_THREADS) {
+            const int i = base + tid;
+            unsigned pass = 0;              // bit j: pixel j of the group goes to the queue
+            int py = 0, gx = 0;
+            if (i < total) {
+                py = (int)(((unsigned)i * ginv) >> 20);
+                gx = g0 + (i - py * ng);
+                const uint32_t* R = reinterpret_cast<const uint32_t*>(T + (py + 3) * TP) + gx;
+                const unsigned cw = R[0], wl = R[-1], wr = R[1];
+                const unsigned up = R[-3 * TPW], dn = R[3 * TPW];
+                const unsigned rt = __funnelshift_r(cw, wr, 24), lf = __funnelshift_r(wl, cw, 8);
+                const uint32_t* Rp = R + 2 * TPW;
+                const uint32_t* Rm = R - 2 * TPW;
+                const unsigned d22 = __funnelshift_r(Rp[0], Rp[1], 16), dm22 = __funnelshift_r(Rp[-1], Rp[0], 16);
+                const unsigned d2m2 = __funnelshift_r(Rm[0], Rm[1], 16), dm2m2 = __funnelshift_r(Rm[-1], Rm[0], 16);
+                const unsigned a = fast_pretest2(lo16x2(cw), lo16x2(up), lo16x2(dn), lo16x2(lf), lo16x2(rt), lo16x2(d22),
+                                                 lo16x2(dm2m2), lo16x2(d2m2), lo16x2(dm22), nthp1, thp);
+                const unsigned b = fast_pretest2(hi16x2(cw), hi16x2(up), hi16x2(dn), hi16x2(lf), hi16x2(rt), hi16x2(d22),
+                                                 hi16x2(dm2m2), hi16x2(d2m2), hi16x2(dm22), nthp1, thp);
+                pass = ((a >> 15) & 1) | ((a >> 30) & 2) | ((b >> 13) & 4) | ((b >> 28) & 8);
+                // drop the pixels of the word that lie outside the region
+                const int px0 = gx * 4 - col0;
+                unsigned m = 0xF;
+                if (px0 < 0) m &= 0xFu << (-px0);
+                if (px0 + 3 >= rw) m &= 0xFu >> (px0 + 4 - rw);
+                pass &= m;
             }
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, pass);
-        if (m) {
-            const int leader = __ffs(m) - 1;
-            int qb = 0;
-            if (lane == leader) qb = atomicAdd(&qCount, __popc(m));
-            qb = __shfl_sync(0xffffffffu, qb, leader);
-            if (pass) Q[qb + __popc(m & ((1u << lane) - 1))] = (uint16_t)p;
+            // warp-wide exclusive scan of popc(pass), one shared atomic per warp
+            const int cnt = __popc(pass);
+            int inc = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += t;
+            }
+            const int tot = __shfl_sync(0xffffffffu, inc, 31);
+            if (tot) {
+                int qb = 0;
+                if (lane == 31) qb = atomicAdd(&qCount, tot);
+                qb = __shfl_sync(0xffffffffu, qb, 31) + inc - cnt;
+                const int p0 = py * rw + gx * 4 - col0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (pass >> j & 1) Q[qb++] = (uint16_t)(p0 + j);
+            }
         }
     }
     __syncthreads();
 
-    // phase B
+    // phase B: dense corner score on the queue
     {
         const int o[16] = {3 * TP, 3 * TP + 1, 2 * TP + 2, TP + 3, 3, -TP + 3, -2 * TP + 2, -3 * TP + 1,
                            -3 * TP, -3 * TP - 1, -2 * TP - 2, -TP - 3, -3, TP - 3, 2 * TP - 2, 3 * TP - 1};
@@ -193,18 +243,29 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
     }
     __syncthreads();
 
-    // phase C
-    for (int p = tid; p < npx; p += VIORB_FAST_THREADS) {
-        const int py = (int)(((unsigned)p * inv) >> 20), px = p - py * rw;
-        const uint8_t* s = S + (py + 1) * SP + px + 1;
-        const int v = s[0];
-        if (v) {
-            const bool keep = v > s[-1] && v > s[1] && v > s[-SP - 1] && v > s[-SP] && v > s[-SP + 1] &&
-                              v > s[SP - 1] && v > s[SP] && v > s[SP + 1];
-            if (keep) {
-                const int i = atomicAdd(&sCount, 1);
-                surv[i] = (uint32_t)(c.x0 + px - VIORB_MINB) | ((uint32_t)(c.y0 + py - VIORB_MINB) << 12) | ((uint32_t)v << 24);
-                if (v >= g.iniTh) hasIni = 1;
+    // phase C: strict 3x3 NMS; whole score words that are zero are skipped
+    {
+        const int SPW = SP >> 2;
+        const unsigned winv = (1u << 20) / (unsigned)SPW + 1;
+        const int total = SPW * rh;
+        for (int i = tid; i < total; i += VIORB_FAST_THREADS) {
+            const int py = (int)(((unsigned)i * winv) >> 20), wx = i - py * SPW;
+            const unsigned w = reinterpret_cast<const uint32_t*>(S + (py + 1) * SP)[wx];
+            if (w == 0) continue;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int v = (w >> (8 * j)) & 0xFF;
+                const int px = wx * 4 + j - 1;
+                if (v && px >= 0 && px < rw) {
+                    const uint8_t* s = S + (py + 1) * SP + px + 1;
+                    const bool keep = v > s[-1] && v > s[1] && v > s[-SP - 1] && v > s[-SP] && v > s[-SP + 1] &&
+                                      v > s[SP - 1] && v > s[SP] && v > s[SP + 1];
+                    if (keep) {
+                        const int k = atomicAdd(&sCount, 1);
+                        surv[k] = (uint32_t)(c.x0 + px - VIORB_MINB) | ((uint32_t)(c.y0 + py - VIORB_MINB) << 12) | ((uint32_t)v << 24);
+                        if (v >= g.iniTh) hasIni = 1;
+                    }
+                }
             }
         }
     }

@@ -266,8 +266,7 @@ int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
     g.tileH = maxRH + 6;
     g.maxNodes = maxNodes;
     g.arenaStride = off;
-    const int TP = (g.tileW + 3 + 3) & ~3, SP = g.tileW - 4;
-    ex->fastSmem = (size_t)g.tileH * TP + (size_t)(((g.tileH - 4) * SP + 3) & ~3) + (size_t)2 * maxRW * maxRH + 16;
+    ex->fastSmem = fast_smem_bytes(g.tileW, g.tileH);
     ex->octSmem = octree_smem_bytes(maxNodes);
     if (ex->octSmem > 220 * 1024) return fail(VIORB_E_ARG, "nfeatures too large for the quadtree's shared memory");
     if (maxRW * maxRH >= 16384) return fail(VIORB_E_ARG, "FAST cell larger than supported");
