@@ -392,6 +392,8 @@ static inline float __fdiv_rn(float a, float b) { return a / b; }
 static inline double __dmul_rn(double a, double b) { return a * b; }
 static inline double __dadd_rn(double a, double b) { return a + b; }
 #pragma GCC pop_options
+static inline float __int_as_float(int v) { float f; std::memcpy(&f, &v, 4); return f; }
+static inline int __float_as_int(float f) { int v; std::memcpy(&v, &f, 4); return v; }
 static inline int __float2int_rn(float v) { return (int)lrintf(v); }
 static inline int __float2int_rz(float v) { return (int)v; }
 static inline int __float2int_rd(float v) { return (int)std::floor(v); }

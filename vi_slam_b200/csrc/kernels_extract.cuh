@@ -22,58 +22,79 @@ __device__ __forceinline__ int reflect101_dev(int p, int n) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Pyramid level l from level l-1.  One thread = 4 adjacent output pixels of one row.
-// Coefficient tables (11-bit, built on the host exactly like cv::resize does) live in global memory.
-// grid (ceil(w/4/64), ceil(h/4), B), block (64,4).
+// Pyramid level l from level l-1.  One thread = 4 adjacent output pixels x VIORB_RS_ROWS rows: the
+// horizontal coefficients (11-bit, built on the host exactly like cv::resize does) are fetched once per
+// thread with two 128-bit loads, and a source row's horizontal pass is reused by the next output row when
+// both need it (the source advances 1.2 rows per output row).
+// grid (ceil(w/256), ceil(h/(4*VIORB_RS_ROWS)), B), block (64,4).
 // ---------------------------------------------------------------------------------------------
+#define VIORB_RS_ROWS 4
 __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int l, const int* __restrict__ xofs,
                                                 const short2* __restrict__ xalpha, const int* __restrict__ yofs,
                                                 const short2* __restrict__ ybeta) {
     const LevelGeom& L = g.lv[l];
     const LevelGeom& S = g.lv[l - 1];
     const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
-    const int dy = blockIdx.y * blockDim.y + threadIdx.y;
+    const int dy0 = (blockIdx.y * blockDim.y + threadIdx.y) * VIORB_RS_ROWS;
     const int f = blockIdx.z;
-    if (x4 >= L.w || dy >= L.h) return;
+    if (x4 >= L.w || dy0 >= L.h) return;
     int sp;
     const uint8_t* src = level_ptr(g, fs, l - 1, f, sp);
-    uint8_t* dst = fs.pyr + (size_t)f * g.arenaStride + L.off + (size_t)dy * L.pitch;
-    uint32_t packed = 0;
+    uint8_t* dst = fs.pyr + (size_t)f * g.arenaStride + L.off;
+    const int nrow = min(VIORB_RS_ROWS, L.h - dy0);
     if (L.areaHalf) {
-        const uint8_t* a = src + (size_t)(2 * dy) * sp;
-        const uint8_t* b = a + sp;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            int x = x4 + i;
-            if (x < L.w) {
-                int v = (a[2 * x] + a[2 * x + 1] + b[2 * x] + b[2 * x + 1] + 2) >> 2;
-                packed |= (uint32_t)v << (8 * i);
+        for (int r = 0; r < nrow; ++r) {
+            const int dy = dy0 + r;
+            const uint8_t* a = src + (size_t)(2 * dy) * sp;
+            const uint8_t* b = a + sp;
+            for (int i = 0; i < 4 && x4 + i < L.w; ++i) {
+                const int x = x4 + i;
+                dst[(size_t)dy * L.pitch + x] = (uint8_t)((a[2 * x] + a[2 * x + 1] + b[2 * x] + b[2 * x + 1] + 2) >> 2);
             }
         }
-    } else {
+        return;
+    }
+    // tables are padded to a multiple of 4 entries per level, so the vector loads stay inside them
+    const int4 sx = __ldg(reinterpret_cast<const int4*>(xofs + L.xTab + x4));
+    const int4 alr = __ldg(reinterpret_cast<const int4*>(xalpha + L.xTab + x4));
+    const int o0[4] = {sx.x, sx.y, sx.z, sx.w};
+    const int ar[4] = {alr.x, alr.y, alr.z, alr.w};
+    int o1[4], a0[4], a1[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        o1[i] = min(o0[i] + 1, S.w - 1);
+        a0[i] = (short)(ar[i] & 0xFFFF);
+        a1[i] = ar[i] >> 16;
+    }
+    int h0[4], h1[4], have = -0x40000000;       // source row whose horizontal pass sits in h1
+    for (int r = 0; r < nrow; ++r) {
+        const int dy = dy0 + r;
         const int sy = __ldg(yofs + L.yTab + dy);
         const short2 bt = __ldg(ybeta + L.yTab + dy);
         const int sy0 = min(max(sy, 0), S.h - 1), sy1 = min(max(sy + 1, 0), S.h - 1);
-        const uint8_t* r0 = src + (size_t)sy0 * sp;
-        const uint8_t* r1 = src + (size_t)sy1 * sp;
+        if (have == sy0) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) h0[i] = h1[i];
+        } else {
+            const uint8_t* r0 = src + (size_t)sy0 * sp;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) h0[i] = r0[o0[i]] * a0[i] + r0[o1[i]] * a1[i];
+        }
+        {
+            const uint8_t* r1 = src + (size_t)sy1 * sp;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) h1[i] = r1[o0[i]] * a0[i] + r1[o1[i]] * a1[i];
+            have = sy1;
+        }
+        uint32_t packed = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            int x = x4 + i;
-            if (x < L.w) {
-                const int sx = __ldg(xofs + L.xTab + x);
-                const short2 al = __ldg(xalpha + L.xTab + x);
-                const int sx1 = min(sx + 1, S.w - 1);
-                const int h0 = r0[sx] * al.x + r0[sx1] * al.y;
-                const int h1 = r1[sx] * al.x + r1[sx1] * al.y;
-                const int v = ((((int)bt.x * (h0 >> 4)) >> 16) + (((int)bt.y * (h1 >> 4)) >> 16) + 2) >> 2;
-                packed |= (uint32_t)(v & 0xFF) << (8 * i);
-            }
+            const int v = ((((int)bt.x * (h0[i] >> 4)) >> 16) + (((int)bt.y * (h1[i] >> 4)) >> 16) + 2) >> 2;
+            packed |= (uint32_t)(v & 0xFF) << (8 * i);
         }
-    }
-    if (x4 + 3 < L.w) {
-        *reinterpret_cast<uint32_t*>(dst + x4) = packed;
-    } else {
-        for (int i = 0; i < 4 && x4 + i < L.w; ++i) dst[x4 + i] = (uint8_t)(packed >> (8 * i));
+        uint8_t* d = dst + (size_t)dy * L.pitch + x4;
+        if (x4 + 3 < L.w) *reinterpret_cast<uint32_t*>(d) = packed;
+        else for (int i = 0; i < 4 && x4 + i < L.w; ++i) d[i] = (uint8_t)(packed >> (8 * i));
     }
 }
 
@@ -743,43 +764,79 @@ __global__ void __launch_bounds__(256) k_emit(ExtractGeom g, const KeptKp* __res
 // ---------------------------------------------------------------------------------------------
 // 7x7 sigma-2 Gaussian, 8-bit fixed point: taps {18,34,48,56,48,34,18}/256, row pass Q8.8, column
 // pass Q16.16, +0.5, >>16; BORDER_REFLECT_101 from the level image itself.  All levels in one launch:
-// grid (totalBlurTiles, B), block 256; tile = 64 x 16 output pixels, halo 3 staged in shared memory.
 // ---------------------------------------------------------------------------------------------
+#define VIORB_BLUR_TW 256        // tile width: 64 threads x 4 pixels
+#define VIORB_BLUR_TH 32         // output rows walked by one thread
 struct BlurTiles { int base[VIORB_MAX_LEVELS + 1]; int tilesX[VIORB_MAX_LEVELS]; };
 
-__global__ void __launch_bounds__(256) k_blur(ExtractGeom g, FrameSrc fs, BlurTiles bt) {
-    __shared__ uint8_t sIn[22 * 72];
-    __shared__ uint16_t sH[22 * 64];
-    const int tid = threadIdx.x, f = blockIdx.y;
+// One image row -> the four Q8.8 row sums of the thread's 4 columns.  w0,w1,w2 = the aligned words
+// holding columns [4t-4, 4t+8); column j needs bytes 1+j .. 7+j of that 12-byte window.
+__device__ __forceinline__ void blur_row4(unsigned w0, unsigned w1, unsigned w2, unsigned h[4]) {
+    const unsigned K0 = 18u | (34u << 8) | (48u << 16) | (56u << 24), K1 = 48u | (34u << 8) | (18u << 16);
+    h[0] = __dp4a(__funnelshift_r(w0, w1, 8), K0, __dp4a(__funnelshift_r(w1, w2, 8), K1, 0u));
+    h[1] = __dp4a(__funnelshift_r(w0, w1, 16), K0, __dp4a(__funnelshift_r(w1, w2, 16), K1, 0u));
+    h[2] = __dp4a(__funnelshift_r(w0, w1, 24), K0, __dp4a(__funnelshift_r(w1, w2, 24), K1, 0u));
+    h[3] = __dp4a(w1, K0, __dp4a(w2, K1, 0u));
+}
+
+// Each thread owns a 4-pixel-wide column strip and walks down VIORB_BLUR_TH output rows keeping the last
+// seven row sums in registers (the loop is unrolled by 7 so the ring needs no moves): per row 3 aligned
+// 32-bit loads, 6 funnel shifts + 8 IDP.4A for the row pass, 28 multiply-adds for the column pass and one
+// 32-bit store.  Strips touching the left/right image border take a byte-wise reflect-101 path.
+// grid (totalBlurTiles, B), block 64.
+__global__ void __launch_bounds__(64) k_blur(ExtractGeom g, FrameSrc fs, BlurTiles bt) {
+    const int f = blockIdx.y;
     int l = 0;
     while (l + 1 < g.nlevels && (int)blockIdx.x >= bt.base[l + 1]) ++l;
     const LevelGeom& L = g.lv[l];
     const int t = blockIdx.x - bt.base[l];
-    const int tx0 = (t % bt.tilesX[l]) * 64, ty0 = (t / bt.tilesX[l]) * 16;
+    const int x0 = (t % bt.tilesX[l]) * VIORB_BLUR_TW + threadIdx.x * 4;
+    const int y0 = (t / bt.tilesX[l]) * VIORB_BLUR_TH;
+    if (x0 >= L.w) return;
     int pitch;
     const uint8_t* img = level_ptr(g, fs, l, f, pitch);
     uint8_t* dst = fs.blur + (size_t)f * g.arenaStride + L.off;
-    const bool interior = tx0 >= 3 && ty0 >= 3 && tx0 + 67 <= L.w && ty0 + 19 <= L.h;
-    for (int i = tid; i < 22 * 70; i += 256) {
-        const int r = i / 70, c = i - r * 70;
-        int sy = ty0 - 3 + r, sx = tx0 - 3 + c;
-        if (!interior) { sy = reflect101_dev(sy, L.h); sx = reflect101_dev(sx, L.w); }
-        sIn[r * 72 + c] = img[(size_t)sy * pitch + sx];
-    }
-    __syncthreads();
-    for (int i = tid; i < 22 * 64; i += 256) {
-        const int r = i >> 6, c = i & 63;
-        const uint8_t* p = sIn + r * 72 + c;
-        sH[i] = (uint16_t)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
-    }
-    __syncthreads();
-    for (int i = tid; i < 16 * 64; i += 256) {
-        const int r = i >> 6, c = i & 63;
-        const int x = tx0 + c, y = ty0 + r;
-        if (x < L.w && y < L.h) {
-            const uint16_t* p = sH + r * 64 + c;
-            const uint32_t acc = 18u * (p[0] + p[6 * 64]) + 34u * (p[64] + p[5 * 64]) + 48u * (p[2 * 64] + p[4 * 64]) + 56u * p[3 * 64];
-            dst[(size_t)y * L.pitch + x] = (uint8_t)((acc + 32768u) >> 16);
+    const bool interior = x0 >= 4 && x0 + 6 < L.w && x0 + 8 <= pitch;
+    const int yEnd = min(y0 + VIORB_BLUR_TH, L.h);
+    unsigned ring[7][4];
+
+    auto load_row = [&](int y, unsigned h[4]) {
+        const int sy = reflect101_dev(y, L.h);
+        const uint8_t* row = img + (size_t)sy * pitch;
+        unsigned w0, w1, w2;
+        if (interior) {
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(row + x0);
+            w0 = __ldg(p - 1); w1 = __ldg(p); w2 = __ldg(p + 1);
+        } else {
+            unsigned w[3] = {0, 0, 0};
+#pragma unroll
+            for (int b = 1; b < 11; ++b)
+                w[b >> 2] |= (unsigned)row[reflect101_dev(x0 - 4 + b, L.w)] << (8 * (b & 3));
+            w0 = w[0]; w1 = w[1]; w2 = w[2];
+        }
+        blur_row4(w0, w1, w2, h);
+    };
+
+#pragma unroll
+    for (int r = 0; r < 6; ++r) load_row(y0 - 3 + r, ring[r]);
+    for (int yb = y0; yb < yEnd; yb += 7) {
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            const int y = yb + k;
+            if (y < yEnd) {
+                // rows y-3 .. y+2 sit in ring[(k+0..5) % 7]; the new row y+3 goes to ring[(k+6) % 7]
+                load_row(y + 3, ring[(k + 6) % 7]);
+                unsigned out = 0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const unsigned acc = 18u * (ring[k % 7][j] + ring[(k + 6) % 7][j]) + 34u * (ring[(k + 1) % 7][j] + ring[(k + 5) % 7][j]) +
+                                         48u * (ring[(k + 2) % 7][j] + ring[(k + 4) % 7][j]) + 56u * ring[(k + 3) % 7][j];
+                    out |= ((acc + 32768u) >> 16) << (8 * j);
+                }
+                uint8_t* o = dst + (size_t)y * L.pitch + x0;
+                if (x0 + 3 < L.w) *reinterpret_cast<uint32_t*>(o) = out;
+                else for (int j = 0; j < 4 && x0 + j < L.w; ++j) o[j] = (uint8_t)(out >> (8 * j));
+            }
         }
     }
 }
@@ -789,22 +846,36 @@ __global__ void __launch_bounds__(256) k_blur(ExtractGeom g, FrameSrc fs, BlurTi
 // Sample offset = cvRound(x*b + y*a), cvRound(x*a - y*b): float32 products and sums rounded
 // separately (no FMA), round-half-even.  grid (ceil(outCap/8), B), block 256.
 // ---------------------------------------------------------------------------------------------
+#define VIORB_DESC_R 18                     // largest rounded sample offset: |(13,13)| = 18.4
+#define VIORB_DESC_PW 44                    // staged patch row: 37 bytes + alignment shift, in whole words
 __global__ void __launch_bounds__(256) k_describe(ExtractGeom g, FrameSrc fs, const KeptKp* __restrict__ kept,
                                                   const int* __restrict__ slot2kept, const int* __restrict__ nOut,
                                                   uint8_t* __restrict__ desc) {
-    __shared__ int8_t pat[1024];
+    __shared__ __align__(16) int8_t pat[1024];
+    __shared__ __align__(16) uint8_t patch[8][(2 * VIORB_DESC_R + 1) * VIORB_DESC_PW];
     for (int i = threadIdx.x; i < 256; i += 256)
         reinterpret_cast<uint32_t*>(pat)[i] = reinterpret_cast<const uint32_t*>(d_orb_pattern)[i];
     __syncthreads();
-    const int lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int slot = blockIdx.x * 8 + wid;
     const int f = blockIdx.y;
     if (slot >= nOut[f]) return;
     const KeptKp k = kept[(size_t)f * g.keptPerFrame + slot2kept[(size_t)f * g.outCap + slot]];
     const int l = k.score >> 16;
     const LevelGeom& L = g.lv[l];
     const uint8_t* img = fs.blur + (size_t)f * g.arenaStride + L.off;
-    const uint8_t* ctr = img + (size_t)k.y * L.pitch + k.x;
+    // stage the (2R+1)-row neighbourhood with coalesced aligned word loads (the 512 samples would
+    // otherwise be 512 scattered byte requests to L1)
+    const int xs = (k.x - VIORB_DESC_R) & ~3, shift = (k.x - VIORB_DESC_R) - xs;
+    uint8_t* P = patch[wid];
+    const uint8_t* src = img + (size_t)(k.y - VIORB_DESC_R) * L.pitch + xs;
+    const int NW = VIORB_DESC_PW / 4;
+    for (int i = lane; i < (2 * VIORB_DESC_R + 1) * NW; i += 32) {
+        const int r = i / NW, c = i - r * NW;
+        reinterpret_cast<uint32_t*>(P)[i] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)r * L.pitch) + c);
+    }
+    __syncwarp();
+    const uint8_t* ctr = P + VIORB_DESC_R * VIORB_DESC_PW + VIORB_DESC_R + shift;
     const float a = k.c, b = k.s;
     int val = 0;
 #pragma unroll
@@ -815,7 +886,7 @@ __global__ void __launch_bounds__(256) k_describe(ExtractGeom g, FrameSrc fs, co
         const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
         const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
         const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
-        const int t0 = ctr[r0 * L.pitch + c0], t1 = ctr[r1 * L.pitch + c1];
+        const int t0 = ctr[r0 * VIORB_DESC_PW + c0], t1 = ctr[r1 * VIORB_DESC_PW + c1];
         val |= (t0 < t1) << t;
     }
     desc[((size_t)f * g.outCap + slot) * 32 + lane] = (uint8_t)val;

@@ -30,10 +30,23 @@ __device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, cons
            __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
+// 256-bit Hamming distance with a carry-save adder tree (Harley-Seal): POPC issues on the quarter-rate
+// XU pipe (ncu: xu 91 % busy with 8 POPC per pair), so seven of the eight XOR words are first compressed
+// by four 3:2 compressors (8 LOP3 on the ALU pipe) into ones/twos/fours words: 4 POPC instead of 8.
+__device__ __forceinline__ int hamming256_csa(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) {
+    const unsigned x0 = a0.x ^ b0.x, x1 = a0.y ^ b0.y, x2 = a0.z ^ b0.z, x3 = a0.w ^ b0.w;
+    const unsigned x4 = a1.x ^ b1.x, x5 = a1.y ^ b1.y, x6 = a1.z ^ b1.z, x7 = a1.w ^ b1.w;
+    const unsigned s0 = x0 ^ x1 ^ x2, c0 = (x0 & x1) | (x2 & (x0 ^ x1));
+    const unsigned s1 = x3 ^ x4 ^ x5, c1 = (x3 & x4) | (x5 & (x3 ^ x4));
+    const unsigned s2 = s0 ^ s1 ^ x6, c2 = (s0 & s1) | (x6 & (s0 ^ s1));
+    const unsigned s3 = c0 ^ c1 ^ c2, c3 = (c0 & c1) | (c2 & (c0 ^ c1));
+    return __popc(s2) + __popc(x7) + 2 * __popc(s3) + 4 * __popc(c3);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Brute-force Hamming 2-NN.  One thread = one query row (256 bits in 8 registers); train rows are
 // staged 128 at a time in shared memory and read as warp-wide broadcasts (2 x LDS.128 per row).
-// Per pair: 8 LOP3(xor) + 8 POPC + adds, then a 3-instruction running top-2 on the packed key
+// Per pair: 8 XOR + 8 LOP3 (carry-save tree) + 4 POPC + adds, then a 3-instruction running top-2 on the packed key
 // (distance << 22 | train index), which also yields cv::BFMatcher's tie rule (lower index first).
 // grid (ceil(maxNq/128), nSets), block 128.
 // ---------------------------------------------------------------------------------------------
@@ -62,7 +75,7 @@ __global__ void __launch_bounds__(VIORB_KNN_THREADS) k_knn2(DescSet Q, DescSet T
 #pragma unroll 4
         for (int j = 0; j < m; ++j) {
             const uint4 b0 = tile[2 * j], b1 = tile[2 * j + 1];
-            const unsigned key = ((unsigned)hamming256(a0, a1, b0, b1) << VIORB_KNN_IDX_BITS) | (kb + j);
+            const unsigned key = ((unsigned)hamming256_csa(a0, a1, b0, b1) << VIORB_KNN_IDX_BITS) | (kb + j);
             const unsigned lo = min(key, best0);
             best1 = min(best1, max(key, best0));
             best0 = lo;
@@ -187,61 +200,83 @@ struct StereoParams {
     int nlevels, outCap;
 };
 
-__global__ void __launch_bounds__(256) k_stereo_coarse(StereoParams sp, const viorb_keypoint* __restrict__ kl,
-                                                       const uint8_t* __restrict__ dl, const int* __restrict__ nL,
-                                                       const viorb_keypoint* __restrict__ kr, const uint8_t* __restrict__ dr,
-                                                       const int* __restrict__ nR, int32_t* __restrict__ bestIdx,
-                                                       int32_t* __restrict__ bestDist) {
-    __shared__ short sMin[256], sMax[256];
-    __shared__ float sU[256];
-    __shared__ int8_t sOct[256];
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, f = blockIdx.y;
-    const int nl = nL[f], nr = nR[f];
-    const int iL = blockIdx.x * 8 + wid;
-    if (blockIdx.x * 8 >= nl) return;
-    const bool active = iL < nl;
-    const viorb_keypoint* KL = kl + (size_t)f * sp.outCap;
+// Row table (frame.cpp:833-850): for every image row the right keypoints whose band
+// [floor(y - 2 s), ceil(y + 2 s)] covers it, as a CSR structure built by one CTA per frame
+// (count, block scan, fill).  Order inside a row is arbitrary; the matcher's winner rule
+// (min over (distance, index)) does not depend on it.  Also packs (x, octave) of the right keypoints.
+// grid (nFrames), block 256, dynamic smem 2 * (rows + 1) ints.
+__global__ void __launch_bounds__(256) k_stereo_rows(StereoParams sp, int rows, int listCap, const viorb_keypoint* __restrict__ kr,
+                                                     const int* __restrict__ nR, int* __restrict__ rowStart,
+                                                     int* __restrict__ rowList, float2* __restrict__ rmeta, int* __restrict__ status) {
+    VIORB_DYN_SMEM(smem);
+    __shared__ int warpSums[20];
+    int* cnt = reinterpret_cast<int*>(smem);
+    int* cur = cnt + rows + 1;
+    const int tid = threadIdx.x, f = blockIdx.x;
+    const int nr = nR[f];
     const viorb_keypoint* KR = kr + (size_t)f * sp.outCap;
+    for (int i = tid; i <= rows; i += 256) { cnt[i] = 0; cur[i] = 0; }
+    __syncthreads();
+    for (int i = tid; i < nr; i += 256) {
+        const viorb_keypoint k = KR[i];
+        const float r = __fmul_rn(2.0f, sp.scale[k.octave]);
+        const int maxr = min(__float2int_ru(__fadd_rn(k.y, r)), rows - 1);
+        const int minr = max(__float2int_rd(__fsub_rn(k.y, r)), 0);
+        for (int y = minr; y <= maxr; ++y) atomicAdd(&cnt[y], 1);
+        rmeta[(size_t)f * sp.outCap + i] = make_float2(k.x, __int_as_float(k.octave));
+    }
+    __syncthreads();
+    const int total = block_excl_scan(cnt, rows + 1, warpSums);      // cnt[y] = start of row y, cnt[rows] = total
+    int* RS = rowStart + (size_t)f * (rows + 1);
+    for (int i = tid; i <= rows; i += 256) RS[i] = min(cnt[i], listCap);
+    if (total > listCap && tid == 0) atomicOr(status, 8);
+    int* RL = rowList + (size_t)f * listCap;
+    for (int i = tid; i < nr; i += 256) {
+        const viorb_keypoint k = KR[i];
+        const float r = __fmul_rn(2.0f, sp.scale[k.octave]);
+        const int maxr = min(__float2int_ru(__fadd_rn(k.y, r)), rows - 1);
+        const int minr = max(__float2int_rd(__fsub_rn(k.y, r)), 0);
+        for (int y = minr; y <= maxr; ++y) {
+            const int pos = cnt[y] + atomicAdd(&cur[y], 1);
+            if (pos < listCap) RL[pos] = i;
+        }
+    }
+}
+
+// One warp per left keypoint: lanes stride over the candidates of its row, test octave and disparity
+// range, and only then pay for the 256-bit Hamming distance.
+__global__ void __launch_bounds__(256) k_stereo_coarse(StereoParams sp, int rows, int listCap, const viorb_keypoint* __restrict__ kl,
+                                                       const uint8_t* __restrict__ dl, const int* __restrict__ nL,
+                                                       const uint8_t* __restrict__ dr, const int* __restrict__ rowStart,
+                                                       const int* __restrict__ rowList, const float2* __restrict__ rmeta,
+                                                       int32_t* __restrict__ bestIdx, int32_t* __restrict__ bestDist) {
+    const int lane = threadIdx.x & 31, f = blockIdx.y;
+    const int iL = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (iL >= nL[f]) return;
+    const viorb_keypoint k = kl[(size_t)f * sp.outCap + iL];
     const uint4* DL = reinterpret_cast<const uint4*>(dl + (size_t)f * sp.outCap * 32);
     const uint4* DR = reinterpret_cast<const uint4*>(dr + (size_t)f * sp.outCap * 32);
-    float uL = 0.f, minU = 0.f;
-    int row = 0, levelL = 0;
-    uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
-    bool search = false;
-    if (active) {
-        const viorb_keypoint k = KL[iL];
-        uL = k.x; row = (int)k.y; levelL = k.octave;
-        minU = __fsub_rn(uL, sp.maxD);
-        search = !(uL < 0.f);                   // maxU = uL - minD, minD = 0
-        a0 = DL[(size_t)iL * 2]; a1 = DL[(size_t)iL * 2 + 1];
-    }
+    const float2* RM = rmeta + (size_t)f * sp.outCap;
+    const float uL = k.x, minU = __fsub_rn(k.x, sp.maxD);
+    const int row = (int)k.y, levelL = k.octave;
     int best = VIORB_TH_HIGH << 20;
-    for (int r0 = 0; r0 < nr; r0 += 256) {
-        __syncthreads();
-        if (r0 + tid < nr) {
-            const viorb_keypoint k = KR[r0 + tid];
-            const float r = __fmul_rn(2.0f, sp.scale[k.octave]);
-            sMax[tid] = (short)__float2int_ru(__fadd_rn(k.y, r));
-            sMin[tid] = (short)__float2int_rd(__fsub_rn(k.y, r));
-            sU[tid] = k.x;
-            sOct[tid] = (int8_t)k.octave;
-        }
-        __syncthreads();
-        if (search) {
-            const int m = min(256, nr - r0);
-            for (int j = lane; j < m; j += 32) {
-                const int oc = sOct[j];
-                const float uR = sU[j];
-                if (row >= sMin[j] && row <= sMax[j] && oc >= levelL - 1 && oc <= levelL + 1 && uR >= minU && uR <= uL) {
-                    const int iR = r0 + j;
-                    const int d = hamming256(a0, a1, DR[(size_t)iR * 2], DR[(size_t)iR * 2 + 1]);
-                    best = min(best, (d << 20) | iR);
-                }
+    if (!(uL < 0.f) && row >= 0 && row < rows) {          // maxU = uL - minD, minD = 0 (frame.cpp:872-876)
+        const uint4 a0 = DL[(size_t)iL * 2], a1 = DL[(size_t)iL * 2 + 1];
+        const int* RS = rowStart + (size_t)f * (rows + 1);
+        const int* RL = rowList + (size_t)f * listCap;
+        const int e = RS[row + 1];
+        for (int j = RS[row] + lane; j < e; j += 32) {
+            const int iR = RL[j];
+            const float2 m = RM[iR];
+            const int oc = __float_as_int(m.y);
+            if (oc >= levelL - 1 && oc <= levelL + 1 && m.x >= minU && m.x <= uL) {
+                const int d = hamming256(a0, a1, DR[(size_t)iR * 2], DR[(size_t)iR * 2 + 1]);
+                best = min(best, (d << 20) | iR);
             }
         }
     }
     best = __reduce_min_sync(0xffffffffu, best);
-    if (active && lane == 0) {
+    if (lane == 0) {
         const bool found = best < (VIORB_TH_HIGH << 20);
         bestIdx[(size_t)f * sp.outCap + iL] = found ? (best & 0xFFFFF) : -1;
         bestDist[(size_t)f * sp.outCap + iL] = found ? (best >> 20) : -1;

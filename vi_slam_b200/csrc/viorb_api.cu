@@ -89,7 +89,9 @@ struct viorb_extractor {
     // stereo / matching results of the last viorb_stereo_batch on this (left) handle
     DevBuf<int32_t> dBestIdx, dBestDist, dSad, dKnnIdx, dKnnDist, dLrMatch;
     DevBuf<float> dURight, dDepth;
-    DevBuf<int> dNStereo, dNRatio;
+    DevBuf<int> dNStereo, dNRatio, dRowStart, dRowList;
+    DevBuf<float2> dRMeta;
+    int rowListCap = 0;
     DevBuf<viorb_match> dMatches;
     // pinned staging
     PinBuf<uint8_t> hIn, hDesc;
@@ -161,6 +163,7 @@ void build_resize_tables(int sw, int sh, int dw, int dh, ResizeTabs& t) {
         t.xofs.push_back(sx);
         t.xalpha.push_back(make_short2(sat_short((1.f - fx) * 2048), sat_short(fx * 2048)));
     }
+    while (t.xofs.size() % 4) { t.xofs.push_back(0); t.xalpha.push_back(make_short2(0, 0)); }   // int4 loads in k_resize
     for (int dy = 0; dy < dh; ++dy) {
         float fy = (float)((dy + 0.5) * scale_y - 0.5);
         int sy = (int)std::floor(fy);
@@ -252,8 +255,8 @@ int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
         keptOff += L.keptCap;
         maxNodes = std::max(maxNodes, L.keptCap + 4);
         ex->blurTiles.base[l] = blurBase;
-        ex->blurTiles.tilesX[l] = (L.w + 63) / 64;
-        blurBase += ex->blurTiles.tilesX[l] * ((L.h + 15) / 16);
+        ex->blurTiles.tilesX[l] = (L.w + VIORB_BLUR_TW - 1) / VIORB_BLUR_TW;
+        blurBase += ex->blurTiles.tilesX[l] * ((L.h + VIORB_BLUR_TH - 1) / VIORB_BLUR_TH);
     }
     ex->blurTiles.base[nl] = blurBase;
     ex->totalBlurTiles = blurBase;
@@ -316,7 +319,7 @@ int run_pipeline(viorb_extractor* ex, int n, int lap0, int lap1) {
     if (tm) CU(cudaEventRecord(ex->evX[0], st));
     for (int l = 1; l < g.nlevels; ++l) {
         const LevelGeom& L = g.lv[l];
-        dim3 grid((L.w + 255) / 256, (L.h + 3) / 4, n), block(64, 4);
+        dim3 grid((L.w + 255) / 256, (L.h + 4 * VIORB_RS_ROWS - 1) / (4 * VIORB_RS_ROWS), n), block(64, 4);
         VIORB_LAUNCH(k_resize, grid, block, 0, st, g, fs, l, ex->dXofs.p, ex->dXalpha.p, ex->dYofs.p, ex->dYbeta.p);
     }
     if (tm) CU(cudaEventRecord(ex->evX[1], st));
@@ -333,7 +336,7 @@ int run_pipeline(viorb_extractor* ex, int n, int lap0, int lap1) {
     VIORB_LAUNCH(k_emit, dim3(n), dim3(256), 0, st, g, ex->dKept.p, ex->dKeptCount.p, lap0, lap1, ex->dKps.p,
                  ex->dSlot2Kept.p, ex->dNOut.p, ex->dMono.p);
     if (tm) CU(cudaEventRecord(ex->evX[5], st));
-    VIORB_LAUNCH(k_blur, dim3(ex->totalBlurTiles, n), dim3(256), 0, st, g, fs, ex->blurTiles);
+    VIORB_LAUNCH(k_blur, dim3(ex->totalBlurTiles, n), dim3(64), 0, st, g, fs, ex->blurTiles);
     if (tm) CU(cudaEventRecord(ex->evX[6], st));
     VIORB_LAUNCH(k_describe, dim3((g.outCap + 7) / 8, n), dim3(256), 0, st, g, fs, ex->dKept.p, ex->dSlot2Kept.p,
                  ex->dNOut.p, ex->dDesc.p);
@@ -364,6 +367,12 @@ int ensure_match_buffers(viorb_extractor* ex) {
     CU(ex->dKnnIdx.alloc(need * 2)); CU(ex->dKnnDist.alloc(need * 2));
     CU(ex->dMatches.alloc(need));
     CU(ex->dNStereo.alloc(ex->prm.max_batch)); CU(ex->dNRatio.alloc(ex->prm.max_batch));
+    // row table of the rectified stereo matcher: a keypoint of the coarsest level spans 2*ceil(2*scale)+3 rows at most
+    const int span = 2 * (int)std::ceil(2.0f * ex->scale[ex->prm.nlevels - 1]) + 3;
+    ex->rowListCap = ex->capOut * span;
+    CU(ex->dRowStart.alloc((size_t)ex->prm.max_batch * (ex->prm.max_height + 2)));
+    CU(ex->dRowList.alloc((size_t)ex->prm.max_batch * ex->rowListCap));
+    CU(ex->dRMeta.alloc(need));
     return VIORB_OK;
 }
 
@@ -389,8 +398,11 @@ int launch_stereo(viorb_extractor* L, viorb_extractor* R, int n, float bf, float
     const int gx = (L->g.outCap + 7) / 8;
     const bool tm = L->timing;
     if (tm) CU(cudaEventRecord(L->evS[0], st));
-    VIORB_LAUNCH(k_stereo_coarse, dim3(gx, n), dim3(256), 0, st, sp, L->dKps.p, L->dDesc.p, L->dNOut.p, R->dKps.p, R->dDesc.p,
-                 R->dNOut.p, L->dBestIdx.p, L->dBestDist.p);
+    const int rows = L->g.H;
+    VIORB_LAUNCH(k_stereo_rows, dim3(n), dim3(256), sizeof(int) * 2 * (rows + 1), st, sp, rows, L->rowListCap, R->dKps.p, R->dNOut.p,
+                 L->dRowStart.p, L->dRowList.p, L->dRMeta.p, L->dStatus.p);
+    VIORB_LAUNCH(k_stereo_coarse, dim3(gx, n), dim3(256), 0, st, sp, rows, L->rowListCap, L->dKps.p, L->dDesc.p, L->dNOut.p,
+                 R->dDesc.p, L->dRowStart.p, L->dRowList.p, L->dRMeta.p, L->dBestIdx.p, L->dBestDist.p);
     if (tm) CU(cudaEventRecord(L->evS[1], st));
     VIORB_LAUNCH(k_stereo_refine, dim3(gx, n), dim3(256), 0, st, sp, L->g, L->src, R->src, L->dKps.p, L->dNOut.p, R->dKps.p,
                  L->dBestIdx.p, L->dBestDist.p, L->dURight.p, L->dDepth.p, L->dSad.p);
@@ -501,7 +513,7 @@ void viorb_extractor_destroy(viorb_extractor* ex) {
     ex->dXalpha.release(); ex->dYbeta.release(); ex->dKept.release(); ex->dKps.release(); ex->dCells.release();
     ex->dBestIdx.release(); ex->dBestDist.release(); ex->dSad.release(); ex->dKnnIdx.release(); ex->dKnnDist.release();
     ex->dLrMatch.release(); ex->dURight.release(); ex->dDepth.release(); ex->dNStereo.release(); ex->dNRatio.release();
-    ex->dMatches.release();
+    ex->dMatches.release(); ex->dRowStart.release(); ex->dRowList.release(); ex->dRMeta.release();
     ex->hIn.release(); ex->hDesc.release(); ex->hKps.release(); ex->hCounts.release();
     for (int i = 0; i < 8; ++i) if (ex->evX[i]) cudaEventDestroy(ex->evX[i]);
     for (int i = 0; i < 6; ++i) if (ex->evS[i]) cudaEventDestroy(ex->evS[i]);
