@@ -59,10 +59,11 @@ __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int 
     const int4 alr = __ldg(reinterpret_cast<const int4*>(xalpha + L.xTab + x4));
     const int o0[4] = {sx.x, sx.y, sx.z, sx.w};
     const int ar[4] = {alr.x, alr.y, alr.z, alr.w};
-    int o1[4], a0[4], a1[4];
+    // the host tables never point at the last source column (it is expressed as (w-2, weight 0|2048)),
+    // so column o0 + 1 is always inside the row
+    int a0[4], a1[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        o1[i] = min(o0[i] + 1, S.w - 1);
         a0[i] = (short)(ar[i] & 0xFFFF);
         a1[i] = ar[i] >> 16;
     }
@@ -78,12 +79,12 @@ __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int 
         } else {
             const uint8_t* r0 = src + (size_t)sy0 * sp;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) h0[i] = r0[o0[i]] * a0[i] + r0[o1[i]] * a1[i];
+            for (int i = 0; i < 4; ++i) { const uint8_t* q = r0 + o0[i]; h0[i] = q[0] * a0[i] + q[1] * a1[i]; }
         }
         {
             const uint8_t* r1 = src + (size_t)sy1 * sp;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) h1[i] = r1[o0[i]] * a0[i] + r1[o1[i]] * a1[i];
+            for (int i = 0; i < 4; ++i) { const uint8_t* q = r1 + o0[i]; h1[i] = q[0] * a0[i] + q[1] * a1[i]; }
             have = sy1;
         }
         uint32_t packed = 0;
@@ -136,7 +137,7 @@ __host__ __device__ inline int fast_tile_pitch(int tileW) { return (((tileW + 6)
 __host__ __device__ inline int fast_score_pitch(int tileW) { return (tileW - 4 + 3) & ~3; }             // region + ring
 __host__ __device__ inline size_t fast_smem_bytes(int tileW, int tileH) {
     return (size_t)tileH * fast_tile_pitch(tileW) + (size_t)(tileH - 4) * fast_score_pitch(tileW) +
-           (size_t)2 * (tileW - 6) * (tileH - 6) + 16;
+           (size_t)3 * (tileW - 6) * (tileH - 6) + 32;      // queue (2 B / px) + survivors (4 B per 2x2 block)
 }
 
 // bytes 0,1 (resp. 2,3) of w zero-extended into the two 16-bit lanes
@@ -168,23 +169,25 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
     const int l = c.level;
     int pitch;
     const uint8_t* img = level_ptr(g, fs, l, f, pitch);
-    const int rw = c.x1 - c.x0, rh = c.y1 - c.y0, npx = rw * rh;
+    const int rw = c.x1 - c.x0, rh = c.y1 - c.y0;
     const int TP = fast_tile_pitch(g.tileW), TPW = TP >> 2;
     const int SP = fast_score_pitch(g.tileW);
     uint8_t* T = smem;
     uint8_t* S = T + g.tileH * TP;
     uint16_t* Q = reinterpret_cast<uint16_t*>(S + (g.tileH - 4) * SP);
-    uint32_t* surv = reinterpret_cast<uint32_t*>(Q);
+    uint32_t* surv = reinterpret_cast<uint32_t*>(S + (g.tileH - 4) * SP + ((2 * (g.tileW - 6) * (g.tileH - 6) + 15) & ~15));
     if (tid == 0) { qCount = 0; sCount = 0; hasIni = 0; }
 
     // phase 0: tile column 0 <-> image x = ax (4-byte aligned, one pad word left of the halo)
     const int ox = c.x0 - 3, oy = c.y0 - 3;
     const int ax = (ox & ~3) - 4, shift = ox - ax;          // shift in [4,7]
     const int nW = ((shift + rw + 9) >> 2) + 1, nR = rh + 6;
-    for (int i = tid; i < nW * nR; i += VIORB_FAST_THREADS) {
-        const int r = i / nW, k = i - r * nW;
-        reinterpret_cast<uint32_t*>(T + r * TP)[k] =
-            __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)(oy + r) * pitch + ax) + k);
+    {
+        const int tx = tid & 15, ty = tid >> 4;              // 16 words x 8 rows per pass, no divisions
+        const uint8_t* src = img + (size_t)oy * pitch + ax;
+        for (int r = ty; r < nR; r += VIORB_FAST_THREADS / 16)
+            for (int k = tx; k < nW; k += 16)
+                reinterpret_cast<uint32_t*>(T + r * TP)[k] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)r * pitch) + k);
     }
     for (int i = tid; i < (((rh + 2) * SP) >> 2); i += VIORB_FAST_THREADS) reinterpret_cast<uint32_t*>(S)[i] = 0;
     __syncthreads();
@@ -264,29 +267,31 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
     }
     __syncthreads();
 
-    // phase C: strict 3x3 NMS; whole score words that are zero are skipped
+    // phase C: strict 3x3 NMS, run densely over the queue (only queued pixels can hold a score)
     {
-        const int SPW = SP >> 2;
-        const unsigned winv = (1u << 20) / (unsigned)SPW + 1;
-        const int total = SPW * rh;
-        for (int i = tid; i < total; i += VIORB_FAST_THREADS) {
-            const int py = (int)(((unsigned)i * winv) >> 20), wx = i - py * SPW;
-            const unsigned w = reinterpret_cast<const uint32_t*>(S + (py + 1) * SP)[wx];
-            if (w == 0) continue;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int v = (w >> (8 * j)) & 0xFF;
-                const int px = wx * 4 + j - 1;
-                if (v && px >= 0 && px < rw) {
-                    const uint8_t* s = S + (py + 1) * SP + px + 1;
-                    const bool keep = v > s[-1] && v > s[1] && v > s[-SP - 1] && v > s[-SP] && v > s[-SP + 1] &&
-                                      v > s[SP - 1] && v > s[SP] && v > s[SP + 1];
-                    if (keep) {
-                        const int k = atomicAdd(&sCount, 1);
-                        surv[k] = (uint32_t)(c.x0 + px - VIORB_MINB) | ((uint32_t)(c.y0 + py - VIORB_MINB) << 12) | ((uint32_t)v << 24);
-                        if (v >= g.iniTh) hasIni = 1;
-                    }
-                }
+        const int nq = qCount;
+        for (int base = 0; base < nq; base += VIORB_FAST_THREADS) {
+            const int i = base + tid;
+            bool keep = false;
+            uint32_t e = 0;
+            if (i < nq) {
+                const int p = Q[i];
+                const int py = (int)(((unsigned)p * inv) >> 20), px = p - py * rw;
+                const uint8_t* s = S + (py + 1) * SP + px + 1;
+                const int v = s[0];
+                const int m = __vimax3_s32(__vimax3_s32(s[-SP - 1], s[-SP], s[-SP + 1]), __vimax3_s32(s[SP - 1], s[SP], s[SP + 1]),
+                                           max((int)s[-1], (int)s[1]));
+                keep = v > m;                 // v == 0 (not a corner) can never be kept
+                e = (uint32_t)(c.x0 + px - VIORB_MINB) | ((uint32_t)(c.y0 + py - VIORB_MINB) << 12) | ((uint32_t)v << 24);
+                if (keep && v >= g.iniTh) hasIni = 1;
+            }
+            const unsigned mk = __ballot_sync(0xffffffffu, keep);
+            if (mk) {
+                const int leader = __ffs(mk) - 1;
+                int sb = 0;
+                if (lane == leader) sb = atomicAdd(&sCount, __popc(mk));
+                sb = __shfl_sync(0xffffffffu, sb, leader);
+                if (keep) surv[sb + __popc(mk & ((1u << lane) - 1))] = e;
             }
         }
     }
@@ -807,6 +812,22 @@ __global__ void __launch_bounds__(64) k_blur(ExtractGeom g, FrameSrc fs, BlurTil
         if (interior) {
             const uint32_t* p = reinterpret_cast<const uint32_t*>(row + x0);
             w0 = __ldg(p - 1); w1 = __ldg(p); w2 = __ldg(p + 1);
+        } else if (L.w >= 8) {
+            // border strips: whole words where they start inside the row, mirrored columns patched in
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(row + x0);
+            unsigned w[3];
+            w[1] = __ldg(p);
+            w[0] = x0 >= 4 ? __ldg(p - 1) : __byte_perm(w[1], 0, 0x1230);      // columns -3..-1 mirror 3..1
+            w[2] = x0 + 8 <= pitch ? __ldg(p + 1) : 0u;
+#pragma unroll
+            for (int b = 5; b < 11; ++b) {
+                const int col = x0 - 4 + b;
+                if (col >= L.w) {
+                    const unsigned v = row[2 * (L.w - 1) - col];
+                    w[b >> 2] = (w[b >> 2] & ~(0xFFu << (8 * (b & 3)))) | (v << (8 * (b & 3)));
+                }
+            }
+            w0 = w[0]; w1 = w[1]; w2 = w[2];
         } else {
             unsigned w[3] = {0, 0, 0};
 #pragma unroll

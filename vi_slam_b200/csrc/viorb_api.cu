@@ -160,8 +160,12 @@ void build_resize_tables(int sw, int sh, int dw, int dh, ResizeTabs& t) {
         fx -= sx;
         if (sx < 0) { fx = 0; sx = 0; }
         if (sx >= sw - 1) { fx = 0; sx = sw - 1; }
+        short a0 = sat_short((1.f - fx) * 2048), a1 = sat_short(fx * 2048);
+        // k_resize reads columns sx and sx+1 unconditionally: express "last column, weight 2048|0" as
+        // "(last-1), weight 0|2048" (same value, both columns inside the row)
+        if (sx == sw - 1 && sw >= 2) { sx = sw - 2; a1 = a0; a0 = 0; }
         t.xofs.push_back(sx);
-        t.xalpha.push_back(make_short2(sat_short((1.f - fx) * 2048), sat_short(fx * 2048)));
+        t.xalpha.push_back(make_short2(a0, a1));
     }
     while (t.xofs.size() % 4) { t.xofs.push_back(0); t.xalpha.push_back(make_short2(0, 0)); }   // int4 loads in k_resize
     for (int dy = 0; dy < dh; ++dy) {
