@@ -100,7 +100,9 @@ __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int 
 }
 
 // ---------------------------------------------------------------------------------------------
-// FAST-9 + cell-local 3x3 NMS + per-cell ini/min threshold.  One CTA = one cell of one frame.
+// FAST-9 + cell-local 3x3 NMS + per-cell ini/min threshold.  One CTA = one strip (up to
+// VIORB_FAST_STRIP_CELLS consecutive cells of one cell row) of one frame: per-CTA fixed costs and the
+// five barriers are amortised over ~8k pixels, and rows are loaded as long coalesced runs.
 //   phase 0  stage the cell region + 3-px halo in shared memory with aligned 32-bit loads
 //   phase A  opposite-pair pre-test per pixel -> warp-ballot compaction into a queue
 //   phase B  dense corner score (cornerScore<16>) on the queue -> 8-bit score tile
@@ -108,9 +110,9 @@ __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int 
 //   phase D  keep score >= iniTh if any survivor reaches it, else all (>= minTh); append to the
 //            (frame, level) candidate list with one global atomic per warp
 // Candidate word: x | y << 12 | score << 24, x/y relative to the 16-px border (as vToDistributeKeys).
-// grid (totalCells, B), block 128.
+// grid (totalStrips, B), block 256.
 // ---------------------------------------------------------------------------------------------
-#define VIORB_FAST_THREADS 128
+#define VIORB_FAST_THREADS 256
 
 __device__ __forceinline__ int fast_score16(const uint8_t* p, const int* o) {
     const int v = p[0];
@@ -162,45 +164,49 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
                                                              uint32_t* __restrict__ cand, int* __restrict__ candCount,
                                                              int* __restrict__ status) {
     VIORB_DYN_SMEM(smem);
-    __shared__ int qCount, sCount, hasIni;
+    __shared__ int qCount, sCount;
+    __shared__ int hasIni[32];                               // per cell of the strip
     const int tid = threadIdx.x, lane = tid & 31;
     const int f = blockIdx.y;
     const CellDesc c = cells[blockIdx.x];
     const int l = c.level;
+    const LevelGeom& L = g.lv[l];
     int pitch;
     const uint8_t* img = level_ptr(g, fs, l, f, pitch);
-    const int rw = c.x1 - c.x0, rh = c.y1 - c.y0;
+    const int rw = c.x1 - c.x0, rh = c.y1 - c.y0, wCell = L.wCell, ncell = c.ncell;
     const int TP = fast_tile_pitch(g.tileW), TPW = TP >> 2;
     const int SP = fast_score_pitch(g.tileW);
     uint8_t* T = smem;
     uint8_t* S = T + g.tileH * TP;
-    uint16_t* Q = reinterpret_cast<uint16_t*>(S + (g.tileH - 4) * SP);
+    uint16_t* Q = reinterpret_cast<uint16_t*>(S + (g.tileH - 4) * SP);          // entries: py << 9 | px
     uint32_t* surv = reinterpret_cast<uint32_t*>(S + (g.tileH - 4) * SP + ((2 * (g.tileW - 6) * (g.tileH - 6) + 15) & ~15));
-    if (tid == 0) { qCount = 0; sCount = 0; hasIni = 0; }
+    if (tid == 0) { qCount = 0; sCount = 0; }
+    if (tid < 32) hasIni[tid] = 0;
 
     // phase 0: tile column 0 <-> image x = ax (4-byte aligned, one pad word left of the halo)
     const int ox = c.x0 - 3, oy = c.y0 - 3;
     const int ax = (ox & ~3) - 4, shift = ox - ax;          // shift in [4,7]
     const int nW = ((shift + rw + 9) >> 2) + 1, nR = rh + 6;
     {
-        const int tx = tid & 15, ty = tid >> 4;              // 16 words x 8 rows per pass, no divisions
+        const int tx = tid & 63, ty = tid >> 6;              // 64 words x 4 rows per pass, no divisions
         const uint8_t* src = img + (size_t)oy * pitch + ax;
-        for (int r = ty; r < nR; r += VIORB_FAST_THREADS / 16)
-            for (int k = tx; k < nW; k += 16)
-                reinterpret_cast<uint32_t*>(T + r * TP)[k] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)r * pitch) + k);
+        for (int r = ty; r < nR; r += VIORB_FAST_THREADS / 64) {
+            const uint32_t* srow = reinterpret_cast<const uint32_t*>(src + (size_t)r * pitch);
+            uint32_t* trow = reinterpret_cast<uint32_t*>(T + r * TP);
+            for (int k = tx; k < nW; k += 64) trow[k] = __ldg(srow + k);
+        }
     }
     for (int i = tid; i < (((rh + 2) * SP) >> 2); i += VIORB_FAST_THREADS) reinterpret_cast<uint32_t*>(S)[i] = 0;
     __syncthreads();
 
     const int th = g.minTh;
-    const unsigned inv = (1u << 20) / (unsigned)rw + 1;     // p / rw == (p * inv) >> 20 for p < 16384
     const int col0 = shift + 3;                             // tile column of region pixel 0
     const uint8_t* T0 = T + 3 * TP + col0;                  // region pixel (0,0)
 
     // phase A: 4 horizontally adjacent pixels (one aligned tile word) per thread, packed 16x2 pre-test
     {
         const int g0 = col0 >> 2, g1 = (col0 + rw - 1) >> 2, ng = g1 - g0 + 1;
-        const unsigned ginv = (1u << 20) / (unsigned)ng + 1;
+        const unsigned ginv = (1u << 20) / (unsigned)ng + 1;                     // i / ng for i < 16384
         const unsigned thp = (unsigned)th | ((unsigned)th << 16);
         const unsigned nthp1 = ((0x10000u - (unsigned)(th + 1)) & 0xFFFFu) * 0x10001u;     // -(th+1) in both lanes
         const int total = ng * rh;
@@ -244,69 +250,77 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
                 int qb = 0;
                 if (lane == 31) qb = atomicAdd(&qCount, tot);
                 qb = __shfl_sync(0xffffffffu, qb, 31) + inc - cnt;
-                const int p0 = py * rw + gx * 4 - col0;
+                const int e0 = (py << 9) + (gx * 4 - col0);       // valid pixels have px0 + j >= 0
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
-                    if (pass >> j & 1) Q[qb++] = (uint16_t)(p0 + j);
+                    if (pass >> j & 1) Q[qb++] = (uint16_t)(e0 + j);
             }
         }
     }
     __syncthreads();
+    const int nq = qCount;
 
     // phase B: dense corner score on the queue
     {
         const int o[16] = {3 * TP, 3 * TP + 1, 2 * TP + 2, TP + 3, 3, -TP + 3, -2 * TP + 2, -3 * TP + 1,
                            -3 * TP, -3 * TP - 1, -2 * TP - 2, -TP - 3, -3, TP - 3, 2 * TP - 2, 3 * TP - 1};
-        const int nq = qCount;
         for (int i = tid; i < nq; i += VIORB_FAST_THREADS) {
-            const int p = Q[i];
-            const int py = (int)(((unsigned)p * inv) >> 20), px = p - py * rw;
+            const int e = Q[i];
+            const int py = e >> 9, px = e & 511;
             const int sc = fast_score16(T0 + py * TP + px, o);
             if (sc >= th) S[(py + 1) * SP + px + 1] = (uint8_t)sc;
         }
     }
     __syncthreads();
 
-    // phase C: strict 3x3 NMS, run densely over the queue (only queued pixels can hold a score)
-    {
-        const int nq = qCount;
-        for (int base = 0; base < nq; base += VIORB_FAST_THREADS) {
-            const int i = base + tid;
-            bool keep = false;
-            uint32_t e = 0;
-            if (i < nq) {
-                const int p = Q[i];
-                const int py = (int)(((unsigned)p * inv) >> 20), px = p - py * rw;
-                const uint8_t* s = S + (py + 1) * SP + px + 1;
-                const int v = s[0];
-                const int m = __vimax3_s32(__vimax3_s32(s[-SP - 1], s[-SP], s[-SP + 1]), __vimax3_s32(s[SP - 1], s[SP], s[SP + 1]),
-                                           max((int)s[-1], (int)s[1]));
-                keep = v > m;                 // v == 0 (not a corner) can never be kept
-                e = (uint32_t)(c.x0 + px - VIORB_MINB) | ((uint32_t)(c.y0 + py - VIORB_MINB) << 12) | ((uint32_t)v << 24);
-                if (keep && v >= g.iniTh) hasIni = 1;
-            }
-            const unsigned mk = __ballot_sync(0xffffffffu, keep);
-            if (mk) {
-                const int leader = __ffs(mk) - 1;
-                int sb = 0;
-                if (lane == leader) sb = atomicAdd(&sCount, __popc(mk));
-                sb = __shfl_sync(0xffffffffu, sb, leader);
-                if (keep) surv[sb + __popc(mk & ((1u << lane) - 1))] = e;
-            }
+    // phase C: strict 3x3 NMS run densely over the queue (only queued pixels can hold a score).  Neighbours in
+    // another cell do not count (cv::FAST ran per cell): rows outside the strip are the zero ring of S, columns
+    // across a cell boundary are masked here.
+    const unsigned cinv = (1u << 20) / (unsigned)wCell + 1;                       // px / wCell for px < 16384
+    for (int base = 0; base < nq; base += VIORB_FAST_THREADS) {
+        const int i = base + tid;
+        bool keep = false;
+        uint32_t e = 0;
+        if (i < nq) {
+            const int q = Q[i];
+            const int py = q >> 9, px = q & 511;
+            const int cell = min((int)(((unsigned)px * cinv) >> 20), ncell - 1);
+            const int cl = px - cell * wCell;
+            const bool hasL = cl > 0, hasR = cl < wCell - 1;      // the strip's own ends fall on the zero ring
+            const uint8_t* s = S + (py + 1) * SP + px + 1;
+            const int v = s[0];
+            const int mc = max((int)s[-SP], (int)s[SP]);
+            const int ml = hasL ? __vimax3_s32(s[-SP - 1], s[-1], s[SP - 1]) : 0;
+            const int mr = hasR ? __vimax3_s32(s[-SP + 1], s[1], s[SP + 1]) : 0;
+            keep = v > __vimax3_s32(mc, ml, mr);                  // v == 0 (not a corner) is never kept
+            e = (uint32_t)(c.x0 + px - VIORB_MINB) | ((uint32_t)(c.y0 + py - VIORB_MINB) << 12) | ((uint32_t)v << 24);
+            if (keep && v >= g.iniTh) hasIni[cell] = 1;
+        }
+        const unsigned mk = __ballot_sync(0xffffffffu, keep);
+        if (mk) {
+            const int leader = __ffs(mk) - 1;
+            int sb = 0;
+            if (lane == leader) sb = atomicAdd(&sCount, __popc(mk));
+            sb = __shfl_sync(0xffffffffu, sb, leader);
+            if (keep) surv[sb + __popc(mk & ((1u << lane) - 1))] = e;
         }
     }
     __syncthreads();
 
-    // phase D
-    const int ns = sCount, needIni = hasIni ? g.iniTh : 0;
-    const LevelGeom& L = g.lv[l];
+    // phase D: per cell keep score >= iniTh if any survivor of that cell reaches it, else all of them
+    const int ns = sCount;
     uint32_t* out = cand + (size_t)f * g.candPerFrame + L.candOff;
     int* cnt = candCount + f * g.nlevels + l;
     for (int base = 0; base < ns; base += VIORB_FAST_THREADS) {
         const int i = base + tid;
         uint32_t e = 0;
         bool keep = false;
-        if (i < ns) { e = surv[i]; keep = (int)(e >> 24) >= needIni; }
+        if (i < ns) {
+            e = surv[i];
+            const int px = (int)(e & 0xFFF) + VIORB_MINB - c.x0;
+            const int cell = min((int)(((unsigned)px * cinv) >> 20), ncell - 1);
+            keep = (int)(e >> 24) >= (hasIni[cell] ? g.iniTh : 0);
+        }
         const unsigned m = __ballot_sync(0xffffffffu, keep);
         if (m) {
             const int leader = __ffs(m) - 1;

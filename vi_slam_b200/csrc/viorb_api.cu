@@ -222,19 +222,30 @@ int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
                 float maxY = iniY + L.hCell + 6;
                 if (iniY >= L.maxBY - 3) continue;
                 if (maxY > L.maxBY) maxY = (float)L.maxBY;
+                const int y0 = (int)iniY + 3, y1 = (int)maxY - 3;
+                if (y1 <= y0) continue;                            // ROI lower than 7: cv::FAST finds nothing
+                // the cells of this row: [x0_j, x1_j), all wCell wide except possibly the last
+                std::vector<std::pair<int, int>> row;
                 for (int j = 0; j < L.nCols; ++j) {
                     const float iniX = (float)(VIORB_MINB + j * L.wCell);
                     float maxX = iniX + L.wCell + 6;
                     if (iniX >= L.maxBX - 6) continue;
                     if (maxX > L.maxBX) maxX = (float)L.maxBX;
-                    CellDesc c;
-                    c.level = (short)l; c.pad = 0;
-                    c.x0 = (short)((int)iniX + 3); c.x1 = (short)((int)maxX - 3);
-                    c.y0 = (short)((int)iniY + 3); c.y1 = (short)((int)maxY - 3);
-                    if (c.x1 <= c.x0 || c.y1 <= c.y0) continue;    // ROI narrower than 7: cv::FAST finds nothing
-                    ex->cells.push_back(c);
+                    const int x0 = (int)iniX + 3, x1 = (int)maxX - 3;
+                    if (x1 <= x0) continue;
+                    row.push_back({x0, x1});
                     L.lastCol = std::max(L.lastCol, j);
                     L.lastRow = std::max(L.lastRow, i);
+                }
+                // k_fast works on strips of consecutive cells of one cell row
+                const int per = std::max(1, std::min(VIORB_FAST_STRIP_CELLS, 500 / L.wCell));
+                for (size_t j0 = 0; j0 < row.size(); j0 += per) {
+                    const size_t j1 = std::min(row.size(), j0 + per);
+                    CellDesc c;
+                    c.level = (short)l; c.ncell = (short)(j1 - j0);
+                    c.x0 = (short)row[j0].first; c.x1 = (short)row[j1 - 1].second;
+                    c.y0 = (short)y0; c.y1 = (short)y1;
+                    ex->cells.push_back(c);
                     maxRW = std::max(maxRW, c.x1 - c.x0);
                     maxRH = std::max(maxRH, c.y1 - c.y0);
                 }
@@ -276,7 +287,7 @@ int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
     ex->fastSmem = fast_smem_bytes(g.tileW, g.tileH);
     ex->octSmem = octree_smem_bytes(maxNodes);
     if (ex->octSmem > 220 * 1024) return fail(VIORB_E_ARG, "nfeatures too large for the quadtree's shared memory");
-    if (maxRW * maxRH >= 16384) return fail(VIORB_E_ARG, "FAST cell larger than supported");
+    if (maxRW > 511 || maxRH > 127) return fail(VIORB_E_ARG, "FAST cell larger than supported");
     return VIORB_OK;
 }
 

@@ -52,10 +52,13 @@ struct ExtractGeom {
     LevelGeom lv[VIORB_MAX_LEVELS];
 };
 
-// One FAST cell: the pixels [x0,x1) x [y0,y1) of level `level` on which cv::FAST would evaluate the
-// corner test for this cell's ROI (ROI inset by 3), fextractor.cpp:780-806.
+// One FAST strip: `ncell` consecutive cells of one cell row of level `level`.  [x0,x1) x [y0,y1) are the
+// pixels on which cv::FAST would evaluate the corner test for those cells' ROIs (each ROI inset by 3),
+// fextractor.cpp:780-806; cell k of the strip covers x0 + k*wCell .. x0 + (k+1)*wCell (the last one may
+// be narrower).
+#define VIORB_FAST_STRIP_CELLS 8
 struct CellDesc {
-    short level, pad;
+    short level, ncell;
     short x0, y0, x1, y1;
 };
 
