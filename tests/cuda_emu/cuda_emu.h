@@ -422,4 +422,7 @@ static inline int __sad(int a, int b, unsigned c) { return (int)(c + (unsigned)s
 using std::max;
 using std::min;
 
+static inline void __pipeline_memcpy_async(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
+static inline void __pipeline_commit() {}
+static inline void __pipeline_wait_prior(int) {}
 #define EMU_DYN_SMEM_PTR ((void*)cuda_emu::C().dyn_smem)

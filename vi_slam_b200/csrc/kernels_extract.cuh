@@ -135,7 +135,7 @@ __device__ __forceinline__ int fast_score16(const uint8_t* p, const int* o) {
 }
 
 // shared-memory layout of one k_fast CTA (all sizes from ExtractGeom::tileW/tileH = max region + 6)
-__host__ __device__ inline int fast_tile_pitch(int tileW) { return (((tileW + 6) >> 2) << 2) + 8; }   // bytes, incl. pad words
+__host__ __device__ inline int fast_tile_pitch(int tileW) { return ((tileW + 19 + 8 + 15) >> 4) << 4; }   // bytes: alignment shift + region + halo + pad word, whole 16-byte chunks
 __host__ __device__ inline int fast_score_pitch(int tileW) { return (tileW - 4 + 3) & ~3; }             // region + ring
 __host__ __device__ inline size_t fast_smem_bytes(int tileW, int tileH) {
     return (size_t)tileH * fast_tile_pitch(tileW) + (size_t)(tileH - 4) * fast_score_pitch(tileW) +
@@ -183,20 +183,32 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
     if (tid == 0) { qCount = 0; sCount = 0; }
     if (tid < 32) hasIni[tid] = 0;
 
-    // phase 0: tile column 0 <-> image x = ax (4-byte aligned, one pad word left of the halo)
+    // phase 0: tile column 0 <-> image x = ax (16-byte aligned, at least one pad word left of the halo).
+    // Rows are copied global -> shared with 16-byte cp.async (LDGSTS): every thread has all its chunks in
+    // flight at once instead of a load -> store dependency per word.
     const int ox = c.x0 - 3, oy = c.y0 - 3;
-    const int ax = (ox & ~3) - 4, shift = ox - ax;          // shift in [4,7]
-    const int nW = ((shift + rw + 9) >> 2) + 1, nR = rh + 6;
+    const int ax = ((ox & ~3) - 4) & ~15, shift = ox - ax;  // shift in [4,19]
+    const int nB = ((((shift + 3 + rw + 2) >> 2) + 2) << 2); // bytes per row incl. the word right of the halo
+    const int nC = (nB + 15) >> 4, nR = rh + 6;
     {
-        const int tx = tid & 63, ty = tid >> 6;              // 64 words x 4 rows per pass, no divisions
+        const int tx = tid & 31, ty = tid >> 5;              // 32 chunks x 8 rows per pass, no divisions
         const uint8_t* src = img + (size_t)oy * pitch + ax;
-        for (int r = ty; r < nR; r += VIORB_FAST_THREADS / 64) {
-            const uint32_t* srow = reinterpret_cast<const uint32_t*>(src + (size_t)r * pitch);
-            uint32_t* trow = reinterpret_cast<uint32_t*>(T + r * TP);
-            for (int k = tx; k < nW; k += 64) trow[k] = __ldg(srow + k);
+        for (int r = ty; r < nR; r += VIORB_FAST_THREADS / 32) {
+            const uint8_t* srow = src + (size_t)r * pitch;
+            uint8_t* trow = T + r * TP;
+            for (int k = tx; k < nC; k += 32) {
+                if (ax + 16 * k + 16 <= pitch) {
+                    __pipeline_memcpy_async(trow + 16 * k, srow + 16 * k, 16);
+                } else {                                     // never read past the end of an image row
+                    for (int j = 0; j < 4; ++j)
+                        if (ax + 16 * k + 4 * j + 4 <= pitch) __pipeline_memcpy_async(trow + 16 * k + 4 * j, srow + 16 * k + 4 * j, 4);
+                }
+            }
         }
+        __pipeline_commit();
     }
     for (int i = tid; i < (((rh + 2) * SP) >> 2); i += VIORB_FAST_THREADS) reinterpret_cast<uint32_t*>(S)[i] = 0;
+    __pipeline_wait_prior(0);
     __syncthreads();
 
     const int th = g.minTh;

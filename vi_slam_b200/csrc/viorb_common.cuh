@@ -9,6 +9,7 @@
 #define VIORB_DYN_SMEM(name) unsigned char* name = (unsigned char*)EMU_DYN_SMEM_PTR
 #else
 #include <cuda_runtime.h>
+#include <cuda_pipeline.h>
 #define VIORB_LAUNCH(kernel, grid, block, smem, stream, ...) \
     kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
 #define VIORB_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
