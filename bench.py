@@ -225,21 +225,29 @@ def run_ours(args, rank, world, local_rank):
     e2e = None
     if not args.no_e2e:
         del exl, exr
-        hl = [left[i, :, :W] for i in range(B)]
-        hr = [right[i, :, :W] for i in range(B)]
+        from vi_slam_b200 import pinned_empty
+        # the step's inputs sit in page-locked host memory (as a capture driver would deliver them) and are
+        # copied host -> device inside every timed step; every result is copied device -> host
+        pl, pr = pinned_empty(left.shape, np.uint8), pinned_empty(right.shape, np.uint8)
+        pl[:], pr[:] = left, right
+        hl = [pl[i, :, :W] for i in range(B)]
+        hr = [pr[i, :, :W] for i in range(B)]
         el = FExtractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, max_size=(W, H), max_batch=B, device=local_rank)
         er = FExtractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, max_size=(W, H), max_batch=B, device=local_rank)
+        outs = [el.alloc_outputs(B), er.alloc_outputs(B)]
         out = [None, None]
-        buf = None
+        cap = el.capacity
+        buf = {"u_right": pinned_empty((B, cap), np.float32), "depth": pinned_empty((B, cap), np.float32),
+               "lr_match": pinned_empty((B, cap), np.int32), "n_left": np.zeros(B, np.int32),
+               "n_stereo": np.zeros(B, np.int32), "n_ratio": np.zeros(B, np.int32)}
 
         def e2e_step():
-            nonlocal buf
-            th = [threading.Thread(target=lambda i=i, e=e, im=im: out.__setitem__(i, e.compute_batch(im, (0, 0))))
+            th = [threading.Thread(target=lambda i=i, e=e, im=im: out.__setitem__(i, e.compute_batch(im, (0, 0), out=outs[i])))
                   for i, (e, im) in enumerate(((el, hl), (er, hr)))]
             [t.start() for t in th]
             [t.join() for t in th]
             matcher.stereo_batch(el, er, B, BF, B_BASELINE, 0.7)
-            buf = matcher.stereo_fetch_all(el, B, buf)
+            matcher.stereo_fetch_all(el, B, buf)
 
         for _ in range(max(1, min(Wm, 2))):
             e2e_step()
@@ -255,8 +263,7 @@ def run_ours(args, rank, world, local_rank):
             t = torch.tensor([dt], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
-        cap = el.capacity
-        h2d = 2 * B * 1280 * H
+        h2d = 2 * B * W * H
         d2h = 2 * B * (el._lib.viorb_extractor_capacity(el._h) - 64) * 60 + 2 * B * 8 + B * cap * 12 + 3 * B * 4
         e2e = {"value": world * B * Ke / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                "ms_per_step": 1e3 * dt / Ke}

@@ -76,6 +76,11 @@ int viorb_extractor_tables(const viorb_extractor* ex, int32_t* nlevels, float* s
 /* Upper bound of keypoints one frame can produce (sum over levels of N_l + slack). */
 int viorb_extractor_capacity(const viorb_extractor* ex);
 
+/* Page-locked host memory.  Images and result buffers that live in memory from viorb_host_alloc (or any
+ * cudaHostRegister'ed block) are DMA'd directly; pageable buffers go through the handle's staging area. */
+void* viorb_host_alloc(size_t bytes);
+void viorb_host_free(void* p);
+
 /* FExtractor::compute (fextractor.cpp:1034-1133) for one host image (CV_8UC1, row step `step`).
  * lap0/lap1 = vLappingArea.  Writes up to `cap` keypoints/descriptors (row i of desc belongs to
  * keypoint i), *n_out = keypoint count, *mono_index_out = compute()'s return value.

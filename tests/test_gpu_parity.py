@@ -200,3 +200,23 @@ def test_stereo_golden(golden_dir):
         assert np.array_equal(np.stack([m["query_idx"], m["train_idx"], m["distance"]], 1), g["ratio_matches"])
     else:
         assert int((dp > 0).sum()) > 0.95 * int((g["depth"] > 0).sum())
+
+
+def test_pinned_buffers_take_the_direct_dma_path():
+    """Images and result buffers in viorb_host_alloc memory give the same rows as pageable ones."""
+    from vi_slam_b200 import FExtractor, pinned_empty
+    syn = _syn()
+    n, w, h = 4, 1241, 376
+    frames = [syn.make_frame(4000 + i, w, h) for i in range(n)]
+    ex = FExtractor(2000, max_size=(w, h), max_batch=n)
+    mono, kps, desc = ex.compute_batch(frames, (0, 0))
+    pin = pinned_empty((n, h, 1280), np.uint8)
+    for i in range(n):
+        pin[i, :, :w] = frames[i]
+    out = ex.alloc_outputs(n, pinned=True)
+    mono2, kps2, desc2 = ex.compute_batch([pin[i, :, :w] for i in range(n)], (0, 0), out=out)
+    for i in range(n):
+        assert mono[i] == mono2[i] and np.array_equal(kps[i], kps2[i]) and np.array_equal(desc[i], desc2[i])
+    # non-contiguous pinned frames (every other slot)
+    mono3, kps3, desc3 = ex.compute_batch([pin[i, :, :w] for i in (0, 2)], (0, 0))
+    assert np.array_equal(kps3[1], kps[2]) and np.array_equal(desc3[0], desc[0])

@@ -32,6 +32,8 @@ SYMBOLS = {
     "viorb_extractor_destroy": (None, [C.c_void_p]),
     "viorb_extractor_tables": (C.c_int, [C.c_void_p, i32p, f32p, f32p, f32p, f32p, i32p]),
     "viorb_extractor_capacity": (C.c_int, [C.c_void_p]),
+    "viorb_host_alloc": (C.c_void_p, [C.c_size_t]),
+    "viorb_host_free": (None, [C.c_void_p]),
     "viorb_extractor_stream": (C.c_void_p, [C.c_void_p]),
     "viorb_extractor_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "viorb_extractor_sync": (C.c_int, [C.c_void_p]),

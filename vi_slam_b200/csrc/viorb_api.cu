@@ -391,6 +391,17 @@ int ensure_match_buffers(viorb_extractor* ex) {
     return VIORB_OK;
 }
 
+bool is_pinned(const void* p) {
+#ifdef VIORB_EMU
+    (void)p;
+    return false;
+#else
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+#endif
+}
+
 bool same_geometry(const viorb_extractor* a, const viorb_extractor* b) {
     return a->g.W == b->g.W && a->g.H == b->g.H && a->g.nlevels == b->g.nlevels && a->g.outCap == b->g.outCap &&
            a->prm.scale_factor == b->prm.scale_factor && a->g.W > 0;
@@ -553,6 +564,15 @@ int viorb_extractor_tables(const viorb_extractor* ex, int32_t* nlevels, float* s
 
 int viorb_extractor_capacity(const viorb_extractor* ex) { return ex ? ex->capOut : 0; }
 
+/* Page-locked host memory for images / results (what a camera driver or a caller that wants zero staging
+ * copies should hand to viorb_extract*).  Thin wrappers over cudaMallocHost / cudaFreeHost. */
+void* viorb_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { fail(VIORB_E_CUDA, "cudaMallocHost failed"); return nullptr; }
+    return p;
+}
+void viorb_host_free(void* p) { if (p) cudaFreeHost(p); }
+
 void* viorb_extractor_stream(viorb_extractor* ex) { return ex ? (void*)ex->stream : nullptr; }
 
 /* Run this handle's work on a caller-owned stream (e.g. the framework's current stream). */
@@ -632,19 +652,44 @@ int viorb_extract_batch(viorb_extractor* ex, const uint8_t* const* imgs, int n, 
     CU(cudaSetDevice(ex->prm.device));
     const int pitch = ex->inPitch;
     const size_t fstride = (size_t)pitch * height;
-    for (int i = 0; i < n; ++i) {
+    for (int i = 0; i < n; ++i)
         if (!imgs[i]) return fail(VIORB_E_EMPTY, "empty image");
-        for (int y = 0; y < height; ++y)
-            std::memcpy(ex->hIn.p + i * fstride + (size_t)y * pitch, imgs[i] + (size_t)y * step, width);
+    // Page-locked inputs (viorb_host_alloc / cudaHostRegister'ed camera buffers) are DMA'd straight from
+    // the caller's memory; pageable inputs are first packed into the handle's pinned staging area.
+    bool pinnedIn = true;
+    for (int i = 0; i < n && pinnedIn; i += std::max(1, n - 1)) pinnedIn = is_pinned(imgs[i]) && is_pinned(imgs[i] + (size_t)(height - 1) * step);
+    if (pinnedIn) {
+        bool contiguous = true;
+        for (int i = 1; i < n && contiguous; ++i) contiguous = imgs[i] == imgs[i - 1] + (size_t)step * height;
+        if (contiguous) {
+            CU(cudaMemcpy2DAsync(ex->dIn.p, pitch, imgs[0], step, width, (size_t)height * n, cudaMemcpyHostToDevice, ex->stream));
+        } else {
+            for (int i = 0; i < n; ++i)
+                CU(cudaMemcpy2DAsync(ex->dIn.p + i * fstride, pitch, imgs[i], step, width, height, cudaMemcpyHostToDevice, ex->stream));
+        }
+    } else {
+        for (int i = 0; i < n; ++i)
+            for (int y = 0; y < height; ++y)
+                std::memcpy(ex->hIn.p + i * fstride + (size_t)y * pitch, imgs[i] + (size_t)y * step, width);
+        CU(cudaMemcpyAsync(ex->dIn.p, ex->hIn.p, fstride * n, cudaMemcpyHostToDevice, ex->stream));
     }
-    CU(cudaMemcpyAsync(ex->dIn.p, ex->hIn.p, fstride * n, cudaMemcpyHostToDevice, ex->stream));
     int rc = viorb_extract_device(ex, ex->dIn.p, n, width, height, pitch, fstride, lap0, lap1);
     if (rc) return rc;
     const size_t oc = ex->g.outCap;
     CU(cudaMemcpyAsync(ex->hCounts.p, ex->dNOut.p, sizeof(int) * n, cudaMemcpyDeviceToHost, ex->stream));
     CU(cudaMemcpyAsync(ex->hCounts.p + n, ex->dMono.p, sizeof(int) * n, cudaMemcpyDeviceToHost, ex->stream));
-    CU(cudaMemcpyAsync(ex->hKps.p, ex->dKps.p, sizeof(viorb_keypoint) * oc * n, cudaMemcpyDeviceToHost, ex->stream));
-    CU(cudaMemcpyAsync(ex->hDesc.p, ex->dDesc.p, 32 * oc * n, cudaMemcpyDeviceToHost, ex->stream));
+    const size_t rowKp = std::min<size_t>(oc, cap);
+    const bool pinnedKps = kps && is_pinned(kps) && is_pinned(kps + (size_t)n * cap - 1);
+    const bool pinnedDesc = desc && is_pinned(desc) && is_pinned(desc + (size_t)n * cap * 32 - 1);
+    if (pinnedKps)
+        CU(cudaMemcpy2DAsync(kps, sizeof(viorb_keypoint) * cap, ex->dKps.p, sizeof(viorb_keypoint) * oc, sizeof(viorb_keypoint) * rowKp, n,
+                             cudaMemcpyDeviceToHost, ex->stream));
+    else if (kps)
+        CU(cudaMemcpyAsync(ex->hKps.p, ex->dKps.p, sizeof(viorb_keypoint) * oc * n, cudaMemcpyDeviceToHost, ex->stream));
+    if (pinnedDesc)
+        CU(cudaMemcpy2DAsync(desc, (size_t)32 * cap, ex->dDesc.p, 32 * oc, 32 * rowKp, n, cudaMemcpyDeviceToHost, ex->stream));
+    else if (desc)
+        CU(cudaMemcpyAsync(ex->hDesc.p, ex->dDesc.p, 32 * oc * n, cudaMemcpyDeviceToHost, ex->stream));
     rc = check_status(ex);          // synchronises the stream
     if (rc) return rc;
     int worst = VIORB_OK;
@@ -654,8 +699,8 @@ int viorb_extract_batch(viorb_extractor* ex, const uint8_t* const* imgs, int n, 
         if (mono_index_out) mono_index_out[i] = ex->hCounts.p[n + i];
         const int m = std::min(cnt, cap);
         if (cnt > cap) worst = VIORB_E_CAPACITY;
-        if (kps && m > 0) std::memcpy(kps + (size_t)i * cap, ex->hKps.p + i * oc, sizeof(viorb_keypoint) * m);
-        if (desc && m > 0) std::memcpy(desc + (size_t)i * cap * 32, ex->hDesc.p + i * oc * 32, (size_t)32 * m);
+        if (kps && !pinnedKps && m > 0) std::memcpy(kps + (size_t)i * cap, ex->hKps.p + i * oc, sizeof(viorb_keypoint) * m);
+        if (desc && !pinnedDesc && m > 0) std::memcpy(desc + (size_t)i * cap * 32, ex->hDesc.p + i * oc * 32, (size_t)32 * m);
     }
     if (worst) return fail(worst, "output buffer smaller than the number of keypoints (n_out holds the count)");
     return VIORB_OK;

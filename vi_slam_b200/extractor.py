@@ -25,6 +25,26 @@ class ViorbError(RuntimeError):
         self.code = code
 
 
+def pinned_empty(shape, dtype, lib_path=None):
+    """numpy array in page-locked host memory (viorb_host_alloc): images / result buffers placed here are
+    DMA'd by the library without a staging copy.  The memory is released when the array is collected."""
+    lib = _lib.load(lib_path)
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape)) * dtype.itemsize
+    ptr = lib.viorb_host_alloc(max(n, 1))
+    if not ptr:
+        raise ViorbError(-3, lib.viorb_last_error().decode())
+    buf = (C.c_uint8 * max(n, 1)).from_address(ptr)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    _PINNED[arr.__array_interface__["data"][0]] = (lib, ptr)
+    import weakref
+    weakref.finalize(buf, lib.viorb_host_free, ptr)
+    return arr
+
+
+_PINNED = {}
+
+
 def _check(lib, rc):
     if rc != 0:
         raise ViorbError(rc, lib.viorb_last_error().decode())
@@ -94,7 +114,16 @@ class FExtractor:
         mono, kps, desc = self.compute_batch([image], vLappingArea)
         return mono[0], kps[0], desc[0]
 
-    def compute_batch(self, images, vLappingArea=(0, 0)):
+    def alloc_outputs(self, n, pinned=True):
+        """Reusable result buffers for ``compute_batch(..., out=...)``."""
+        cap = self.capacity
+        mk = (lambda sh, dt: pinned_empty(sh, dt)) if pinned else (lambda sh, dt: np.zeros(sh, dt))
+        return {"kps": mk((n, cap), KP_DTYPE), "desc": mk((n, cap, 32), np.uint8), "count": np.zeros(n, np.int32),
+                "mono": np.zeros(n, np.int32)}
+
+    def compute_batch(self, images, vLappingArea=(0, 0), out=None):
+        """Batch form of ``compute``.  With ``out`` (from ``alloc_outputs``) results are written in place and the
+        return value holds views (rows beyond count[i] are undefined) instead of fresh copies."""
         n = len(images)
         h, w = images[0].shape
         step = images[0].strides[0]
@@ -109,14 +138,20 @@ class FExtractor:
             keep.append(im)
             ptrs[i] = im.ctypes.data
         cap = self.capacity
-        kps = np.zeros((n, cap), KP_DTYPE)
-        desc = np.zeros((n, cap, 32), np.uint8)
-        cnt = np.zeros(n, np.int32)
-        mono = np.zeros(n, np.int32)
+        if out is None:
+            kps = np.zeros((n, cap), KP_DTYPE)
+            desc = np.zeros((n, cap, 32), np.uint8)
+            cnt = np.zeros(n, np.int32)
+            mono = np.zeros(n, np.int32)
+        else:
+            kps, desc, cnt, mono = out["kps"], out["desc"], out["count"], out["mono"]
+            assert kps.shape[0] >= n and kps.shape[1] == cap
         _check(self._lib, self._lib.viorb_extract_batch(
             self._h, ptrs, n, w, h, step, int(vLappingArea[0]), int(vLappingArea[1]), kps.ctypes.data,
             desc.ctypes.data, cap, cnt.ctypes.data_as(_lib.i32p), mono.ctypes.data_as(_lib.i32p)))
         self._last_n = n
+        if out is not None:
+            return mono[:n], [kps[i, :cnt[i]] for i in range(n)], [desc[i, :cnt[i]] for i in range(n)]
         return ([int(m) for m in mono], [kps[i, :cnt[i]].copy() for i in range(n)],
                 [desc[i, :cnt[i]].copy() for i in range(n)])
 
