@@ -62,28 +62,67 @@ public:
     FExtractor& operator=(const FExtractor&) = delete;
 
     // fextractor.cpp:1034-1133.  `mask` is ignored like in the reference.  Returns monoIndex, -1 on an empty image.
+#ifdef VIORB_WITH_OPENCV
+    int compute(cv::InputArray _image, cv::InputArray /*mask*/, std::vector<cv::KeyPoint>& keypoints,
+                cv::OutputArray _descriptors, std::vector<int>& vLappingArea) {
+        if (_image.empty()) return -1;
+        cv::Mat image = _image.getMat();
+        CV_Assert(image.type() == CV_8UC1);                       // fextractor.cpp:1041
+        int n = 0;
+        const int mono = run(image.data, image.cols, image.rows, (int)image.step, vLappingArea, keypoints, n);
+        if (n == 0) _descriptors.release();
+        else {
+            _descriptors.create(n, 32, CV_8U);
+            cv::Mat d = _descriptors.getMat();
+            for (int i = 0; i < n; ++i) std::memcpy(d.ptr(i), &desc_[(size_t)i * 32], 32);
+        }
+        fill_pyramid();
+        return mono;
+    }
+#else
     int compute(const viorb_cv::Mat& image, const viorb_cv::Mat& /*mask*/, std::vector<viorb_cv::KeyPoint>& keypoints,
                 viorb_cv::Mat& descriptors, std::vector<int>& vLappingArea) {
         if (image.empty()) return -1;
-        kp_.resize(cap_); desc_.resize((size_t)cap_ * 32);
-        int n = 0, mono = -1;
-        int rc = viorb_extract(h_, image.data, image.cols, image.rows, (int)image.step, vLappingArea[0], vLappingArea[1],
-                               kp_.data(), desc_.data(), cap_, &n, &mono);
-        if (rc == VIORB_E_EMPTY) return -1;
-        if (rc != VIORB_OK) throw std::runtime_error(viorb_last_error());
-        keypoints.resize(n);
-        static_assert(sizeof(viorb_cv::KeyPoint) == 28, "");
-        if (n) std::memcpy((void*)keypoints.data(), kp_.data(), sizeof(viorb_keypoint) * (size_t)n);
+        int n = 0;
+        const int mono = run(image.data, image.cols, image.rows, (int)image.step, vLappingArea, keypoints, n);
         if (n == 0) descriptors.release();
         else {
-#ifdef VIORB_WITH_OPENCV
-            descriptors.create(n, 32, CV_8U);
-#else
             descriptors.create(n, 32);
-#endif
-            for (int i = 0; i < n; ++i) std::memcpy(descriptors.data + (size_t)i * descriptors.step, &desc_[(size_t)i * 32], 32);
+            std::memcpy(descriptors.data, desc_.data(), (size_t)n * 32);
         }
-        // mvImagePyramid stays valid until the next compute (read by Frame::ComputeStereoMatches, frame.cpp:830,920,937)
+        fill_pyramid();
+        return mono;
+    }
+#endif
+
+    int GetLevels() { return nlevels_; }
+    float GetScaleFactor() { return scaleFactor_; }
+    std::vector<float> GetScaleFactors() { return mvScaleFactor; }
+    std::vector<float> GetInverseScaleFactors() { return mvInvScaleFactor; }
+    std::vector<float> GetScaleSigmaSquares() { return mvLevelSigma2; }
+    std::vector<float> GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
+    viorb_extractor* handle() { return h_; }
+    // When ComputeStereoMatches is rerouted to viorb_stereo_match nothing on the host reads mvImagePyramid:
+    // switch the per-frame device->host copy of the 8 levels off.
+    void SetPyramidReadback(bool on) { readback_ = on; }
+
+    std::vector<viorb_cv::Mat> mvImagePyramid;
+
+protected:
+    int run(const uint8_t* data, int cols, int rows, int step, const std::vector<int>& lap,
+            std::vector<viorb_cv::KeyPoint>& keypoints, int& n) {
+        kp_.resize(cap_); desc_.resize((size_t)cap_ * 32);
+        int mono = -1;
+        const int rc = viorb_extract(h_, data, cols, rows, step, lap.at(0), lap.at(1), kp_.data(), desc_.data(), cap_, &n, &mono);
+        if (rc == VIORB_E_EMPTY) { n = 0; keypoints.clear(); return -1; }
+        if (rc != VIORB_OK) throw std::runtime_error(viorb_last_error());
+        keypoints.resize(n);
+        if (n) std::memcpy((void*)keypoints.data(), kp_.data(), sizeof(viorb_keypoint) * (size_t)n);
+        return mono;
+    }
+    // mvImagePyramid stays valid until the next compute (read by Frame::ComputeStereoMatches, frame.cpp:830,920,937)
+    void fill_pyramid() {
+        if (!readback_) return;
         for (int l = 0; l < nlevels_; ++l) {
             int w = 0, hgt = 0;
             viorb_pyramid_level(h_, 0, l, nullptr, 0, &w, &hgt);
@@ -94,22 +133,10 @@ public:
 #endif
             viorb_pyramid_level(h_, 0, l, mvImagePyramid[l].data, (int)mvImagePyramid[l].step, &w, &hgt);
         }
-        return mono;
     }
-
-    int GetLevels() { return nlevels_; }
-    float GetScaleFactor() { return scaleFactor_; }
-    std::vector<float> GetScaleFactors() { return mvScaleFactor; }
-    std::vector<float> GetInverseScaleFactors() { return mvInvScaleFactor; }
-    std::vector<float> GetScaleSigmaSquares() { return mvLevelSigma2; }
-    std::vector<float> GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
-    viorb_extractor* handle() { return h_; }
-
-    std::vector<viorb_cv::Mat> mvImagePyramid;
-
-protected:
     viorb_extractor* h_ = nullptr;
     int nlevels_, cap_ = 0;
+    bool readback_ = true;
     float scaleFactor_;
     std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
     std::vector<viorb_keypoint> kp_;
