@@ -58,3 +58,16 @@ def test_batch_matches_single(emu):
     for i, f in enumerate(frames):
         _, _, (m1, k1, d1), _ = parity.check_extract(f, 500, (0, 0), lib_path=emu, stages=False)
         assert m1 == mono[i] and np.array_equal(k1, kps[i]) and np.array_equal(d1, desc[i])
+
+
+def test_chunked_batch(emu):
+    """More than 32 frames: viorb_extract_batch cuts the batch into chunks (frame0 offsets in every kernel)."""
+    from vi_slam_b200 import FExtractor
+    frames = [synthetic.make_frame(40 + i, 96, 80) for i in range(81)]
+    ex = FExtractor(100, 1.2, 4, 20, 7, max_size=(96, 80), max_batch=81, lib_path=emu)
+    one = FExtractor(100, 1.2, 4, 20, 7, max_size=(96, 80), max_batch=1, lib_path=emu)
+    mono, kps, desc = ex.compute_batch(frames, (0, 0))
+    for i, f in enumerate(frames):
+        m1, k1, d1 = one.compute(f, None, (0, 0))
+        assert m1 == mono[i] and np.array_equal(k1, kps[i]) and np.array_equal(d1, desc[i])
+    assert sum(len(k) for k in kps) > 300

@@ -117,6 +117,25 @@ def test_batch_and_device_resident_paths():
         assert np.array_equal(ex.pyramid_level(0, i), frames[i])
 
 
+def test_chunked_host_batch_matches_single_frames():
+    """viorb_extract_batch pipelines a large host batch in chunks (H2D / kernels / D2H overlapped): every
+    frame must equal the single-frame result, for pageable and for page-locked buffers, ragged last chunk."""
+    from vi_slam_b200 import FExtractor, pinned_empty
+    syn = _syn()
+    n, w, h = 83, 640, 360
+    frames = [syn.make_frame(4000 + i, w, h) for i in range(n)]
+    ex = FExtractor(1000, max_size=(w, h), max_batch=n)
+    single = FExtractor(1000, max_size=(w, h))
+    want = [single.compute(f, None, (0, 0)) for f in frames]
+    pin = pinned_empty((n, h, w), np.uint8)
+    pin[:] = np.stack(frames)
+    for imgs, out in ((frames, None), ([pin[i] for i in range(n)], ex.alloc_outputs(n))):
+        for _ in range(2):
+            mono, kps, desc = ex.compute_batch(imgs, (0, 0), out=out)
+            for i in range(n):
+                assert want[i][0] == mono[i] and np.array_equal(want[i][1], kps[i]) and np.array_equal(want[i][2], desc[i])
+
+
 def test_two_handles_from_two_threads():
     """frame.cpp:107-111: left and right extractors run concurrently on two host threads."""
     from vi_slam_b200 import FExtractor

@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int 
     const LevelGeom& S = g.lv[l - 1];
     const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     const int dy0 = (blockIdx.y * blockDim.y + threadIdx.y) * VIORB_RS_ROWS;
-    const int f = blockIdx.z;
+    const int f = blockIdx.z + g.frame0;
     if (x4 >= L.w || dy0 >= L.h) return;
     int sp;
     const uint8_t* src = level_ptr(g, fs, l - 1, f, sp);
@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
     __shared__ int qCount, sCount;
     __shared__ int hasIni[32];                               // per cell of the strip
     const int tid = threadIdx.x, lane = tid & 31;
-    const int f = blockIdx.y;
+    const int f = blockIdx.y + g.frame0;
     const CellDesc c = cells[blockIdx.x];
     const int l = c.level;
     const LevelGeom& L = g.lv[l];
@@ -410,7 +410,7 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
     __shared__ int warpSums[20];
     __shared__ int sh_live, sh_nExp, sh_cut, sh_remap[64];
     const int tid = threadIdx.x, nth = VIORB_OCT_THREADS;
-    const int l = blockIdx.x, f = blockIdx.y;
+    const int l = blockIdx.x, f = blockIdx.y + g.frame0;
     const LevelGeom& L = g.lv[l];
     const int NC = g.maxNodes;
     const int n = min(candCount[f * g.nlevels + l], L.candCap);
@@ -688,7 +688,7 @@ __global__ void __launch_bounds__(256) k_orient(ExtractGeom g, FrameSrc fs, Umax
                                                 const int* __restrict__ keptCount) {
     const int lane = threadIdx.x & 31;
     const int slot = blockIdx.x * 8 + (threadIdx.x >> 5);
-    const int f = blockIdx.y;
+    const int f = blockIdx.y + g.frame0;
     if (slot >= g.keptPerFrame) return;
     int l = -1;
     for (int i = 0; i < g.nlevels; ++i) {
@@ -741,7 +741,7 @@ __global__ void __launch_bounds__(256) k_emit(ExtractGeom g, const KeptKp* __res
     __shared__ int warpCnt[8];
     __shared__ int sh_mono, sh_lap;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int f = blockIdx.x;
+    const int f = blockIdx.x + g.frame0;
     int total = 0;
     for (int l = 0; l < g.nlevels; ++l) total += keptCount[f * g.nlevels + l];
     if (tid == 0) { sh_mono = 0; sh_lap = 0; }
@@ -816,7 +816,7 @@ __device__ __forceinline__ void blur_row4(unsigned w0, unsigned w1, unsigned w2,
 // 32-bit store.  Strips touching the left/right image border take a byte-wise reflect-101 path.
 // grid (totalBlurTiles, B), block 64.
 __global__ void __launch_bounds__(64) k_blur(ExtractGeom g, FrameSrc fs, BlurTiles bt) {
-    const int f = blockIdx.y;
+    const int f = blockIdx.y + g.frame0;
     int l = 0;
     while (l + 1 < g.nlevels && (int)blockIdx.x >= bt.base[l + 1]) ++l;
     const LevelGeom& L = g.lv[l];
@@ -905,7 +905,7 @@ __global__ void __launch_bounds__(256) k_describe(ExtractGeom g, FrameSrc fs, co
     __syncthreads();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int slot = blockIdx.x * 8 + wid;
-    const int f = blockIdx.y;
+    const int f = blockIdx.y + g.frame0;
     if (slot >= nOut[f]) return;
     const KeptKp k = kept[(size_t)f * g.keptPerFrame + slot2kept[(size_t)f * g.outCap + slot]];
     const int l = k.score >> 16;

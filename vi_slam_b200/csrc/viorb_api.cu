@@ -15,6 +15,8 @@
 #include "kernels_extract.cuh"
 #include "kernels_match.cuh"
 
+#define VIORB_MAX_CHUNKS 8
+
 namespace {
 
 thread_local std::string g_err;
@@ -78,6 +80,11 @@ struct viorb_extractor {
     // device state
     cudaStream_t stream = nullptr;
     bool ownStream = false;
+    // host-batch pipelining (viorb_extract_batch): images go up on cpStream and results come down on outStream
+    // chunk by chunk while the kernels of the neighbouring chunks run on `stream`
+    cudaStream_t cpStream = nullptr, outStream = nullptr;
+    cudaEvent_t evIn[VIORB_MAX_CHUNKS] = {}, evDone[VIORB_MAX_CHUNKS] = {}, evEntry = nullptr;
+    cudaEvent_t evJoin = nullptr;     // orders this handle's stream against a partner handle's (stereo)
     DevBuf<uint8_t> dIn, dPyr, dBlur, dDesc;
     DevBuf<uint32_t> dCand;
     DevBuf<uint16_t> dKeyNode;
@@ -315,6 +322,9 @@ int set_size(viorb_extractor* ex, int W, int H) {
         ex->g.W = ex->g.H = 0;
         return fail(VIORB_E_CAPACITY, "image size exceeds the arenas sized at create time");
     }
+    // per-frame stride of the keypoint / descriptor / match arrays = the handle's capacity, whatever the image
+    // size: host buffers of viorb_extractor_capacity() rows then have the device layout (linear DMA)
+    ex->g.outCap = ex->capOut;
     rc = upload_geometry(ex, tabs);
     if (rc) { ex->g.W = ex->g.H = 0; return rc; }
 #ifndef VIORB_EMU
@@ -325,11 +335,13 @@ int set_size(viorb_extractor* ex, int W, int H) {
 }
 
 // ---- the extraction pipeline on n frames already on the device ------------------------------
-int run_pipeline(viorb_extractor* ex, int n, int lap0, int lap1) {
-    const ExtractGeom& g = ex->g;
+// Frames [f0, f0 + n) of the current batch (ex->src); the kernels add g.frame0 to their frame index.
+int run_pipeline(viorb_extractor* ex, int f0, int n, int lap0, int lap1) {
+    ExtractGeom g = ex->g;
+    g.frame0 = f0;
     const FrameSrc& fs = ex->src;
     cudaStream_t st = ex->stream;
-    CU(cudaMemsetAsync(ex->dCandCount.p, 0, sizeof(int) * (size_t)n * g.nlevels, st));
+    CU(cudaMemsetAsync(ex->dCandCount.p + (size_t)f0 * g.nlevels, 0, sizeof(int) * (size_t)n * g.nlevels, st));
     const bool tm = ex->timing;
     if (tm) CU(cudaEventRecord(ex->evX[0], st));
     for (int l = 1; l < g.nlevels; ++l) {
@@ -357,7 +369,7 @@ int run_pipeline(viorb_extractor* ex, int n, int lap0, int lap1) {
                  ex->dNOut.p, ex->dDesc.p);
     if (tm) { CU(cudaEventRecord(ex->evX[7], st)); ex->haveX = true; }
     CU(cudaGetLastError());
-    ex->lastN = n;
+    ex->lastN = f0 + n;
     return VIORB_OK;
 }
 
@@ -440,9 +452,19 @@ int launch_stereo(viorb_extractor* L, viorb_extractor* R, int n, float bf, float
     return VIORB_OK;
 }
 
-// both handles must be quiescent w.r.t. each other: wait for the right handle's stream
+// Work queued on L's stream from here on sees everything queued on R's stream so far (device-side
+// ordering, the host does not wait) ...
 int join_streams(viorb_extractor* L, viorb_extractor* R) {
-    if (L->stream != R->stream) CU(cudaStreamSynchronize(R->stream));
+    if (L->stream == R->stream) return VIORB_OK;
+    CU(cudaEventRecord(R->evJoin, R->stream));
+    CU(cudaStreamWaitEvent(L->stream, R->evJoin, 0));
+    return VIORB_OK;
+}
+// ... and R's next work (its next extract overwrites the arenas the matcher reads) waits for what L queued.
+int release_partner(viorb_extractor* L, viorb_extractor* R) {
+    if (L->stream == R->stream) return VIORB_OK;
+    CU(cudaEventRecord(L->evJoin, L->stream));
+    CU(cudaStreamWaitEvent(R->stream, L->evJoin, 0));
     return VIORB_OK;
 }
 
@@ -516,6 +538,14 @@ int viorb_extractor_create(const viorb_params* params, viorb_extractor** out) {
     ok(ex->hKps.alloc(B * ex->capOut));
     ok(ex->hDesc.alloc(B * ex->capOut * 32));
     ok(ex->hCounts.alloc(B * 2 + 8));
+    ok(cudaStreamCreateWithFlags(&ex->cpStream, cudaStreamNonBlocking));
+    ok(cudaStreamCreateWithFlags(&ex->outStream, cudaStreamNonBlocking));
+    for (int i = 0; i < VIORB_MAX_CHUNKS; ++i) {
+        ok(cudaEventCreateWithFlags(&ex->evIn[i], cudaEventDisableTiming));
+        ok(cudaEventCreateWithFlags(&ex->evDone[i], cudaEventDisableTiming));
+    }
+    ok(cudaEventCreateWithFlags(&ex->evEntry, cudaEventDisableTiming));
+    ok(cudaEventCreateWithFlags(&ex->evJoin, cudaEventDisableTiming));
     for (int i = 0; i < 8; ++i) ok(cudaEventCreate(&ex->evX[i]));
     for (int i = 0; i < 6; ++i) ok(cudaEventCreate(&ex->evS[i]));
     if (e == cudaSuccess) e = cudaMemset(ex->dStatus.p, 0, sizeof(int));
@@ -543,6 +573,14 @@ void viorb_extractor_destroy(viorb_extractor* ex) {
     ex->hIn.release(); ex->hDesc.release(); ex->hKps.release(); ex->hCounts.release();
     for (int i = 0; i < 8; ++i) if (ex->evX[i]) cudaEventDestroy(ex->evX[i]);
     for (int i = 0; i < 6; ++i) if (ex->evS[i]) cudaEventDestroy(ex->evS[i]);
+    for (int i = 0; i < VIORB_MAX_CHUNKS; ++i) {
+        if (ex->evIn[i]) cudaEventDestroy(ex->evIn[i]);
+        if (ex->evDone[i]) cudaEventDestroy(ex->evDone[i]);
+    }
+    if (ex->evEntry) cudaEventDestroy(ex->evEntry);
+    if (ex->evJoin) cudaEventDestroy(ex->evJoin);
+    if (ex->cpStream) { cudaStreamSynchronize(ex->cpStream); cudaStreamDestroy(ex->cpStream); }
+    if (ex->outStream) { cudaStreamSynchronize(ex->outStream); cudaStreamDestroy(ex->outStream); }
     if (ex->ownStream && ex->stream) cudaStreamDestroy(ex->stream);
     delete ex;
 }
@@ -635,7 +673,7 @@ int viorb_extract_device(viorb_extractor* ex, const uint8_t* d_imgs, int n, int 
     ex->src.l0Stride = frame_stride;
     ex->src.pyr = ex->dPyr.p;
     ex->src.blur = ex->dBlur.p;
-    return run_pipeline(ex, n, lap0, lap1);
+    return run_pipeline(ex, 0, n, lap0, lap1);
 }
 
 int viorb_extract_batch(viorb_extractor* ex, const uint8_t* const* imgs, int n, int width, int height, int step, int lap0,
@@ -654,43 +692,79 @@ int viorb_extract_batch(viorb_extractor* ex, const uint8_t* const* imgs, int n, 
     const size_t fstride = (size_t)pitch * height;
     for (int i = 0; i < n; ++i)
         if (!imgs[i]) return fail(VIORB_E_EMPTY, "empty image");
+    int rc = set_size(ex, width, height);
+    if (rc) return rc;
+    ex->src.l0 = ex->dIn.p;
+    ex->src.l0Pitch = pitch;
+    ex->src.l0Stride = fstride;
+    ex->src.pyr = ex->dPyr.p;
+    ex->src.blur = ex->dBlur.p;
     // Page-locked inputs (viorb_host_alloc / cudaHostRegister'ed camera buffers) are DMA'd straight from
     // the caller's memory; pageable inputs are first packed into the handle's pinned staging area.
     bool pinnedIn = true;
     for (int i = 0; i < n && pinnedIn; i += std::max(1, n - 1)) pinnedIn = is_pinned(imgs[i]) && is_pinned(imgs[i] + (size_t)(height - 1) * step);
-    if (pinnedIn) {
-        bool contiguous = true;
-        for (int i = 1; i < n && contiguous; ++i) contiguous = imgs[i] == imgs[i - 1] + (size_t)step * height;
-        if (contiguous) {
-            CU(cudaMemcpy2DAsync(ex->dIn.p, pitch, imgs[0], step, width, (size_t)height * n, cudaMemcpyHostToDevice, ex->stream));
-        } else {
-            for (int i = 0; i < n; ++i)
-                CU(cudaMemcpy2DAsync(ex->dIn.p + i * fstride, pitch, imgs[i], step, width, height, cudaMemcpyHostToDevice, ex->stream));
-        }
-    } else {
-        for (int i = 0; i < n; ++i)
-            for (int y = 0; y < height; ++y)
-                std::memcpy(ex->hIn.p + i * fstride + (size_t)y * pitch, imgs[i] + (size_t)y * step, width);
-        CU(cudaMemcpyAsync(ex->dIn.p, ex->hIn.p, fstride * n, cudaMemcpyHostToDevice, ex->stream));
-    }
-    int rc = viorb_extract_device(ex, ex->dIn.p, n, width, height, pitch, fstride, lap0, lap1);
-    if (rc) return rc;
     const size_t oc = ex->g.outCap;
-    CU(cudaMemcpyAsync(ex->hCounts.p, ex->dNOut.p, sizeof(int) * n, cudaMemcpyDeviceToHost, ex->stream));
-    CU(cudaMemcpyAsync(ex->hCounts.p + n, ex->dMono.p, sizeof(int) * n, cudaMemcpyDeviceToHost, ex->stream));
     const size_t rowKp = std::min<size_t>(oc, cap);
     const bool pinnedKps = kps && is_pinned(kps) && is_pinned(kps + (size_t)n * cap - 1);
     const bool pinnedDesc = desc && is_pinned(desc) && is_pinned(desc + (size_t)n * cap * 32 - 1);
-    if (pinnedKps)
-        CU(cudaMemcpy2DAsync(kps, sizeof(viorb_keypoint) * cap, ex->dKps.p, sizeof(viorb_keypoint) * oc, sizeof(viorb_keypoint) * rowKp, n,
-                             cudaMemcpyDeviceToHost, ex->stream));
-    else if (kps)
-        CU(cudaMemcpyAsync(ex->hKps.p, ex->dKps.p, sizeof(viorb_keypoint) * oc * n, cudaMemcpyDeviceToHost, ex->stream));
-    if (pinnedDesc)
-        CU(cudaMemcpy2DAsync(desc, (size_t)32 * cap, ex->dDesc.p, 32 * oc, 32 * rowKp, n, cudaMemcpyDeviceToHost, ex->stream));
-    else if (desc)
-        CU(cudaMemcpyAsync(ex->hDesc.p, ex->dDesc.p, 32 * oc * n, cudaMemcpyDeviceToHost, ex->stream));
-    rc = check_status(ex);          // synchronises the stream
+    // The batch is cut into chunks: while the kernels of chunk c run on the handle's stream, the images of
+    // chunk c+1 travel host -> device on cpStream and the results of chunk c-1 device -> host on outStream
+    // (the three engines of the PCIe / copy path work concurrently).  With stage timing on, one chunk.
+    int nChunks = ex->timing ? 1 : std::min(VIORB_MAX_CHUNKS, std::max(1, n / 40));
+    if (const char* e = std::getenv("VIORB_CHUNKS")) nChunks = std::min(VIORB_MAX_CHUNKS, std::max(1, std::atoi(e)));   // tuning knob
+    nChunks = std::min(nChunks, n);
+    const int per = (n + nChunks - 1) / nChunks;
+    nChunks = (n + per - 1) / per;
+    CU(cudaEventRecord(ex->evEntry, ex->stream));              // earlier work on the handle may still read the arenas
+    CU(cudaStreamWaitEvent(ex->cpStream, ex->evEntry, 0));
+    CU(cudaStreamWaitEvent(ex->outStream, ex->evEntry, 0));
+    for (int c = 0; c < nChunks; ++c) {
+        const int f0 = c * per, m = std::min(per, n - f0);
+        if (pinnedIn) {
+            bool contiguous = true;
+            for (int i = f0 + 1; i < f0 + m && contiguous; ++i) contiguous = imgs[i] == imgs[i - 1] + (size_t)step * height;
+            if (contiguous && step == pitch) {
+                // same row stride on both sides: one linear DMA (the bytes between width and step of a row belong
+                // to the caller's rows; the copy stops after the last pixel of the last row)
+                CU(cudaMemcpyAsync(ex->dIn.p + f0 * fstride, imgs[f0], ((size_t)height * m - 1) * step + width, cudaMemcpyHostToDevice, ex->cpStream));
+            } else if (contiguous) {
+                CU(cudaMemcpy2DAsync(ex->dIn.p + f0 * fstride, pitch, imgs[f0], step, width, (size_t)height * m, cudaMemcpyHostToDevice, ex->cpStream));
+            } else {
+                for (int i = f0; i < f0 + m; ++i)
+                    CU(cudaMemcpy2DAsync(ex->dIn.p + i * fstride, pitch, imgs[i], step, width, height, cudaMemcpyHostToDevice, ex->cpStream));
+            }
+        } else {
+            for (int i = f0; i < f0 + m; ++i)
+                for (int y = 0; y < height; ++y)
+                    std::memcpy(ex->hIn.p + i * fstride + (size_t)y * pitch, imgs[i] + (size_t)y * step, width);
+            CU(cudaMemcpyAsync(ex->dIn.p + f0 * fstride, ex->hIn.p + f0 * fstride, fstride * m, cudaMemcpyHostToDevice, ex->cpStream));
+        }
+        CU(cudaEventRecord(ex->evIn[c], ex->cpStream));
+        CU(cudaStreamWaitEvent(ex->stream, ex->evIn[c], 0));
+        rc = run_pipeline(ex, f0, m, lap0, lap1);
+        if (rc) return rc;
+        CU(cudaEventRecord(ex->evDone[c], ex->stream));
+        CU(cudaStreamWaitEvent(ex->outStream, ex->evDone[c], 0));
+        cudaStream_t os = ex->outStream;
+        if (pinnedKps && (size_t)cap == oc)
+            CU(cudaMemcpyAsync(kps + (size_t)f0 * cap, ex->dKps.p + f0 * oc, sizeof(viorb_keypoint) * oc * m, cudaMemcpyDeviceToHost, os));
+        else if (pinnedKps)
+            CU(cudaMemcpy2DAsync(kps + (size_t)f0 * cap, sizeof(viorb_keypoint) * cap, ex->dKps.p + f0 * oc, sizeof(viorb_keypoint) * oc,
+                                 sizeof(viorb_keypoint) * rowKp, m, cudaMemcpyDeviceToHost, os));
+        else if (kps)
+            CU(cudaMemcpyAsync(ex->hKps.p + f0 * oc, ex->dKps.p + f0 * oc, sizeof(viorb_keypoint) * oc * m, cudaMemcpyDeviceToHost, os));
+        if (pinnedDesc && (size_t)cap == oc)
+            CU(cudaMemcpyAsync(desc + (size_t)f0 * cap * 32, ex->dDesc.p + f0 * oc * 32, 32 * oc * m, cudaMemcpyDeviceToHost, os));
+        else if (pinnedDesc)
+            CU(cudaMemcpy2DAsync(desc + (size_t)f0 * cap * 32, (size_t)32 * cap, ex->dDesc.p + f0 * oc * 32, 32 * oc, 32 * rowKp, m,
+                                 cudaMemcpyDeviceToHost, os));
+        else if (desc)
+            CU(cudaMemcpyAsync(ex->hDesc.p + f0 * oc * 32, ex->dDesc.p + f0 * oc * 32, 32 * oc * m, cudaMemcpyDeviceToHost, os));
+    }
+    CU(cudaMemcpyAsync(ex->hCounts.p, ex->dNOut.p, sizeof(int) * n, cudaMemcpyDeviceToHost, ex->outStream));
+    CU(cudaMemcpyAsync(ex->hCounts.p + n, ex->dMono.p, sizeof(int) * n, cudaMemcpyDeviceToHost, ex->outStream));
+    CU(cudaStreamSynchronize(ex->outStream));
+    rc = check_status(ex);          // synchronises the handle's stream
     if (rc) return rc;
     int worst = VIORB_OK;
     for (int i = 0; i < n; ++i) {
@@ -992,7 +1066,7 @@ int viorb_stereo_batch(viorb_extractor* L, viorb_extractor* R, int n, float bf, 
                  L->dNRatio.p, L->dLrMatch.p);
     if (L->timing) { CU(cudaEventRecord(L->evS[5], L->stream)); L->haveS = true; }
     CU(cudaGetLastError());
-    return VIORB_OK;
+    return release_partner(L, R);
 }
 
 int viorb_stereo_fetch(viorb_extractor* L, int frame, float* u_right, float* depth, int32_t* lr_match, int cap, int* n_left,
@@ -1047,6 +1121,8 @@ int viorb_stereo_match(viorb_extractor* L, viorb_extractor* R, int frame, float 
     if (rc) return rc;
     // the kernels are batched over frames [0, n): run up to and including `frame`
     rc = launch_stereo(L, R, frame + 1, bf, b);
+    if (rc) return rc;
+    rc = release_partner(L, R);
     if (rc) return rc;
     int nl = 0;
     CU(cudaMemcpyAsync(&nl, L->dNOut.p + frame, sizeof(int), cudaMemcpyDeviceToHost, L->stream));

@@ -49,6 +49,7 @@ struct ExtractGeom {
     int outCap;            // per-frame output capacity (keypoints)
     int tileW, tileH;      // FAST smem tile (max cell region + 6)
     int maxNodes;          // octree node capacity in shared memory
+    int frame0;            // first frame of the batch this launch works on (chunked host batches)
     size_t arenaStride;    // bytes per frame in the pyramid and blur arenas
     LevelGeom lv[VIORB_MAX_LEVELS];
 };
