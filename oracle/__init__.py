@@ -66,6 +66,12 @@ def lib():
         L.orc_bench_frames.restype = C.c_long
         L.orc_bench_frames.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, u8p, C.c_int, C.c_int, C.c_int,
                                        C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.POINTER(C.c_long)]
+        L.orc_features_in_area.argtypes = [C.c_void_p, C.c_int, f32p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int,
+                                           i32p, C.c_int]
+        L.orc_search_for_initialization.argtypes = [C.c_void_p, u8p, C.c_int, C.c_void_p, u8p, C.c_int, f32p, f32p, C.c_int,
+                                                    C.c_float, C.c_int, i32p]
+        L.orc_search_by_projection.argtypes = [f32p, f32p, i32p, f32p, u8p, u8p, u8p, C.c_int, C.c_void_p, u8p, f32p, u8p,
+                                               C.c_int, f32p, f32p, C.c_float, C.c_float, C.c_int, C.c_int, i32p]
         _lib = L
     return _lib
 
@@ -246,3 +252,49 @@ def bench_frames(frames: np.ndarray, nfeatures=2000, scale_factor=1.2, nlevels=8
     tot = lib().orc_bench_frames(nfeatures, scale_factor, nlevels, ini_th, min_th, _u8(frames), n, w, h,
                                  int(lapping[0]), int(lapping[1]), int(stereo), bf, b, nthreads, C.byref(nm))
     return tot, nm.value
+
+
+def features_in_area(kps, bounds, x, y, r, min_level=-1, max_level=-1):
+    """Frame::GetFeaturesInArea (frame.cpp:678-744) on a grid built by AssignFeaturesToGrid (frame.cpp:386-414)."""
+    kps = np.ascontiguousarray(kps)
+    b = np.ascontiguousarray(bounds, np.float32)
+    out = np.zeros(max(len(kps), 1), np.int32)
+    n = lib().orc_features_in_area(kps.ctypes.data, len(kps), _f32(b), x, y, r, min_level, max_level, _i32(out), len(out))
+    return out[:n].copy()
+
+
+def search_for_initialization(k1, d1, k2, d2, bounds, prev_matched, window_size=100, nn_ratio=0.9, check_orientation=True):
+    """FMatcher::SearchForInitialization (fmatcher.cpp:983-1098) -> (nmatches, vnMatches12, updated vbPrevMatched)."""
+    k1, k2 = np.ascontiguousarray(k1), np.ascontiguousarray(k2)
+    d1, d2 = np.ascontiguousarray(d1, np.uint8), np.ascontiguousarray(d2, np.uint8)
+    b = np.ascontiguousarray(bounds, np.float32)
+    pm = np.ascontiguousarray(prev_matched, np.float32).copy()
+    m12 = np.full(len(k1), -1, np.int32)
+    n = lib().orc_search_for_initialization(k1.ctypes.data, _u8(d1), len(k1), k2.ctypes.data, _u8(d2), len(k2), _f32(b), _f32(pm),
+                                            int(window_size), float(nn_ratio), int(check_orientation), _i32(m12))
+    return n, m12, pm
+
+
+def search_by_projection(uv, invz, last_octave, last_angle, desc_mp, valid, observed, k2, d2, u_right2, blocked2, bounds,
+                         scale_factors, th, bf, direction=0, check_orientation=True):
+    """FMatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (fmatcher.cpp:2471-2688), single-camera branch;
+    the projection is done by the caller.  -> (nmatches, assigned[n2])."""
+    uv = np.ascontiguousarray(uv, np.float32)
+    invz = np.ascontiguousarray(invz, np.float32)
+    lo = np.ascontiguousarray(last_octave, np.int32)
+    la = np.ascontiguousarray(last_angle, np.float32)
+    dm = np.ascontiguousarray(desc_mp, np.uint8)
+    va = np.ascontiguousarray(valid, np.uint8)
+    ob = np.ascontiguousarray(observed, np.uint8)
+    k2 = np.ascontiguousarray(k2)
+    d2 = np.ascontiguousarray(d2, np.uint8)
+    ur = None if u_right2 is None else np.ascontiguousarray(u_right2, np.float32)
+    bl = None if blocked2 is None else np.ascontiguousarray(blocked2, np.uint8)
+    b = np.ascontiguousarray(bounds, np.float32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    out = np.full(len(k2), -1, np.int32)
+    n = lib().orc_search_by_projection(_f32(uv), _f32(invz), _i32(lo), _f32(la), _u8(dm), _u8(va), _u8(ob), len(lo),
+                                       k2.ctypes.data, _u8(d2), None if ur is None else _f32(ur),
+                                       None if bl is None else _u8(bl), len(k2), _f32(b), _f32(sf), float(th), float(bf),
+                                       int(direction), int(check_orientation), _i32(out))
+    return n, out

@@ -140,3 +140,32 @@ def test_dedup_by_train(oracle_mod):
     m = np.array([[0, 5, 10], [1, 3, 7], [2, 5, 4], [3, 3, 9], [4, 1, 1]], np.int32)
     out = oracle_mod.dedup_by_train(m)
     assert out.tolist() == [[4, 1, 1], [1, 3, 7], [0, 5, 10]]
+
+
+def _window_cases(golden_dir):
+    g = np.load(os.path.join(golden_dir, "window_match.npz"))
+    return g
+
+
+def test_search_for_initialization_matches_transliteration(oracle_mod, golden_dir):
+    """oracle search_for_initialization == tests/golden/ref_match.py (statement-by-statement transliteration of
+    fmatcher.cpp:983-1098 + frame.cpp:386-414,678-757)."""
+    g = _window_cases(golden_dir)
+    pm = np.stack([g["k1"]["x"], g["k1"]["y"]], 1).astype(np.float32)
+    for tag in "abc":
+        win, ratio, chk = g[f"ini_{tag}_args"]
+        n, m12, pm2 = oracle_mod.search_for_initialization(g["k1"], g["d1"], g["k2"], g["d2"], g["bounds"], pm, int(win), ratio, bool(chk))
+        assert n == int(g[f"ini_{tag}_n"])
+        assert np.array_equal(m12, g[f"ini_{tag}_m12"])
+        assert np.array_equal(pm2.view(np.uint32), g[f"ini_{tag}_pm"].view(np.uint32))
+
+
+def test_search_by_projection_matches_transliteration(oracle_mod, golden_dir):
+    g = _window_cases(golden_dir)
+    for tag in "abcd":
+        th, direction, chk, stereo = g[f"proj_{tag}_args"]
+        n, asg = oracle_mod.search_by_projection(g["uv"], g["invz"], g["k1"]["octave"], g["k1"]["angle"], g["d1"], g["valid"],
+                                                 g["observed"], g["k2"], g["d2"], g["uright2"] if stereo else None, g["blocked2"],
+                                                 g["bounds"], g["sf"], th, 386.1448, int(direction), bool(chk))
+        assert n == int(g[f"proj_{tag}_n"])
+        assert np.array_equal(asg, g[f"proj_{tag}_asg"])
