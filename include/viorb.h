@@ -173,6 +173,44 @@ int viorb_stereo_fetch_all(viorb_extractor* left, int n, float* u_right, float* 
 int viorb_match_resident(viorb_extractor* cur, int frame_q, viorb_extractor* prev, int frame_t, double ratio,
                          int rule, viorb_match* out, int cap, int* n_out);
 
+/* ---- windowed (grid) matchers: SURVEY.md section 8 row a-11 ------------------------------------ */
+
+/* Frame::mnMinX, mnMaxX, mnMinY, mnMaxY (src/datastructures/frame.cpp:133-145).  The cell-size inverses
+ * mfGridElementWidthInv / mfGridElementHeightInv are derived as 64 / (max_x - min_x), 48 / (max_y - min_y)
+ * (frame.cpp:235-236, FRAME_GRID_COLS / FRAME_GRID_ROWS of frame.h:42-43). */
+typedef struct viorb_grid_bounds { float min_x, max_x, min_y, max_y; } viorb_grid_bounds;
+
+/* Frame::AssignFeaturesToGrid + Frame::GetFeaturesInArea (frame.cpp:386-414, 678-757) for one query:
+ * indices of the keypoints inside the square of half size r around (x, y) with min_level <= octave <=
+ * max_level (the reference's "-1 = no bound" convention), in the reference's order.  Host buffers. */
+int viorb_features_in_area(const viorb_keypoint* kps, int n, const viorb_grid_bounds* bounds, float x, float y, float r,
+                           int min_level, int max_level, int32_t* out, int cap, int* n_out, int device);
+
+/* FMatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/geometry/fmatcher.cpp:983-1098)
+ * for npairs frame pairs.  Pair p: F1 = rows [p*cap1, p*cap1 + n1[p]) of kps1 (F1.ukeypoints_) / desc1, F2 likewise
+ * with cap2 / n2 (< 65536 keypoints).  prev_matched [npairs][cap1][2] is vbPrevMatched (in/out), matches12
+ * [npairs][cap1] is vnMatches12, nmatches[p] the return value.  nn_ratio = mfNNratio, check_orientation =
+ * mbCheckOrientation (FMatcher ctor).  bounds: F2's grid.  Host buffers; npairs = 1, cap = n for one pair. */
+int viorb_search_for_initialization(int npairs, int cap1, int cap2, const viorb_keypoint* kps1, const uint8_t* desc1,
+                                    const int32_t* n1, const viorb_keypoint* kps2, const uint8_t* desc2, const int32_t* n2,
+                                    const viorb_grid_bounds* bounds, float* prev_matched, int window_size, float nn_ratio,
+                                    int check_orientation, int32_t* matches12, int32_t* nmatches, int device);
+
+/* FMatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (fmatcher.cpp:2471-2688), single-camera branch
+ * (Nleft == -1).  Pose, map points and the camera model stay with the caller, which passes per LastFrame keypoint i:
+ * uv[i][2] = mpCamera->project(Rcw*x3Dw+tcw), invz[i], last_octave[i], last_angle[i] (kpLF.angle), desc_mp[i][32] =
+ * pMP->GetDescriptor(), valid[i] = map point present && !mvbOutlier && invz >= 0 && uv inside [mnMinX,mnMaxX]x[mnMinY,mnMaxY]
+ * (fmatcher.cpp:2496-2517), observed[i] = pMP->Observations() > 0.  Current frame: kps2 / desc2 / u_right2 (mvuRight, NULL
+ * for monocular) / blocked2 (mvpMapPoints[i2] && Observations() > 0; NULL = none).  direction 0: octave window
+ * nLastOctave-1..+1, 1: bForward, 2: bBackward.  assigned [npairs][cap2]: -1 untouched, -2 set to NULL by the rotation
+ * check, i >= 0: CurrentFrame.mvpMapPoints[i2] = LastFrame.mvpMapPoints[i].  nmatches[p] = return value. */
+int viorb_search_by_projection(int npairs, int cap1, int cap2, const float* uv, const float* invz, const int32_t* last_octave,
+                               const float* last_angle, const uint8_t* desc_mp, const uint8_t* valid, const uint8_t* observed,
+                               const int32_t* n1, const viorb_keypoint* kps2, const uint8_t* desc2, const float* u_right2,
+                               const uint8_t* blocked2, const int32_t* n2, const viorb_grid_bounds* bounds,
+                               const float* scale_factors, int nlevels, float th, float bf, int direction,
+                               int check_orientation, int32_t* assigned, int32_t* nmatches, int device);
+
 #ifdef __cplusplus
 }
 #endif

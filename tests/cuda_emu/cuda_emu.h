@@ -351,6 +351,13 @@ static inline int __reduce_min_sync(unsigned mask, int v) {
     return (int)s;
 }
 
+static inline unsigned __reduce_min_sync(unsigned mask, unsigned v) {
+    cuda_emu::warp_arrive(mask, (unsigned long long)v, 0);
+    auto& x = cuda_emu::my_warp(); unsigned long long s = ~0ull;
+    for (int l = 0; l < 32; ++l) if (mask >> l & 1) s = std::min(s, (unsigned long long)x.res_val[l]);
+    return (unsigned)s;
+}
+
 // ---- atomics (fibers are cooperative: plain RMW) ----
 template <class T> static inline T atomicAdd(T* p, T v) { T o = *p; *p = o + v; return o; }
 template <class T> static inline T atomicSub(T* p, T v) { T o = *p; *p = o - v; return o; }

@@ -63,6 +63,15 @@ SYMBOLS = {
     "viorb_stereo_fetch": (C.c_int, [C.c_void_p, C.c_int, f32p, f32p, i32p, C.c_int, i32p, i32p, i32p]),
     "viorb_match_resident": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_void_p,
                                        C.c_int, i32p]),
+    "viorb_features_in_area": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int,
+                                         i32p, C.c_int, i32p, C.c_int]),
+    "viorb_search_for_initialization": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, i32p, C.c_void_p,
+                                                  C.c_void_p, i32p, C.c_void_p, f32p, C.c_int, C.c_float, C.c_int, i32p,
+                                                  i32p, C.c_int]),
+    "viorb_search_by_projection": (C.c_int, [C.c_int, C.c_int, C.c_int, f32p, f32p, i32p, f32p, C.c_void_p, C.c_void_p,
+                                             C.c_void_p, i32p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, i32p,
+                                             C.c_void_p, f32p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, i32p, i32p,
+                                             C.c_int]),
 }
 
 _cache = {}

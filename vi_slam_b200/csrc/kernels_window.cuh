@@ -1,0 +1,401 @@
+// kernels_window.cuh — sm_100a kernels of the windowed (grid-accelerated) frame-to-frame matchers.
+//
+//   k_grid_build        Frame::AssignFeaturesToGrid / PosInGrid      frame.cpp:386-414, 746-757
+//   k_window_src_*      the per-keypoint search window of            fmatcher.cpp:997-1003 / :2519-2530
+//   k_window_list       Frame::GetFeaturesInArea + DescriptorDistance frame.cpp:678-744, fmatcher.cpp:2859
+//   k_resolve_ini       FMatcher::SearchForInitialization            fmatcher.cpp:983-1098
+//   k_resolve_proj      FMatcher::SearchByProjection(Cur, Last)      fmatcher.cpp:2471-2688 (Nleft == -1)
+//   (both)              FMatcher::ComputeThreeMaxima                 fmatcher.cpp:2813-2854
+//
+// The reference loops are sequential in the source keypoint: whether a candidate counts depends on what
+// earlier keypoints matched (vMatchedDistance / mvpMapPoints).  The expensive, order-independent part - the
+// window query and the Hamming distances - is done by one warp per source keypoint into a CSR candidate list
+// that keeps GetFeaturesInArea's order; the order-dependent bookkeeping then runs in ONE warp per frame pair
+// that walks the source keypoints in order with the candidate scan spread over its lanes.
+#pragma once
+#include "kernels_match.cuh"
+
+#define VIORB_GRID_COLS 64            // FRAME_GRID_COLS (frame.h:43)
+#define VIORB_GRID_ROWS 48            // FRAME_GRID_ROWS (frame.h:42)
+#define VIORB_GRID_CELLS (VIORB_GRID_COLS * VIORB_GRID_ROWS)
+#define VIORB_HISTO_LENGTH 30         // fmatcher.cpp:315
+
+struct GridBounds { float minX, maxX, minY, maxY, invW, invH; };
+
+// One search window: centre, half size, octave range (GetFeaturesInArea's minLevel / maxLevel), and for the
+// projection matcher the predicted right-image coordinate.  r < 0: this source keypoint is skipped.
+struct WinSrc {
+    float x, y, r, ur;
+    int minLevel, maxLevel;
+};
+
+// A batch of frame pairs: pair p uses rows [p*cap1, p*cap1 + n1[p]) of the source arrays and
+// [p*cap2, p*cap2 + n2[p]) of the target arrays.
+struct WinBatch {
+    int cap1, cap2;
+    const int* n1;
+    const int* n2;
+};
+
+// ---------------------------------------------------------------------------------------------
+// Grid: CSR table over the 64x48 cells, cell id = ix * 48 + iy (so the cells of one column are
+// contiguous, which is GetFeaturesInArea's inner loop), entries of a cell in ascending keypoint index
+// (= push_back order).  grid (nPairs), block 256.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_grid_build(WinBatch wb, GridBounds gb, const viorb_keypoint* __restrict__ kps2,
+                                                    int* __restrict__ cellStart, int* __restrict__ cellList) {
+    __shared__ int cnt[VIORB_GRID_CELLS + 1];
+    __shared__ int cur[VIORB_GRID_CELLS];
+    __shared__ int warpSums[20];
+    const int tid = threadIdx.x, p = blockIdx.x;
+    const int n2 = wb.n2[p];
+    const viorb_keypoint* K = kps2 + (size_t)p * wb.cap2;
+    int* CS = cellStart + (size_t)p * (VIORB_GRID_CELLS + 1);
+    int* CL = cellList + (size_t)p * wb.cap2;
+    for (int i = tid; i <= VIORB_GRID_CELLS; i += 256) cnt[i] = 0;
+    for (int i = tid; i < VIORB_GRID_CELLS; i += 256) cur[i] = 0;
+    __syncthreads();
+    auto cell_of = [&](const viorb_keypoint& k) {
+        const int px = (int)roundf(__fmul_rn(__fsub_rn(k.x, gb.minX), gb.invW));
+        const int py = (int)roundf(__fmul_rn(__fsub_rn(k.y, gb.minY), gb.invH));
+        if (px < 0 || px >= VIORB_GRID_COLS || py < 0 || py >= VIORB_GRID_ROWS) return -1;
+        return px * VIORB_GRID_ROWS + py;
+    };
+    for (int i = tid; i < n2; i += 256) {
+        const int c = cell_of(K[i]);
+        if (c >= 0) atomicAdd(&cnt[c], 1);
+    }
+    __syncthreads();
+    block_excl_scan(cnt, VIORB_GRID_CELLS + 1, warpSums);
+    for (int i = tid; i <= VIORB_GRID_CELLS; i += 256) CS[i] = cnt[i];
+    for (int i = tid; i < n2; i += 256) {
+        const int c = cell_of(K[i]);
+        if (c >= 0) CL[cnt[c] + atomicAdd(&cur[c], 1)] = i;
+    }
+    __syncthreads();
+    // cells hold a handful of entries: insertion sort per cell restores ascending index order
+    for (int c = tid; c < VIORB_GRID_CELLS; c += 256) {
+        const int s = cnt[c], e = cnt[c + 1];
+        for (int a = s + 1; a < e; ++a) {
+            const int v = CL[a];
+            int b = a - 1;
+            while (b >= s && CL[b] > v) { CL[b + 1] = CL[b]; --b; }
+            CL[b + 1] = v;
+        }
+    }
+}
+
+// SearchForInitialization: level-0 keypoints of F1 search a square of half size windowSize around
+// vbPrevMatched[i1], level 0 only (fmatcher.cpp:997-1003).  grid (ceil(cap1/256), nPairs).
+__global__ void k_window_src_ini(WinBatch wb, const viorb_keypoint* __restrict__ kps1, const float* __restrict__ prevMatched,
+                                 float windowSize, WinSrc* __restrict__ src) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, p = blockIdx.y;
+    if (i >= wb.n1[p]) return;
+    const size_t o = (size_t)p * wb.cap1 + i;
+    WinSrc s;
+    s.x = prevMatched[2 * o];
+    s.y = prevMatched[2 * o + 1];
+    s.r = kps1[o].octave > 0 ? -1.f : windowSize;
+    s.ur = 0.f;
+    s.minLevel = 0;
+    s.maxLevel = 0;
+    src[o] = s;
+}
+
+// SearchByProjection: radius = th * mvScaleFactors[nLastOctave]; octave window by direction (fmatcher.cpp:2519-2530).
+struct ProjParams {
+    float th, bf;
+    int direction, nlevels;            // 0: nLastOctave-1..+1, 1: forward (>= nLastOctave), 2: backward (<= nLastOctave)
+    float scale[VIORB_MAX_LEVELS];
+};
+__global__ void k_window_src_proj(WinBatch wb, ProjParams pp, const float* __restrict__ uv, const float* __restrict__ invz,
+                                  const int32_t* __restrict__ lastOctave, const uint8_t* __restrict__ valid,
+                                  WinSrc* __restrict__ src) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, p = blockIdx.y;
+    if (i >= wb.n1[p]) return;
+    const size_t o = (size_t)p * wb.cap1 + i;
+    WinSrc s;
+    const int oc = min(max(lastOctave[o], 0), pp.nlevels - 1);
+    s.x = uv[2 * o];
+    s.y = uv[2 * o + 1];
+    s.r = valid[o] ? __fmul_rn(pp.th, pp.scale[oc]) : -1.f;
+    s.ur = __fsub_rn(s.x, __fmul_rn(pp.bf, invz[o]));
+    if (pp.direction == 1) { s.minLevel = oc; s.maxLevel = -1; }
+    else if (pp.direction == 2) { s.minLevel = 0; s.maxLevel = oc; }
+    else { s.minLevel = oc - 1; s.maxLevel = oc + 1; }
+    src[o] = s;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Window query.  One warp per source keypoint walks the covered grid columns; the cells of one column are
+// one contiguous run of the CSR list, scanned by the lanes with a ballot prefix so that accepted candidates
+// keep GetFeaturesInArea's order.  fill == 0: count only (listStart receives the counts);
+// fill == 1: write (distance << 16 | target index) at listStart[i] + position.
+// uRight2 != nullptr adds the stereo consistency predicate of fmatcher.cpp:2549-2555 (it does not depend
+// on earlier matches, so it is applied here).  grid (ceil(cap1/8), nPairs), block 256.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_window_list(WinBatch wb, GridBounds gb, const WinSrc* __restrict__ src,
+                                                     const uint8_t* __restrict__ desc1, const viorb_keypoint* __restrict__ kps2,
+                                                     const uint8_t* __restrict__ desc2, const float* __restrict__ uRight2,
+                                                     const int* __restrict__ cellStart, const int* __restrict__ cellList,
+                                                     int* __restrict__ listStart, uint32_t* __restrict__ list, int fill) {
+    const int lane = threadIdx.x & 31, p = blockIdx.y;
+    const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (i >= wb.n1[p]) return;
+    const size_t o = (size_t)p * wb.cap1 + i;
+    const WinSrc s = src[o];
+    int total = 0;
+    const int* LS = listStart + (size_t)p * (wb.cap1 + 1);
+    uint32_t* out = fill ? list + LS[i] : nullptr;
+    if (s.r >= 0.f) {
+        const float x = s.x, y = s.y, r = s.r;
+        const int c0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, gb.minX), r), gb.invW)));
+        const int c1 = min(VIORB_GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, gb.minX), r), gb.invW)));
+        const int r0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, gb.minY), r), gb.invH)));
+        const int r1 = min(VIORB_GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, gb.minY), r), gb.invH)));
+        if (c0 < VIORB_GRID_COLS && c1 >= 0 && r0 < VIORB_GRID_ROWS && r1 >= 0) {
+            const bool check = s.minLevel > 0 || s.maxLevel >= 0;
+            const int* CS = cellStart + (size_t)p * (VIORB_GRID_CELLS + 1);
+            const int* CL = cellList + (size_t)p * wb.cap2;
+            const viorb_keypoint* K = kps2 + (size_t)p * wb.cap2;
+            const uint4* D2 = reinterpret_cast<const uint4*>(desc2 + (size_t)p * wb.cap2 * 32);
+            uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+            if (fill && desc1) {
+                const uint4* q = reinterpret_cast<const uint4*>(desc1 + o * 32);
+                a0 = q[0]; a1 = q[1];
+            }
+            for (int ix = c0; ix <= c1; ++ix) {
+                const int b = CS[ix * VIORB_GRID_ROWS + r0], e = CS[ix * VIORB_GRID_ROWS + r1 + 1];
+                for (int j0 = b; j0 < e; j0 += 32) {
+                    const int j = j0 + lane;
+                    bool ok = false;
+                    int i2 = 0;
+                    if (j < e) {
+                        i2 = CL[j];
+                        const viorb_keypoint k = K[i2];
+                        ok = true;
+                        if (check) {
+                            if (k.octave < s.minLevel) ok = false;
+                            if (s.maxLevel >= 0 && k.octave > s.maxLevel) ok = false;
+                        }
+                        if (!(fabsf(__fsub_rn(k.x, x)) < r && fabsf(__fsub_rn(k.y, y)) < r)) ok = false;
+                        if (ok && uRight2) {
+                            const float u2 = uRight2[(size_t)p * wb.cap2 + i2];
+                            if (u2 > 0.f && fabsf(__fsub_rn(s.ur, u2)) > r) ok = false;
+                        }
+                    }
+                    const unsigned m = __ballot_sync(0xffffffffu, ok);
+                    if (fill && ok) {
+                        const int d = desc1 ? hamming256(a0, a1, D2[(size_t)i2 * 2], D2[(size_t)i2 * 2 + 1]) : 0;
+                        out[total + __popc(m & ((1u << lane) - 1))] = ((uint32_t)d << 16) | (uint32_t)i2;
+                    }
+                    total += __popc(m);
+                }
+            }
+        }
+    }
+    if (!fill && lane == 0) listStart[(size_t)p * (wb.cap1 + 1) + i] = total;
+}
+
+// exclusive scan of the per-source counts of one pair -> list offsets relative to the pair's base, which
+// is pairBase[p] (filled by the host from the totals).  grid (nPairs), block 256.
+__global__ void __launch_bounds__(256) k_window_scan(WinBatch wb, int* __restrict__ listStart, int* __restrict__ totals) {
+    __shared__ int warpSums[20];
+    const int p = blockIdx.x;
+    int* LS = listStart + (size_t)p * (wb.cap1 + 1);
+    const int n1 = wb.n1[p];
+    const int total = block_excl_scan(LS, n1, warpSums);
+    if (threadIdx.x == 0) { LS[n1] = total; totals[p] = total; }
+}
+__global__ void k_window_rebase(WinBatch wb, int* __restrict__ listStart, const int* __restrict__ pairBase) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, p = blockIdx.y;
+    if (i <= wb.n1[p]) listStart[(size_t)p * (wb.cap1 + 1) + i] += pairBase[p];
+}
+
+// ---------------------------------------------------------------------------------------------
+// Order-dependent part.  One warp per frame pair.
+// ---------------------------------------------------------------------------------------------
+#define VIORB_WIN_EMPTY 0xFFFFFFFFu
+
+__device__ __forceinline__ void three_maxima_dev(const int* count, int& ind1, int& ind2, int& ind3) {
+    int max1 = 0, max2 = 0, max3 = 0;
+    ind1 = ind2 = ind3 = -1;
+    for (int i = 0; i < VIORB_HISTO_LENGTH; ++i) {
+        const int s = count[i];
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+    else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) ind3 = -1;
+}
+
+__device__ __forceinline__ int rot_bin_dev(float a1, float a2) {
+    const float factor = __fdiv_rn(1.0f, (float)VIORB_HISTO_LENGTH);
+    float rot = __fsub_rn(a1, a2);
+    if (rot < 0.f) rot = __fadd_rn(rot, 360.0f);
+    int bin = (int)roundf(__fmul_rn(rot, factor));
+    if (bin == VIORB_HISTO_LENGTH) bin = 0;
+    return bin;
+}
+
+// SearchForInitialization (fmatcher.cpp:983-1098).  matchedDist / m21 / binOf: per-pair scratch of cap2 / cap2 /
+// cap1 entries.  matches12 [cap1] and prevMatched are outputs.  grid (nPairs), block 32.
+__global__ void __launch_bounds__(32) k_resolve_ini(WinBatch wb, const viorb_keypoint* __restrict__ kps1,
+                                                    const viorb_keypoint* __restrict__ kps2, const int* __restrict__ listStart,
+                                                    const uint32_t* __restrict__ list, float nnRatio, int checkOrientation,
+                                                    int* __restrict__ matchedDist, int* __restrict__ m21, int8_t* __restrict__ binOf,
+                                                    int32_t* __restrict__ matches12, float* __restrict__ prevMatched,
+                                                    int* __restrict__ nMatches) {
+    __shared__ int hist[VIORB_HISTO_LENGTH];
+    __shared__ int keep[3];
+    const int lane = threadIdx.x, p = blockIdx.x;
+    const int n1 = wb.n1[p], n2 = wb.n2[p];
+    const int* LS = listStart + (size_t)p * (wb.cap1 + 1);
+    int* MD = matchedDist + (size_t)p * wb.cap2;
+    int* M21 = m21 + (size_t)p * wb.cap2;
+    int8_t* BO = binOf + (size_t)p * wb.cap1;
+    int32_t* M12 = matches12 + (size_t)p * wb.cap1;
+    const viorb_keypoint* K1 = kps1 + (size_t)p * wb.cap1;
+    const viorb_keypoint* K2 = kps2 + (size_t)p * wb.cap2;
+    for (int i = lane; i < n2; i += 32) { MD[i] = 0x7fffffff; M21[i] = -1; }
+    for (int i = lane; i < n1; i += 32) { M12[i] = -1; BO[i] = -1; }
+    if (lane < VIORB_HISTO_LENGTH) hist[lane] = 0;
+    __syncwarp();
+    int s0 = LS[0];
+    for (int i1 = 0; i1 < n1; ++i1) {
+        const int s1 = LS[i1 + 1];
+        const int cnt = s1 - s0;
+        if (cnt > 0) {
+            unsigned b1 = VIORB_WIN_EMPTY, b2 = VIORB_WIN_EMPTY;          // keys: distance << 16 | list position
+            for (int j = lane; j < cnt; j += 32) {
+                const uint32_t e = list[s0 + j];
+                const int dist = (int)(e >> 16), i2 = (int)(e & 0xFFFF);
+                if (MD[i2] <= dist) continue;                               // fmatcher.cpp:1024
+                const unsigned key = ((unsigned)dist << 16) | (unsigned)j;
+                b2 = min(b2, max(key, b1));
+                b1 = min(b1, key);
+            }
+#pragma unroll
+            for (int d = 16; d >= 1; d >>= 1) {
+                const unsigned o1 = __shfl_xor_sync(0xffffffffu, b1, d), o2 = __shfl_xor_sync(0xffffffffu, b2, d);
+                b2 = min(max(b1, o1), min(b2, o2));
+                b1 = min(b1, o1);
+            }
+            if (b1 != VIORB_WIN_EMPTY) {
+                const int bestDist = (int)(b1 >> 16);
+                const float second = b2 == VIORB_WIN_EMPTY ? (float)0x7fffffff : (float)(int)(b2 >> 16);
+                if (bestDist <= VIORB_TH_LOW && (float)bestDist < __fmul_rn(second, nnRatio)) {
+                    const int bestIdx2 = (int)(list[s0 + (int)(b1 & 0xFFFF)] & 0xFFFF);
+                    if (lane == 0) {
+                        const int old = M21[bestIdx2];
+                        if (old >= 0) M12[old] = -1;
+                        M12[i1] = bestIdx2;
+                        M21[bestIdx2] = i1;
+                        MD[bestIdx2] = bestDist;
+                        if (checkOrientation) {
+                            const int bin = rot_bin_dev(K1[i1].angle, K2[bestIdx2].angle);
+                            BO[i1] = (int8_t)bin;
+                            hist[bin] += 1;
+                        }
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+        s0 = s1;
+    }
+    __syncwarp();
+    if (checkOrientation) {
+        if (lane == 0) three_maxima_dev(hist, keep[0], keep[1], keep[2]);
+        __syncwarp();
+        const int a = keep[0], b = keep[1], c = keep[2];
+        for (int i = lane; i < n1; i += 32) {
+            const int bin = BO[i];
+            if (bin >= 0 && bin != a && bin != b && bin != c && M12[i] >= 0) M12[i] = -1;
+        }
+        __syncwarp();
+    }
+    int nm = 0;
+    for (int i = lane; i < n1; i += 32) {
+        const int m = M12[i];
+        if (m >= 0) {
+            ++nm;
+            prevMatched[2 * ((size_t)p * wb.cap1 + i)] = K2[m].x;
+            prevMatched[2 * ((size_t)p * wb.cap1 + i) + 1] = K2[m].y;
+        }
+    }
+    nm = __reduce_add_sync(0xffffffffu, nm);
+    if (lane == 0) nMatches[p] = nm;
+}
+
+// SearchByProjection(CurrentFrame, LastFrame) (fmatcher.cpp:2471-2688, single-camera branch).
+// blocked [cap2]: in: current keypoint already holds an observed map point; updated as matches are made.
+// assigned [cap2]: -1 untouched, -2 cleared by the rotation check, >= 0 the source index now held.
+// pushIdx / pushBin: per-pair scratch of cap1 entries (the rotHist lists).  grid (nPairs), block 32.
+__global__ void __launch_bounds__(32) k_resolve_proj(WinBatch wb, const float* __restrict__ lastAngle,
+                                                     const uint8_t* __restrict__ observed, const viorb_keypoint* __restrict__ kps2,
+                                                     const int* __restrict__ listStart, const uint32_t* __restrict__ list,
+                                                     int checkOrientation, uint8_t* __restrict__ blocked,
+                                                     int* __restrict__ pushIdx, int8_t* __restrict__ pushBin,
+                                                     int32_t* __restrict__ assigned, int* __restrict__ nMatches) {
+    __shared__ int hist[VIORB_HISTO_LENGTH];
+    __shared__ int keep[3];
+    const int lane = threadIdx.x, p = blockIdx.x;
+    const int n1 = wb.n1[p], n2 = wb.n2[p];
+    const int* LS = listStart + (size_t)p * (wb.cap1 + 1);
+    uint8_t* BL = blocked + (size_t)p * wb.cap2;
+    int32_t* AS = assigned + (size_t)p * wb.cap2;
+    int* PI = pushIdx + (size_t)p * wb.cap1;
+    int8_t* PB = pushBin + (size_t)p * wb.cap1;
+    const viorb_keypoint* K2 = kps2 + (size_t)p * wb.cap2;
+    for (int i = lane; i < n2; i += 32) AS[i] = -1;
+    if (lane < VIORB_HISTO_LENGTH) hist[lane] = 0;
+    __syncwarp();
+    int nPush = 0;
+    int s0 = LS[0];
+    for (int i = 0; i < n1; ++i) {
+        const int s1 = LS[i + 1];
+        const int cnt = s1 - s0;
+        if (cnt > 0) {
+            unsigned b1 = VIORB_WIN_EMPTY;
+            for (int j = lane; j < cnt; j += 32) {
+                const uint32_t e = list[s0 + j];
+                if (BL[e & 0xFFFF]) continue;                               // fmatcher.cpp:2545-2547
+                b1 = min(b1, (e & 0xFFFF0000u) | (unsigned)j);
+            }
+            b1 = __reduce_min_sync(0xffffffffu, b1);
+            if (b1 != VIORB_WIN_EMPTY && (int)(b1 >> 16) <= VIORB_TH_HIGH) {
+                const int bestIdx2 = (int)(list[s0 + (int)(b1 & 0xFFFF)] & 0xFFFF);
+                if (lane == 0) {
+                    const size_t o = (size_t)p * wb.cap1 + i;
+                    AS[bestIdx2] = i;
+                    BL[bestIdx2] = observed[o];
+                    int bin = 0;
+                    if (checkOrientation) {
+                        bin = rot_bin_dev(lastAngle[o], K2[bestIdx2].angle);
+                        hist[bin] += 1;
+                    }
+                    PI[nPush] = bestIdx2;
+                    PB[nPush] = (int8_t)bin;
+                }
+                ++nPush;
+                __syncwarp();
+            }
+        }
+        s0 = s1;
+    }
+    __syncwarp();
+    int removed = 0;
+    if (checkOrientation) {
+        if (lane == 0) three_maxima_dev(hist, keep[0], keep[1], keep[2]);
+        __syncwarp();
+        const int a = keep[0], b = keep[1], c = keep[2];
+        for (int k = lane; k < nPush; k += 32) {
+            const int bin = PB[k];
+            if (bin != a && bin != b && bin != c) { AS[PI[k]] = -2; ++removed; }
+        }
+    }
+    removed = __reduce_add_sync(0xffffffffu, removed);
+    if (lane == 0) nMatches[p] = nPush - removed;
+}

@@ -14,6 +14,7 @@
 
 #include "kernels_extract.cuh"
 #include "kernels_match.cuh"
+#include "kernels_window.cuh"
 
 #define VIORB_MAX_CHUNKS 8
 
@@ -1139,6 +1140,251 @@ int viorb_stereo_match(viorb_extractor* L, viorb_extractor* R, int frame, float 
     }
     if (nl > cap) return fail(VIORB_E_CAPACITY, "output buffer smaller than the number of left keypoints");
     return VIORB_OK;
+}
+
+
+// ---- windowed (grid) matchers ---------------------------------------------------------------------
+}  // extern "C"
+
+namespace {
+
+template <class T>
+cudaError_t upload(DevBuf<T>& d, const T* h, size_t n) {
+    cudaError_t e = d.alloc(n);
+    if (e == cudaSuccess && n > 0 && h) e = cudaMemcpy(d.p, h, n * sizeof(T), cudaMemcpyHostToDevice);
+    return e;
+}
+
+GridBounds make_bounds(const viorb_grid_bounds& b) {
+    GridBounds g;
+    g.minX = b.min_x; g.maxX = b.max_x; g.minY = b.min_y; g.maxY = b.max_y;
+    g.invW = (float)VIORB_GRID_COLS / (b.max_x - b.min_x);      // frame.cpp:235-236
+    g.invH = (float)VIORB_GRID_ROWS / (b.max_y - b.min_y);
+    return g;
+}
+
+// Grid build + window lists for a batch whose sources (dSrc) are already on the device.  Leaves listStart /
+// list filled.  desc1 may be null (distance 0: plain GetFeaturesInArea).
+struct WindowWork {
+    DevBuf<int> cellStart, cellList, listStart, totals, pairBase, n1, n2;
+    DevBuf<uint32_t> list;
+    WinBatch wb{};
+    void release() {
+        cellStart.release(); cellList.release(); listStart.release(); totals.release(); pairBase.release();
+        n1.release(); n2.release(); list.release();
+    }
+};
+
+int window_lists(WindowWork& w, int npairs, int cap1, int cap2, const int32_t* n1, const int32_t* n2, const GridBounds& gb,
+                 const WinSrc* dSrc, const uint8_t* dDesc1, const viorb_keypoint* dKps2, const uint8_t* dDesc2,
+                 const float* dURight2) {
+    CU(upload(w.n1, n1, npairs));
+    CU(upload(w.n2, n2, npairs));
+    w.wb.cap1 = cap1; w.wb.cap2 = cap2; w.wb.n1 = w.n1.p; w.wb.n2 = w.n2.p;
+    CU(w.cellStart.alloc((size_t)npairs * (VIORB_GRID_CELLS + 1)));
+    CU(w.cellList.alloc((size_t)npairs * cap2));
+    CU(w.listStart.alloc((size_t)npairs * (cap1 + 1)));
+    CU(w.totals.alloc(npairs));
+    CU(w.pairBase.alloc(npairs));
+    cudaStream_t st = 0;
+    VIORB_LAUNCH(k_grid_build, dim3(npairs), dim3(256), 0, st, w.wb, gb, dKps2, w.cellStart.p, w.cellList.p);
+    const dim3 gl((cap1 + 7) / 8, npairs);
+    VIORB_LAUNCH(k_window_list, gl, dim3(256), 0, st, w.wb, gb, dSrc, dDesc1, dKps2, dDesc2, dURight2, w.cellStart.p, w.cellList.p,
+                 w.listStart.p, (uint32_t*)nullptr, 0);
+    VIORB_LAUNCH(k_window_scan, dim3(npairs), dim3(256), 0, st, w.wb, w.listStart.p, w.totals.p);
+    std::vector<int> tot(npairs), base(npairs);
+    CU(cudaMemcpy(tot.data(), w.totals.p, sizeof(int) * npairs, cudaMemcpyDeviceToHost));
+    size_t sum = 0;
+    for (int p = 0; p < npairs; ++p) { base[p] = (int)sum; sum += (size_t)tot[p]; }
+    if (sum >= 0x7fffffffull) return fail(VIORB_E_CAPACITY, "candidate lists exceed 2^31 entries");
+    CU(cudaMemcpy(w.pairBase.p, base.data(), sizeof(int) * npairs, cudaMemcpyHostToDevice));
+    VIORB_LAUNCH(k_window_rebase, dim3((cap1 + 256) / 256, npairs), dim3(256), 0, st, w.wb, w.listStart.p, w.pairBase.p);
+    CU(w.list.alloc(sum));
+    VIORB_LAUNCH(k_window_list, gl, dim3(256), 0, st, w.wb, gb, dSrc, dDesc1, dKps2, dDesc2, dURight2, w.cellStart.p, w.cellList.p,
+                 w.listStart.p, w.list.p, 1);
+    CU(cudaGetLastError());
+    return VIORB_OK;
+}
+
+int need_device(int device) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= device) return fail(VIORB_E_NO_DEVICE, "no CUDA device: libviorb has no CPU path");
+    CU(cudaSetDevice(device));
+    return VIORB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int viorb_features_in_area(const viorb_keypoint* kps, int n, const viorb_grid_bounds* bounds, float x, float y, float r,
+                           int min_level, int max_level, int32_t* out, int cap, int* n_out, int device) {
+    if (n < 0 || (n > 0 && !kps) || !bounds || !n_out) return fail(VIORB_E_ARG, "bad argument");
+    if (n >= 65536) return fail(VIORB_E_ARG, "more than 65535 keypoints per frame are not supported");
+    *n_out = 0;
+    if (n == 0) return VIORB_OK;
+    int rc = need_device(device);
+    if (rc) return rc;
+    const GridBounds gb = make_bounds(*bounds);
+    DevBuf<viorb_keypoint> dK;
+    DevBuf<WinSrc> dS;
+    WindowWork w;
+    WinSrc s{x, y, r, 0.f, min_level, max_level};
+    const int32_t one = 1, nn = n;
+    cudaError_t e = upload(dK, kps, n);
+    if (e == cudaSuccess) e = upload(dS, &s, 1);
+    rc = e == cudaSuccess ? VIORB_OK : fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    if (!rc) rc = window_lists(w, 1, 1, n, &one, &nn, gb, dS.p, nullptr, dK.p, nullptr, nullptr);
+    if (!rc) {
+        std::vector<uint32_t> l(w.list.n);
+        if (!l.empty()) e = cudaMemcpy(l.data(), w.list.p, sizeof(uint32_t) * l.size(), cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+        else {
+            *n_out = (int)l.size();
+            for (int i = 0; i < (int)l.size() && i < cap && out; ++i) out[i] = (int32_t)(l[i] & 0xFFFF);
+            if ((int)l.size() > cap && out) rc = fail(VIORB_E_CAPACITY, "output buffer too small (n_out holds the count)");
+        }
+    }
+    dK.release(); dS.release(); w.release();
+    return rc;
+}
+
+int viorb_search_for_initialization(int npairs, int cap1, int cap2, const viorb_keypoint* kps1, const uint8_t* desc1,
+                                    const int32_t* n1, const viorb_keypoint* kps2, const uint8_t* desc2, const int32_t* n2,
+                                    const viorb_grid_bounds* bounds, float* prev_matched, int window_size, float nn_ratio,
+                                    int check_orientation, int32_t* matches12, int32_t* nmatches, int device) {
+    if (npairs < 1 || cap1 < 0 || cap2 < 0 || !n1 || !n2 || !bounds || !matches12 || !prev_matched)
+        return fail(VIORB_E_ARG, "bad argument");
+    if (cap2 >= 65536) return fail(VIORB_E_ARG, "more than 65535 keypoints per frame are not supported");
+    for (int p = 0; p < npairs; ++p)
+        if (n1[p] < 0 || n1[p] > cap1 || n2[p] < 0 || n2[p] > cap2) return fail(VIORB_E_ARG, "n1 / n2 outside [0, cap]");
+    if ((cap1 > 0 && (!kps1 || !desc1)) || (cap2 > 0 && (!kps2 || !desc2))) return fail(VIORB_E_ARG, "null keypoints or descriptors");
+    if (cap1 == 0) { if (nmatches) for (int p = 0; p < npairs; ++p) nmatches[p] = 0; return VIORB_OK; }
+    int rc = need_device(device);
+    if (rc) return rc;
+    const GridBounds gb = make_bounds(*bounds);
+    const size_t N1 = (size_t)npairs * cap1, N2 = (size_t)npairs * std::max(cap2, 1);
+    DevBuf<viorb_keypoint> dK1, dK2;
+    DevBuf<uint8_t> dD1, dD2;
+    DevBuf<float> dPM;
+    DevBuf<WinSrc> dS;
+    DevBuf<int> dMD, dM21, dM12, dNM;
+    DevBuf<int8_t> dBin;
+    WindowWork w;
+    cudaError_t e = upload(dK1, kps1, N1);
+    if (e == cudaSuccess) e = upload(dD1, desc1, N1 * 32);
+    if (e == cudaSuccess) e = upload(dK2, cap2 ? kps2 : nullptr, N2);
+    if (e == cudaSuccess) e = upload(dD2, cap2 ? desc2 : nullptr, N2 * 32);
+    if (e == cudaSuccess) e = upload(dPM, prev_matched, N1 * 2);
+    if (e == cudaSuccess) e = dS.alloc(N1);
+    if (e == cudaSuccess) e = dMD.alloc(N2);
+    if (e == cudaSuccess) e = dM21.alloc(N2);
+    if (e == cudaSuccess) e = dM12.alloc(N1);
+    if (e == cudaSuccess) e = dBin.alloc(N1);
+    if (e == cudaSuccess) e = dNM.alloc(npairs);
+    rc = e == cudaSuccess ? VIORB_OK : fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    if (!rc) {
+        DevBuf<int> tn1;                     // the source kernel needs n1 on the device before window_lists uploads it
+        e = upload(tn1, n1, npairs);
+        if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+        else {
+            WinBatch wb{cap1, cap2, tn1.p, nullptr};
+            VIORB_LAUNCH(k_window_src_ini, dim3((cap1 + 255) / 256, npairs), dim3(256), 0, (cudaStream_t)0, wb, dK1.p, dPM.p,
+                         (float)window_size, dS.p);
+            e = cudaDeviceSynchronize();
+            if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+        }
+        tn1.release();
+    }
+    if (!rc) rc = window_lists(w, npairs, cap1, cap2, n1, n2, gb, dS.p, dD1.p, dK2.p, dD2.p, nullptr);
+    if (!rc) {
+        VIORB_LAUNCH(k_resolve_ini, dim3(npairs), dim3(32), 0, (cudaStream_t)0, w.wb, dK1.p, dK2.p, w.listStart.p, w.list.p, nn_ratio,
+                     check_orientation, dMD.p, dM21.p, dBin.p, dM12.p, dPM.p, dNM.p);
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaMemcpy(matches12, dM12.p, sizeof(int32_t) * N1, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(prev_matched, dPM.p, sizeof(float) * 2 * N1, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess && nmatches) e = cudaMemcpy(nmatches, dNM.p, sizeof(int32_t) * npairs, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    }
+    dK1.release(); dK2.release(); dD1.release(); dD2.release(); dPM.release(); dS.release(); dMD.release(); dM21.release();
+    dM12.release(); dBin.release(); dNM.release(); w.release();
+    return rc;
+}
+
+int viorb_search_by_projection(int npairs, int cap1, int cap2, const float* uv, const float* invz, const int32_t* last_octave,
+                               const float* last_angle, const uint8_t* desc_mp, const uint8_t* valid, const uint8_t* observed,
+                               const int32_t* n1, const viorb_keypoint* kps2, const uint8_t* desc2, const float* u_right2,
+                               const uint8_t* blocked2, const int32_t* n2, const viorb_grid_bounds* bounds,
+                               const float* scale_factors, int nlevels, float th, float bf, int direction,
+                               int check_orientation, int32_t* assigned, int32_t* nmatches, int device) {
+    if (npairs < 1 || cap1 < 0 || cap2 < 0 || !n1 || !n2 || !bounds || !assigned || !scale_factors || nlevels < 1 ||
+        nlevels > VIORB_MAX_LEVELS || direction < 0 || direction > 2)
+        return fail(VIORB_E_ARG, "bad argument");
+    if (cap2 >= 65536) return fail(VIORB_E_ARG, "more than 65535 keypoints per frame are not supported");
+    for (int p = 0; p < npairs; ++p)
+        if (n1[p] < 0 || n1[p] > cap1 || n2[p] < 0 || n2[p] > cap2) return fail(VIORB_E_ARG, "n1 / n2 outside [0, cap]");
+    if (cap1 > 0 && (!uv || !invz || !last_octave || !last_angle || !desc_mp || !valid || !observed)) return fail(VIORB_E_ARG, "null source array");
+    if (cap2 > 0 && (!kps2 || !desc2)) return fail(VIORB_E_ARG, "null keypoints or descriptors");
+    if (cap2 == 0) { if (nmatches) for (int p = 0; p < npairs; ++p) nmatches[p] = 0; return VIORB_OK; }
+    int rc = need_device(device);
+    if (rc) return rc;
+    const GridBounds gb = make_bounds(*bounds);
+    ProjParams pp;
+    std::memset(&pp, 0, sizeof pp);
+    pp.th = th; pp.bf = bf; pp.direction = direction; pp.nlevels = nlevels;
+    for (int l = 0; l < nlevels; ++l) pp.scale[l] = scale_factors[l];
+    const size_t N1 = (size_t)npairs * std::max(cap1, 1), N2 = (size_t)npairs * cap2;
+    DevBuf<float> dUV, dIZ, dLA, dUR;
+    DevBuf<int32_t> dLO, dAS, dNM, dPI;
+    DevBuf<uint8_t> dDM, dVA, dOB, dD2, dBL;
+    DevBuf<int8_t> dPB;
+    DevBuf<viorb_keypoint> dK2;
+    DevBuf<WinSrc> dS;
+    WindowWork w;
+    const bool have1 = cap1 > 0;
+    cudaError_t e = upload(dUV, have1 ? uv : nullptr, N1 * 2);
+    if (e == cudaSuccess) e = upload(dIZ, have1 ? invz : nullptr, N1);
+    if (e == cudaSuccess) e = upload(dLA, have1 ? last_angle : nullptr, N1);
+    if (e == cudaSuccess) e = upload(dLO, have1 ? last_octave : nullptr, N1);
+    if (e == cudaSuccess) e = upload(dDM, have1 ? desc_mp : nullptr, N1 * 32);
+    if (e == cudaSuccess) e = upload(dVA, have1 ? valid : nullptr, N1);
+    if (e == cudaSuccess) e = upload(dOB, have1 ? observed : nullptr, N1);
+    if (e == cudaSuccess) e = upload(dK2, kps2, N2);
+    if (e == cudaSuccess) e = upload(dD2, desc2, N2 * 32);
+    if (e == cudaSuccess && u_right2) e = upload(dUR, u_right2, N2);
+    if (e == cudaSuccess) e = upload(dBL, blocked2, N2);
+    if (e == cudaSuccess && !blocked2) e = cudaMemset(dBL.p, 0, N2);
+    if (e == cudaSuccess) e = dS.alloc(N1);
+    if (e == cudaSuccess) e = dAS.alloc(N2);
+    if (e == cudaSuccess) e = dPI.alloc(N1);
+    if (e == cudaSuccess) e = dPB.alloc(N1);
+    if (e == cudaSuccess) e = dNM.alloc(npairs);
+    rc = e == cudaSuccess ? VIORB_OK : fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    if (!rc && have1) {
+        DevBuf<int> tn1;
+        e = upload(tn1, n1, npairs);
+        if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+        else {
+            WinBatch wb{cap1, cap2, tn1.p, nullptr};
+            VIORB_LAUNCH(k_window_src_proj, dim3((cap1 + 255) / 256, npairs), dim3(256), 0, (cudaStream_t)0, wb, pp, dUV.p, dIZ.p, dLO.p,
+                         dVA.p, dS.p);
+            e = cudaDeviceSynchronize();
+            if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+        }
+        tn1.release();
+    }
+    if (!rc) rc = window_lists(w, npairs, cap1, cap2, n1, n2, gb, dS.p, dDM.p, dK2.p, dD2.p, u_right2 ? dUR.p : nullptr);
+    if (!rc) {
+        VIORB_LAUNCH(k_resolve_proj, dim3(npairs), dim3(32), 0, (cudaStream_t)0, w.wb, dLA.p, dOB.p, dK2.p, w.listStart.p, w.list.p,
+                     check_orientation, dBL.p, dPI.p, dPB.p, dAS.p, dNM.p);
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaMemcpy(assigned, dAS.p, sizeof(int32_t) * N2, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess && nmatches) e = cudaMemcpy(nmatches, dNM.p, sizeof(int32_t) * npairs, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    }
+    dUV.release(); dIZ.release(); dLA.release(); dUR.release(); dLO.release(); dAS.release(); dNM.release(); dPI.release();
+    dDM.release(); dVA.release(); dOB.release(); dD2.release(); dBL.release(); dPB.release(); dK2.release(); dS.release(); w.release();
+    return rc;
 }
 
 }  // extern "C"

@@ -6,6 +6,9 @@
 * ``fisheye_ratio_match``      the 0.7 ratio rule of ComputeStereoFishEyeMatches (frame.cpp:1170)
 * ``compute_stereo_matches``   Frame::ComputeStereoMatches                    (frame.cpp:823-997)
 * ``stereo_batch``             both stereo matchers on a resident batch
+* ``features_in_area``         Frame::GetFeaturesInArea on Frame::AssignFeaturesToGrid   (frame.cpp:386-414,678-757)
+* ``search_for_initialization`` FMatcher::SearchForInitialization                        (fmatcher.cpp:983-1098)
+* ``search_by_projection``     FMatcher::SearchByProjection(CurrentFrame, LastFrame, ..) (fmatcher.cpp:2471-2688)
 All compute happens in libviorb.so (CUDA); no CPU path.
 """
 from __future__ import annotations
@@ -15,7 +18,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from .extractor import MATCH_DTYPE, FExtractor, _check
+from .extractor import KP_DTYPE, MATCH_DTYPE, FExtractor, _check
 
 TH_HIGH, TH_LOW, HISTO_LENGTH = 100, 50, 30      # fmatcher.cpp:313-315
 
@@ -133,3 +136,84 @@ def stereo_fetch_all(left: FExtractor, n: int, out=None):
                                            cap, out["n_left"].ctypes.data_as(_lib.i32p),
                                            out["n_stereo"].ctypes.data_as(_lib.i32p), out["n_ratio"].ctypes.data_as(_lib.i32p)))
     return out
+
+
+# ---- windowed (grid) matchers -------------------------------------------------------------------
+
+def _bounds(b):
+    return np.ascontiguousarray(b, np.float32)          # (mnMinX, mnMaxX, mnMinY, mnMaxY)
+
+
+def features_in_area(kps, bounds, x, y, r, min_level=-1, max_level=-1, device=0, lib_path=None):
+    lib = _lib.load(lib_path)
+    kps = np.ascontiguousarray(kps)
+    b = _bounds(bounds)
+    out = np.zeros(max(len(kps), 1), np.int32)
+    n = C.c_int32()
+    _check(lib, lib.viorb_features_in_area(kps.ctypes.data, len(kps), b.ctypes.data, x, y, r, min_level, max_level,
+                                           out.ctypes.data_as(_lib.i32p), len(out), C.byref(n), device))
+    return out[:n.value].copy()
+
+
+def search_for_initialization(k1, d1, k2, d2, bounds, prev_matched, window_size=100, nn_ratio=0.9, check_orientation=True,
+                              device=0, lib_path=None):
+    """FMatcher(nn_ratio, check_orientation).SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)
+    -> (nmatches, vnMatches12, updated vbPrevMatched).  One frame pair; see ``search_for_initialization_batch``."""
+    n, m12, pm = search_for_initialization_batch([k1], [d1], [k2], [d2], bounds, [prev_matched], window_size, nn_ratio,
+                                                 check_orientation, device, lib_path)
+    return int(n[0]), m12[0], pm[0]
+
+
+def search_for_initialization_batch(k1s, d1s, k2s, d2s, bounds, prev_matched, window_size=100, nn_ratio=0.9,
+                                    check_orientation=True, device=0, lib_path=None):
+    lib = _lib.load(lib_path)
+    P = len(k1s)
+    n1 = np.array([len(k) for k in k1s], np.int32)
+    n2 = np.array([len(k) for k in k2s], np.int32)
+    c1, c2 = int(n1.max(initial=0)), int(n2.max(initial=0))
+    K1, K2 = np.zeros((P, max(c1, 1)), KP_DTYPE), np.zeros((P, max(c2, 1)), KP_DTYPE)
+    D1, D2 = np.zeros((P, max(c1, 1), 32), np.uint8), np.zeros((P, max(c2, 1), 32), np.uint8)
+    PM = np.zeros((P, max(c1, 1), 2), np.float32)
+    for p in range(P):
+        K1[p, :n1[p]], D1[p, :n1[p]], PM[p, :n1[p]] = k1s[p], d1s[p], prev_matched[p]
+        K2[p, :n2[p]], D2[p, :n2[p]] = k2s[p], d2s[p]
+    m12 = np.full((P, max(c1, 1)), -1, np.int32)
+    nm = np.zeros(P, np.int32)
+    b = _bounds(bounds)
+    _check(lib, lib.viorb_search_for_initialization(P, c1, c2, K1.ctypes.data, D1.ctypes.data, n1.ctypes.data_as(_lib.i32p),
+                                                    K2.ctypes.data, D2.ctypes.data, n2.ctypes.data_as(_lib.i32p), b.ctypes.data,
+                                                    PM.ctypes.data_as(_lib.f32p), int(window_size), float(nn_ratio),
+                                                    int(check_orientation), m12.ctypes.data_as(_lib.i32p),
+                                                    nm.ctypes.data_as(_lib.i32p), device))
+    return nm, [m12[p, :n1[p]].copy() for p in range(P)], [PM[p, :n1[p]].copy() for p in range(P)]
+
+
+def search_by_projection(uv, invz, last_octave, last_angle, desc_mp, valid, observed, k2, d2, u_right2, blocked2, bounds,
+                         scale_factors, th, bf, direction=0, check_orientation=True, device=0, lib_path=None):
+    """FMatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono), single-camera branch; the caller projects.
+    -> (nmatches, assigned[n2]) with assigned: -1 untouched, -2 cleared by the rotation check, i >= 0 matched source."""
+    lib = _lib.load(lib_path)
+    uv = np.ascontiguousarray(uv, np.float32)
+    invz = np.ascontiguousarray(invz, np.float32)
+    lo = np.ascontiguousarray(last_octave, np.int32)
+    la = np.ascontiguousarray(last_angle, np.float32)
+    dm = np.ascontiguousarray(desc_mp, np.uint8)
+    va = np.ascontiguousarray(valid, np.uint8)
+    ob = np.ascontiguousarray(observed, np.uint8)
+    k2 = np.ascontiguousarray(k2)
+    d2 = np.ascontiguousarray(d2, np.uint8)
+    ur = None if u_right2 is None else np.ascontiguousarray(u_right2, np.float32)
+    bl = None if blocked2 is None else np.ascontiguousarray(blocked2, np.uint8)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    b = _bounds(bounds)
+    n1 = np.array([len(lo)], np.int32)
+    n2 = np.array([len(k2)], np.int32)
+    out = np.full(max(len(k2), 1), -1, np.int32)
+    nm = np.zeros(1, np.int32)
+    _check(lib, lib.viorb_search_by_projection(
+        1, len(lo), len(k2), uv.ctypes.data_as(_lib.f32p), invz.ctypes.data_as(_lib.f32p), lo.ctypes.data_as(_lib.i32p),
+        la.ctypes.data_as(_lib.f32p), dm.ctypes.data, va.ctypes.data, ob.ctypes.data, n1.ctypes.data_as(_lib.i32p),
+        k2.ctypes.data, d2.ctypes.data, None if ur is None else ur.ctypes.data, None if bl is None else bl.ctypes.data,
+        n2.ctypes.data_as(_lib.i32p), b.ctypes.data, sf.ctypes.data_as(_lib.f32p), len(sf), float(th), float(bf),
+        int(direction), int(check_orientation), out.ctypes.data_as(_lib.i32p), nm.ctypes.data_as(_lib.i32p), device))
+    return int(nm[0]), out[:len(k2)].copy()
