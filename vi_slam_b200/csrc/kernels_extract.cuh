@@ -684,48 +684,95 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 
 struct UmaxTable { int v[16]; };
 
+// dot product of 4 unsigned bytes with 4 signed bytes (IDP.4A.U8.S8)
+__device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {
+#ifdef VIORB_EMU
+    for (int i = 0; i < 4; ++i) c += (int)((a >> (8 * i)) & 0xFF) * (int)(int8_t)((unsigned)b >> (8 * i));
+    return c;
+#else
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+#endif
+}
+
+// One warp per retained keypoint.  lane = (row group rg = lane >> 3, word column wc = lane & 7): the lane handles
+// bytes [4 wc, 4 wc + 4) of rows rg, rg + 4, ... of the 31x31 patch.  Every load instruction fetches 4 rows x 32
+// contiguous bytes (coalesced sectors), all 16 loads of a lane are independent, and each row word costs one funnel
+// shift and two IDP.4A against per-row weight tables built from umax: sum(I) and sum(u * I) over the row's disc
+// segment.  m01 = sum_v v * sum(I), m10 = sum_v sum(u * I); integer, so the order of the adds is free.
 __global__ void __launch_bounds__(256) k_orient(ExtractGeom g, FrameSrc fs, UmaxTable um, KeptKp* __restrict__ kept,
                                                 const int* __restrict__ keptCount) {
+    __shared__ int wOnes[16][8], wU[16][8];           // [|v|][word]: bytes = 1 resp. u inside the disc, 0 outside
+    {
+        const int t = threadIdx.x;                    // 256 threads: table (t >> 7), row (t >> 3) & 15, word t & 7
+        const int av = (t >> 3) & 15, k = t & 7;
+        unsigned w = 0;
+        for (int j = 0; j < 4; ++j) {
+            const int col = 4 * k + j, u = col - VIORB_HALF_PATCH;
+            const bool in = col < 31 && (u < 0 ? -u : u) <= um.v[av];
+            const int val = (t >> 7) ? u : 1;
+            if (in) w |= (unsigned)(val & 0xFF) << (8 * j);
+        }
+        if (t >> 7) wU[av][k] = (int)w; else wOnes[av][k] = (int)w;
+    }
+    __syncthreads();
     const int lane = threadIdx.x & 31;
     const int slot = blockIdx.x * 8 + (threadIdx.x >> 5);
     const int f = blockIdx.y + g.frame0;
     if (slot >= g.keptPerFrame) return;
-    int l = -1;
-    for (int i = 0; i < g.nlevels; ++i) {
-        const int o = g.lv[i].keptOff;
-        if (slot >= o && slot < o + keptCount[f * g.nlevels + i]) l = i;
+    // level of this slot: lane i tests level i
+    bool mine = false;
+    if (lane < g.nlevels) {
+        const int o = g.lv[lane].keptOff;
+        mine = slot >= o && slot < o + keptCount[f * g.nlevels + lane];
     }
-    if (l < 0) return;
+    const unsigned lm = __ballot_sync(0xffffffffu, mine);
+    if (lm == 0) return;
+    const int l = __ffs(lm) - 1;
     KeptKp* kp = kept + (size_t)f * g.keptPerFrame + slot;
     int pitch;
     const uint8_t* img = level_ptr(g, fs, l, f, pitch);
     const int x = kp->x, y = kp->y;
-    const int u = lane - VIORB_HALF_PATCH;
-    int colSum = 0, m01 = 0;
-    if (lane < 31) {
-        const int au = u < 0 ? -u : u;
-        const uint8_t* c = img + (size_t)y * pitch + x + u;
-        for (int v = -VIORB_HALF_PATCH; v <= VIORB_HALF_PATCH; ++v) {
-            const int av = v < 0 ? -v : v;
-            if (au <= um.v[av]) {
-                const int val = c[v * pitch];
-                colSum += val;
-                m01 += v * val;
+    int m10 = 0, m01 = 0;
+    {
+        // keypoints stay >= 19 px inside the level, so rows y - 15 .. y + 15 exist and none is the last one: the
+        // aligned words around [x - 15, x + 15] never leave the image buffer.  pitch % 4 == 0: one shift for all rows.
+        const int wc = lane & 7, rg = lane >> 3;
+        const uint8_t* p = img + (size_t)(y - VIORB_HALF_PATCH) * pitch + (x - VIORB_HALF_PATCH);
+        const unsigned sh = ((unsigned)(uintptr_t)p & 3u) * 8u;
+        const uint8_t* a = p - ((uintptr_t)p & 3) + 4 * wc;
+        unsigned lo[8], hi[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int r = rg + 4 * i;
+            if (r < 31) {
+                const uint32_t* q = reinterpret_cast<const uint32_t*>(a + (size_t)r * pitch);
+                lo[i] = __ldg(q);
+                hi[i] = __ldg(q + 1);
+            } else { lo[i] = hi[i] = 0; }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int r = rg + 4 * i;
+            if (r < 31) {
+                const int v = r - VIORB_HALF_PATCH, av = v < 0 ? -v : v;
+                const unsigned b = __funnelshift_r(lo[i], hi[i], sh);
+                const int sumI = (int)__dp4a(b, (unsigned)wOnes[av][wc], 0u);
+                m10 = dp4a_us(b, wU[av][wc], m10);
+                m01 += v * sumI;
             }
         }
     }
-    int m10 = u * colSum;
     m10 = __reduce_add_sync(0xffffffffu, m10);
     m01 = __reduce_add_sync(0xffffffffu, m01);
-    if (lane == 0) {
+    // lane 0: angle + sine, lane 1: cosine (double-precision libm rounded to float32, side by side)
+    if (lane < 2) {
         const float ang = fast_atan2_deg((float)m01, (float)m10);
         const float factorPI = (float)(3.14159265358979323846 / 180.0);
-        const float rad = __fmul_rn(ang, factorPI);
-        double sn, cs;
-        sincos((double)rad, &sn, &cs);
-        kp->angle = ang;
-        kp->c = (float)cs;
-        kp->s = (float)sn;
+        const double rad = (double)__fmul_rn(ang, factorPI);
+        if (lane == 0) { kp->angle = ang; kp->s = (float)sin(rad); }
+        else kp->c = (float)cos(rad);
     }
 }
 
@@ -831,7 +878,9 @@ __global__ void __launch_bounds__(64) k_blur(ExtractGeom g, FrameSrc fs, BlurTil
     const int yEnd = min(y0 + VIORB_BLUR_TH, L.h);
     unsigned ring[7][4];
 
-    auto load_row = [&](int y, unsigned h[4]) {
+    struct Raw { unsigned w0, w1, w2; };
+    // the three aligned words of image row y around the strip (reflect-101 applied)
+    auto fetch = [&](int y) {
         const int sy = reflect101_dev(y, L.h);
         const uint8_t* row = img + (size_t)sy * pitch;
         unsigned w0, w1, w2;
@@ -861,18 +910,19 @@ __global__ void __launch_bounds__(64) k_blur(ExtractGeom g, FrameSrc fs, BlurTil
                 w[b >> 2] |= (unsigned)row[reflect101_dev(x0 - 4 + b, L.w)] << (8 * (b & 3));
             w0 = w[0]; w1 = w[1]; w2 = w[2];
         }
-        blur_row4(w0, w1, w2, h);
+        return Raw{w0, w1, w2};
     };
 
 #pragma unroll
-    for (int r = 0; r < 6; ++r) load_row(y0 - 3 + r, ring[r]);
+    for (int r = 0; r < 6; ++r) { const Raw q = fetch(y0 - 3 + r); blur_row4(q.w0, q.w1, q.w2, ring[r]); }
     for (int yb = y0; yb < yEnd; yb += 7) {
 #pragma unroll
         for (int k = 0; k < 7; ++k) {
             const int y = yb + k;
             if (y < yEnd) {
                 // rows y-3 .. y+2 sit in ring[(k+0..5) % 7]; the new row y+3 goes to ring[(k+6) % 7]
-                load_row(y + 3, ring[(k + 6) % 7]);
+                const Raw cur = fetch(y + 3);
+                blur_row4(cur.w0, cur.w1, cur.w2, ring[(k + 6) % 7]);
                 unsigned out = 0;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
@@ -894,14 +944,24 @@ __global__ void __launch_bounds__(64) k_blur(ExtractGeom g, FrameSrc fs, BlurTil
 // separately (no FMA), round-half-even.  grid (ceil(outCap/8), B), block 256.
 // ---------------------------------------------------------------------------------------------
 #define VIORB_DESC_R 18                     // largest rounded sample offset: |(13,13)| = 18.4
-#define VIORB_DESC_PW 44                    // staged patch row: 37 bytes + alignment shift, in whole words
+#define VIORB_DESC_PW 44                    // staged patch row: 37 bytes + alignment shift, in whole words (11: see i / 11 in k_describe)
+// round-half-even of |v| < 2^22 on the FMA pipe (F2I would go to the quarter-rate XU pipe): adding 1.5 * 2^23
+// leaves the integer in the low mantissa bits.  Same result as cvRound / lrintf.
+__device__ __forceinline__ int round_rn_magic(float v) {
+    return __float_as_int(__fadd_rn(v, 12582912.0f)) - 0x4B400000;
+}
+
 __global__ void __launch_bounds__(256) k_describe(ExtractGeom g, FrameSrc fs, const KeptKp* __restrict__ kept,
                                                   const int* __restrict__ slot2kept, const int* __restrict__ nOut,
                                                   uint8_t* __restrict__ desc) {
-    __shared__ __align__(16) int8_t pat[1024];
+    // pattern as float4 (x0, y0, x1, y1) per test, test (lane*8 + t) at [t*32 + lane]: conflict-free LDS.128
+    __shared__ __align__(16) float4 pat[256];
     __shared__ __align__(16) uint8_t patch[8][(2 * VIORB_DESC_R + 1) * VIORB_DESC_PW];
-    for (int i = threadIdx.x; i < 256; i += 256)
-        reinterpret_cast<uint32_t*>(pat)[i] = reinterpret_cast<const uint32_t*>(d_orb_pattern)[i];
+    {
+        const int i = threadIdx.x;                                  // test index
+        const int8_t* q = d_orb_pattern + 4 * i;
+        pat[(i & 7) * 32 + (i >> 3)] = make_float4((float)q[0], (float)q[1], (float)q[2], (float)q[3]);
+    }
     __syncthreads();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int slot = blockIdx.x * 8 + wid;
@@ -917,22 +977,29 @@ __global__ void __launch_bounds__(256) k_describe(ExtractGeom g, FrameSrc fs, co
     uint8_t* P = patch[wid];
     const uint8_t* src = img + (size_t)(k.y - VIORB_DESC_R) * L.pitch + xs;
     const int NW = VIORB_DESC_PW / 4;
-    for (int i = lane; i < (2 * VIORB_DESC_R + 1) * NW; i += 32) {
-        const int r = i / NW, c = i - r * NW;
-        reinterpret_cast<uint32_t*>(P)[i] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)r * L.pitch) + c);
+    // asynchronous global -> shared copies: all of a lane's words are in flight together (a load -> store loop
+    // serialises 13 L2 latencies per warp)
+#pragma unroll
+    for (int i0 = 0; i0 < (2 * VIORB_DESC_R + 1) * NW; i0 += 32) {
+        const int i = i0 + lane;
+        if (i < (2 * VIORB_DESC_R + 1) * NW) {
+            const int r = (i * 373) >> 12, c = i - r * NW;            // i / 11 (exact for i < 593; i < 407 here)
+            __pipeline_memcpy_async(P + 4 * i, src + (size_t)r * L.pitch + 4 * c, 4);
+        }
     }
+    __pipeline_commit();
+    __pipeline_wait_prior(0);
     __syncwarp();
     const uint8_t* ctr = P + VIORB_DESC_R * VIORB_DESC_PW + VIORB_DESC_R + shift;
     const float a = k.c, b = k.s;
     int val = 0;
 #pragma unroll
     for (int t = 0; t < 8; ++t) {
-        const int8_t* p = pat + (lane * 16 + 2 * t) * 2;
-        const float x0 = (float)p[0], y0 = (float)p[1], x1 = (float)p[2], y1 = (float)p[3];
-        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
-        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
-        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+        const float4 p = pat[t * 32 + lane];
+        const int r0 = round_rn_magic(__fadd_rn(__fmul_rn(p.x, b), __fmul_rn(p.y, a)));
+        const int c0 = round_rn_magic(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, b)));
+        const int r1 = round_rn_magic(__fadd_rn(__fmul_rn(p.z, b), __fmul_rn(p.w, a)));
+        const int c1 = round_rn_magic(__fsub_rn(__fmul_rn(p.z, a), __fmul_rn(p.w, b)));
         const int t0 = ctr[r0 * VIORB_DESC_PW + c0], t1 = ctr[r1 * VIORB_DESC_PW + c1];
         val |= (t0 < t1) << t;
     }

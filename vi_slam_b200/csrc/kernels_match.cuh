@@ -30,17 +30,19 @@ __device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, cons
            __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
-// 256-bit Hamming distance with a carry-save adder tree (Harley-Seal): POPC issues on the quarter-rate
-// XU pipe (ncu: xu 91 % busy with 8 POPC per pair), so seven of the eight XOR words are first compressed
-// by four 3:2 compressors (8 LOP3 on the ALU pipe) into ones/twos/fours words: 4 POPC instead of 8.
-__device__ __forceinline__ int hamming256_csa(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) {
+// 256-bit Hamming distance with a carry-save adder tree.  POPC issues on the XU pipe (one warp instruction per
+// 8 clocks per SM sub-partition: ncu showed xu 91 % busy with 8 POPC per pair), LOP3 / IADD3 on the ALU pipe (one
+// per 2 clocks).  Three 3:2 compressors (6 LOP3) over seven of the eight XOR words leave five words to count:
+// XU 5 x 8 = 40 clocks and ALU (8 XOR + 6 CSA + 2 IADD3 + 3 min/max) x 2 = 38 clocks per warp-pair - the balance
+// point between the two pipes (4 POPC + 8 LOP3 is ALU bound at 44, 6 POPC is XU bound at 48).
+// Returns (ones, twos) with distance = ones + 2 * twos.
+__device__ __forceinline__ int2 hamming256_csa(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) {
     const unsigned x0 = a0.x ^ b0.x, x1 = a0.y ^ b0.y, x2 = a0.z ^ b0.z, x3 = a0.w ^ b0.w;
     const unsigned x4 = a1.x ^ b1.x, x5 = a1.y ^ b1.y, x6 = a1.z ^ b1.z, x7 = a1.w ^ b1.w;
     const unsigned s0 = x0 ^ x1 ^ x2, c0 = (x0 & x1) | (x2 & (x0 ^ x1));
     const unsigned s1 = x3 ^ x4 ^ x5, c1 = (x3 & x4) | (x5 & (x3 ^ x4));
     const unsigned s2 = s0 ^ s1 ^ x6, c2 = (s0 & s1) | (x6 & (s0 ^ s1));
-    const unsigned s3 = c0 ^ c1 ^ c2, c3 = (c0 & c1) | (c2 & (c0 ^ c1));
-    return __popc(s2) + __popc(x7) + 2 * __popc(s3) + 4 * __popc(c3);
+    return make_int2(__popc(s2) + __popc(x7), __popc(c0) + __popc(c1) + __popc(c2));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -75,7 +77,9 @@ __global__ void __launch_bounds__(VIORB_KNN_THREADS) k_knn2(DescSet Q, DescSet T
 #pragma unroll 4
         for (int j = 0; j < m; ++j) {
             const uint4 b0 = tile[2 * j], b1 = tile[2 * j + 1];
-            const unsigned key = ((unsigned)hamming256_csa(a0, a1, b0, b1) << VIORB_KNN_IDX_BITS) | (kb + j);
+            // key = (ones + 2 twos) << 22 | index, built with two multiply-adds (FMA pipe, not the ALU pipe)
+            const int2 h = hamming256_csa(a0, a1, b0, b1);
+            const unsigned key = (unsigned)h.y * (2u << VIORB_KNN_IDX_BITS) + ((unsigned)h.x * (1u << VIORB_KNN_IDX_BITS) + (kb + j));
             const unsigned lo = min(key, best0);
             best1 = min(best1, max(key, best0));
             best0 = lo;
