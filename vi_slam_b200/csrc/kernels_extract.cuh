@@ -682,7 +682,6 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
     return a;
 }
 
-struct UmaxTable { int v[16]; };
 
 // dot product of 4 unsigned bytes with 4 signed bytes (IDP.4A.U8.S8)
 __device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {
@@ -701,35 +700,61 @@ __device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {
 // contiguous bytes (coalesced sectors), all 16 loads of a lane are independent, and each row word costs one funnel
 // shift and two IDP.4A against per-row weight tables built from umax: sum(I) and sum(u * I) over the row's disc
 // segment.  m01 = sum_v v * sum(I), m10 = sum_v sum(u * I); integer, so the order of the adds is free.
-__global__ void __launch_bounds__(256) k_orient(ExtractGeom g, FrameSrc fs, UmaxTable um, KeptKp* __restrict__ kept,
+// Weight tables of k_orient, built once on the host from umax: [0][|v|][k] = bytes 1 inside the disc segment of row
+// v (word k of the 32-byte row window starting at column -15), [1][|v|][k] = the column offsets u as signed bytes.
+struct OrientTab { int w[2][16][8]; };
+__host__ inline void build_orient_tab(const int* umax, OrientTab& t) {
+    for (int tb = 0; tb < 2; ++tb)
+        for (int av = 0; av < 16; ++av)
+            for (int k = 0; k < 8; ++k) {
+                unsigned w = 0;
+                for (int j = 0; j < 4; ++j) {
+                    const int col = 4 * k + j, u = col - VIORB_HALF_PATCH;
+                    if (col < 31 && (u < 0 ? -u : u) <= umax[av]) w |= (unsigned)((tb ? u : 1) & 0xFF) << (8 * j);
+                }
+                t.w[tb][av][k] = (int)w;
+            }
+}
+
+// sin and cos of x in [0, 2 pi] in double precision (Cody-Waite reduction by pi/2 in two parts, fdlibm kernel
+// polynomials, |error| < 1e-15): rounded to float32 they stand in for the reference's cosf / sinf.
+__device__ __forceinline__ void sincos_small(double x, double& sn, double& cs) {
+    const double q = rint(x * 6.36619772367581382433e-01);                     // 2 / pi
+    double r = fma(-q, 1.57079632679489655800e+00, x);                         // pi/2 high
+    r = fma(-q, 6.12323399573676603587e-17, r);                                // pi/2 low
+    const double z = r * r;
+    double ps = fma(z, 1.58969099521155010221e-10, -2.50507602534068634195e-08);
+    ps = fma(z, ps, 2.75573137070700676789e-06);
+    ps = fma(z, ps, -1.98412698298579493134e-04);
+    ps = fma(z, ps, 8.33333333332248946124e-03);
+    ps = fma(z, ps, -1.66666666666666324348e-01);
+    const double s = fma(z * r, ps, r);
+    double pc = fma(z, -1.13596475577881948265e-11, 2.08757232129817482790e-09);
+    pc = fma(z, pc, -2.75573143513906633035e-07);
+    pc = fma(z, pc, 2.48015872894767294178e-05);
+    pc = fma(z, pc, -1.38888888888741095749e-03);
+    pc = fma(z, pc, 4.16666666666666019037e-02);
+    const double c = fma(z * z, pc, fma(z, -0.5, 1.0));
+    const int n = (int)q & 3;
+    sn = (n & 1) ? c : s;
+    cs = (n & 1) ? s : c;
+    if (n & 2) sn = -sn;
+    if ((n + 1) & 2) cs = -cs;
+}
+
+__global__ void __launch_bounds__(256) k_orient(ExtractGeom g, FrameSrc fs, const int* __restrict__ orientTab,
+                                                const uint8_t* __restrict__ slotLevel, KeptKp* __restrict__ kept,
                                                 const int* __restrict__ keptCount) {
     __shared__ int wOnes[16][8], wU[16][8];           // [|v|][word]: bytes = 1 resp. u inside the disc, 0 outside
-    {
-        const int t = threadIdx.x;                    // 256 threads: table (t >> 7), row (t >> 3) & 15, word t & 7
-        const int av = (t >> 3) & 15, k = t & 7;
-        unsigned w = 0;
-        for (int j = 0; j < 4; ++j) {
-            const int col = 4 * k + j, u = col - VIORB_HALF_PATCH;
-            const bool in = col < 31 && (u < 0 ? -u : u) <= um.v[av];
-            const int val = (t >> 7) ? u : 1;
-            if (in) w |= (unsigned)(val & 0xFF) << (8 * j);
-        }
-        if (t >> 7) wU[av][k] = (int)w; else wOnes[av][k] = (int)w;
-    }
+    if (threadIdx.x < 128) (&wOnes[0][0])[threadIdx.x] = orientTab[threadIdx.x];
+    else (&wU[0][0])[threadIdx.x - 128] = orientTab[threadIdx.x];
     __syncthreads();
     const int lane = threadIdx.x & 31;
     const int slot = blockIdx.x * 8 + (threadIdx.x >> 5);
     const int f = blockIdx.y + g.frame0;
     if (slot >= g.keptPerFrame) return;
-    // level of this slot: lane i tests level i
-    bool mine = false;
-    if (lane < g.nlevels) {
-        const int o = g.lv[lane].keptOff;
-        mine = slot >= o && slot < o + keptCount[f * g.nlevels + lane];
-    }
-    const unsigned lm = __ballot_sync(0xffffffffu, mine);
-    if (lm == 0) return;
-    const int l = __ffs(lm) - 1;
+    const int l = slotLevel[slot];                    // the level whose slice of the kept arena holds this slot
+    if (slot - g.lv[l].keptOff >= keptCount[f * g.nlevels + l]) return;
     KeptKp* kp = kept + (size_t)f * g.keptPerFrame + slot;
     int pitch;
     const uint8_t* img = level_ptr(g, fs, l, f, pitch);
@@ -766,13 +791,14 @@ __global__ void __launch_bounds__(256) k_orient(ExtractGeom g, FrameSrc fs, Umax
     }
     m10 = __reduce_add_sync(0xffffffffu, m10);
     m01 = __reduce_add_sync(0xffffffffu, m01);
-    // lane 0: angle + sine, lane 1: cosine (double-precision libm rounded to float32, side by side)
-    if (lane < 2) {
+    if (lane == 0) {
         const float ang = fast_atan2_deg((float)m01, (float)m10);
         const float factorPI = (float)(3.14159265358979323846 / 180.0);
-        const double rad = (double)__fmul_rn(ang, factorPI);
-        if (lane == 0) { kp->angle = ang; kp->s = (float)sin(rad); }
-        else kp->c = (float)cos(rad);
+        double sn, cs;
+        sincos_small((double)__fmul_rn(ang, factorPI), sn, cs);
+        kp->angle = ang;
+        kp->c = (float)cs;
+        kp->s = (float)sn;
     }
 }
 

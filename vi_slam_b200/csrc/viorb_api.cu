@@ -68,7 +68,7 @@ struct viorb_extractor {
     // FExtractor ctor tables (fextractor.cpp:401-461)
     float scale[VIORB_MAX_LEVELS], invScale[VIORB_MAX_LEVELS], sigma2[VIORB_MAX_LEVELS], invSigma2[VIORB_MAX_LEVELS];
     int featPerLevel[VIORB_MAX_LEVELS];
-    UmaxTable umax;
+    int umaxv[16];
     // geometry of the current image size
     ExtractGeom g;
     BlurTiles blurTiles;
@@ -94,6 +94,8 @@ struct viorb_extractor {
     DevBuf<KeptKp> dKept;
     DevBuf<viorb_keypoint> dKps;
     DevBuf<CellDesc> dCells;
+    DevBuf<int> dOrientTab;
+    DevBuf<uint8_t> dSlotLevel;
     // stereo / matching results of the last viorb_stereo_batch on this (left) handle
     DevBuf<int32_t> dBestIdx, dBestDist, dSad, dKnnIdx, dKnnDist, dLrMatch;
     DevBuf<float> dURight, dDepth;
@@ -141,7 +143,7 @@ void build_tables(viorb_extractor* ex) {
     }
     ex->featPerLevel[nl - 1] = std::max(p.nfeatures - sum, 0);
     // umax: end of each row of the radius-15 disc, made symmetric (fextractor.cpp:444-460)
-    int* um = ex->umax.v;
+    int* um = ex->umaxv;
     const int hp = VIORB_HALF_PATCH;
     const int vmax = (int)std::floor(hp * std::sqrt(2.f) / 2 + 1);
     const int vmin = (int)std::ceil(hp * std::sqrt(2.f) / 2);
@@ -307,6 +309,13 @@ int upload_geometry(viorb_extractor* ex, const ResizeTabs& tabs) {
     CU(cudaMemcpyAsync(ex->dXalpha.p, tabs.xalpha.data(), tabs.xalpha.size() * sizeof(short2), cudaMemcpyHostToDevice, ex->stream));
     CU(cudaMemcpyAsync(ex->dYofs.p, tabs.yofs.data(), tabs.yofs.size() * sizeof(int), cudaMemcpyHostToDevice, ex->stream));
     CU(cudaMemcpyAsync(ex->dYbeta.p, tabs.ybeta.data(), tabs.ybeta.size() * sizeof(short2), cudaMemcpyHostToDevice, ex->stream));
+    std::vector<uint8_t> slotLevel((size_t)ex->g.keptPerFrame, 0);
+    for (int l = 0; l < ex->g.nlevels; ++l)
+        for (int i = 0; i < ex->g.lv[l].keptCap; ++i) slotLevel[ex->g.lv[l].keptOff + i] = (uint8_t)l;
+    CU(cudaMemcpyAsync(ex->dSlotLevel.p, slotLevel.data(), slotLevel.size(), cudaMemcpyHostToDevice, ex->stream));
+    OrientTab ot;
+    build_orient_tab(ex->umaxv, ot);
+    CU(cudaMemcpyAsync(ex->dOrientTab.p, &ot, sizeof ot, cudaMemcpyHostToDevice, ex->stream));
     CU(cudaStreamSynchronize(ex->stream));      // the host vectors go out of scope
     return VIORB_OK;
 }
@@ -359,7 +368,8 @@ int run_pipeline(viorb_extractor* ex, int f0, int n, int lap0, int lap1) {
     VIORB_LAUNCH(k_octree, dim3(g.nlevels, n), dim3(VIORB_OCT_THREADS), ex->octSmem, st, g, ex->dCand.p, ex->dCandCount.p,
                  ex->dKeyNode.p, ex->dKept.p, ex->dKeptCount.p, ex->dStatus.p);
     if (tm) CU(cudaEventRecord(ex->evX[3], st));
-    VIORB_LAUNCH(k_orient, dim3((g.keptPerFrame + 7) / 8, n), dim3(256), 0, st, g, fs, ex->umax, ex->dKept.p, ex->dKeptCount.p);
+    VIORB_LAUNCH(k_orient, dim3((g.keptPerFrame + 7) / 8, n), dim3(256), 0, st, g, fs, ex->dOrientTab.p, ex->dSlotLevel.p, ex->dKept.p,
+                 ex->dKeptCount.p);
     if (tm) CU(cudaEventRecord(ex->evX[4], st));
     VIORB_LAUNCH(k_emit, dim3(n), dim3(256), 0, st, g, ex->dKept.p, ex->dKeptCount.p, lap0, lap1, ex->dKps.p,
                  ex->dSlot2Kept.p, ex->dNOut.p, ex->dMono.p);
@@ -531,6 +541,8 @@ int viorb_extractor_create(const viorb_params* params, viorb_extractor** out) {
     ok(ex->dMono.alloc(B));
     ok(ex->dStatus.alloc(1));
     ok(ex->dCells.alloc(ex->capCells));
+    ok(ex->dOrientTab.alloc(256));
+    ok(ex->dSlotLevel.alloc(ex->capKept));
     ok(ex->dXofs.alloc(ex->capXTab));
     ok(ex->dXalpha.alloc(ex->capXTab));
     ok(ex->dYofs.alloc(ex->capYTab));
@@ -568,6 +580,7 @@ void viorb_extractor_destroy(viorb_extractor* ex) {
     ex->dKeyNode.release(); ex->dCandCount.release(); ex->dKeptCount.release(); ex->dSlot2Kept.release();
     ex->dNOut.release(); ex->dMono.release(); ex->dStatus.release(); ex->dXofs.release(); ex->dYofs.release();
     ex->dXalpha.release(); ex->dYbeta.release(); ex->dKept.release(); ex->dKps.release(); ex->dCells.release();
+    ex->dOrientTab.release(); ex->dSlotLevel.release();
     ex->dBestIdx.release(); ex->dBestDist.release(); ex->dSad.release(); ex->dKnnIdx.release(); ex->dKnnDist.release();
     ex->dLrMatch.release(); ex->dURight.release(); ex->dDepth.release(); ex->dNStereo.release(); ex->dNRatio.release();
     ex->dMatches.release(); ex->dRowStart.release(); ex->dRowList.release(); ex->dRMeta.release();
