@@ -883,72 +883,64 @@ __device__ __forceinline__ void blur_row4(unsigned w0, unsigned w1, unsigned w2,
     h[3] = __dp4a(w1, K0, __dp4a(w2, K1, 0u));
 }
 
-// Each thread owns a 4-pixel-wide column strip and walks down VIORB_BLUR_TH output rows keeping the last
-// seven row sums in registers (the loop is unrolled by 7 so the ring needs no moves): per row 3 aligned
-// 32-bit loads, 6 funnel shifts + 8 IDP.4A for the row pass, 28 multiply-adds for the column pass and one
-// 32-bit store.  Strips touching the left/right image border take a byte-wise reflect-101 path.
+// One CTA = one 256 x 32 output tile.  The tile plus a 3-row / 16-byte apron is staged in shared memory with
+// 16-byte cp.async copies (every load of the CTA is in flight at once; ncu showed the previous register-only
+// version stalled on long-scoreboard global loads at 43 % occupancy and on instruction fetch of its three
+// border paths).  Chunks that touch the image border are filled byte-wise with BORDER_REFLECT_101, so the
+// compute phase is branch-free: each thread owns a 4-pixel column strip and walks down the rows keeping the
+// last seven row sums in registers (unrolled by 7, the ring needs no moves): per row 3 LDS, 6 funnel shifts +
+// 8 IDP.4A for the row pass, 28 multiply-adds for the column pass and one 32-bit store.
 // grid (totalBlurTiles, B), block 64.
+#define VIORB_BLUR_SP (VIORB_BLUR_TW + 32)       // shared row pitch: 16-byte apron left and right
 __global__ void __launch_bounds__(64) k_blur(ExtractGeom g, FrameSrc fs, BlurTiles bt) {
+    __shared__ __align__(16) uint8_t tile[(VIORB_BLUR_TH + 6) * VIORB_BLUR_SP];
     const int f = blockIdx.y + g.frame0;
     int l = 0;
     while (l + 1 < g.nlevels && (int)blockIdx.x >= bt.base[l + 1]) ++l;
     const LevelGeom& L = g.lv[l];
     const int t = blockIdx.x - bt.base[l];
-    const int x0 = (t % bt.tilesX[l]) * VIORB_BLUR_TW + threadIdx.x * 4;
-    const int y0 = (t / bt.tilesX[l]) * VIORB_BLUR_TH;
-    if (x0 >= L.w) return;
+    const int ty = t / bt.tilesX[l], tx = t - ty * bt.tilesX[l];
+    const int X0 = tx * VIORB_BLUR_TW, y0 = ty * VIORB_BLUR_TH;
     int pitch;
     const uint8_t* img = level_ptr(g, fs, l, f, pitch);
     uint8_t* dst = fs.blur + (size_t)f * g.arenaStride + L.off;
-    const bool interior = x0 >= 4 && x0 + 6 < L.w && x0 + 8 <= pitch;
     const int yEnd = min(y0 + VIORB_BLUR_TH, L.h);
-    unsigned ring[7][4];
-
-    struct Raw { unsigned w0, w1, w2; };
-    // the three aligned words of image row y around the strip (reflect-101 applied)
-    auto fetch = [&](int y) {
-        const int sy = reflect101_dev(y, L.h);
-        const uint8_t* row = img + (size_t)sy * pitch;
-        unsigned w0, w1, w2;
-        if (interior) {
-            const uint32_t* p = reinterpret_cast<const uint32_t*>(row + x0);
-            w0 = __ldg(p - 1); w1 = __ldg(p); w2 = __ldg(p + 1);
-        } else if (L.w >= 8) {
-            // border strips: whole words where they start inside the row, mirrored columns patched in
-            const uint32_t* p = reinterpret_cast<const uint32_t*>(row + x0);
-            unsigned w[3];
-            w[1] = __ldg(p);
-            w[0] = x0 >= 4 ? __ldg(p - 1) : __byte_perm(w[1], 0, 0x1230);      // columns -3..-1 mirror 3..1
-            w[2] = x0 + 8 <= pitch ? __ldg(p + 1) : 0u;
-#pragma unroll
-            for (int b = 5; b < 11; ++b) {
-                const int col = x0 - 4 + b;
-                if (col >= L.w) {
-                    const unsigned v = row[2 * (L.w - 1) - col];
-                    w[b >> 2] = (w[b >> 2] & ~(0xFFu << (8 * (b & 3)))) | (v << (8 * (b & 3)));
-                }
+    const int nrows = yEnd - y0 + 6;
+    const int NCH = VIORB_BLUR_SP / 16;              // 18 chunks per staged row
+    for (int i = threadIdx.x; i < nrows * NCH; i += 64) {
+        const int r = (i * 3641) >> 16, c = i - r * NCH;            // i / 18 for i < 2^13
+        const int sy = reflect101_dev(y0 - 3 + r, L.h);
+        const int cx = X0 - 16 + 16 * c;
+        uint8_t* d = tile + r * VIORB_BLUR_SP + 16 * c;
+        const uint8_t* srow = img + (size_t)sy * pitch;
+        if (cx >= 0 && cx + 16 <= L.w) {
+            __pipeline_memcpy_async(d, srow + cx, 16);
+        } else if (cx + 16 > -3 && cx < L.w + 3) {
+            for (int b = 0; b < 16; ++b) {
+                const int col = cx + b;
+                if (col >= -3 && col < L.w + 3) d[b] = srow[reflect101_dev(col, L.w)];
             }
-            w0 = w[0]; w1 = w[1]; w2 = w[2];
-        } else {
-            unsigned w[3] = {0, 0, 0};
-#pragma unroll
-            for (int b = 1; b < 11; ++b)
-                w[b >> 2] |= (unsigned)row[reflect101_dev(x0 - 4 + b, L.w)] << (8 * (b & 3));
-            w0 = w[0]; w1 = w[1]; w2 = w[2];
         }
-        return Raw{w0, w1, w2};
-    };
-
+    }
+    __pipeline_commit();
+    __pipeline_wait_prior(0);
+    __syncthreads();
+    const int x0 = X0 + threadIdx.x * 4;
+    if (x0 >= L.w) return;
+    const uint32_t* col = reinterpret_cast<const uint32_t*>(tile + 16 + threadIdx.x * 4);
+    const int SPW = VIORB_BLUR_SP / 4;
+    unsigned ring[7][4];
 #pragma unroll
-    for (int r = 0; r < 6; ++r) { const Raw q = fetch(y0 - 3 + r); blur_row4(q.w0, q.w1, q.w2, ring[r]); }
+    for (int r = 0; r < 6; ++r) blur_row4(col[r * SPW - 1], col[r * SPW], col[r * SPW + 1], ring[r]);
+    const uint32_t* nxt = col + 6 * SPW;             // staged row of image row y + 3
     for (int yb = y0; yb < yEnd; yb += 7) {
 #pragma unroll
         for (int k = 0; k < 7; ++k) {
             const int y = yb + k;
             if (y < yEnd) {
                 // rows y-3 .. y+2 sit in ring[(k+0..5) % 7]; the new row y+3 goes to ring[(k+6) % 7]
-                const Raw cur = fetch(y + 3);
-                blur_row4(cur.w0, cur.w1, cur.w2, ring[(k + 6) % 7]);
+                blur_row4(nxt[-1], nxt[0], nxt[1], ring[(k + 6) % 7]);
+                nxt += SPW;
                 unsigned out = 0;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
