@@ -134,6 +134,29 @@ __device__ __forceinline__ int fast_score16(const uint8_t* p, const int* o) {
     return max(a, -b) - 1;
 }
 
+// cornerScore<16> of TWO pixels at once in s16x2 lanes (pixel A low, pixel B high): the 96 min/max of the
+// arc network are shared, the ring bytes are packed with one multiply-add (FMA pipe) per ring position.
+// Returns (scoreA & 0xFFFF) | scoreB << 16 (scores may be negative = not a corner).
+__device__ __forceinline__ unsigned fast_score16x2(const uint8_t* pa, const uint8_t* pb, const int* o) {
+    const unsigned v = (unsigned)pa[0] + ((unsigned)pb[0] << 16);
+    unsigned d[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) d[k] = __vsub2(v, (unsigned)pb[o[k]] * 65536u + (unsigned)pa[o[k]]);
+    unsigned t[16], u[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        t[k] = __vimin3_s16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+        u[k] = __vimax3_s16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+    }
+    unsigned a = 0xFF00FF00u, b = 0x01000100u;          // -256 / +256 per lane
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        a = __vmaxs2(a, __vimin3_s16x2(t[k], t[(k + 3) & 15], t[(k + 6) & 15]));
+        b = __vmins2(b, __vimax3_s16x2(u[k], u[(k + 3) & 15], u[(k + 6) & 15]));
+    }
+    return __vsub2(__vmaxs2(a, __vsub2(0u, b)), 0x00010001u);
+}
+
 // shared-memory layout of one k_fast CTA (all sizes from ExtractGeom::tileW/tileH = max region + 6)
 __host__ __device__ inline int fast_tile_pitch(int tileW) { return ((tileW + 19 + 8 + 15) >> 4) << 4; }   // bytes: alignment shift + region + halo + pad word, whole 16-byte chunks
 __host__ __device__ inline int fast_score_pitch(int tileW) { return (tileW - 4 + 3) & ~3; }             // region + ring
@@ -215,21 +238,23 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
     const int col0 = shift + 3;                             // tile column of region pixel 0
     const uint8_t* T0 = T + 3 * TP + col0;                  // region pixel (0,0)
 
-    // phase A: 4 horizontally adjacent pixels (one aligned tile word) per thread, packed 16x2 pre-test
+    // phase A: one warp per tile row, lane = aligned tile word (4 horizontally adjacent pixels), packed 16x2
+    // pre-test.  Pixels that may be corners go to the queue; its order is irrelevant, so a thread claims its
+    // slots with one shared-memory atomic (MIO pipe) instead of a warp scan (the kernel is ALU-pipe bound).
     {
-        const int g0 = col0 >> 2, g1 = (col0 + rw - 1) >> 2, ng = g1 - g0 + 1;
-        const unsigned ginv = (1u << 20) / (unsigned)ng + 1;                     // i / ng for i < 16384
+        const int g0 = col0 >> 2, g1 = (col0 + rw - 1) >> 2;
         const unsigned thp = (unsigned)th | ((unsigned)th << 16);
         const unsigned nthp1 = ((0x10000u - (unsigned)(th + 1)) & 0xFFFFu) * 0x10001u;     // -(th+1) in both lanes
-        const int total = ng * rh;
-        for (int base = 0; base < total; base += VIORB_FAST_THREADS) {
-            const int i = base + tid;
-            unsigned pass = 0;              // bit j: pixel j of the group goes to the queue
-            int py = 0, gx = 0;
-            if (i < total) {
-                py = (int)(((unsigned)i * ginv) >> 20);
-                gx = g0 + (i - py * ng);
-                const uint32_t* R = reinterpret_cast<const uint32_t*>(T + (py + 3) * TP) + gx;
+        // pixels of the first / last word that lie inside the region, as 0x8000-per-lane masks (a: px 0,1; b: px 2,3)
+        const int s0 = col0 - 4 * g0, e1 = col0 + rw - 1 - 4 * g1;
+        const unsigned firstA = (s0 <= 0 ? 0x8000u : 0u) | (s0 <= 1 ? 0x80000000u : 0u);
+        const unsigned firstB = (s0 <= 2 ? 0x8000u : 0u) | 0x80000000u;
+        const unsigned lastA = 0x8000u | (e1 >= 1 ? 0x80000000u : 0u);
+        const unsigned lastB = (e1 >= 2 ? 0x8000u : 0u) | (e1 >= 3 ? 0x80000000u : 0u);
+        for (int py = tid >> 5; py < rh; py += VIORB_FAST_THREADS / 32) {
+            const uint32_t* Rrow = reinterpret_cast<const uint32_t*>(T + (py + 3) * TP);
+            for (int gx = g0 + lane; gx <= g1; gx += 32) {
+                const uint32_t* R = Rrow + gx;
                 const unsigned cw = R[0], wl = R[-1], wr = R[1];
                 const unsigned up = R[-3 * TPW], dn = R[3 * TPW];
                 const unsigned rt = __funnelshift_r(cw, wr, 24), lf = __funnelshift_r(wl, cw, 8);
@@ -237,50 +262,38 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
                 const uint32_t* Rm = R - 2 * TPW;
                 const unsigned d22 = __funnelshift_r(Rp[0], Rp[1], 16), dm22 = __funnelshift_r(Rp[-1], Rp[0], 16);
                 const unsigned d2m2 = __funnelshift_r(Rm[0], Rm[1], 16), dm2m2 = __funnelshift_r(Rm[-1], Rm[0], 16);
-                const unsigned a = fast_pretest2(lo16x2(cw), lo16x2(up), lo16x2(dn), lo16x2(lf), lo16x2(rt), lo16x2(d22),
-                                                 lo16x2(dm2m2), lo16x2(d2m2), lo16x2(dm22), nthp1, thp);
-                const unsigned b = fast_pretest2(hi16x2(cw), hi16x2(up), hi16x2(dn), hi16x2(lf), hi16x2(rt), hi16x2(d22),
-                                                 hi16x2(dm2m2), hi16x2(d2m2), hi16x2(dm22), nthp1, thp);
-                pass = ((a >> 15) & 1) | ((a >> 30) & 2) | ((b >> 13) & 4) | ((b >> 28) & 8);
-                // drop the pixels of the word that lie outside the region
-                const int px0 = gx * 4 - col0;
-                unsigned m = 0xF;
-                if (px0 < 0) m &= 0xFu << (-px0);
-                if (px0 + 3 >= rw) m &= 0xFu >> (px0 + 4 - rw);
-                pass &= m;
-            }
-            // warp-wide exclusive scan of popc(pass), one shared atomic per warp
-            const int cnt = __popc(pass);
-            int inc = cnt;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const int t = __shfl_up_sync(0xffffffffu, inc, d);
-                if (lane >= d) inc += t;
-            }
-            const int tot = __shfl_sync(0xffffffffu, inc, 31);
-            if (tot) {
-                int qb = 0;
-                if (lane == 31) qb = atomicAdd(&qCount, tot);
-                qb = __shfl_sync(0xffffffffu, qb, 31) + inc - cnt;
-                const int e0 = (py << 9) + (gx * 4 - col0);       // valid pixels have px0 + j >= 0
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    if (pass >> j & 1) Q[qb++] = (uint16_t)(e0 + j);
+                unsigned a = fast_pretest2(lo16x2(cw), lo16x2(up), lo16x2(dn), lo16x2(lf), lo16x2(rt), lo16x2(d22),
+                                           lo16x2(dm2m2), lo16x2(d2m2), lo16x2(dm22), nthp1, thp);
+                unsigned b = fast_pretest2(hi16x2(cw), hi16x2(up), hi16x2(dn), hi16x2(lf), hi16x2(rt), hi16x2(d22),
+                                           hi16x2(dm2m2), hi16x2(d2m2), hi16x2(dm22), nthp1, thp);
+                if (gx == g0) { a &= firstA; b &= firstB; }
+                if (gx == g1) { a &= lastA; b &= lastB; }
+                const unsigned ab = a | (b >> 1);
+                if (ab) {
+                    int q = atomicAdd(&qCount, __popc(ab));
+                    const int e0 = (py << 9) + (gx * 4 - col0);       // valid pixels have e0 + j >= py << 9
+                    if (a & 0x8000u) Q[q++] = (uint16_t)e0;
+                    if (a & 0x80000000u) Q[q++] = (uint16_t)(e0 + 1);
+                    if (b & 0x8000u) Q[q++] = (uint16_t)(e0 + 2);
+                    if (b & 0x80000000u) Q[q++] = (uint16_t)(e0 + 3);
+                }
             }
         }
     }
     __syncthreads();
     const int nq = qCount;
 
-    // phase B: dense corner score on the queue
+    // phase B: dense corner score on the queue, two queued pixels per thread (s16x2 lanes)
     {
         const int o[16] = {3 * TP, 3 * TP + 1, 2 * TP + 2, TP + 3, 3, -TP + 3, -2 * TP + 2, -3 * TP + 1,
                            -3 * TP, -3 * TP - 1, -2 * TP - 2, -TP - 3, -3, TP - 3, 2 * TP - 2, 3 * TP - 1};
-        for (int i = tid; i < nq; i += VIORB_FAST_THREADS) {
-            const int e = Q[i];
-            const int py = e >> 9, px = e & 511;
-            const int sc = fast_score16(T0 + py * TP + px, o);
-            if (sc >= th) S[(py + 1) * SP + px + 1] = (uint8_t)sc;
+        for (int i = 2 * tid; i < nq; i += 2 * VIORB_FAST_THREADS) {
+            const int ea = Q[i], eb = Q[min(i + 1, nq - 1)];
+            const int pya = ea >> 9, pxa = ea & 511, pyb = eb >> 9, pxb = eb & 511;
+            const unsigned sc = fast_score16x2(T0 + pya * TP + pxa, T0 + pyb * TP + pxb, o);
+            const int sa = (int)(short)(sc & 0xFFFF), sb = (int)sc >> 16;
+            if (sa >= th) S[(pya + 1) * SP + pxa + 1] = (uint8_t)sa;
+            if (sb >= th) S[(pyb + 1) * SP + pxb + 1] = (uint8_t)sb;
         }
     }
     __syncthreads();
@@ -289,32 +302,21 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
     // another cell do not count (cv::FAST ran per cell): rows outside the strip are the zero ring of S, columns
     // across a cell boundary are masked here.
     const unsigned cinv = (1u << 20) / (unsigned)wCell + 1;                       // px / wCell for px < 16384
-    for (int base = 0; base < nq; base += VIORB_FAST_THREADS) {
-        const int i = base + tid;
-        bool keep = false;
-        uint32_t e = 0;
-        if (i < nq) {
-            const int q = Q[i];
-            const int py = q >> 9, px = q & 511;
-            const int cell = min((int)(((unsigned)px * cinv) >> 20), ncell - 1);
-            const int cl = px - cell * wCell;
-            const bool hasL = cl > 0, hasR = cl < wCell - 1;      // the strip's own ends fall on the zero ring
-            const uint8_t* s = S + (py + 1) * SP + px + 1;
-            const int v = s[0];
-            const int mc = max((int)s[-SP], (int)s[SP]);
-            const int ml = hasL ? __vimax3_s32(s[-SP - 1], s[-1], s[SP - 1]) : 0;
-            const int mr = hasR ? __vimax3_s32(s[-SP + 1], s[1], s[SP + 1]) : 0;
-            keep = v > __vimax3_s32(mc, ml, mr);                  // v == 0 (not a corner) is never kept
-            e = (uint32_t)(c.x0 + px - VIORB_MINB) | ((uint32_t)(c.y0 + py - VIORB_MINB) << 12) | ((uint32_t)v << 24);
-            if (keep && v >= g.iniTh) hasIni[cell] = 1;
-        }
-        const unsigned mk = __ballot_sync(0xffffffffu, keep);
-        if (mk) {
-            const int leader = __ffs(mk) - 1;
-            int sb = 0;
-            if (lane == leader) sb = atomicAdd(&sCount, __popc(mk));
-            sb = __shfl_sync(0xffffffffu, sb, leader);
-            if (keep) surv[sb + __popc(mk & ((1u << lane) - 1))] = e;
+    for (int i = tid; i < nq; i += VIORB_FAST_THREADS) {
+        const int q = Q[i];
+        const int py = q >> 9, px = q & 511;
+        const uint8_t* s = S + (py + 1) * SP + px + 1;
+        const int v = s[0];
+        if (v == 0) continue;                                  // not a corner
+        const int cell = min((int)(((unsigned)px * cinv) >> 20), ncell - 1);
+        const int cl = px - cell * wCell;
+        const bool hasL = cl > 0, hasR = cl < wCell - 1;      // the strip's own ends fall on the zero ring
+        const int mc = max((int)s[-SP], (int)s[SP]);
+        const int ml = hasL ? __vimax3_s32(s[-SP - 1], s[-1], s[SP - 1]) : 0;
+        const int mr = hasR ? __vimax3_s32(s[-SP + 1], s[1], s[SP + 1]) : 0;
+        if (v > __vimax3_s32(mc, ml, mr)) {
+            if (v >= g.iniTh) hasIni[cell] = 1;
+            surv[atomicAdd(&sCount, 1)] = (uint32_t)(c.x0 + px - VIORB_MINB) | ((uint32_t)(c.y0 + py - VIORB_MINB) << 12) | ((uint32_t)v << 24);
         }
     }
     __syncthreads();
