@@ -238,7 +238,7 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
     const int col0 = shift + 3;                             // tile column of region pixel 0
     const uint8_t* T0 = T + 3 * TP + col0;                  // region pixel (0,0)
 
-    // phase A: one warp per tile row, lane = aligned tile word (4 horizontally adjacent pixels), packed 16x2
+    // phase A: thread = aligned tile word (4 horizontally adjacent pixels) of the flattened region, packed 16x2
     // pre-test.  Pixels that may be corners go to the queue; its order is irrelevant, so a thread claims its
     // slots with one shared-memory atomic (MIO pipe) instead of a warp scan (the kernel is ALU-pipe bound).
     {
@@ -251,10 +251,13 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
         const unsigned firstB = (s0 <= 2 ? 0x8000u : 0u) | 0x80000000u;
         const unsigned lastA = 0x8000u | (e1 >= 1 ? 0x80000000u : 0u);
         const unsigned lastB = (e1 >= 2 ? 0x8000u : 0u) | (e1 >= 3 ? 0x80000000u : 0u);
-        for (int py = tid >> 5; py < rh; py += VIORB_FAST_THREADS / 32) {
-            const uint32_t* Rrow = reinterpret_cast<const uint32_t*>(T + (py + 3) * TP);
-            for (int gx = g0 + lane; gx <= g1; gx += 32) {
-                const uint32_t* R = Rrow + gx;
+        const int ng = g1 - g0 + 1, total = ng * rh;
+        const unsigned ginv = (1u << 22) / (unsigned)ng + 1;     // i / ng = (i * ginv) >> 22, exact while i * ng < 2^22 (ng <= 130, rh <= 127)
+        {
+            for (int i = tid; i < total; i += VIORB_FAST_THREADS) {
+                const int py = (int)(((unsigned)i * ginv) >> 22);
+                const int gx = g0 + (i - py * ng);
+                const uint32_t* R = reinterpret_cast<const uint32_t*>(T + (py + 3) * TP) + gx;
                 const unsigned cw = R[0], wl = R[-1], wr = R[1];
                 const unsigned up = R[-3 * TPW], dn = R[3 * TPW];
                 const unsigned rt = __funnelshift_r(cw, wr, 24), lf = __funnelshift_r(wl, cw, 8);
