@@ -423,6 +423,7 @@ static inline unsigned __vmaxs2(unsigned a, unsigned b) { return emu_pack16(std:
 static inline unsigned __vmins2(unsigned a, unsigned b) { return emu_pack16(std::min(emu_lo16(a), emu_lo16(b)), std::min(emu_hi16(a), emu_hi16(b))); }
 static inline unsigned __vimax3_s16x2(unsigned a, unsigned b, unsigned c) { return __vmaxs2(__vmaxs2(a, b), c); }
 static inline unsigned __vimin3_s16x2(unsigned a, unsigned b, unsigned c) { return __vmins2(__vmins2(a, b), c); }
+static inline unsigned __dp2a_lo(unsigned a, unsigned b, unsigned c) { return c + (a & 0xFFFFu) * (b & 0xFFu) + (a >> 16) * ((b >> 8) & 0xFFu); }
 static inline unsigned __dp4a(unsigned a, unsigned b, unsigned c) {
     for (int i = 0; i < 4; ++i) c += ((a >> (8 * i)) & 0xFF) * ((b >> (8 * i)) & 0xFF);
     return c;

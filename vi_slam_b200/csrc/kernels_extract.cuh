@@ -67,6 +67,56 @@ __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int 
         a0[i] = (short)(ar[i] & 0xFFFF);
         a1[i] = ar[i] >> 16;
     }
+    if (L.rsWords) {
+        // word path: a source row contributes three aligned 32-bit loads; the (left, right) byte pair of each output
+        // pixel is picked with one PRMT and weighted with one IDP.2A (alpha pair as u16x2) - instead of two byte
+        // loads and two multiply-adds per pixel and row
+        const int wb = o0[0] >> 2;
+        const int lastWord = (sp >> 2) - 1;
+        const int w0i = min(wb, lastWord), w1i = min(wb + 1, lastWord), w2i = min(wb + 2, lastWord);
+        unsigned sel[4];
+        bool hi[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int o = o0[i] - 4 * wb;                 // 0 .. 10
+            hi[i] = o > 6;
+            const int b = hi[i] ? o - 4 : o;              // first byte inside the chosen register pair
+            sel[i] = (unsigned)b | ((unsigned)(b + 1) << 4);
+        }
+        unsigned g0[4], g1[4];
+        int haveRow = -0x40000000;
+        auto hpass = [&](int sy, unsigned h[4]) {
+            const uint32_t* r = reinterpret_cast<const uint32_t*>(src + (size_t)sy * sp);
+            const unsigned a = __ldg(r + w0i), b = __ldg(r + w1i), c = __ldg(r + w2i);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                h[i] = __dp2a_lo((unsigned)ar[i], __byte_perm(hi[i] ? b : a, hi[i] ? c : b, sel[i]), 0u);
+        };
+        for (int r = 0; r < nrow; ++r) {
+            const int dy = dy0 + r;
+            const int sy = __ldg(yofs + L.yTab + dy);
+            const short2 bt = __ldg(ybeta + L.yTab + dy);
+            const int sy0 = min(max(sy, 0), S.h - 1), sy1 = min(max(sy + 1, 0), S.h - 1);
+            if (haveRow == sy0) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) g0[i] = g1[i];
+            } else {
+                hpass(sy0, g0);
+            }
+            hpass(sy1, g1);
+            haveRow = sy1;
+            uint32_t packed = 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int v = ((((int)bt.x * ((int)g0[i] >> 4)) >> 16) + (((int)bt.y * ((int)g1[i] >> 4)) >> 16) + 2) >> 2;
+                packed |= (uint32_t)(v & 0xFF) << (8 * i);
+            }
+            uint8_t* d = dst + (size_t)dy * L.pitch + x4;
+            if (x4 + 3 < L.w) *reinterpret_cast<uint32_t*>(d) = packed;
+            else for (int i = 0; i < 4 && x4 + i < L.w; ++i) d[i] = (uint8_t)(packed >> (8 * i));
+        }
+        return;
+    }
     int h0[4], h1[4], have = -0x40000000;       // source row whose horizontal pass sits in h1
     for (int r = 0; r < nrow; ++r) {
         const int dy = dy0 + r;

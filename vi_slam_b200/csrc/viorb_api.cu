@@ -217,6 +217,16 @@ int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
             const LevelGeom& S = g.lv[l - 1];
             L.areaHalf = (S.w == 2 * L.w && S.h == 2 * L.h) ? 1 : 0;
             build_resize_tables(S.w, S.h, L.w, L.h, tabs);
+            // word path of k_resize: the two source columns of each of the 4 pixels of a group lie within 12 bytes
+            // of the aligned word holding the group's first column (true for any scale factor <= 2)
+            L.rsWords = 1;
+            for (size_t k = (size_t)L.xTab; k + 3 < tabs.xofs.size(); k += 4) {
+                const int wb = tabs.xofs[k] & ~3;
+                for (int i = 0; i < 4 && (int)(k - L.xTab) + i < L.w; ++i) {      // the table's padding entries do not count
+                    const int o = tabs.xofs[k + i] - wb;
+                    if (o < 0 || o + 1 > 11) L.rsWords = 0;
+                }
+            }
         }
         // FAST cell grid (fextractor.cpp:769-806)
         const float width = (float)(L.maxBX - VIORB_MINB), height = (float)(L.maxBY - VIORB_MINB);

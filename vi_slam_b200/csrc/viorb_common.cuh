@@ -37,6 +37,7 @@ struct LevelGeom {
     int keptOff, keptCap;  // slice of one frame's kept-keypoint arena
     int xTab, yTab;        // offsets into the resize coefficient tables (entries)
     int areaHalf;          // 1: exact 2x decimation (INTER_AREA fast path)
+    int rsWords;           // 1: every 4-pixel output group reads <= 12 source bytes from its first aligned word (k_resize word path)
     float scale;           // mvScaleFactor[l]
     float kpSize;          // (float)(int)(31 * scale)
 };
