@@ -97,6 +97,151 @@ __global__ void __launch_bounds__(VIORB_KNN_THREADS) k_knn2(DescSet Q, DescSet T
 }
 
 // ---------------------------------------------------------------------------------------------
+// Brute-force Hamming 2-NN on the tensor cores.  Hamming(a, b) = popc(a) + popc(b) - 2 a.b, and the dot product
+// of two 256-bit rows is an integer GEMM once the bits are expanded to {0,1} bytes.  sm_100a has no native
+// 1-bit MMA (mma.sync ... b1 lowers to 8x IMMA.16832.U8 plus software expansion); the warp
+// level IMMA.16832.U8.U8 itself runs at 0.5 MMA / clk / SM (measured, tools/probe/imma_probe.cu) = 8 descriptor
+// pairs / clk / SM against 3.2 for the LOP3/POPC kernel at its pipe limit.
+//   warp = 32 query rows (two 16-row A tiles, bits expanded once into 64 registers)
+//   CTA  = 4 warps = 128 query rows; train rows are staged 128 at a time as BITS (4 KB) and a thread expands
+//          the nibble it needs with one multiply and one AND ((n * 0x00204081) & 0x01010101) right before the
+//          MMA, so shared-memory traffic stays 1/8 of an expanded tile
+//   per 8 train rows: 16 IMMA (8 k-steps x 2 A tiles), then per accumulator one multiply-add builds the packed
+//          key (distance << 22 | train index) and three min/max keep the running top-2, exactly as in k_knn2.
+// Results are bit-identical to k_knn2 (same keys, same tie rule).  grid (ceil(maxNq/128), nSets), block 128.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned expand_nibble(unsigned n) { return (n * 0x00204081u) & 0x01010101u; }
+
+// D(16x8, s32) += A(16x32, u8, row) * B(32x8, u8, col); PTX fragment layout of mma.m16n8k32 (g = lane >> 2, t = lane & 3):
+// a0 (g, 4t..4t+3)  a1 (g+8, 4t..)  a2 (g, 16+4t..)  a3 (g+8, 16+4t..);  b0 (k 4t.., n g)  b1 (k 16+4t.., n g);
+// c0 (g, 2t)  c1 (g, 2t+1)  c2 (g+8, 2t)  c3 (g+8, 2t+1).
+__device__ __forceinline__ void mma_u8_16832(int c[4], const unsigned a[4], unsigned b0, unsigned b1) {
+#ifdef VIORB_EMU
+    const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    auto dot4 = [](unsigned x, unsigned y) {
+        int s = 0;
+        for (int i = 0; i < 4; ++i) s += (int)((x >> (8 * i)) & 0xFF) * (int)((y >> (8 * i)) & 0xFF);
+        return s;
+    };
+    for (int tp = 0; tp < 4; ++tp) {
+        const unsigned A0 = __shfl_sync(0xffffffffu, a[0], 4 * g + tp), A1 = __shfl_sync(0xffffffffu, a[1], 4 * g + tp);
+        const unsigned A2 = __shfl_sync(0xffffffffu, a[2], 4 * g + tp), A3 = __shfl_sync(0xffffffffu, a[3], 4 * g + tp);
+        for (int j = 0; j < 2; ++j) {
+            const unsigned B0 = __shfl_sync(0xffffffffu, b0, 4 * (2 * t + j) + tp), B1 = __shfl_sync(0xffffffffu, b1, 4 * (2 * t + j) + tp);
+            c[j] += dot4(A0, B0) + dot4(A2, B1);
+            c[2 + j] += dot4(A1, B0) + dot4(A3, B1);
+        }
+    }
+#else
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+#endif
+}
+
+#define VIORB_KNN_NONE 0x80000000u      // key of a padding train row: above every real key, no overflow when a query term is added
+
+__global__ void __launch_bounds__(VIORB_KNN_THREADS) k_knn2_mma(DescSet Q, DescSet T, int32_t* __restrict__ idx,
+                                                                int32_t* __restrict__ dist, size_t outStride) {
+    __shared__ uint4 tile[VIORB_KNN_THREADS * 2];          // 128 train rows as bits
+    __shared__ unsigned kc[VIORB_KNN_THREADS];             // popc(train row) << 22 | train index
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, p = blockIdx.y;
+    const int g = lane >> 2, t = lane & 3;
+    const int nq = descset_count(Q, p), nt = descset_count(T, p);
+    const int q0 = blockIdx.x * VIORB_KNN_THREADS;
+    if (q0 >= nq) return;
+    const uint4* qb = reinterpret_cast<const uint4*>(Q.base + (size_t)p * Q.stride);
+    const uint4* tb = reinterpret_cast<const uint4*>(T.base + (size_t)p * T.stride);
+    // A fragments: rows q0 + 32 warp + 16 a + {g, g + 8}
+    unsigned A[2][8][4];
+    unsigned pqk[2][2];
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int row = min(q0 + 32 * warp + 16 * a + g + 8 * h, nq - 1);
+            const uint4 w0 = __ldg(qb + (size_t)row * 2), w1 = __ldg(qb + (size_t)row * 2 + 1);
+            const unsigned w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+            int pc = 0;
+#pragma unroll
+            for (int s = 0; s < 8; ++s) {
+                pc += __popc(w[s]);
+                A[a][s][h] = expand_nibble((w[s] >> (4 * t)) & 15u);
+                A[a][s][2 + h] = expand_nibble((w[s] >> (4 * t + 16)) & 15u);
+            }
+            pqk[a][h] = (unsigned)pc << VIORB_KNN_IDX_BITS;
+        }
+    }
+    unsigned best0[2][2], best1[2][2];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) best0[a][h] = best1[a][h] = 0xFFFFFFFFu;
+    for (int t0 = 0; t0 < nt; t0 += VIORB_KNN_THREADS) {
+        const int m = min(VIORB_KNN_THREADS, nt - t0);
+        __syncthreads();
+        if (tid < m) {
+            const uint4 r0 = __ldg(tb + (size_t)(t0 + tid) * 2), r1 = __ldg(tb + (size_t)(t0 + tid) * 2 + 1);
+            tile[tid * 2] = r0;
+            tile[tid * 2 + 1] = r1;
+            const int pc = __popc(r0.x) + __popc(r0.y) + __popc(r0.z) + __popc(r0.w) + __popc(r1.x) + __popc(r1.y) + __popc(r1.z) + __popc(r1.w);
+            kc[tid] = ((unsigned)pc << VIORB_KNN_IDX_BITS) | (unsigned)(t0 + tid);
+        } else {
+            tile[tid * 2] = make_uint4(0, 0, 0, 0);
+            tile[tid * 2 + 1] = make_uint4(0, 0, 0, 0);
+            kc[tid] = VIORB_KNN_NONE;
+        }
+        __syncthreads();
+        for (int nb = 0; nb * 8 < m; ++nb) {
+            const uint4 r0 = tile[(nb * 8 + g) * 2], r1 = tile[(nb * 8 + g) * 2 + 1];
+            const unsigned tw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+            int acc[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+#pragma unroll
+            for (int s = 0; s < 8; ++s) {
+                const unsigned b0 = expand_nibble((tw[s] >> (4 * t)) & 15u), b1 = expand_nibble((tw[s] >> (4 * t + 16)) & 15u);
+                mma_u8_16832(acc[0], A[0][s], b0, b1);
+                mma_u8_16832(acc[1], A[1][s], b0, b1);
+            }
+            const unsigned k0 = kc[nb * 8 + 2 * t], k1 = kc[nb * 8 + 2 * t + 1];
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        // key = (popc(q) + popc(t) - 2 q.t) << 22 | train index
+                        const unsigned key = (j ? k1 : k0) + pqk[a][h] - (unsigned)acc[a][2 * h + j] * (2u << VIORB_KNN_IDX_BITS);
+                        best1[a][h] = min(best1[a][h], max(key, best0[a][h]));
+                        best0[a][h] = min(best0[a][h], key);
+                    }
+        }
+    }
+    // the candidates of one query row sit in the four lanes of a quad: merge the (best, second) pairs
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            unsigned b0 = best0[a][h], b1 = best1[a][h];
+#pragma unroll
+            for (int d = 1; d <= 2; d <<= 1) {
+                const unsigned o0 = __shfl_xor_sync(0xffffffffu, b0, d), o1 = __shfl_xor_sync(0xffffffffu, b1, d);
+                b1 = min(max(b0, o0), min(b1, o1));
+                b0 = min(b0, o0);
+            }
+            const int qi = q0 + 32 * warp + 16 * a + g + 8 * h;
+            if (t == 0 && qi < nq) {
+                const unsigned mask = (1u << VIORB_KNN_IDX_BITS) - 1;
+                int32_t* oi = idx + (size_t)p * outStride * 2 + (size_t)qi * 2;
+                int32_t* od = dist + (size_t)p * outStride * 2 + (size_t)qi * 2;
+                oi[0] = b0 >= VIORB_KNN_NONE ? -1 : (int)(b0 & mask);
+                od[0] = b0 >= VIORB_KNN_NONE ? -1 : (int)(b0 >> VIORB_KNN_IDX_BITS);
+                oi[1] = b1 >= VIORB_KNN_NONE ? -1 : (int)(b1 & mask);
+                od[1] = b1 >= VIORB_KNN_NONE ? -1 : (int)(b1 >> VIORB_KNN_IDX_BITS);
+            }
+        }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Ratio test + ordered compaction.  One CTA per set; accepted matches are written in query order.
 // rule 0: d0 < d1 * ratio with d as float, product in double (frame.cpp:1170).
 // rule 1: (double)d0 < ratio * d1 (fmatcher.cpp:220-223).

@@ -491,6 +491,19 @@ int release_partner(viorb_extractor* L, viorb_extractor* R) {
 
 }  // namespace
 
+// Brute-force kNN-2 of a batch of descriptor sets.  Default: the tensor-core kernel (k_knn2_mma, IMMA u8 on
+// {0,1}-expanded bits); VIORB_KNN=popc selects the LOP3/POPC integer-pipe kernel (k_knn2) - both give identical
+// results, the choice is a measured one.
+static int launch_knn2(const DescSet& Q, const DescSet& T, int maxNq, int nSets, int32_t* dIdx, int32_t* dDist, size_t outStride,
+                       cudaStream_t st) {
+    static const bool popc = [] { const char* e = std::getenv("VIORB_KNN"); return e && std::strcmp(e, "popc") == 0; }();
+    const dim3 grid((maxNq + VIORB_KNN_THREADS - 1) / VIORB_KNN_THREADS, nSets), block(VIORB_KNN_THREADS);
+    if (popc) VIORB_LAUNCH(k_knn2, grid, block, 0, st, Q, T, dIdx, dDist, outStride);
+    else VIORB_LAUNCH(k_knn2_mma, grid, block, 0, st, Q, T, dIdx, dDist, outStride);
+    CU(cudaGetLastError());
+    return VIORB_OK;
+}
+
 // =================================================================================================
 // C ABI
 // =================================================================================================
@@ -922,10 +935,7 @@ int viorb_knn2_device(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, in
     if (((uintptr_t)d_q & 15) || ((uintptr_t)d_t & 15)) return fail(VIORB_E_ARG, "descriptor buffers must be 16-byte aligned");
     if (nq == 0) return VIORB_OK;
     DescSet Q{d_q, 0, nullptr, nq}, T{d_t, 0, nullptr, nt};
-    VIORB_LAUNCH(k_knn2, dim3((nq + VIORB_KNN_THREADS - 1) / VIORB_KNN_THREADS, 1), dim3(VIORB_KNN_THREADS), 0,
-                 (cudaStream_t)stream, Q, T, d_idx, d_dist, (size_t)nq);
-    CU(cudaGetLastError());
-    return VIORB_OK;
+    return launch_knn2(Q, T, nq, 1, d_idx, d_dist, (size_t)nq, (cudaStream_t)stream);
 }
 
 int viorb_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx, int32_t* dist, int device) {
@@ -1083,8 +1093,8 @@ int viorb_stereo_batch(viorb_extractor* L, viorb_extractor* R, int n, float bf, 
     // fisheye-style brute force kNN-2 + ratio, left -> right (frame.cpp:1167-1170)
     const size_t oc = L->g.outCap;
     DescSet Q{L->dDesc.p, oc * 32, L->dNOut.p, 0}, T{R->dDesc.p, oc * 32, R->dNOut.p, 0};
-    VIORB_LAUNCH(k_knn2, dim3((L->g.outCap + VIORB_KNN_THREADS - 1) / VIORB_KNN_THREADS, n), dim3(VIORB_KNN_THREADS), 0, L->stream,
-                 Q, T, L->dKnnIdx.p, L->dKnnDist.p, oc);
+    rc = launch_knn2(Q, T, L->g.outCap, n, L->dKnnIdx.p, L->dKnnDist.p, oc, L->stream);
+    if (rc) return rc;
     if (L->timing) CU(cudaEventRecord(L->evS[4], L->stream));
     VIORB_LAUNCH(k_ratio, dim3(n), dim3(256), 0, L->stream, Q, L->dKnnIdx.p, L->dKnnDist.p, oc, ratio, 0, L->dMatches.p, oc,
                  L->dNRatio.p, L->dLrMatch.p);
