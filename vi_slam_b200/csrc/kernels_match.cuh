@@ -139,12 +139,16 @@ __device__ __forceinline__ void mma_u8_16832(int c[4], const unsigned a[4], unsi
 #endif
 }
 
-#define VIORB_KNN_NONE 0x80000000u      // key of a padding train row: above every real key, no overflow when a query term is added
+#define VIORB_KNN_NONE 0x7F000000      // key of a padding train row: above every real key ((256 << 22) | index < 2^30 + 2^22)
 
 __global__ void __launch_bounds__(VIORB_KNN_THREADS) k_knn2_mma(DescSet Q, DescSet T, int32_t* __restrict__ idx,
                                                                 int32_t* __restrict__ dist, size_t outStride) {
-    __shared__ uint4 tile[VIORB_KNN_THREADS * 2];          // 128 train rows as bits
-    __shared__ unsigned kc[VIORB_KNN_THREADS];             // popc(train row) << 22 | train index
+    // train tile, 128 rows: as bits (staging), and expanded to {0,1} bytes in B-fragment order
+    // [n-block 16][chunk 4][lane 32] x 16 bytes: lane (g, t) of n-block nb finds its b0 / b1 words of k-steps 2c, 2c+1
+    // in chunk c, so a warp reads its fragments with four conflict-free LDS.128 per n-block
+    __shared__ uint4 bits[VIORB_KNN_THREADS * 2];
+    __shared__ uint4 frag[16 * 4 * 32];
+    __shared__ int kc[VIORB_KNN_THREADS];                  // popc(train row) << 22 | train index
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, p = blockIdx.y;
     const int g = lane >> 2, t = lane & 3;
     const int nq = descset_count(Q, p), nt = descset_count(T, p);
@@ -154,7 +158,7 @@ __global__ void __launch_bounds__(VIORB_KNN_THREADS) k_knn2_mma(DescSet Q, DescS
     const uint4* tb = reinterpret_cast<const uint4*>(T.base + (size_t)p * T.stride);
     // A fragments: rows q0 + 32 warp + 16 a + {g, g + 8}
     unsigned A[2][8][4];
-    unsigned pqk[2][2];
+    int pqk[2][2];
 #pragma unroll
     for (int a = 0; a < 2; ++a) {
 #pragma unroll
@@ -169,48 +173,65 @@ __global__ void __launch_bounds__(VIORB_KNN_THREADS) k_knn2_mma(DescSet Q, DescS
                 A[a][s][h] = expand_nibble((w[s] >> (4 * t)) & 15u);
                 A[a][s][2 + h] = expand_nibble((w[s] >> (4 * t + 16)) & 15u);
             }
-            pqk[a][h] = (unsigned)pc << VIORB_KNN_IDX_BITS;
+            pqk[a][h] = pc << VIORB_KNN_IDX_BITS;
         }
     }
-    unsigned best0[2][2], best1[2][2];
+    // running top-2 per query row on keys WITHOUT the query term popc(q) << 22 (constant per row: it does not change
+    // the order and is added at the end); the keys are signed: (popc(t) - 2 q.t) << 22 | index
+    int best0[2][2], best1[2][2];
 #pragma unroll
     for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int h = 0; h < 2; ++h) best0[a][h] = best1[a][h] = 0xFFFFFFFFu;
+        for (int h = 0; h < 2; ++h) best0[a][h] = best1[a][h] = 0x7FFFFFFF;
     for (int t0 = 0; t0 < nt; t0 += VIORB_KNN_THREADS) {
         const int m = min(VIORB_KNN_THREADS, nt - t0);
-        __syncthreads();
+        __syncthreads();                                   // the previous tile's fragments are no longer read
         if (tid < m) {
             const uint4 r0 = __ldg(tb + (size_t)(t0 + tid) * 2), r1 = __ldg(tb + (size_t)(t0 + tid) * 2 + 1);
-            tile[tid * 2] = r0;
-            tile[tid * 2 + 1] = r1;
+            bits[tid * 2] = r0;
+            bits[tid * 2 + 1] = r1;
             const int pc = __popc(r0.x) + __popc(r0.y) + __popc(r0.z) + __popc(r0.w) + __popc(r1.x) + __popc(r1.y) + __popc(r1.z) + __popc(r1.w);
-            kc[tid] = ((unsigned)pc << VIORB_KNN_IDX_BITS) | (unsigned)(t0 + tid);
+            kc[tid] = (pc << VIORB_KNN_IDX_BITS) | (t0 + tid);
         } else {
-            tile[tid * 2] = make_uint4(0, 0, 0, 0);
-            tile[tid * 2 + 1] = make_uint4(0, 0, 0, 0);
+            bits[tid * 2] = make_uint4(0, 0, 0, 0);
+            bits[tid * 2 + 1] = make_uint4(0, 0, 0, 0);
             kc[tid] = VIORB_KNN_NONE;
         }
         __syncthreads();
+        // expand once per CTA: producer thread (warp pw, lane (g, t)) writes the chunks of n-blocks pw, pw + 4, ...
+        const unsigned* bw = reinterpret_cast<const unsigned*>(bits);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int nb = warp + 4 * i;
+            if (nb * 8 < m) {
+                const unsigned* row = bw + (nb * 8 + g) * 8;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const unsigned wa = row[2 * c], wb = row[2 * c + 1];
+                    frag[(nb * 4 + c) * 32 + lane] = make_uint4(expand_nibble((wa >> (4 * t)) & 15u), expand_nibble((wa >> (4 * t + 16)) & 15u),
+                                                                expand_nibble((wb >> (4 * t)) & 15u), expand_nibble((wb >> (4 * t + 16)) & 15u));
+                }
+            }
+        }
+        __syncthreads();
         for (int nb = 0; nb * 8 < m; ++nb) {
-            const uint4 r0 = tile[(nb * 8 + g) * 2], r1 = tile[(nb * 8 + g) * 2 + 1];
-            const unsigned tw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
             int acc[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
 #pragma unroll
-            for (int s = 0; s < 8; ++s) {
-                const unsigned b0 = expand_nibble((tw[s] >> (4 * t)) & 15u), b1 = expand_nibble((tw[s] >> (4 * t + 16)) & 15u);
-                mma_u8_16832(acc[0], A[0][s], b0, b1);
-                mma_u8_16832(acc[1], A[1][s], b0, b1);
+            for (int c = 0; c < 4; ++c) {
+                const uint4 f = frag[(nb * 4 + c) * 32 + lane];
+                mma_u8_16832(acc[0], A[0][2 * c], f.x, f.y);
+                mma_u8_16832(acc[1], A[1][2 * c], f.x, f.y);
+                mma_u8_16832(acc[0], A[0][2 * c + 1], f.z, f.w);
+                mma_u8_16832(acc[1], A[1][2 * c + 1], f.z, f.w);
             }
-            const unsigned k0 = kc[nb * 8 + 2 * t], k1 = kc[nb * 8 + 2 * t + 1];
+            const int k0 = kc[nb * 8 + 2 * t], k1 = kc[nb * 8 + 2 * t + 1];
 #pragma unroll
             for (int a = 0; a < 2; ++a)
 #pragma unroll
                 for (int h = 0; h < 2; ++h)
 #pragma unroll
                     for (int j = 0; j < 2; ++j) {
-                        // key = (popc(q) + popc(t) - 2 q.t) << 22 | train index
-                        const unsigned key = (j ? k1 : k0) + pqk[a][h] - (unsigned)acc[a][2 * h + j] * (2u << VIORB_KNN_IDX_BITS);
+                        const int key = (j ? k1 : k0) - acc[a][2 * h + j] * (2 << VIORB_KNN_IDX_BITS);
                         best1[a][h] = min(best1[a][h], max(key, best0[a][h]));
                         best0[a][h] = min(best0[a][h], key);
                     }
@@ -221,22 +242,24 @@ __global__ void __launch_bounds__(VIORB_KNN_THREADS) k_knn2_mma(DescSet Q, DescS
     for (int a = 0; a < 2; ++a)
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            unsigned b0 = best0[a][h], b1 = best1[a][h];
+            int b0 = best0[a][h], b1 = best1[a][h];
 #pragma unroll
             for (int d = 1; d <= 2; d <<= 1) {
-                const unsigned o0 = __shfl_xor_sync(0xffffffffu, b0, d), o1 = __shfl_xor_sync(0xffffffffu, b1, d);
+                const int o0 = __shfl_xor_sync(0xffffffffu, b0, d), o1 = __shfl_xor_sync(0xffffffffu, b1, d);
                 b1 = min(max(b0, o0), min(b1, o1));
                 b0 = min(b0, o0);
             }
             const int qi = q0 + 32 * warp + 16 * a + g + 8 * h;
             if (t == 0 && qi < nq) {
-                const unsigned mask = (1u << VIORB_KNN_IDX_BITS) - 1;
+                const int mask = (1 << VIORB_KNN_IDX_BITS) - 1;
                 int32_t* oi = idx + (size_t)p * outStride * 2 + (size_t)qi * 2;
                 int32_t* od = dist + (size_t)p * outStride * 2 + (size_t)qi * 2;
-                oi[0] = b0 >= VIORB_KNN_NONE ? -1 : (int)(b0 & mask);
-                od[0] = b0 >= VIORB_KNN_NONE ? -1 : (int)(b0 >> VIORB_KNN_IDX_BITS);
-                oi[1] = b1 >= VIORB_KNN_NONE ? -1 : (int)(b1 & mask);
-                od[1] = b1 >= VIORB_KNN_NONE ? -1 : (int)(b1 >> VIORB_KNN_IDX_BITS);
+                const bool h0 = b0 < VIORB_KNN_NONE, h1 = b1 < VIORB_KNN_NONE;
+                const int f0 = b0 + pqk[a][h], f1 = b1 + pqk[a][h];
+                oi[0] = h0 ? (f0 & mask) : -1;
+                od[0] = h0 ? (f0 >> VIORB_KNN_IDX_BITS) : -1;
+                oi[1] = h1 ? (f1 & mask) : -1;
+                od[1] = h1 ? (f1 >> VIORB_KNN_IDX_BITS) : -1;
             }
         }
 }
