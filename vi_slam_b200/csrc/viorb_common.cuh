@@ -87,3 +87,32 @@ __device__ __forceinline__ const uint8_t* level_ptr(const ExtractGeom& g, const 
     pitch = g.lv[l].pitch;
     return fs.pyr + (size_t)f * g.arenaStride + g.lv[l].off;
 }
+
+// ---- warp-level integer MMA (IMMA.16832.U8.U8) --------------------------------------------------------
+// D(16x8, s32) += A(16x32, u8, row) * B(32x8, u8, col); PTX fragment layout of mma.m16n8k32 (g = lane >> 2, t = lane & 3):
+// a0 (g, 4t..4t+3)  a1 (g+8, 4t..)  a2 (g, 16+4t..)  a3 (g+8, 16+4t..);  b0 (k 4t.., n g)  b1 (k 16+4t.., n g);
+// c0 (g, 2t)  c1 (g, 2t+1)  c2 (g+8, 2t)  c3 (g+8, 2t+1).
+__device__ __forceinline__ void mma_u8_16832(int c[4], const unsigned a[4], unsigned b0, unsigned b1) {
+#ifdef VIORB_EMU
+    const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    auto dot4 = [](unsigned x, unsigned y) {
+        int s = 0;
+        for (int i = 0; i < 4; ++i) s += (int)((x >> (8 * i)) & 0xFF) * (int)((y >> (8 * i)) & 0xFF);
+        return s;
+    };
+    for (int tp = 0; tp < 4; ++tp) {
+        const unsigned A0 = __shfl_sync(0xffffffffu, a[0], 4 * g + tp), A1 = __shfl_sync(0xffffffffu, a[1], 4 * g + tp);
+        const unsigned A2 = __shfl_sync(0xffffffffu, a[2], 4 * g + tp), A3 = __shfl_sync(0xffffffffu, a[3], 4 * g + tp);
+        for (int j = 0; j < 2; ++j) {
+            const unsigned B0 = __shfl_sync(0xffffffffu, b0, 4 * (2 * t + j) + tp), B1 = __shfl_sync(0xffffffffu, b1, 4 * (2 * t + j) + tp);
+            c[j] += dot4(A0, B0) + dot4(A2, B1);
+            c[2 + j] += dot4(A1, B0) + dot4(A3, B1);
+        }
+    }
+#else
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+#endif
+}
+
