@@ -303,6 +303,14 @@ def run_ours(args, rank, world, local_rank):
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "bytes_per_launch": bytes_per_step / launches_per_step, "ms_per_launch": mean[dom] / launches_per_step,
                 "path_hbm_frac": 2 * B * K * BYTES_EXTRACT_PER_IMAGE / (ms * 1e-3) / 1e9 / peak}
+    # matcher: brute-force kNN-2 left -> right on the tensor cores; denominator = the IMMA.16832.U8 issue rate measured
+    # on this pool's B200 with tools/probe/imma_probe.cu (574 T u8 MAC/s) / 256 MAC per descriptor pair
+    pairs = float((res["n_left"].astype(np.float64) ** 2).sum())
+    imma_pairs_peak = 574.2e12 / 256.0
+    match_roofline = {"kernel": "k_knn2_mma", "bound": "tensor (IMMA u8, legacy warp MMA)", "pairs_per_launch": pairs,
+                      "achieved": pairs / (mean["knn2"] * 1e-3), "peak": imma_pairs_peak, "unit": "descriptor pairs/s",
+                      "frac": pairs / (mean["knn2"] * 1e-3) / imma_pairs_peak,
+                      "peak_source": "measured: tools/probe/imma_probe.cu, 574.2 T u8 MAC/s"}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
@@ -315,6 +323,7 @@ def run_ours(args, rank, world, local_rank):
         "clocks": clk, "e2e": e2e, "gpu_launches": K * (2 * (NLEVELS - 1 + 6) + 5),
         "stages_ms_per_step": mean,
         "stage_timing": "second pass of K steps, both handles on one stream, CUDA events around each stage", "roofline": roofline,
+        "match_roofline": match_roofline,
     }
     if world == 1 and not args.no_cpu_baseline:
         cores = host_threads()

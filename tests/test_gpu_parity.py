@@ -239,3 +239,25 @@ def test_pinned_buffers_take_the_direct_dma_path():
     # non-contiguous pinned frames (every other slot)
     mono3, kps3, desc3 = ex.compute_batch([pin[i, :, :w] for i in (0, 2)], (0, 0))
     assert np.array_equal(kps3[1], kps[2]) and np.array_equal(desc3[0], desc[0])
+
+
+@pytest.mark.gpu
+def test_knn2_integer_pipe_kernel_matches_too(tmp_path):
+    """k_knn2 (LOP3/POPC, VIORB_KNN=popc) and the default k_knn2_mma (tensor cores) must both equal the oracle; the
+    kernel choice is read once per process, so the integer-pipe kernel runs in a child process."""
+    import subprocess
+    import sys
+    code = ("import numpy as np, oracle\n"
+            "from vi_slam_b200 import matcher, synthetic\n"
+            "for nq, nt in ((2000, 2000), (130, 129), (5, 1), (1, 4000), (3000, 257)):\n"
+            "    q, t = synthetic.make_descriptors(nq, nt, seed=nq + nt)\n"
+            "    i, d = matcher.knn_match(q, t)\n"
+            "    oi, od = oracle.knn2(q, t, nthreads=4)\n"
+            "    assert np.array_equal(i, oi) and np.array_equal(d, od), (nq, nt)\n"
+            "print('ok')\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for kern in ("popc", "mma"):
+        env = dict(os.environ, VIORB_KNN=kern, PYTHONPATH=root)
+        env.pop("VIORB_LIBRARY", None)
+        out = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True)
+        assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
