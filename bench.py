@@ -65,46 +65,51 @@ def make_pairs(n, distinct, seed0=1000):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled DURING the timed region: an NVML polling thread (5 ms period; the
+    timed region is tens of milliseconds, too short for `nvidia-smi -lms`)."""
+    REASONS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
 
     def __init__(self, index):
-        self.proc = None
+        self.samples, self.mask, self.max_mhz, self.err = [], 0, None, None
+        self._stop = threading.Event()
+        self._thread = None
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-        except OSError:
-            pass
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            try:
+                uuid = "GPU-" + str(torch.cuda.get_device_properties(index).uuid)
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode() if hasattr(uuid, "encode") else uuid)
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.nv = pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+        except Exception as e:          # no NVML: report that instead of a made-up clock
+            self.err = f"nvml unavailable: {e}"
+
+    def _run(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                self.mask |= int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+            except Exception as e:
+                self.err = str(e)
+                return
+            time.sleep(0.005)
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            out = self.proc.communicate(timeout=5)[0]
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
-            out = ""
-        sm, mx, reasons = [], 0, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in out.strip().splitlines():
-            p = [t.strip() for t in line.split(",")]
-            if len(p) < 7:
-                continue
-            try:
-                sm.append(float(p[0]))
-                mx = max(mx, float(p[1]))
-            except ValueError:
-                continue
-            for nme, v in zip(names, p[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(nme)
-        # under-load median: ignore idle samples taken before the first launch
-        load = [v for v in sm if v >= 0.5 * max(sm)] if sm else []
-        return {"sm_mhz": float(np.median(load)) if load else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        self._stop.set()
+        if self._thread:
+            self._thread.join(timeout=2)
+        sm = self.samples
+        reasons = sorted(k for k, bit in self.REASONS.items() if self.mask & bit)
+        if self.err and not sm:
+            reasons = [self.err]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                "samples": len(sm)}
 
 
 def cpu_baseline(nthreads, pairs):
