@@ -211,6 +211,26 @@ int viorb_search_by_projection(int npairs, int cap1, int cap2, const float* uv, 
                                const float* scale_factors, int nlevels, float th, float bf, int direction,
                                int check_orientation, int32_t* assigned, int32_t* nmatches, int device);
 
+/* ---- keypoint undistortion: SURVEY.md section 8 row f-2 ----------------------------------------- */
+
+/* Camera of Frame::UndistortKeyPoints / ComputeImageBounds (src/datastructures/frame.cpp:758-791, 793-821):
+ * cam = fx fy cx cy of mK, dist = mDistCoef = k1 k2 p1 p2 [k3] (ndist 4 or 5), both CV_32F in the reference
+ * (src/core/tracking.cpp:490-593).  The computation is cv::undistortPoints(pts, pts, mK, mDistCoef, Mat(), mK) with
+ * OpenCV's default 5 iterations, in double; k1 == 0 copies the keypoints (frame.cpp:762-766).
+ *
+ * viorb_extractor_set_camera: from the next extract on, the extractor's epilogue also writes ukeypoints_ (same order
+ * as the keypoints) and keeps them resident; read them with viorb_fetch_undistorted.  dist == NULL switches it off. */
+int viorb_extractor_set_camera(viorb_extractor* ex, const float* cam, const float* dist, int ndist);
+int viorb_fetch_undistorted(viorb_extractor* ex, int frame, viorb_keypoint* kps_un, int cap, int* n_out);
+/* Host arrays: keypoints_ -> ukeypoints_ (every field but pt copied), and bare points xy [n][2] -> out [n][2]. */
+int viorb_undistort_keypoints(const viorb_keypoint* kps, int n, const float* cam, const float* dist, int ndist,
+                              viorb_keypoint* out, int device);
+int viorb_undistort_points(const float* xy, int n, const float* cam, const float* dist, int ndist, float* out, int device);
+/* Frame::ComputeImageBounds(imLeft): the undistorted image corners -> mnMinX, mnMaxX, mnMinY, mnMaxY
+ * ((0, cols, 0, rows) when k1 == 0). */
+int viorb_image_bounds(int cols, int rows, const float* cam, const float* dist, int ndist, viorb_grid_bounds* bounds,
+                       int device);
+
 #ifdef __cplusplus
 }
 #endif

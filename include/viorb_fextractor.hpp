@@ -105,6 +105,19 @@ public:
     // When ComputeStereoMatches is rerouted to viorb_stereo_match nothing on the host reads mvImagePyramid:
     // switch the per-frame device->host copy of the 8 levels off.
     void SetPyramidReadback(bool on) { readback_ = on; }
+    // Frame::UndistortKeyPoints (frame.cpp:758-791) fused into compute(): give the extractor the Frame's mK
+    // (fx fy cx cy) and mDistCoef (4 or 5 floats) once; after every compute() UndistortedKeyPoints() returns
+    // ukeypoints_ of that frame.  dist == nullptr switches it off.
+    void SetCamera(const float* cam, const float* dist, int ndist) {
+        if (viorb_extractor_set_camera(h_, cam, dist, ndist) != VIORB_OK) throw std::runtime_error(viorb_last_error());
+    }
+    void UndistortedKeyPoints(std::vector<viorb_cv::KeyPoint>& ukeypoints) {
+        int n = 0;
+        kp_.resize(cap_);
+        if (viorb_fetch_undistorted(h_, 0, kp_.data(), cap_, &n) != VIORB_OK) throw std::runtime_error(viorb_last_error());
+        ukeypoints.resize(n);
+        if (n) std::memcpy((void*)ukeypoints.data(), kp_.data(), sizeof(viorb_keypoint) * (size_t)n);
+    }
 
     std::vector<viorb_cv::Mat> mvImagePyramid;
 

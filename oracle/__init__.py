@@ -72,6 +72,9 @@ def lib():
                                                     C.c_float, C.c_int, i32p]
         L.orc_search_by_projection.argtypes = [f32p, f32p, i32p, f32p, u8p, u8p, u8p, C.c_int, C.c_void_p, u8p, f32p, u8p,
                                                C.c_int, f32p, f32p, C.c_float, C.c_float, C.c_int, C.c_int, i32p]
+        L.orc_undistort_points.argtypes = [f32p, C.c_int, f32p, f32p, C.c_int, f32p]
+        L.orc_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, f32p, f32p, C.c_int, C.c_void_p]
+        L.orc_image_bounds.argtypes = [C.c_int, C.c_int, f32p, f32p, C.c_int, f32p]
         _lib = L
     return _lib
 
@@ -298,3 +301,32 @@ def search_by_projection(uv, invz, last_octave, last_angle, desc_mp, valid, obse
                                        None if bl is None else _u8(bl), len(k2), _f32(b), _f32(sf), float(th), float(bf),
                                        int(direction), int(check_orientation), _i32(out))
     return n, out
+
+
+def undistort_points(xy, cam, dist):
+    """cv::undistortPoints(pts, pts, mK, mDistCoef, Mat(), mK) as Frame::UndistortKeyPoints calls it (frame.cpp:779)."""
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    cam = np.ascontiguousarray(cam, np.float32)
+    dist = np.ascontiguousarray(dist, np.float32)
+    out = np.empty_like(xy)
+    lib().orc_undistort_points(_f32(xy), len(xy), _f32(cam), _f32(dist), len(dist), _f32(out))
+    return out
+
+
+def undistort_keypoints(kps, cam, dist):
+    """Frame::UndistortKeyPoints (frame.cpp:758-791): keypoints_ -> ukeypoints_."""
+    kps = np.ascontiguousarray(kps)
+    cam = np.ascontiguousarray(cam, np.float32)
+    dist = np.ascontiguousarray(dist, np.float32)
+    out = np.empty_like(kps)
+    lib().orc_undistort_keypoints(kps.ctypes.data, len(kps), _f32(cam), _f32(dist), len(dist), out.ctypes.data)
+    return out
+
+
+def image_bounds(cols, rows, cam, dist):
+    """Frame::ComputeImageBounds (frame.cpp:793-821) -> (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+    cam = np.ascontiguousarray(cam, np.float32)
+    dist = np.ascontiguousarray(dist, np.float32)
+    out = np.zeros(4, np.float32)
+    lib().orc_image_bounds(int(cols), int(rows), _f32(cam), _f32(dist), len(dist), _f32(out))
+    return out

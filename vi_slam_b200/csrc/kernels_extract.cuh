@@ -10,6 +10,7 @@
 //   k_describe  computeOrbDescriptor        :99-138     (steered BRIEF-256)
 #pragma once
 #include "viorb_common.cuh"
+#include "kernels_undistort.cuh"
 
 static __device__ __align__(16) const int8_t d_orb_pattern[1024] = {
 #include "orb_pattern.inc"
@@ -865,7 +866,8 @@ __global__ void __launch_bounds__(256) k_orient(ExtractGeom g, FrameSrc fs, cons
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_emit(ExtractGeom g, const KeptKp* __restrict__ kept, const int* __restrict__ keptCount,
                                               int lap0, int lap1, viorb_keypoint* __restrict__ kps, int* __restrict__ slot2kept,
-                                              int* __restrict__ nOut, int* __restrict__ monoOut) {
+                                              int* __restrict__ nOut, int* __restrict__ monoOut, CamModel cam,
+                                              viorb_keypoint* __restrict__ kpsUn) {
     __shared__ int warpCnt[8];
     __shared__ int sh_mono, sh_lap;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -907,6 +909,13 @@ __global__ void __launch_bounds__(256) k_emit(ExtractGeom g, const KeptKp* __res
                 const int slot = lap ? total - 1 - (lapBefore + __popc(mLap & lt)) : monoBefore + __popc(mMono & lt);
                 okp[slot] = kp;
                 s2k[slot] = L.keptOff + i;
+                if (cam.mode) {   // Frame::UndistortKeyPoints fused into the epilogue (frame.cpp:758-791)
+                    if (cam.mode == 2) {
+                        const float2 p = undistort_point_dev(kp.x, kp.y, cam);
+                        kp.x = p.x; kp.y = p.y;
+                    }
+                    kpsUn[(size_t)f * g.outCap + slot] = kp;
+                }
             }
             __syncthreads();
             if (tid == 0) {

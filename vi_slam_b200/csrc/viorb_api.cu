@@ -93,6 +93,8 @@ struct viorb_extractor {
     DevBuf<short2> dXalpha, dYbeta;
     DevBuf<KeptKp> dKept;
     DevBuf<viorb_keypoint> dKps;
+    DevBuf<viorb_keypoint> dKpsUn;    // ukeypoints_, filled by k_emit once viorb_extractor_set_camera was called
+    CamModel cam{};
     DevBuf<CellDesc> dCells;
     DevBuf<int> dOrientTab;
     DevBuf<uint8_t> dSlotLevel;
@@ -382,7 +384,7 @@ int run_pipeline(viorb_extractor* ex, int f0, int n, int lap0, int lap1) {
                  ex->dKeptCount.p);
     if (tm) CU(cudaEventRecord(ex->evX[4], st));
     VIORB_LAUNCH(k_emit, dim3(n), dim3(256), 0, st, g, ex->dKept.p, ex->dKeptCount.p, lap0, lap1, ex->dKps.p,
-                 ex->dSlot2Kept.p, ex->dNOut.p, ex->dMono.p);
+                 ex->dSlot2Kept.p, ex->dNOut.p, ex->dMono.p, ex->cam, ex->dKpsUn.p);
     if (tm) CU(cudaEventRecord(ex->evX[5], st));
     VIORB_LAUNCH(k_blur, dim3(ex->totalBlurTiles, n), dim3(64), 0, st, g, fs, ex->blurTiles);
     if (tm) CU(cudaEventRecord(ex->evX[6], st));
@@ -602,7 +604,7 @@ void viorb_extractor_destroy(viorb_extractor* ex) {
     ex->dIn.release(); ex->dPyr.release(); ex->dBlur.release(); ex->dDesc.release(); ex->dCand.release();
     ex->dKeyNode.release(); ex->dCandCount.release(); ex->dKeptCount.release(); ex->dSlot2Kept.release();
     ex->dNOut.release(); ex->dMono.release(); ex->dStatus.release(); ex->dXofs.release(); ex->dYofs.release();
-    ex->dXalpha.release(); ex->dYbeta.release(); ex->dKept.release(); ex->dKps.release(); ex->dCells.release();
+    ex->dXalpha.release(); ex->dYbeta.release(); ex->dKept.release(); ex->dKps.release(); ex->dKpsUn.release(); ex->dCells.release();
     ex->dOrientTab.release(); ex->dSlotLevel.release();
     ex->dBestIdx.release(); ex->dBestDist.release(); ex->dSad.release(); ex->dKnnIdx.release(); ex->dKnnDist.release();
     ex->dLrMatch.release(); ex->dURight.release(); ex->dDepth.release(); ex->dNStereo.release(); ex->dNRatio.release();
@@ -1418,6 +1420,119 @@ int viorb_search_by_projection(int npairs, int cap1, int cap2, const float* uv, 
     dUV.release(); dIZ.release(); dLA.release(); dUR.release(); dLO.release(); dAS.release(); dNM.release(); dPI.release();
     dDM.release(); dVA.release(); dOB.release(); dD2.release(); dBL.release(); dPB.release(); dK2.release(); dS.release(); w.release();
     return rc;
+}
+
+// ---- keypoint undistortion (row f-2) ----------------------------------------------------------------
+}  // extern "C"
+
+namespace {
+
+// mK / mDistCoef (CV_32F) -> the double model cvUndistortPointsInternal works on.
+int make_cam(const float* cam, const float* dist, int ndist, CamModel* out) {
+    CamModel c{};
+    if (!dist) { *out = c; return VIORB_OK; }
+    if (!cam || (ndist != 4 && ndist != 5)) return fail(VIORB_E_ARG, "camera needs fx fy cx cy and 4 or 5 radtan coefficients");
+    c.fx = cam[0]; c.fy = cam[1]; c.cx = cam[2]; c.cy = cam[3];
+    c.ifx = 1.0 / c.fx; c.ify = 1.0 / c.fy;
+    for (int i = 0; i < ndist; ++i) c.k[i] = dist[i];
+    c.mode = dist[0] == 0.0f ? 1 : 2;
+    *out = c;
+    return VIORB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int viorb_extractor_set_camera(viorb_extractor* ex, const float* cam, const float* dist, int ndist) {
+    if (!ex) return fail(VIORB_E_ARG, "null handle");
+    CamModel c;
+    int rc = make_cam(cam, dist, ndist, &c);
+    if (rc) return rc;
+    CU(cudaSetDevice(ex->prm.device));
+    if (c.mode && !ex->dKpsUn.p) CU(ex->dKpsUn.alloc((size_t)ex->prm.max_batch * ex->capOut));
+    ex->cam = c;
+    return VIORB_OK;
+}
+
+int viorb_fetch_undistorted(viorb_extractor* ex, int frame, viorb_keypoint* kps_un, int cap, int* n_out) {
+    if (!ex || frame < 0 || frame >= ex->lastN) return fail(VIORB_E_ARG, "bad handle or frame index");
+    if (!ex->cam.mode) return fail(VIORB_E_ARG, "no camera set: call viorb_extractor_set_camera before extracting");
+    CU(cudaSetDevice(ex->prm.device));
+    int rc = check_status(ex);
+    if (rc) return rc;
+    int cnt = 0;
+    CU(cudaMemcpyAsync(&cnt, ex->dNOut.p + frame, sizeof(int), cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaStreamSynchronize(ex->stream));
+    if (n_out) *n_out = cnt;
+    const int m = std::min(cnt, cap);
+    if (kps_un && m > 0) {
+        CU(cudaMemcpyAsync(kps_un, ex->dKpsUn.p + (size_t)frame * ex->g.outCap, sizeof(viorb_keypoint) * m, cudaMemcpyDeviceToHost,
+                           ex->stream));
+        CU(cudaStreamSynchronize(ex->stream));
+    }
+    if (cnt > cap && kps_un) return fail(VIORB_E_CAPACITY, "output buffer smaller than the number of keypoints");
+    return VIORB_OK;
+}
+
+int viorb_undistort_keypoints(const viorb_keypoint* kps, int n, const float* cam, const float* dist, int ndist,
+                              viorb_keypoint* out, int device) {
+    if (n < 0 || (n > 0 && (!kps || !out)) || !dist) return fail(VIORB_E_ARG, "bad argument");
+    CamModel c;
+    int rc = make_cam(cam, dist, ndist, &c);
+    if (rc) return rc;
+    if (n == 0) return VIORB_OK;
+    rc = need_device(device);
+    if (rc) return rc;
+    DevBuf<viorb_keypoint> dIn, dOut;
+    cudaError_t e = upload(dIn, kps, n);
+    if (e == cudaSuccess) e = dOut.alloc(n);
+    if (e == cudaSuccess) {
+        VIORB_LAUNCH(k_undistort_keypoints, dim3((n + 255) / 256, 1), dim3(256), 0, (cudaStream_t)0, dIn.p, (const int*)nullptr, n, c, dOut.p);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(out, dOut.p, sizeof(viorb_keypoint) * n, cudaMemcpyDeviceToHost);
+    dIn.release(); dOut.release();
+    return e == cudaSuccess ? VIORB_OK : fail(VIORB_E_CUDA, cudaGetErrorString(e));
+}
+
+int viorb_undistort_points(const float* xy, int n, const float* cam, const float* dist, int ndist, float* out, int device) {
+    if (n < 0 || (n > 0 && (!xy || !out)) || !dist) return fail(VIORB_E_ARG, "bad argument");
+    CamModel c;
+    int rc = make_cam(cam, dist, ndist, &c);
+    if (rc) return rc;
+    if (n == 0) return VIORB_OK;
+    rc = need_device(device);
+    if (rc) return rc;
+    DevBuf<float2> dIn, dOut;
+    cudaError_t e = upload(dIn, reinterpret_cast<const float2*>(xy), n);
+    if (e == cudaSuccess) e = dOut.alloc(n);
+    if (e == cudaSuccess) {
+        // bare points are always undistorted (the k1 == 0 shortcut belongs to the two Frame functions)
+        c.mode = 2;
+        VIORB_LAUNCH(k_undistort_points, dim3((n + 255) / 256), dim3(256), 0, (cudaStream_t)0, dIn.p, n, c, dOut.p);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(out, dOut.p, sizeof(float2) * n, cudaMemcpyDeviceToHost);
+    dIn.release(); dOut.release();
+    return e == cudaSuccess ? VIORB_OK : fail(VIORB_E_CUDA, cudaGetErrorString(e));
+}
+
+int viorb_image_bounds(int cols, int rows, const float* cam, const float* dist, int ndist, viorb_grid_bounds* bounds, int device) {
+    if (!bounds || !dist || cols <= 0 || rows <= 0) return fail(VIORB_E_ARG, "bad argument");
+    if (dist[0] == 0.0f) {
+        bounds->min_x = 0.f; bounds->max_x = (float)cols; bounds->min_y = 0.f; bounds->max_y = (float)rows;
+        return VIORB_OK;
+    }
+    const float c[8] = {0.f, 0.f, (float)cols, 0.f, 0.f, (float)rows, (float)cols, (float)rows};
+    float u[8];
+    int rc = viorb_undistort_points(c, 4, cam, dist, ndist, u, device);
+    if (rc) return rc;
+    bounds->min_x = std::min(u[0], u[4]);
+    bounds->max_x = std::max(u[2], u[6]);
+    bounds->min_y = std::min(u[1], u[3]);
+    bounds->max_y = std::max(u[5], u[7]);
+    return VIORB_OK;
 }
 
 }  // extern "C"

@@ -170,6 +170,27 @@ class FExtractor:
                                                 C.byref(cnt), C.byref(mono)))
         return mono.value, kps[:cnt.value].copy(), desc[:cnt.value].copy()
 
+    def set_camera(self, K, dist):
+        """mK (fx, fy, cx, cy or a 3x3 matrix) and mDistCoef (k1 k2 p1 p2 [k3]) of the Frame this extractor feeds: from the
+        next compute on, the epilogue also produces Frame::UndistortKeyPoints' ukeypoints_ (frame.cpp:758-791).
+        ``dist=None`` switches it off."""
+        if dist is None:
+            _check(self._lib, self._lib.viorb_extractor_set_camera(self._h, None, None, 0))
+            return
+        K = np.asarray(K, np.float32)
+        cam = np.array([K[0, 0], K[1, 1], K[0, 2], K[1, 2]], np.float32) if K.ndim == 2 else np.ascontiguousarray(K, np.float32)
+        d = np.ascontiguousarray(dist, np.float32).ravel()
+        _check(self._lib, self._lib.viorb_extractor_set_camera(self._h, cam.ctypes.data_as(_lib.f32p), d.ctypes.data_as(_lib.f32p),
+                                                               len(d)))
+
+    def fetch_undistorted(self, frame=0):
+        """ukeypoints_ of a resident frame (same order as ``fetch``'s keypoints)."""
+        cap = self.capacity
+        kps = np.zeros(cap, KP_DTYPE)
+        cnt = C.c_int32()
+        _check(self._lib, self._lib.viorb_fetch_undistorted(self._h, frame, kps.ctypes.data, cap, C.byref(cnt)))
+        return kps[:cnt.value].copy()
+
     def sync(self):
         _check(self._lib, self._lib.viorb_extractor_sync(self._h))
 
