@@ -231,6 +231,42 @@ int viorb_undistort_points(const float* xy, int n, const float* cam, const float
 int viorb_image_bounds(int cols, int rows, const float* cam, const float* dist, int ndist, viorb_grid_bounds* bounds,
                        int device);
 
+/* ---- bag of words: SURVEY.md section 8 row f-3 --------------------------------------------------- */
+
+/* The vocabulary tree of DBoW3::Vocabulary (thirdparty/DBoW3/DBoW3/src/Vocabulary.h:323-355: m_nodes, m_L, m_weighting,
+ * m_scoring) as flat arrays; node 0 is the root.  children[child_start[i] .. child_start[i+1]) = m_nodes[i].children in
+ * their stored order (the order decides ties), descriptors[i][32] = m_nodes[i].descriptor (CV_8U, 32 bytes), weight[i] =
+ * m_nodes[i].weight, word_id[i] = m_nodes[i].word_id for leaves (-1 otherwise).  weighting: 0 TF_IDF, 1 TF, 2 IDF,
+ * 3 BINARY; scoring: 0 L1_NORM, 1 L2_NORM, 2 CHI_SQUARE, 3 KL, 4 BHATTACHARYYA, 5 DOT_PRODUCT (BowVector.h:38-55).
+ * The arrays are copied to the device; the caller may free them after the call. */
+typedef struct viorb_vocab_desc {
+    int32_t nnodes, levels, weighting, scoring;
+    const int32_t* child_start;
+    const int32_t* children;
+    const uint8_t* descriptors;
+    const double* weight;
+    const int32_t* word_id;
+} viorb_vocab_desc;
+typedef struct viorb_vocabulary viorb_vocabulary;
+int viorb_vocabulary_create(const viorb_vocab_desc* desc, int device, viorb_vocabulary** out);
+void viorb_vocabulary_destroy(viorb_vocabulary* voc);
+
+/* Frame::ComputeBoW (src/datastructures/frame.cpp:455-462) = Vocabulary::transform(features, mBowVec, mFeatVec, levelsup)
+ * (Vocabulary.cpp:754-820) for nframes descriptor sets: set f = rows [f*cap, f*cap + n[f]) of desc (host, 32 bytes per
+ * row, cap <= 16384).  Per set, with row stride cap (cap + 1 for fv_start):
+ *   mBowVec  = { bow_word[j] -> bow_value[j] : j < nbow[f] } in std::map (ascending word id) order, doubles bit-identical;
+ *   mFeatVec = { fv_node[j] -> fv_feature[fv_start[j] .. fv_start[j+1]) : j < nfv[f] } in ascending node id order, feature
+ *              indices ascending inside a node.
+ * A leaf above level levels - levelsup leaves the node id unset in the reference; 0 is reported here. */
+int viorb_bow_transform(const viorb_vocabulary* voc, int nframes, int cap, const uint8_t* desc, const int32_t* n, int levelsup,
+                        uint32_t* bow_word, double* bow_value, int32_t* nbow, uint32_t* fv_node, int32_t* fv_start,
+                        uint32_t* fv_feature, int32_t* nfv);
+/* The same on the descriptors the extractor still holds on the device for its last batch (queued on the handle's stream,
+ * no host pass); viorb_bow_fetch copies one frame's result (buffers of viorb_extractor_capacity entries, + 1 for fv_start). */
+int viorb_bow_resident(viorb_extractor* ex, const viorb_vocabulary* voc, int levelsup);
+int viorb_bow_fetch(viorb_extractor* ex, int frame, uint32_t* bow_word, double* bow_value, int32_t* nbow, uint32_t* fv_node,
+                    int32_t* fv_start, uint32_t* fv_feature, int32_t* nfv);
+
 #ifdef __cplusplus
 }
 #endif

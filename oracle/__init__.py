@@ -75,6 +75,11 @@ def lib():
         L.orc_undistort_points.argtypes = [f32p, C.c_int, f32p, f32p, C.c_int, f32p]
         L.orc_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, f32p, f32p, C.c_int, C.c_void_p]
         L.orc_image_bounds.argtypes = [C.c_int, C.c_int, f32p, f32p, C.c_int, f32p]
+        f64p, u32p = C.POINTER(C.c_double), C.POINTER(C.c_uint32)
+        L.orc_vocab_create.restype = C.c_void_p
+        L.orc_vocab_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, i32p, i32p, u8p, f64p, i32p]
+        L.orc_vocab_destroy.argtypes = [C.c_void_p]
+        L.orc_bow_transform.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int, u32p, f64p, i32p, u32p, i32p, u32p, i32p]
         _lib = L
     return _lib
 
@@ -330,3 +335,33 @@ def image_bounds(cols, rows, cam, dist):
     out = np.zeros(4, np.float32)
     lib().orc_image_bounds(int(cols), int(rows), _f32(cam), _f32(dist), len(dist), _f32(out))
     return out
+
+
+class OracleVocabulary:
+    """DBoW3::Vocabulary restricted to transform() (thirdparty/DBoW3/DBoW3/src/Vocabulary.cpp:754-876) on a tree given as flat
+    arrays (see vi_slam_b200.synthetic.make_vocabulary)."""
+
+    def __init__(self, voc):
+        self._keep = [np.ascontiguousarray(voc["child_start"], np.int32), np.ascontiguousarray(voc["children"], np.int32),
+                      np.ascontiguousarray(voc["descriptors"], np.uint8), np.ascontiguousarray(voc["weight"], np.float64),
+                      np.ascontiguousarray(voc["word_id"], np.int32)]
+        cs, ch, de, we, wi = self._keep
+        self._h = lib().orc_vocab_create(len(we), int(voc["levels"]), int(voc["weighting"]), int(voc["scoring"]), _i32(cs), _i32(ch),
+                                         _u8(de), we.ctypes.data_as(C.POINTER(C.c_double)), _i32(wi))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_vocab_destroy(self._h)
+            self._h = None
+
+    def transform(self, desc, levelsup=4):
+        """-> (bow_word uint32[m], bow_value float64[m], fv_node uint32[k], fv_start int32[k+1], fv_feature uint32[...])"""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(desc)
+        bw, bv = np.zeros(n + 1, np.uint32), np.zeros(n + 1, np.float64)
+        fn, fs, ff = np.zeros(n + 1, np.uint32), np.zeros(n + 2, np.int32), np.zeros(n + 1, np.uint32)
+        nb, nf = C.c_int32(), C.c_int32()
+        u32 = C.POINTER(C.c_uint32)
+        lib().orc_bow_transform(self._h, _u8(desc), n, int(levelsup), bw.ctypes.data_as(u32), bv.ctypes.data_as(C.POINTER(C.c_double)),
+                                C.byref(nb), fn.ctypes.data_as(u32), _i32(fs), ff.ctypes.data_as(u32), C.byref(nf))
+        return bw[:nb.value].copy(), bv[:nb.value].copy(), fn[:nf.value].copy(), fs[:nf.value + 1].copy(), ff[:fs[nf.value]].copy()

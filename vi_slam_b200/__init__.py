@@ -4,4 +4,4 @@ The compute lives in libviorb.so (hand-written sm_100a CUDA behind the C ABI of 
 this package is the thin host-side mirror of the reference's interface for that path.
 """
 from .extractor import KP_DTYPE, MATCH_DTYPE, FExtractor, ViorbError, pinned_empty  # noqa: F401
-from . import frame, matcher, synthetic  # noqa: F401
+from . import bow, frame, matcher, synthetic  # noqa: F401

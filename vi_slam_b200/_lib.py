@@ -13,6 +13,12 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 DEFAULT_LIB = os.path.join(_HERE, "libviorb.so")
 
+class ViorbVocabDesc(C.Structure):
+    _fields_ = [("nnodes", C.c_int32), ("levels", C.c_int32), ("weighting", C.c_int32), ("scoring", C.c_int32),
+                ("child_start", C.c_void_p), ("children", C.c_void_p), ("descriptors", C.c_void_p), ("weight", C.c_void_p),
+                ("word_id", C.c_void_p)]
+
+
 u8p = C.POINTER(C.c_uint8)
 i32p = C.POINTER(C.c_int32)
 f32p = C.POINTER(C.c_float)
@@ -77,6 +83,12 @@ SYMBOLS = {
     "viorb_undistort_keypoints": (C.c_int, [C.c_void_p, C.c_int, f32p, f32p, C.c_int, C.c_void_p, C.c_int]),
     "viorb_undistort_points": (C.c_int, [f32p, C.c_int, f32p, f32p, C.c_int, f32p, C.c_int]),
     "viorb_image_bounds": (C.c_int, [C.c_int, C.c_int, f32p, f32p, C.c_int, C.c_void_p, C.c_int]),
+    "viorb_vocabulary_create": (C.c_int, [C.POINTER(ViorbVocabDesc), C.c_int, C.POINTER(C.c_void_p)]),
+    "viorb_vocabulary_destroy": (None, [C.c_void_p]),
+    "viorb_bow_transform": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, i32p, C.c_int, C.c_void_p, C.c_void_p, i32p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, i32p]),
+    "viorb_bow_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
+    "viorb_bow_fetch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, i32p, C.c_void_p, C.c_void_p, C.c_void_p, i32p]),
 }
 
 _cache = {}

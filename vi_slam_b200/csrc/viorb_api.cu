@@ -15,6 +15,7 @@
 #include "kernels_extract.cuh"
 #include "kernels_match.cuh"
 #include "kernels_window.cuh"
+#include "kernels_bow.cuh"
 
 #define VIORB_MAX_CHUNKS 8
 
@@ -61,7 +62,38 @@ struct PinBuf {
     void release() { if (p) cudaFreeHost(p); p = nullptr; n = 0; }
 };
 
+// Results of viorb_bow_* for `frames` sets of `cap` slots (device side).
+struct BowBufs {
+    DevBuf<int> leaf, nid, nBow, nFv, fvStart;
+    DevBuf<uint32_t> bowWord, fvNode, fvFeature;
+    DevBuf<double> bowValue;
+    size_t frames = 0, cap = 0;
+    cudaError_t ensure(size_t f, size_t c) {
+        if (f <= frames && c == cap && leaf.p) return cudaSuccess;
+        release();
+        cudaError_t e = cudaSuccess;
+        auto ok = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+        ok(leaf.alloc(f * c)); ok(nid.alloc(f * c)); ok(nBow.alloc(f)); ok(nFv.alloc(f)); ok(fvStart.alloc(f * (c + 1)));
+        ok(bowWord.alloc(f * c)); ok(fvNode.alloc(f * c)); ok(fvFeature.alloc(f * c)); ok(bowValue.alloc(f * c));
+        frames = f; cap = c;
+        return e;
+    }
+    void release() {
+        leaf.release(); nid.release(); nBow.release(); nFv.release(); fvStart.release(); bowWord.release(); fvNode.release();
+        fvFeature.release(); bowValue.release();
+        frames = cap = 0;
+    }
+};
+
 }  // namespace
+
+struct viorb_vocabulary {
+    int device = 0;
+    VocabDev d{};
+    DevBuf<int> childStart, children, wordId;
+    DevBuf<uint4> desc;
+    DevBuf<double> weight;
+};
 
 struct viorb_extractor {
     viorb_params prm;
@@ -95,6 +127,8 @@ struct viorb_extractor {
     DevBuf<viorb_keypoint> dKps;
     DevBuf<viorb_keypoint> dKpsUn;    // ukeypoints_, filled by k_emit once viorb_extractor_set_camera was called
     CamModel cam{};
+    BowBufs bow;                      // viorb_bow_resident results of the last batch
+    int bowN = 0;
     DevBuf<CellDesc> dCells;
     DevBuf<int> dOrientTab;
     DevBuf<uint8_t> dSlotLevel;
@@ -604,7 +638,7 @@ void viorb_extractor_destroy(viorb_extractor* ex) {
     ex->dIn.release(); ex->dPyr.release(); ex->dBlur.release(); ex->dDesc.release(); ex->dCand.release();
     ex->dKeyNode.release(); ex->dCandCount.release(); ex->dKeptCount.release(); ex->dSlot2Kept.release();
     ex->dNOut.release(); ex->dMono.release(); ex->dStatus.release(); ex->dXofs.release(); ex->dYofs.release();
-    ex->dXalpha.release(); ex->dYbeta.release(); ex->dKept.release(); ex->dKps.release(); ex->dKpsUn.release(); ex->dCells.release();
+    ex->dXalpha.release(); ex->dYbeta.release(); ex->dKept.release(); ex->dKps.release(); ex->dKpsUn.release(); ex->bow.release(); ex->dCells.release();
     ex->dOrientTab.release(); ex->dSlotLevel.release();
     ex->dBestIdx.release(); ex->dBestDist.release(); ex->dSad.release(); ex->dKnnIdx.release(); ex->dKnnDist.release();
     ex->dLrMatch.release(); ex->dURight.release(); ex->dDepth.release(); ex->dNStereo.release(); ex->dNRatio.release();
@@ -1532,6 +1566,148 @@ int viorb_image_bounds(int cols, int rows, const float* cam, const float* dist, 
     bounds->max_x = std::max(u[2], u[6]);
     bounds->min_y = std::min(u[1], u[3]);
     bounds->max_y = std::max(u[5], u[7]);
+    return VIORB_OK;
+}
+
+// ---- bag of words (row f-3) ----------------------------------------------------------------------------
+}  // extern "C"
+
+namespace {
+
+int bow_run(const viorb_vocabulary* voc, const uint8_t* dDesc, const int* dCounts, int nframes, int cap, int levelsup, BowBufs& b,
+            cudaStream_t st) {
+    if (cap > 16384) return fail(VIORB_E_CAPACITY, "bag-of-words transform supports at most 16384 descriptors per frame");
+    CU(b.ensure(nframes, cap));
+    int P = 256;                       // k_bow_build walks the sorted slots blockDim.x at a time: P >= 256
+    while (P < cap) P <<= 1;
+    const size_t smem = (size_t)P * sizeof(unsigned long long);
+    CU(cudaFuncSetAttribute(k_bow_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    VIORB_LAUNCH(k_bow_walk, dim3((cap + 7) / 8, nframes), dim3(256), 0, st, voc->d, dDesc, dCounts, cap, levelsup, b.leaf.p, b.nid.p);
+    VIORB_LAUNCH(k_bow_build, dim3(nframes), dim3(256), smem, st, voc->d, dCounts, cap, P, b.leaf.p, b.nid.p, b.bowWord.p,
+                 b.bowValue.p, b.nBow.p, b.fvNode.p, b.fvStart.p, b.fvFeature.p, b.nFv.p);
+    CU(cudaGetLastError());
+    return VIORB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int viorb_vocabulary_create(const viorb_vocab_desc* desc, int device, viorb_vocabulary** out) {
+    if (!desc || !out || desc->nnodes < 1 || !desc->child_start || !desc->descriptors || !desc->weight || !desc->word_id)
+        return fail(VIORB_E_ARG, "bad vocabulary description");
+    if (desc->weighting < 0 || desc->weighting > 3 || desc->scoring < 0 || desc->scoring > 5)
+        return fail(VIORB_E_ARG, "unknown weighting or scoring type");
+    const int nn = desc->nnodes;
+    if (desc->child_start[0] != 0) return fail(VIORB_E_ARG, "child_start[0] must be 0");
+    bool anyWord = false;
+    for (int i = 0; i < nn; ++i) {
+        const int c = desc->child_start[i + 1] - desc->child_start[i];
+        if (c < 0 || c >= (1 << 22)) return fail(VIORB_E_ARG, "child_start must be non-decreasing (fewer than 2^22 children per node)");
+        if (c == 0 && i > 0) anyWord = true;
+    }
+    const int nc = desc->child_start[nn];
+    if (nc > 0 && !desc->children) return fail(VIORB_E_ARG, "children missing");
+    for (int i = 0; i < nc; ++i)
+        if (desc->children[i] <= 0 || desc->children[i] >= nn) return fail(VIORB_E_ARG, "child id out of range");
+    int rc = need_device(device);
+    if (rc) return rc;
+    viorb_vocabulary* v = new viorb_vocabulary;
+    v->device = device;
+    cudaError_t e = upload(v->childStart, desc->child_start, (size_t)nn + 1);
+    if (e == cudaSuccess) e = upload(v->children, desc->children, (size_t)nc);
+    if (e == cudaSuccess) e = upload(v->wordId, desc->word_id, (size_t)nn);
+    if (e == cudaSuccess) e = upload(v->weight, desc->weight, (size_t)nn);
+    if (e == cudaSuccess) e = upload(v->desc, reinterpret_cast<const uint4*>(desc->descriptors), (size_t)nn * 2);
+    if (e != cudaSuccess) {
+        viorb_vocabulary_destroy(v);
+        return fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    }
+    v->d.nnodes = nn; v->d.levels = desc->levels; v->d.weighting = desc->weighting; v->d.scoring = desc->scoring;
+    v->d.anyWord = anyWord ? 1 : 0;
+    v->d.childStart = v->childStart.p; v->d.children = v->children.p; v->d.desc = v->desc.p; v->d.weight = v->weight.p;
+    v->d.wordId = v->wordId.p;
+    *out = v;
+    return VIORB_OK;
+}
+
+void viorb_vocabulary_destroy(viorb_vocabulary* v) {
+    if (!v) return;
+    cudaSetDevice(v->device);
+    v->childStart.release(); v->children.release(); v->wordId.release(); v->desc.release(); v->weight.release();
+    delete v;
+}
+
+int viorb_bow_transform(const viorb_vocabulary* voc, int nframes, int cap, const uint8_t* desc, const int32_t* n, int levelsup,
+                        uint32_t* bow_word, double* bow_value, int32_t* nbow, uint32_t* fv_node, int32_t* fv_start,
+                        uint32_t* fv_feature, int32_t* nfv) {
+    if (!voc || nframes < 0 || cap < 0 || (nframes > 0 && (!n || !nbow || !nfv))) return fail(VIORB_E_ARG, "bad argument");
+    if (nframes == 0) return VIORB_OK;
+    for (int f = 0; f < nframes; ++f)
+        if (n[f] < 0 || n[f] > cap) return fail(VIORB_E_ARG, "n[f] outside [0, cap]");
+    if (cap == 0) {
+        for (int f = 0; f < nframes; ++f) { nbow[f] = 0; nfv[f] = 0; if (fv_start) fv_start[f] = 0; }
+        return VIORB_OK;
+    }
+    if (!desc) return fail(VIORB_E_ARG, "descriptors missing");
+    int rc = need_device(voc->device);
+    if (rc) return rc;
+    const size_t N = (size_t)nframes * cap;
+    DevBuf<uint8_t> dD;
+    DevBuf<int> dN;
+    BowBufs b;
+    cudaError_t e = upload(dD, desc, N * 32);
+    if (e == cudaSuccess) e = upload(dN, n, (size_t)nframes);
+    rc = e == cudaSuccess ? VIORB_OK : fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    if (!rc) rc = bow_run(voc, dD.p, dN.p, nframes, cap, levelsup, b, (cudaStream_t)0);
+    if (!rc) {
+        auto down = [&](void* h, const void* d, size_t bytes) { if (e == cudaSuccess && h) e = cudaMemcpy(h, d, bytes, cudaMemcpyDeviceToHost); };
+        down(nbow, b.nBow.p, sizeof(int) * nframes);
+        down(nfv, b.nFv.p, sizeof(int) * nframes);
+        down(bow_word, b.bowWord.p, sizeof(uint32_t) * N);
+        down(bow_value, b.bowValue.p, sizeof(double) * N);
+        down(fv_node, b.fvNode.p, sizeof(uint32_t) * N);
+        down(fv_start, b.fvStart.p, sizeof(int) * (size_t)nframes * (cap + 1));
+        down(fv_feature, b.fvFeature.p, sizeof(uint32_t) * N);
+        if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    }
+    dD.release(); dN.release(); b.release();
+    return rc;
+}
+
+int viorb_bow_resident(viorb_extractor* ex, const viorb_vocabulary* voc, int levelsup) {
+    if (!ex || !voc || ex->lastN <= 0) return fail(VIORB_E_ARG, "bad handle, or nothing extracted yet");
+    if (voc->device != ex->prm.device) return fail(VIORB_E_ARG, "vocabulary and extractor live on different devices");
+    CU(cudaSetDevice(ex->prm.device));
+    int rc = bow_run(voc, ex->dDesc.p, ex->dNOut.p, ex->lastN, ex->g.outCap, levelsup, ex->bow, ex->stream);
+    if (rc) return rc;
+    ex->bowN = ex->lastN;
+    return VIORB_OK;
+}
+
+int viorb_bow_fetch(viorb_extractor* ex, int frame, uint32_t* bow_word, double* bow_value, int32_t* nbow, uint32_t* fv_node,
+                    int32_t* fv_start, uint32_t* fv_feature, int32_t* nfv) {
+    if (!ex || frame < 0 || frame >= ex->bowN) return fail(VIORB_E_ARG, "bad handle or frame index (call viorb_bow_resident first)");
+    CU(cudaSetDevice(ex->prm.device));
+    const BowBufs& b = ex->bow;
+    const size_t cap = b.cap, o = (size_t)frame * cap;
+    int cnt[2];
+    CU(cudaMemcpyAsync(&cnt[0], b.nBow.p + frame, sizeof(int), cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaMemcpyAsync(&cnt[1], b.nFv.p + frame, sizeof(int), cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaStreamSynchronize(ex->stream));
+    if (nbow) *nbow = cnt[0];
+    if (nfv) *nfv = cnt[1];
+    int nlisted = 0;
+    CU(cudaMemcpyAsync(&nlisted, b.fvStart.p + (size_t)frame * (cap + 1) + cnt[1], sizeof(int), cudaMemcpyDeviceToHost, ex->stream));
+    if (bow_word && cnt[0]) CU(cudaMemcpyAsync(bow_word, b.bowWord.p + o, sizeof(uint32_t) * cnt[0], cudaMemcpyDeviceToHost, ex->stream));
+    if (bow_value && cnt[0]) CU(cudaMemcpyAsync(bow_value, b.bowValue.p + o, sizeof(double) * cnt[0], cudaMemcpyDeviceToHost, ex->stream));
+    if (fv_node && cnt[1]) CU(cudaMemcpyAsync(fv_node, b.fvNode.p + o, sizeof(uint32_t) * cnt[1], cudaMemcpyDeviceToHost, ex->stream));
+    if (fv_start) CU(cudaMemcpyAsync(fv_start, b.fvStart.p + (size_t)frame * (cap + 1), sizeof(int) * (cnt[1] + 1), cudaMemcpyDeviceToHost, ex->stream));
+    CU(cudaStreamSynchronize(ex->stream));
+    if (fv_feature && nlisted) {
+        CU(cudaMemcpyAsync(fv_feature, b.fvFeature.p + o, sizeof(uint32_t) * nlisted, cudaMemcpyDeviceToHost, ex->stream));
+        CU(cudaStreamSynchronize(ex->stream));
+    }
     return VIORB_OK;
 }
 

@@ -135,3 +135,92 @@ def make_descriptors(nq: int, nt: int, seed: int = 0):
         perm = rng.permutation(nq)
         q = q[perm]
     return np.ascontiguousarray(q), np.ascontiguousarray(t)
+
+
+# DBoW3 enums (thirdparty/DBoW3/DBoW3/src/BowVector.h:38-55)
+TF_IDF, TF, IDF, BINARY = 0, 1, 2, 3
+L1_NORM, L2_NORM, CHI_SQUARE, KL, BHATTACHARYYA, DOT_PRODUCT = 0, 1, 2, 3, 4, 5
+
+
+def make_vocabulary(seed: int, k: int = 10, levels: int = 6, weighting: int = TF_IDF, scoring: int = L1_NORM,
+                    stop_fraction: float = 0.02, prune: float = 0.0, flip_bits: int = 40):
+    """Seeded stand-in for the ORBvoc tree (the real file is not part of the reference checkout): a k-ary tree of depth
+    ``levels`` in DBoW3's node numbering (children of a node get consecutive ids, level by level, like HKmeansStep creates
+    them), node descriptors = the parent's descriptor with ``flip_bits`` random bits flipped, leaf weights = idf-like
+    positive doubles with a share of stopped (weight 0) words.  ``prune`` removes that share of inner nodes' subtrees so
+    that leaves appear above the last level (irregular tree).  Returns the flat arrays libviorb's viorb_vocab_desc takes."""
+    rng = np.random.default_rng(seed)
+    desc = [rng.integers(0, 256, 32, dtype=np.uint8)]
+    children = [[]]
+    frontier = [0]
+    for lvl in range(levels):
+        nxt = []
+        for node in frontier:
+            if lvl > 0 and rng.random() < prune:
+                continue
+            for _ in range(k):
+                nid = len(desc)
+                d = desc[node].copy()
+                bits = rng.choice(256, flip_bits, replace=False)
+                np.bitwise_xor.at(d, bits >> 3, (1 << (bits & 7)).astype(np.uint8))
+                desc.append(d)
+                children.append([])
+                children[node].append(nid)
+                nxt.append(nid)
+        frontier = nxt
+    n = len(desc)
+    child_start = np.zeros(n + 1, np.int32)
+    child_start[1:] = np.cumsum([len(c) for c in children])
+    flat = np.array([c for cs in children for c in cs], np.int32)
+    word_id = np.full(n, -1, np.int32)
+    weight = np.zeros(n, np.float64)
+    leaves = [i for i in range(1, n) if not children[i]]
+    word_id[leaves] = np.arange(len(leaves), dtype=np.int32)
+    if weighting in (TF, BINARY):
+        w = np.ones(len(leaves))
+    else:
+        ni = rng.integers(1, 5000, len(leaves))
+        w = np.log(5000.0 / ni)
+        w[rng.random(len(leaves)) < stop_fraction] = 0.0
+    weight[leaves] = w
+    return {"levels": levels, "k": k, "weighting": weighting, "scoring": scoring, "child_start": child_start, "children": flat,
+            "descriptors": np.stack(desc), "weight": weight, "word_id": word_id}
+
+
+def make_vocabulary_fast(seed: int, k: int = 10, levels: int = 6, flip_bits: int = 40):
+    """Vectorised builder of a full k-ary TF-IDF / L1 tree for benchmark-size vocabularies (k=10, L=6: 1.1 M nodes)."""
+    rng = np.random.default_rng(seed)
+    level_desc = [rng.integers(0, 256, (1, 32), dtype=np.uint8)]
+    for _ in range(levels):
+        parent = np.repeat(level_desc[-1], k, axis=0)
+        m = len(parent)
+        bits = rng.integers(0, 256, (m, flip_bits))
+        mask = np.zeros((m, 32), np.uint8)
+        np.bitwise_xor.at(mask, (np.repeat(np.arange(m), flip_bits), (bits >> 3).ravel()), (1 << (bits & 7)).astype(np.uint8).ravel())
+        level_desc.append(parent ^ mask)
+    desc = np.concatenate(level_desc)
+    n = len(desc)
+    sizes = [len(d) for d in level_desc]
+    first = np.cumsum([0] + sizes)
+    child_start = np.zeros(n + 1, np.int32)
+    ninner = first[levels]
+    child_start[1:ninner + 1] = np.arange(1, ninner + 1) * k
+    child_start[ninner + 1:] = ninner * k
+    children = np.arange(1, n, dtype=np.int32)
+    word_id = np.full(n, -1, np.int32)
+    word_id[ninner:] = np.arange(n - ninner, dtype=np.int32)
+    weight = np.zeros(n, np.float64)
+    ni = rng.integers(1, 5000, n - ninner)
+    weight[ninner:] = np.log(5000.0 / ni)
+    return {"levels": levels, "k": k, "weighting": TF_IDF, "scoring": L1_NORM, "child_start": child_start, "children": children,
+            "descriptors": desc, "weight": weight, "word_id": word_id}
+
+
+def descriptors_near_words(voc, n: int, seed: int, flip_bits: int = 25):
+    """n descriptors = random leaf descriptors with a few bits flipped (so that walks spread over the tree and tie often)."""
+    rng = np.random.default_rng(seed)
+    leaves = np.nonzero(voc["word_id"] >= 0)[0]
+    d = voc["descriptors"][rng.choice(leaves, n)].copy()
+    bits = rng.integers(0, 256, (n, flip_bits))
+    np.bitwise_xor.at(d, (np.repeat(np.arange(n), flip_bits), (bits >> 3).ravel()), (1 << (bits & 7)).astype(np.uint8).ravel())
+    return d
