@@ -267,6 +267,30 @@ int viorb_bow_resident(viorb_extractor* ex, const viorb_vocabulary* voc, int lev
 int viorb_bow_fetch(viorb_extractor* ex, int frame, uint32_t* bow_word, double* bow_value, int32_t* nbow, uint32_t* fv_node,
                     int32_t* fv_start, uint32_t* fv_feature, int32_t* nfv);
 
+/* ---- fisheye stereo epilogue: SURVEY.md section 8 row f-4 ---------------------------------------- */
+
+/* The two KannalaBrandt8 cameras of a fisheye stereo rig: cam1 / cam2 = Camera::mvParameters (fx fy cx cy k0 k1 k2 k3) of
+ * mpCamera / mpCamera2, R12 (row-major) / t12 = Frame::mRlr / mtlr, precision = KannalaBrandt8::precision (1e-6,
+ * include/vi_slam/geometry/cameramodels/kannalabrandt8.h:29). */
+typedef struct viorb_kb8_rig { float cam1[8], cam2[8], R12[9], t12[3], precision; } viorb_kb8_rig;
+
+/* KannalaBrandt8::TriangulateMatches (src/geometry/cameramodels/kannalabrandt8.cpp:324-393) for n keypoint pairs:
+ * pt1 / pt2 [n][2] = kp1.pt / kp2.pt, sigma1 / sigma2 [n] = sigmaLevel / unc -> depth[n] = the return value (-1 when the
+ * parallax, depth or reprojection checks reject the pair), p3d [n][3] = p3D (0 when rejected).  Float: 1e-3 relative. */
+int viorb_kb8_triangulate_matches(const viorb_kb8_rig* rig, const float* pt1, const float* pt2, const float* sigma1,
+                                  const float* sigma2, int n, float* depth, float* p3d, int device);
+
+/* Frame::ComputeStereoFishEyeMatches (src/datastructures/frame.cpp:1148-1189): brute-force kNN-2 between the lapping-area
+ * descriptors (rows mono_left.. of the left frame, mono_right.. of the right), the 0.7 ratio rule, TriangulateMatches with
+ * level_sigma2[octave] (mvLevelSigma2), depth > 0.0001.  Outputs: left_to_right [n_left] = mvLeftToRightMatch,
+ * right_to_left [n_right] = mvRightToLeftMatch, depth [n_left] = mvDepth (-1), p3d [n_left][3] = mvStereo3Dpoints (valid
+ * where depth > 0), n_desc_matches = descMatches, n_matches = nMatches.  Host buffers. */
+int viorb_fisheye_stereo_matches(const viorb_kb8_rig* rig, const viorb_keypoint* kps_left, const uint8_t* desc_left, int n_left,
+                                 int mono_left, const viorb_keypoint* kps_right, const uint8_t* desc_right, int n_right,
+                                 int mono_right, const float* level_sigma2, int nlevels, int32_t* left_to_right,
+                                 int32_t* right_to_left, float* depth, float* p3d, int32_t* n_desc_matches, int32_t* n_matches,
+                                 int device);
+
 #ifdef __cplusplus
 }
 #endif

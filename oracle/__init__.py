@@ -80,6 +80,7 @@ def lib():
         L.orc_vocab_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, i32p, i32p, u8p, f64p, i32p]
         L.orc_vocab_destroy.argtypes = [C.c_void_p]
         L.orc_bow_transform.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int, u32p, f64p, i32p, u32p, i32p, u32p, i32p]
+        L.orc_kb8_triangulate.argtypes = [f32p, f32p, f32p, f32p, f32p, C.c_int, f32p, f32p, f32p]
         _lib = L
     return _lib
 
@@ -365,3 +366,48 @@ class OracleVocabulary:
         lib().orc_bow_transform(self._h, _u8(desc), n, int(levelsup), bw.ctypes.data_as(u32), bv.ctypes.data_as(C.POINTER(C.c_double)),
                                 C.byref(nb), fn.ctypes.data_as(u32), _i32(fs), ff.ctypes.data_as(u32), C.byref(nf))
         return bw[:nb.value].copy(), bv[:nb.value].copy(), fn[:nf.value].copy(), fs[:nf.value + 1].copy(), ff[:fs[nf.value]].copy()
+
+
+def kb8_rig(prm1, prm2, R12, t12, precision=1e-6):
+    """The 29 floats the KB8 functions take: cam1 (fx fy cx cy k0..k3), cam2, R12 row-major, t12, Newton precision."""
+    return np.concatenate([np.asarray(prm1, np.float32).ravel(), np.asarray(prm2, np.float32).ravel(), np.asarray(R12, np.float32).ravel(),
+                           np.asarray(t12, np.float32).ravel(), np.array([precision], np.float32)]).astype(np.float32)
+
+
+def kb8_triangulate(rig, pt1, pt2, sigma1, sigma2):
+    """KannalaBrandt8::TriangulateMatches (kannalabrandt8.cpp:324-393) per pair -> (depth, p3d, margin)."""
+    rig = np.ascontiguousarray(rig, np.float32)
+    pt1, pt2 = np.ascontiguousarray(pt1, np.float32).reshape(-1, 2), np.ascontiguousarray(pt2, np.float32).reshape(-1, 2)
+    s1, s2 = np.ascontiguousarray(sigma1, np.float32), np.ascontiguousarray(sigma2, np.float32)
+    n = len(pt1)
+    depth, p3d, margin = np.zeros(n, np.float32), np.zeros((n, 3), np.float32), np.zeros(n, np.float32)
+    lib().orc_kb8_triangulate(_f32(rig), _f32(pt1), _f32(pt2), _f32(s1), _f32(s2), n, _f32(depth), _f32(p3d), _f32(margin))
+    return depth, p3d, margin
+
+
+def stereo_fisheye_matches(rig, kps_left, desc_left, mono_left, kps_right, desc_right, mono_right, level_sigma2):
+    """Frame::ComputeStereoFishEyeMatches (frame.cpp:1148-1189) composed from the oracle's knnMatch and TriangulateMatches.
+    -> dict like vi_slam_b200.matcher.compute_stereo_fisheye_matches, plus the per-query triangulation margin."""
+    nl, nr = len(kps_left), len(kps_right)
+    out = {"left_to_right": np.full(nl, -1, np.int32), "right_to_left": np.full(nr, -1, np.int32), "depth": np.full(nl, -1, np.float32),
+           "p3d": np.zeros((nl, 3), np.float32), "desc_matches": 0, "matches": 0, "margin": np.full(nl, np.inf, np.float32)}
+    nq, nt = nl - mono_left, nr - mono_right
+    if nq == 0 or nt < 2:
+        return out
+    idx, dist = knn2(desc_left[mono_left:], desc_right[mono_right:])
+    sig = np.asarray(level_sigma2, np.float32)
+    for q in range(nq):
+        if not (np.float32(dist[q, 0]) < float(np.float32(dist[q, 1])) * 0.7):
+            continue
+        out["desc_matches"] += 1
+        il, ir = q + mono_left, int(idx[q, 0]) + mono_right
+        a, b = kps_left[il], kps_right[ir]
+        d, p, m = kb8_triangulate(rig, [[a["x"], a["y"]]], [[b["x"], b["y"]]], [sig[a["octave"]]], [sig[b["octave"]]])
+        out["margin"][il] = m[0]
+        if d[0] > np.float32(0.0001):
+            out["left_to_right"][il] = ir
+            out["right_to_left"][ir] = il
+            out["p3d"][il] = p[0]
+            out["depth"][il] = d[0]
+            out["matches"] += 1
+    return out

@@ -89,6 +89,9 @@ SYMBOLS = {
                                       C.c_void_p, C.c_void_p, C.c_void_p, i32p]),
     "viorb_bow_resident": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
     "viorb_bow_fetch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, i32p, C.c_void_p, C.c_void_p, C.c_void_p, i32p]),
+    "viorb_kb8_triangulate_matches": (C.c_int, [f32p, f32p, f32p, f32p, f32p, C.c_int, f32p, f32p, C.c_int]),
+    "viorb_fisheye_stereo_matches": (C.c_int, [f32p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                               C.c_int, f32p, C.c_int, i32p, i32p, f32p, f32p, i32p, i32p, C.c_int]),
 }
 
 _cache = {}

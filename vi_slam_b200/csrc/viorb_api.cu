@@ -16,6 +16,7 @@
 #include "kernels_match.cuh"
 #include "kernels_window.cuh"
 #include "kernels_bow.cuh"
+#include "kernels_kb8.cuh"
 
 #define VIORB_MAX_CHUNKS 8
 
@@ -1709,6 +1710,97 @@ int viorb_bow_fetch(viorb_extractor* ex, int frame, uint32_t* bow_word, double* 
         CU(cudaStreamSynchronize(ex->stream));
     }
     return VIORB_OK;
+}
+
+// ---- fisheye stereo epilogue (row f-4) ------------------------------------------------------------------
+static_assert(sizeof(Kb8Rig) == sizeof(viorb_kb8_rig), "rig layouts must match");
+
+int viorb_kb8_triangulate_matches(const viorb_kb8_rig* rig, const float* pt1, const float* pt2, const float* sigma1,
+                                  const float* sigma2, int n, float* depth, float* p3d, int device) {
+    if (!rig || n < 0 || (n > 0 && (!pt1 || !pt2 || !sigma1 || !sigma2 || !depth || !p3d))) return fail(VIORB_E_ARG, "bad argument");
+    if (n == 0) return VIORB_OK;
+    int rc = need_device(device);
+    if (rc) return rc;
+    Kb8Rig g;
+    std::memcpy(&g, rig, sizeof(g));
+    DevBuf<float2> d1, d2;
+    DevBuf<float> s1, s2, dz, dp;
+    cudaError_t e = upload(d1, reinterpret_cast<const float2*>(pt1), n);
+    if (e == cudaSuccess) e = upload(d2, reinterpret_cast<const float2*>(pt2), n);
+    if (e == cudaSuccess) e = upload(s1, sigma1, n);
+    if (e == cudaSuccess) e = upload(s2, sigma2, n);
+    if (e == cudaSuccess) e = dz.alloc(n);
+    if (e == cudaSuccess) e = dp.alloc((size_t)n * 3);
+    if (e == cudaSuccess) {
+        VIORB_LAUNCH(k_kb8_triangulate, dim3((n + 127) / 128), dim3(128), 0, (cudaStream_t)0, g, d1.p, d2.p, s1.p, s2.p, n, dz.p, dp.p);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(depth, dz.p, sizeof(float) * n, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(p3d, dp.p, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost);
+    d1.release(); d2.release(); s1.release(); s2.release(); dz.release(); dp.release();
+    return e == cudaSuccess ? VIORB_OK : fail(VIORB_E_CUDA, cudaGetErrorString(e));
+}
+
+int viorb_fisheye_stereo_matches(const viorb_kb8_rig* rig, const viorb_keypoint* kps_left, const uint8_t* desc_left, int n_left,
+                                 int mono_left, const viorb_keypoint* kps_right, const uint8_t* desc_right, int n_right,
+                                 int mono_right, const float* level_sigma2, int nlevels, int32_t* left_to_right,
+                                 int32_t* right_to_left, float* depth, float* p3d, int32_t* n_desc_matches, int32_t* n_matches,
+                                 int device) {
+    if (!rig || n_left < 0 || n_right < 0 || mono_left < 0 || mono_left > n_left || mono_right < 0 || mono_right > n_right ||
+        !level_sigma2 || nlevels <= 0 || (n_left > 0 && (!kps_left || !desc_left || !left_to_right || !depth || !p3d)) ||
+        (n_right > 0 && (!kps_right || !desc_right || !right_to_left)))
+        return fail(VIORB_E_ARG, "bad argument");
+    for (int i = 0; i < n_left; ++i) { left_to_right[i] = -1; depth[i] = -1.0f; p3d[3 * i] = p3d[3 * i + 1] = p3d[3 * i + 2] = 0.f; }
+    for (int i = 0; i < n_right; ++i) right_to_left[i] = -1;
+    if (n_desc_matches) *n_desc_matches = 0;
+    if (n_matches) *n_matches = 0;
+    const int nq = n_left - mono_left, nt = n_right - mono_right;
+    if (nq == 0 || nt < 2) return VIORB_OK;                  // knnMatch returns fewer than 2 neighbours: nothing passes
+    for (int i = mono_left; i < n_left; ++i)
+        if (kps_left[i].octave < 0 || kps_left[i].octave >= nlevels) return fail(VIORB_E_ARG, "keypoint octave outside level_sigma2");
+    for (int i = mono_right; i < n_right; ++i)
+        if (kps_right[i].octave < 0 || kps_right[i].octave >= nlevels) return fail(VIORB_E_ARG, "keypoint octave outside level_sigma2");
+    int rc = need_device(device);
+    if (rc) return rc;
+    Kb8Rig g;
+    std::memcpy(&g, rig, sizeof(g));
+    DevBuf<viorb_keypoint> dKL, dKR;
+    DevBuf<uint8_t> dDL, dDR;
+    DevBuf<int32_t> dIdx, dDist, dL2R, dR2L;
+    DevBuf<float> dSig, dZ, dP;
+    DevBuf<int> dCnt;
+    cudaError_t e = upload(dKL, kps_left, n_left);
+    if (e == cudaSuccess) e = upload(dKR, kps_right, n_right);
+    if (e == cudaSuccess) e = upload(dDL, desc_left + (size_t)mono_left * 32, (size_t)nq * 32);
+    if (e == cudaSuccess) e = upload(dDR, desc_right + (size_t)mono_right * 32, (size_t)nt * 32);
+    if (e == cudaSuccess) e = upload(dSig, level_sigma2, nlevels);
+    if (e == cudaSuccess) e = upload(dL2R, left_to_right, n_left);
+    if (e == cudaSuccess) e = upload(dR2L, right_to_left, n_right);
+    if (e == cudaSuccess) e = upload(dZ, depth, n_left);
+    if (e == cudaSuccess) e = upload(dP, p3d, (size_t)n_left * 3);
+    if (e == cudaSuccess) e = dIdx.alloc((size_t)nq * 2);
+    if (e == cudaSuccess) e = dDist.alloc((size_t)nq * 2);
+    if (e == cudaSuccess) e = dCnt.alloc(2);
+    if (e == cudaSuccess) e = cudaMemset(dCnt.p, 0, sizeof(int) * 2);
+    rc = e == cudaSuccess ? VIORB_OK : fail(VIORB_E_CUDA, cudaGetErrorString(e));
+    if (!rc) rc = viorb_knn2_device(dDL.p, nq, dDR.p, nt, dIdx.p, dDist.p, nullptr);
+    if (!rc) {
+        VIORB_LAUNCH(k_fisheye_epilogue, dim3((nq + 127) / 128), dim3(128), 0, (cudaStream_t)0, g, dKL.p, mono_left, dKR.p, mono_right, nq,
+                     dIdx.p, dDist.p, dSig.p, dL2R.p, dR2L.p, dZ.p, dP.p, dCnt.p);
+        e = cudaGetLastError();
+        int cnt[2] = {0, 0};
+        if (e == cudaSuccess) e = cudaMemcpy(left_to_right, dL2R.p, sizeof(int32_t) * n_left, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(right_to_left, dR2L.p, sizeof(int32_t) * n_right, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(depth, dZ.p, sizeof(float) * n_left, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(p3d, dP.p, sizeof(float) * 3 * n_left, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(cnt, dCnt.p, sizeof(int) * 2, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
+        if (n_desc_matches) *n_desc_matches = cnt[0];
+        if (n_matches) *n_matches = cnt[1];
+    }
+    dKL.release(); dKR.release(); dDL.release(); dDR.release(); dIdx.release(); dDist.release(); dL2R.release(); dR2L.release();
+    dSig.release(); dZ.release(); dP.release(); dCnt.release();
+    return rc;
 }
 
 }  // extern "C"

@@ -9,6 +9,8 @@
 * ``features_in_area``         Frame::GetFeaturesInArea on Frame::AssignFeaturesToGrid   (frame.cpp:386-414,678-757)
 * ``search_for_initialization`` FMatcher::SearchForInitialization                        (fmatcher.cpp:983-1098)
 * ``search_by_projection``     FMatcher::SearchByProjection(CurrentFrame, LastFrame, ..) (fmatcher.cpp:2471-2688)
+* ``kb8_rig`` / ``triangulate_matches``  KannalaBrandt8::TriangulateMatches (src/geometry/cameramodels/kannalabrandt8.cpp:324-393)
+* ``compute_stereo_fisheye_matches``      Frame::ComputeStereoFishEyeMatches     (frame.cpp:1148-1189)
 All compute happens in libviorb.so (CUDA); no CPU path.
 """
 from __future__ import annotations
@@ -217,3 +219,45 @@ def search_by_projection(uv, invz, last_octave, last_angle, desc_mp, valid, obse
         n2.ctypes.data_as(_lib.i32p), b.ctypes.data, sf.ctypes.data_as(_lib.f32p), len(sf), float(th), float(bf),
         int(direction), int(check_orientation), out.ctypes.data_as(_lib.i32p), nm.ctypes.data_as(_lib.i32p), device))
     return int(nm[0]), out[:len(k2)].copy()
+
+
+def kb8_rig(cam1, cam2, R12, t12, precision=1e-6):
+    """viorb_kb8_rig as 29 floats: mpCamera / mpCamera2 parameters (fx fy cx cy k0..k3), mRlr (row-major), mtlr, precision."""
+    r = np.concatenate([np.asarray(cam1, np.float32).ravel(), np.asarray(cam2, np.float32).ravel(), np.asarray(R12, np.float32).ravel(),
+                        np.asarray(t12, np.float32).ravel(), np.array([precision], np.float32)]).astype(np.float32)
+    assert r.size == 29
+    return r
+
+
+def triangulate_matches(rig, pt1, pt2, sigma1, sigma2, device=0, lib_path=None):
+    """-> (depth float32[n] (-1 = rejected), p3d float32[n, 3])"""
+    lib = _lib.load(lib_path)
+    rig = np.ascontiguousarray(rig, np.float32)
+    pt1, pt2 = np.ascontiguousarray(pt1, np.float32).reshape(-1, 2), np.ascontiguousarray(pt2, np.float32).reshape(-1, 2)
+    s1, s2 = np.ascontiguousarray(sigma1, np.float32), np.ascontiguousarray(sigma2, np.float32)
+    n = len(pt1)
+    depth, p3d = np.zeros(n, np.float32), np.zeros((n, 3), np.float32)
+    f = _lib.f32p
+    _check(lib, lib.viorb_kb8_triangulate_matches(rig.ctypes.data_as(f), pt1.ctypes.data_as(f), pt2.ctypes.data_as(f), s1.ctypes.data_as(f),
+                                                  s2.ctypes.data_as(f), n, depth.ctypes.data_as(f), p3d.ctypes.data_as(f), device))
+    return depth, p3d
+
+
+def compute_stereo_fisheye_matches(rig, kps_left, desc_left, mono_left, kps_right, desc_right, mono_right, level_sigma2, device=0,
+                                   lib_path=None):
+    """-> dict(left_to_right, right_to_left, depth, p3d, desc_matches, matches) = mvLeftToRightMatch, mvRightToLeftMatch, mvDepth,
+    mvStereo3Dpoints, descMatches, nMatches."""
+    lib = _lib.load(lib_path)
+    rig = np.ascontiguousarray(rig, np.float32)
+    kl, kr = np.ascontiguousarray(kps_left, KP_DTYPE), np.ascontiguousarray(kps_right, KP_DTYPE)
+    dl, dr = _desc(desc_left) if len(kl) else np.zeros((0, 32), np.uint8), _desc(desc_right) if len(kr) else np.zeros((0, 32), np.uint8)
+    sig = np.ascontiguousarray(level_sigma2, np.float32)
+    l2r, r2l = np.zeros(len(kl), np.int32), np.zeros(len(kr), np.int32)
+    depth, p3d = np.zeros(len(kl), np.float32), np.zeros((len(kl), 3), np.float32)
+    nd, nm = C.c_int32(), C.c_int32()
+    f, i = _lib.f32p, _lib.i32p
+    _check(lib, lib.viorb_fisheye_stereo_matches(rig.ctypes.data_as(f), kl.ctypes.data, dl.ctypes.data, len(kl), int(mono_left),
+                                                 kr.ctypes.data, dr.ctypes.data, len(kr), int(mono_right), sig.ctypes.data_as(f), len(sig),
+                                                 l2r.ctypes.data_as(i), r2l.ctypes.data_as(i), depth.ctypes.data_as(f),
+                                                 p3d.ctypes.data_as(f), C.byref(nd), C.byref(nm), device))
+    return {"left_to_right": l2r, "right_to_left": r2l, "depth": depth, "p3d": p3d, "desc_matches": nd.value, "matches": nm.value}
