@@ -973,16 +973,26 @@ __global__ void __launch_bounds__(64) k_blur(ExtractGeom g, FrameSrc fs, BlurTil
     const int NCH = VIORB_BLUR_SP / 16;              // 18 chunks per staged row
     for (int i = threadIdx.x; i < nrows * NCH; i += 64) {
         const int r = (i * 3641) >> 16, c = i - r * NCH;            // i / 18 for i < 2^13
-        const int sy = reflect101_dev(y0 - 3 + r, L.h);
         const int cx = X0 - 16 + 16 * c;
-        uint8_t* d = tile + r * VIORB_BLUR_SP + 16 * c;
-        const uint8_t* srow = img + (size_t)sy * pitch;
         if (cx >= 0 && cx + 16 <= L.w) {
-            __pipeline_memcpy_async(d, srow + cx, 16);
-        } else if (cx + 16 > -3 && cx < L.w + 3) {
-            for (int b = 0; b < 16; ++b) {
-                const int col = cx + b;
-                if (col >= -3 && col < L.w + 3) d[b] = srow[reflect101_dev(col, L.w)];
+            const int sy = reflect101_dev(y0 - 3 + r, L.h);
+            __pipeline_memcpy_async(tile + r * VIORB_BLUR_SP + 16 * c, img + (size_t)sy * pitch + cx, 16);
+        }
+    }
+    // Columns that no whole in-image chunk covers: the 3 reflected columns left of the image (first tile column) and
+    // the tail [w & ~15, w + 3) (last tile column), at most 3 + 18 bytes per row.  One lane per such column, two rows per
+    // pass: a lane-serial byte loop inside the chunk loop above made the whole warp wait ~300 instructions per chunk.
+    {
+        const int nL = X0 == 0 ? 3 : 0;
+        const int cR = max(L.w & ~15, X0 - 16), eR = min(L.w + 3, X0 + VIORB_BLUR_TW + 16);
+        const int nE = nL + max(eR - cR, 0);
+        const int e = threadIdx.x & 31;
+        if (e < nE) {
+            const int colx = e < nL ? e - 3 : cR + (e - nL);
+            const int sx = reflect101_dev(colx, L.w);
+            for (int r = threadIdx.x >> 5; r < nrows; r += 2) {
+                const int sy = reflect101_dev(y0 - 3 + r, L.h);
+                tile[r * VIORB_BLUR_SP + (colx - X0 + 16)] = img[(size_t)sy * pitch + sx];
             }
         }
     }
