@@ -404,6 +404,7 @@ static inline double __dsub_rn(double a, double b) { return a - b; }
 static inline double __ddiv_rn(double a, double b) { return a / b; }
 static inline float __double2float_rn(double a) { return (float)a; }
 static inline double __dsqrt_rn(double a) { return std::sqrt(a); }
+static inline unsigned __umulhi(unsigned a, unsigned b) { return (unsigned)(((unsigned long long)a * b) >> 32); }
 #pragma GCC pop_options
 static inline float __int_as_float(int v) { float f; std::memcpy(&f, &v, 4); return f; }
 static inline int __float_as_int(float f) { int v; std::memcpy(&v, &f, 4); return v; }

@@ -86,18 +86,21 @@ __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int 
         }
         unsigned g0[4], g1[4];
         int haveRow = -0x40000000;
+        // h = (row sum) >> 4, the form the vertical pass consumes (each row sum is used by up to two output rows)
         auto hpass = [&](int sy, unsigned h[4]) {
             const uint32_t* r = reinterpret_cast<const uint32_t*>(src + (size_t)sy * sp);
             const unsigned a = __ldg(r + w0i), b = __ldg(r + w1i), c = __ldg(r + w2i);
 #pragma unroll
             for (int i = 0; i < 4; ++i)
-                h[i] = __dp2a_lo((unsigned)ar[i], __byte_perm(hi[i] ? b : a, hi[i] ? c : b, sel[i]), 0u);
+                h[i] = __dp2a_lo((unsigned)ar[i], __byte_perm(hi[i] ? b : a, hi[i] ? c : b, sel[i]), 0u) >> 4;
         };
+        const int srcH1 = S.h - 1, opitch = L.pitch;
+        uint8_t* d = dst + (size_t)dy0 * opitch + x4;
         for (int r = 0; r < nrow; ++r) {
             const int dy = dy0 + r;
             const int sy = __ldg(yofs + L.yTab + dy);
             const short2 bt = __ldg(ybeta + L.yTab + dy);
-            const int sy0 = min(max(sy, 0), S.h - 1), sy1 = min(max(sy + 1, 0), S.h - 1);
+            const int sy0 = min(max(sy, 0), srcH1), sy1 = min(max(sy + 1, 0), srcH1);
             if (haveRow == sy0) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) g0[i] = g1[i];
@@ -106,15 +109,17 @@ __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int 
             }
             hpass(sy1, g1);
             haveRow = sy1;
+            // (beta * h) >> 16 as the high half of (beta << 16) * h: beta in [0, 2048], h < 2^20, one IMAD.HI each
+            const unsigned B0 = (unsigned)(int)bt.x << 16, B1 = (unsigned)(int)bt.y << 16;
             uint32_t packed = 0;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                const int v = ((((int)bt.x * ((int)g0[i] >> 4)) >> 16) + (((int)bt.y * ((int)g1[i] >> 4)) >> 16) + 2) >> 2;
-                packed |= (uint32_t)(v & 0xFF) << (8 * i);
+                const unsigned v = (__umulhi(B0, g0[i]) + __umulhi(B1, g1[i]) + 2u) >> 2;      // <= 255
+                packed = v * (1u << (8 * i)) + packed;
             }
-            uint8_t* d = dst + (size_t)dy * L.pitch + x4;
-            if (x4 + 3 < L.w) *reinterpret_cast<uint32_t*>(d) = packed;
-            else for (int i = 0; i < 4 && x4 + i < L.w; ++i) d[i] = (uint8_t)(packed >> (8 * i));
+            // rows are padded to 64 bytes: the last word of a row may spill into the padding
+            *reinterpret_cast<uint32_t*>(d) = packed;
+            d += opitch;
         }
         return;
     }
@@ -1007,6 +1012,8 @@ __global__ void __launch_bounds__(64) k_blur(ExtractGeom g, FrameSrc fs, BlurTil
 #pragma unroll
     for (int r = 0; r < 6; ++r) blur_row4(col[r * SPW - 1], col[r * SPW], col[r * SPW + 1], ring[r]);
     const uint32_t* nxt = col + 6 * SPW;             // staged row of image row y + 3
+    const int opitch = L.pitch;
+    uint8_t* orow = dst + (size_t)y0 * opitch + x0;
     for (int yb = y0; yb < yEnd; yb += 7) {
 #pragma unroll
         for (int k = 0; k < 7; ++k) {
@@ -1022,9 +1029,9 @@ __global__ void __launch_bounds__(64) k_blur(ExtractGeom g, FrameSrc fs, BlurTil
                                          48u * (ring[(k + 2) % 7][j] + ring[(k + 4) % 7][j]) + 56u * ring[(k + 3) % 7][j];
                     out |= ((acc + 32768u) >> 16) << (8 * j);
                 }
-                uint8_t* o = dst + (size_t)y * L.pitch + x0;
-                if (x0 + 3 < L.w) *reinterpret_cast<uint32_t*>(o) = out;
-                else for (int j = 0; j < 4 && x0 + j < L.w; ++j) o[j] = (uint8_t)(out >> (8 * j));
+                // rows are padded to 64 bytes, so the last word of a row may spill into the padding
+                *reinterpret_cast<uint32_t*>(orow) = out;
+                orow += opitch;
             }
         }
     }
