@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--distinct", type=int, default=8, help="distinct synthetic stereo pairs generated (tiled to --pairs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--variant-lib", default=None, help="experimental build of libviorb.so to measure instead of the product one")
     ap.add_argument("--e2e-workers", type=int, default=3, help="pipeline workers (handle pairs in flight) of the end-to-end leg")
     return ap.parse_args()
 
@@ -166,6 +167,9 @@ def run_ours(args, rank, world, local_rank):
     from vi_slam_b200 import FExtractor, matcher
 
     os.environ.pop("VIORB_LIBRARY", None)            # the product library only
+    if args.variant_lib:                             # A/B experiments (tools/variants_bench.sh); flagged in the output
+        from vi_slam_b200 import _lib
+        _lib.DEFAULT_LIB = os.path.abspath(args.variant_lib)
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
@@ -343,6 +347,7 @@ def run_ours(args, rank, world, local_rank):
                    "input_bytes_per_step": 2 * B * PITCH * H, "parallelism": f"frame-batch x{world}, no collective",
                    "keypoints_per_frame": n_kp / B, "stereo_matches_per_s": n_stereo / B * value,
                    "ratio_matches_per_s": n_ratio / B * value},
+        **({"variant_lib": args.variant_lib} if args.variant_lib else {}),
         "clocks": clk, "e2e": e2e, "gpu_launches": K * (2 * (NLEVELS - 1 + 6) + 5),
         "stages_ms_per_step": mean,
         "stage_timing": "second pass of K steps, both handles on one stream, CUDA events around each stage", "roofline": roofline,

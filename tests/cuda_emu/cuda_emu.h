@@ -39,6 +39,7 @@ struct dim3 {
     dim3(unsigned x_ = 1, unsigned y_ = 1, unsigned z_ = 1) : x(x_), y(y_), z(z_) {}
 };
 struct uchar4 { unsigned char x, y, z, w; };
+struct char4 { signed char x, y, z, w; };
 struct uchar2 { unsigned char x, y; };
 struct ushort2 { unsigned short x, y; };
 struct short2 { short x, y; };

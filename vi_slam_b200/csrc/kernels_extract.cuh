@@ -1050,57 +1050,84 @@ __device__ __forceinline__ int round_rn_magic(float v) {
     return __float_as_int(__fadd_rn(v, 12582912.0f)) - 0x4B400000;
 }
 
-__global__ void __launch_bounds__(256) k_describe(ExtractGeom g, FrameSrc fs, const KeptKp* __restrict__ kept,
+#ifndef VIORB_DESC_KPW
+#define VIORB_DESC_KPW 4                    // consecutive output slots handled by one warp
+#endif
+#ifndef VIORB_DESC_MINB
+#define VIORB_DESC_MINB 4                   // <= 64 registers: 4 CTAs per SM (measured: 0.37 ms against 0.39 at 79 registers)
+#endif
+__global__ void __launch_bounds__(256, VIORB_DESC_MINB) k_describe(ExtractGeom g, FrameSrc fs, const KeptKp* __restrict__ kept,
                                                   const int* __restrict__ slot2kept, const int* __restrict__ nOut,
                                                   uint8_t* __restrict__ desc) {
-    // pattern as float4 (x0, y0, x1, y1) per test, test (lane*8 + t) at [t*32 + lane]: conflict-free LDS.128
-    __shared__ __align__(16) float4 pat[256];
-    __shared__ __align__(16) uint8_t patch[8][(2 * VIORB_DESC_R + 1) * VIORB_DESC_PW];
-    {
-        const int i = threadIdx.x;                                  // test index
-        const int8_t* q = d_orb_pattern + 4 * i;
-        pat[(i & 7) * 32 + (i >> 3)] = make_float4((float)q[0], (float)q[1], (float)q[2], (float)q[3]);
-    }
-    __syncthreads();
+    // two patch buffers per warp: the next keypoint's patch is in flight (cp.async) while this one is sampled
+    __shared__ __align__(16) uint8_t patch[8][2][(2 * VIORB_DESC_R + 1) * VIORB_DESC_PW];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int slot = blockIdx.x * 8 + wid;
     const int f = blockIdx.y + g.frame0;
-    if (slot >= nOut[f]) return;
-    const KeptKp k = kept[(size_t)f * g.keptPerFrame + slot2kept[(size_t)f * g.outCap + slot]];
-    const int l = k.score >> 16;
-    const LevelGeom& L = g.lv[l];
-    const uint8_t* img = fs.blur + (size_t)f * g.arenaStride + L.off;
-    // stage the (2R+1)-row neighbourhood with coalesced aligned word loads (the 512 samples would
-    // otherwise be 512 scattered byte requests to L1)
-    const int xs = (k.x - VIORB_DESC_R) & ~3, shift = (k.x - VIORB_DESC_R) - xs;
-    uint8_t* P = patch[wid];
-    const uint8_t* src = img + (size_t)(k.y - VIORB_DESC_R) * L.pitch + xs;
-    const int NW = VIORB_DESC_PW / 4;
-    // asynchronous global -> shared copies: all of a lane's words are in flight together (a load -> store loop
-    // serialises 13 L2 latencies per warp)
-#pragma unroll
-    for (int i0 = 0; i0 < (2 * VIORB_DESC_R + 1) * NW; i0 += 32) {
-        const int i = i0 + lane;
-        if (i < (2 * VIORB_DESC_R + 1) * NW) {
-            const int r = (i * 373) >> 12, c = i - r * NW;            // i / 11 (exact for i < 593; i < 407 here)
-            __pipeline_memcpy_async(P + 4 * i, src + (size_t)r * L.pitch + 4 * c, 4);
-        }
-    }
-    __pipeline_commit();
-    __pipeline_wait_prior(0);
-    __syncwarp();
-    const uint8_t* ctr = P + VIORB_DESC_R * VIORB_DESC_PW + VIORB_DESC_R + shift;
-    const float a = k.c, b = k.s;
-    int val = 0;
+    const int n = nOut[f];
+    const int slot0 = (blockIdx.x * 8 + wid) * VIORB_DESC_KPW;
+    if (slot0 >= n) return;
+    // the lane's 8 tests (descriptor byte `lane`) stay in registers for all of the warp's keypoints: the shared-memory
+    // pattern table of the previous version cost 8 LDS.128 (32 L1 wavefronts) per keypoint in a kernel that ncu showed
+    // bound by L1 wavefronts
+    float4 pt[8];
 #pragma unroll
     for (int t = 0; t < 8; ++t) {
-        const float4 p = pat[t * 32 + lane];
-        const int r0 = round_rn_magic(__fadd_rn(__fmul_rn(p.x, b), __fmul_rn(p.y, a)));
-        const int c0 = round_rn_magic(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, b)));
-        const int r1 = round_rn_magic(__fadd_rn(__fmul_rn(p.z, b), __fmul_rn(p.w, a)));
-        const int c1 = round_rn_magic(__fsub_rn(__fmul_rn(p.z, a), __fmul_rn(p.w, b)));
-        const int t0 = ctr[r0 * VIORB_DESC_PW + c0], t1 = ctr[r1 * VIORB_DESC_PW + c1];
-        val |= (t0 < t1) << t;
+        const char4 q = *reinterpret_cast<const char4*>(d_orb_pattern + 4 * (lane * 8 + t));
+        pt[t] = make_float4((float)q.x, (float)q.y, (float)q.z, (float)q.w);
     }
-    desc[((size_t)f * g.outCap + slot) * 32 + lane] = (uint8_t)val;
+    const KeptKp* kf = kept + (size_t)f * g.keptPerFrame;
+    const int* s2k = slot2kept + (size_t)f * g.outCap;
+    const int NW = VIORB_DESC_PW / 4;
+    // stage the (2R+1)-row neighbourhood of keypoint k with aligned 4-byte asynchronous copies (the 512 samples would
+    // otherwise be 512 scattered byte requests to L1); returns the byte shift of the patch inside its first word
+    auto stage = [&](const KeptKp& k, uint8_t* P) {
+        const LevelGeom& L = g.lv[k.score >> 16];
+        const uint8_t* img = fs.blur + (size_t)f * g.arenaStride + L.off;
+        const int xs = (k.x - VIORB_DESC_R) & ~3;
+        const uint8_t* src = img + (size_t)(k.y - VIORB_DESC_R) * L.pitch + xs;
+        const int lp = L.pitch;
+#pragma unroll
+        for (int i0 = 0; i0 < (2 * VIORB_DESC_R + 1) * NW; i0 += 32) {
+            const int i = i0 + lane;
+            if (i < (2 * VIORB_DESC_R + 1) * NW) {
+                const int r = (i * 373) >> 12, c = i - r * NW;            // i / 11 (exact for i < 593; i < 407 here)
+                __pipeline_memcpy_async(P + 4 * i, src + (size_t)r * lp + 4 * c, 4);
+            }
+        }
+        __pipeline_commit();
+    };
+    KeptKp k = kf[s2k[slot0]];
+    stage(k, patch[wid][0]);
+#pragma unroll 1
+    for (int j = 0; j < VIORB_DESC_KPW; ++j) {
+        const int slot = slot0 + j;
+        const bool more = j + 1 < VIORB_DESC_KPW && slot + 1 < n;
+        KeptKp kn = k;
+        if (more) {
+            kn = kf[s2k[slot + 1]];
+            stage(kn, patch[wid][(j + 1) & 1]);
+            __pipeline_wait_prior(1);
+        } else {
+            __pipeline_wait_prior(0);
+        }
+        __syncwarp();
+        const int shift = (k.x - VIORB_DESC_R) & 3;
+        const uint8_t* ctr = patch[wid][j & 1] + VIORB_DESC_R * VIORB_DESC_PW + VIORB_DESC_R + shift;
+        const float a = k.c, b = k.s;
+        int val = 0;
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            const float4 p = pt[t];
+            const int r0 = round_rn_magic(__fadd_rn(__fmul_rn(p.x, b), __fmul_rn(p.y, a)));
+            const int c0 = round_rn_magic(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, b)));
+            const int r1 = round_rn_magic(__fadd_rn(__fmul_rn(p.z, b), __fmul_rn(p.w, a)));
+            const int c1 = round_rn_magic(__fsub_rn(__fmul_rn(p.z, a), __fmul_rn(p.w, b)));
+            const int t0 = ctr[r0 * VIORB_DESC_PW + c0], t1 = ctr[r1 * VIORB_DESC_PW + c1];
+            val |= (t0 < t1) << t;
+        }
+        desc[((size_t)f * g.outCap + slot) * 32 + lane] = (uint8_t)val;
+        if (!more) break;
+        __syncwarp();                       // everyone is done with buffer j & 1 before it is refilled
+        k = kn;
+    }
 }

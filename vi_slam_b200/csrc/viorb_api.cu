@@ -423,7 +423,7 @@ int run_pipeline(viorb_extractor* ex, int f0, int n, int lap0, int lap1) {
     if (tm) CU(cudaEventRecord(ex->evX[5], st));
     VIORB_LAUNCH(k_blur, dim3(ex->totalBlurTiles, n), dim3(64), 0, st, g, fs, ex->blurTiles);
     if (tm) CU(cudaEventRecord(ex->evX[6], st));
-    VIORB_LAUNCH(k_describe, dim3((g.outCap + 7) / 8, n), dim3(256), 0, st, g, fs, ex->dKept.p, ex->dSlot2Kept.p,
+    VIORB_LAUNCH(k_describe, dim3((g.outCap + 8 * VIORB_DESC_KPW - 1) / (8 * VIORB_DESC_KPW), n), dim3(256), 0, st, g, fs, ex->dKept.p, ex->dSlot2Kept.p,
                  ex->dNOut.p, ex->dDesc.p);
     if (tm) { CU(cudaEventRecord(ex->evX[7], st)); ex->haveX = true; }
     CU(cudaGetLastError());
