@@ -29,7 +29,9 @@ __device__ __forceinline__ int reflect101_dev(int p, int n) {
 // both need it (the source advances 1.2 rows per output row).
 // grid (ceil(w/256), ceil(h/(4*VIORB_RS_ROWS)), B), block (64,4).
 // ---------------------------------------------------------------------------------------------
-#define VIORB_RS_ROWS 4
+#ifndef VIORB_RS_ROWS
+#define VIORB_RS_ROWS 8
+#endif
 __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int l, const int* __restrict__ xofs,
                                                 const short2* __restrict__ xalpha, const int* __restrict__ yofs,
                                                 const short2* __restrict__ ybeta) {
@@ -168,7 +170,9 @@ __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int 
 // Candidate word: x | y << 12 | score << 24, x/y relative to the 16-px border (as vToDistributeKeys).
 // grid (totalStrips, B), block 256.
 // ---------------------------------------------------------------------------------------------
+#ifndef VIORB_FAST_THREADS
 #define VIORB_FAST_THREADS 256
+#endif
 
 __device__ __forceinline__ int fast_score16(const uint8_t* p, const int* o) {
     const int v = p[0];
@@ -227,16 +231,17 @@ __device__ __forceinline__ unsigned hi16x2(unsigned w) { return __byte_perm(w, 0
 
 // opposite-pair pre-test of 2 pixels packed as s16x2: a 9-arc brighter (darker) than centre +/- th
 // contains one pixel of each opposite pair, so min over pairs of max(pair) > c + th (resp. max over
-// pairs of min(pair) < c - th) is necessary.  Returns 0x8000 per lane that may be a corner.
+// pairs of min(pair) < c - th) is necessary.  Returns 0x4000 per lane that may be a corner.
+// The comparisons run on biased lanes: with K = 0x4000 and kc = (K - th - 1) per lane, mb + kc - c >= K <=> bright
+// possible and kc + c - md >= K <=> dark possible; every lane stays inside (0, 2K), so the two 3-input 32-bit adds
+// never carry between lanes and bit 14 of each lane is the answer (3 instructions instead of 7 packed ones).
 __device__ __forceinline__ unsigned fast_pretest2(unsigned c, unsigned up, unsigned dn, unsigned lf, unsigned rt,
-                                                  unsigned d22, unsigned dm2m2, unsigned d2m2, unsigned dm22,
-                                                  unsigned nthp1, unsigned th) {
-    const unsigned nc = __vadd2(~c, 0x00010001u);                                  // -c per lane
+                                                  unsigned d22, unsigned dm2m2, unsigned d2m2, unsigned dm22, unsigned kc) {
     const unsigned mb = __vmins2(__vimin3_s16x2(__vmaxs2(up, dn), __vmaxs2(lf, rt), __vmaxs2(d22, dm2m2)), __vmaxs2(d2m2, dm22));
     const unsigned md = __vmaxs2(__vimax3_s16x2(__vmins2(up, dn), __vmins2(lf, rt), __vmins2(d22, dm2m2)), __vmins2(d2m2, dm22));
-    const unsigned xb = __vadd2(__vadd2(mb, nc), nthp1);                           // mb - c - (th+1): >= 0 <=> bright possible
-    const unsigned yd = __vadd2(__vadd2(md, nc), th);                              // md - c + th: < 0 <=> dark possible
-    return (~xb | yd) & 0x80008000u;
+    const unsigned xb = mb + kc - c;
+    const unsigned yd = kc + c - md;
+    return (xb | yd) & 0x40004000u;
 }
 
 __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, FrameSrc fs, const CellDesc* __restrict__ cells,
@@ -299,14 +304,13 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
     // slots with one shared-memory atomic (MIO pipe) instead of a warp scan (the kernel is ALU-pipe bound).
     {
         const int g0 = col0 >> 2, g1 = (col0 + rw - 1) >> 2;
-        const unsigned thp = (unsigned)th | ((unsigned)th << 16);
-        const unsigned nthp1 = ((0x10000u - (unsigned)(th + 1)) & 0xFFFFu) * 0x10001u;     // -(th+1) in both lanes
-        // pixels of the first / last word that lie inside the region, as 0x8000-per-lane masks (a: px 0,1; b: px 2,3)
+        const unsigned kc = (0x4000u - (unsigned)(th + 1)) * 0x10001u;                     // K - th - 1 in both lanes
+        // pixels of the first / last word that lie inside the region, as 0x4000-per-lane masks (a: px 0,1; b: px 2,3)
         const int s0 = col0 - 4 * g0, e1 = col0 + rw - 1 - 4 * g1;
-        const unsigned firstA = (s0 <= 0 ? 0x8000u : 0u) | (s0 <= 1 ? 0x80000000u : 0u);
-        const unsigned firstB = (s0 <= 2 ? 0x8000u : 0u) | 0x80000000u;
-        const unsigned lastA = 0x8000u | (e1 >= 1 ? 0x80000000u : 0u);
-        const unsigned lastB = (e1 >= 2 ? 0x8000u : 0u) | (e1 >= 3 ? 0x80000000u : 0u);
+        const unsigned firstA = (s0 <= 0 ? 0x4000u : 0u) | (s0 <= 1 ? 0x40000000u : 0u);
+        const unsigned firstB = (s0 <= 2 ? 0x4000u : 0u) | 0x40000000u;
+        const unsigned lastA = 0x4000u | (e1 >= 1 ? 0x40000000u : 0u);
+        const unsigned lastB = (e1 >= 2 ? 0x4000u : 0u) | (e1 >= 3 ? 0x40000000u : 0u);
         const int ng = g1 - g0 + 1, total = ng * rh;
         const unsigned ginv = (1u << 22) / (unsigned)ng + 1;     // i / ng = (i * ginv) >> 22, exact while i * ng < 2^22 (ng <= 130, rh <= 127)
         {
@@ -322,19 +326,19 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
                 const unsigned d22 = __funnelshift_r(Rp[0], Rp[1], 16), dm22 = __funnelshift_r(Rp[-1], Rp[0], 16);
                 const unsigned d2m2 = __funnelshift_r(Rm[0], Rm[1], 16), dm2m2 = __funnelshift_r(Rm[-1], Rm[0], 16);
                 unsigned a = fast_pretest2(lo16x2(cw), lo16x2(up), lo16x2(dn), lo16x2(lf), lo16x2(rt), lo16x2(d22),
-                                           lo16x2(dm2m2), lo16x2(d2m2), lo16x2(dm22), nthp1, thp);
+                                           lo16x2(dm2m2), lo16x2(d2m2), lo16x2(dm22), kc);
                 unsigned b = fast_pretest2(hi16x2(cw), hi16x2(up), hi16x2(dn), hi16x2(lf), hi16x2(rt), hi16x2(d22),
-                                           hi16x2(dm2m2), hi16x2(d2m2), hi16x2(dm22), nthp1, thp);
+                                           hi16x2(dm2m2), hi16x2(d2m2), hi16x2(dm22), kc);
                 if (gx == g0) { a &= firstA; b &= firstB; }
                 if (gx == g1) { a &= lastA; b &= lastB; }
                 const unsigned ab = a | (b >> 1);
                 if (ab) {
                     int q = atomicAdd(&qCount, __popc(ab));
                     const int e0 = (py << 9) + (gx * 4 - col0);       // valid pixels have e0 + j >= py << 9
-                    if (a & 0x8000u) Q[q++] = (uint16_t)e0;
-                    if (a & 0x80000000u) Q[q++] = (uint16_t)(e0 + 1);
-                    if (b & 0x8000u) Q[q++] = (uint16_t)(e0 + 2);
-                    if (b & 0x80000000u) Q[q++] = (uint16_t)(e0 + 3);
+                    if (a & 0x4000u) Q[q++] = (uint16_t)e0;
+                    if (a & 0x40000000u) Q[q++] = (uint16_t)(e0 + 1);
+                    if (b & 0x4000u) Q[q++] = (uint16_t)(e0 + 2);
+                    if (b & 0x40000000u) Q[q++] = (uint16_t)(e0 + 3);
                 }
             }
         }
@@ -420,7 +424,9 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
 // Final pick per node: max response, first in cell-major raster order wins ties          (:735-751).
 // grid (nlevels, B), block 512, dynamic smem = octree_smem_bytes(maxNodes).
 // ---------------------------------------------------------------------------------------------
+#ifndef VIORB_OCT_THREADS
 #define VIORB_OCT_THREADS 512
+#endif
 
 struct OctBounds { short ulx, uly, brx, bry; };
 
@@ -939,7 +945,9 @@ __global__ void __launch_bounds__(256) k_emit(ExtractGeom g, const KeptKp* __res
 // pass Q16.16, +0.5, >>16; BORDER_REFLECT_101 from the level image itself.  All levels in one launch:
 // ---------------------------------------------------------------------------------------------
 #define VIORB_BLUR_TW 256        // tile width: 64 threads x 4 pixels
+#ifndef VIORB_BLUR_TH
 #define VIORB_BLUR_TH 32         // output rows walked by one thread
+#endif
 struct BlurTiles { int base[VIORB_MAX_LEVELS + 1]; int tilesX[VIORB_MAX_LEVELS]; };
 
 // One image row -> the four Q8.8 row sums of the thread's 4 columns.  w0,w1,w2 = the aligned words

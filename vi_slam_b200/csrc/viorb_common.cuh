@@ -59,7 +59,9 @@ struct ExtractGeom {
 // pixels on which cv::FAST would evaluate the corner test for those cells' ROIs (each ROI inset by 3),
 // fextractor.cpp:780-806; cell k of the strip covers x0 + k*wCell .. x0 + (k+1)*wCell (the last one may
 // be narrower).
+#ifndef VIORB_FAST_STRIP_CELLS
 #define VIORB_FAST_STRIP_CELLS 8
+#endif
 struct CellDesc {
     short level, ncell;
     short x0, y0, x1, y1;
