@@ -208,12 +208,19 @@ __device__ __forceinline__ unsigned fast_score16x2(const uint8_t* pa, const uint
         t[k] = __vimin3_s16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
         u[k] = __vimax3_s16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
     }
-    unsigned a = 0xFF00FF00u, b = 0x01000100u;          // -256 / +256 per lane
+    // arc minima / maxima, then their max / min as 3-input trees (8 instead of 16 dependent 2-input steps each)
+    unsigned m[16], n[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
-        a = __vmaxs2(a, __vimin3_s16x2(t[k], t[(k + 3) & 15], t[(k + 6) & 15]));
-        b = __vmins2(b, __vimax3_s16x2(u[k], u[(k + 3) & 15], u[(k + 6) & 15]));
+        m[k] = __vimin3_s16x2(t[k], t[(k + 3) & 15], t[(k + 6) & 15]);
+        n[k] = __vimax3_s16x2(u[k], u[(k + 3) & 15], u[(k + 6) & 15]);
     }
+    unsigned a = __vimax3_s16x2(__vimax3_s16x2(m[0], m[1], m[2]), __vimax3_s16x2(m[3], m[4], m[5]), __vimax3_s16x2(m[6], m[7], m[8]));
+    a = __vimax3_s16x2(a, __vimax3_s16x2(m[9], m[10], m[11]), __vimax3_s16x2(m[12], m[13], m[14]));
+    a = __vimax3_s16x2(a, m[15], 0xFF00FF00u);                                      // -256 per lane
+    unsigned b = __vimin3_s16x2(__vimin3_s16x2(n[0], n[1], n[2]), __vimin3_s16x2(n[3], n[4], n[5]), __vimin3_s16x2(n[6], n[7], n[8]));
+    b = __vimin3_s16x2(b, __vimin3_s16x2(n[9], n[10], n[11]), __vimin3_s16x2(n[12], n[13], n[14]));
+    b = __vimin3_s16x2(b, n[15], 0x01000100u);                                      // +256 per lane
     return __vsub2(__vmaxs2(a, __vsub2(0u, b)), 0x00010001u);
 }
 
