@@ -322,14 +322,22 @@ def run_ours(args, rank, world, local_rank):
         bytes_per_step = 2 * B * BYTES_EXTRACT_PER_IMAGE
         bound = "hbm"
     achieved = bytes_per_step / (mean[dom] * 1e-3) / 1e9
-    traffic = None
+    # DRAM traffic of the dominant kernel and the pipe that actually bounds it come from the committed ncu capture
+    # (profiles/traffic.json <- profiles/r1_ncu_v5.md), scaled to the images one launch processes here; not live
+    traffic, pipe = None, None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get(dom)
+        tj = json.load(open(tpath))
+        per_image = tj.get("dram_bytes_per_image", {}).get(dom)
+        if per_image is not None:
+            traffic = per_image * 2 * B / launches_per_step
+        pipe = tj.get("pipe_pct_of_peak", {}).get(dom)
     roofline = {"bound": bound, "kernel": "k_" + dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "bytes_per_launch": bytes_per_step / launches_per_step, "ms_per_launch": mean[dom] / launches_per_step,
-                "path_hbm_frac": 2 * B * K * BYTES_EXTRACT_PER_IMAGE / (ms * 1e-3) / 1e9 / peak}
+                "path_hbm_frac": 2 * B * K * BYTES_EXTRACT_PER_IMAGE / (ms * 1e-3) / 1e9 / peak,
+                "traffic_source": "ncu capture (profiles/r1_ncu_v5.md), per image x images per launch" if traffic else None,
+                "binding_pipe_ncu": pipe}
     # matcher: brute-force kNN-2 left -> right on the tensor cores; denominator = the IMMA.16832.U8 issue rate measured
     # on this pool's B200 with tools/probe/imma_probe.cu (574 T u8 MAC/s) / 256 MAC per descriptor pair
     pairs = float((res["n_left"].astype(np.float64) ** 2).sum())
