@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--distinct", type=int, default=8, help="distinct synthetic stereo pairs generated (tiled to --pairs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-bind", action="store_true", help="multi-rank runs: do not bind the rank to its GPU's local CPUs")
     ap.add_argument("--variant-lib", default=None, help="experimental build of libviorb.so to measure instead of the product one")
     ap.add_argument("--e2e-workers", type=int, default=3, help="pipeline workers (handle pairs in flight) of the end-to-end leg")
     return ap.parse_args()
@@ -128,6 +129,20 @@ def cpu_baseline(nthreads, pairs):
     return pairs / dt, dt, tot, nm
 
 
+def bind_near_gpu(local_rank):
+    """Multi-rank runs: keep this rank's threads (and so the first-touch pages of its pinned buffers) on the CPUs NVML
+    reports as local to its GPU.  Returns (cpus before, cpus after); a failure leaves the affinity untouched."""
+    before = host_threads()
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+    except Exception:
+        pass
+    return before, host_threads()
+
+
 def host_threads():
     try:
         return len(os.sched_getaffinity(0))
@@ -171,6 +186,10 @@ def run_ours(args, rank, world, local_rank):
         from vi_slam_b200 import _lib
         _lib.DEFAULT_LIB = os.path.abspath(args.variant_lib)
     torch.cuda.set_device(local_rank)
+    host = {"cpus": host_threads()}
+    if world > 1 and not args.no_bind:
+        b, a = bind_near_gpu(local_rank)
+        host = {"cpus": b, "cpus_near_gpu": a}
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -356,7 +375,7 @@ def run_ours(args, rank, world, local_rank):
                    "keypoints_per_frame": n_kp / B, "stereo_matches_per_s": n_stereo / B * value,
                    "ratio_matches_per_s": n_ratio / B * value},
         **({"variant_lib": args.variant_lib} if args.variant_lib else {}),
-        "clocks": clk, "e2e": e2e, "gpu_launches": K * (2 * (NLEVELS - 1 + 6) + 5),
+        "host": host, "clocks": clk, "e2e": e2e, "gpu_launches": K * (2 * (NLEVELS - 1 + 6) + 5),
         "stages_ms_per_step": mean,
         "stage_timing": "second pass of K steps, both handles on one stream, CUDA events around each stage", "roofline": roofline,
         "match_roofline": match_roofline,

@@ -119,6 +119,7 @@ struct viorb_extractor {
     cudaStream_t cpStream = nullptr, outStream = nullptr;
     cudaEvent_t evIn[VIORB_MAX_CHUNKS] = {}, evDone[VIORB_MAX_CHUNKS] = {}, evEntry = nullptr;
     cudaEvent_t evJoin = nullptr;     // orders this handle's stream against a partner handle's (stereo)
+    cudaEvent_t evBlock = nullptr;    // blocking-sync event: batch calls sleep on it instead of spinning in the driver
     DevBuf<uint8_t> dIn, dPyr, dBlur, dDesc;
     DevBuf<uint32_t> dCand;
     DevBuf<uint16_t> dKeyNode;
@@ -431,10 +432,20 @@ int run_pipeline(viorb_extractor* ex, int f0, int n, int lap0, int lap1) {
     return VIORB_OK;
 }
 
+// Host wait for a stream.  Single frames spin in the driver (lowest latency); batch calls, whose waits last
+// milliseconds, sleep on a blocking-sync event so that several pipeline workers / ranks do not burn one host core each
+// (on a 32-core host with 8 GPUs the spinning waits, not the GPUs, bounded the end-to-end rate).
+#define VIORB_BLOCKING_BATCH 8
+cudaError_t wait_stream(viorb_extractor* ex, cudaStream_t st) {
+    if (ex->lastN < VIORB_BLOCKING_BATCH || !ex->evBlock) return cudaStreamSynchronize(st);
+    cudaError_t e = cudaEventRecord(ex->evBlock, st);
+    return e == cudaSuccess ? cudaEventSynchronize(ex->evBlock) : e;
+}
+
 int check_status(viorb_extractor* ex) {
     int st = 0;
     CU(cudaMemcpyAsync(&st, ex->dStatus.p, sizeof(int), cudaMemcpyDeviceToHost, ex->stream));
-    CU(cudaStreamSynchronize(ex->stream));
+    CU(wait_stream(ex, ex->stream));
     if (st) {
         CU(cudaMemsetAsync(ex->dStatus.p, 0, sizeof(int), ex->stream));
         char buf[96];
@@ -619,6 +630,7 @@ int viorb_extractor_create(const viorb_params* params, viorb_extractor** out) {
     }
     ok(cudaEventCreateWithFlags(&ex->evEntry, cudaEventDisableTiming));
     ok(cudaEventCreateWithFlags(&ex->evJoin, cudaEventDisableTiming));
+    ok(cudaEventCreateWithFlags(&ex->evBlock, cudaEventDisableTiming | cudaEventBlockingSync));
     for (int i = 0; i < 8; ++i) ok(cudaEventCreate(&ex->evX[i]));
     for (int i = 0; i < 6; ++i) ok(cudaEventCreate(&ex->evS[i]));
     if (e == cudaSuccess) e = cudaMemset(ex->dStatus.p, 0, sizeof(int));
@@ -653,6 +665,7 @@ void viorb_extractor_destroy(viorb_extractor* ex) {
     }
     if (ex->evEntry) cudaEventDestroy(ex->evEntry);
     if (ex->evJoin) cudaEventDestroy(ex->evJoin);
+    if (ex->evBlock) cudaEventDestroy(ex->evBlock);
     if (ex->cpStream) { cudaStreamSynchronize(ex->cpStream); cudaStreamDestroy(ex->cpStream); }
     if (ex->outStream) { cudaStreamSynchronize(ex->outStream); cudaStreamDestroy(ex->outStream); }
     if (ex->ownStream && ex->stream) cudaStreamDestroy(ex->stream);
@@ -837,7 +850,7 @@ int viorb_extract_batch(viorb_extractor* ex, const uint8_t* const* imgs, int n, 
     }
     CU(cudaMemcpyAsync(ex->hCounts.p, ex->dNOut.p, sizeof(int) * n, cudaMemcpyDeviceToHost, ex->outStream));
     CU(cudaMemcpyAsync(ex->hCounts.p + n, ex->dMono.p, sizeof(int) * n, cudaMemcpyDeviceToHost, ex->outStream));
-    CU(cudaStreamSynchronize(ex->outStream));
+    CU(wait_stream(ex, ex->outStream));
     rc = check_status(ex);          // synchronises the handle's stream
     if (rc) return rc;
     int worst = VIORB_OK;
@@ -1177,7 +1190,7 @@ int viorb_stereo_fetch_all(viorb_extractor* L, int n, float* u_right, float* dep
     if (u_right) CU(cudaMemcpy2DAsync(u_right, sizeof(float) * cap, L->dURight.p, sizeof(float) * oc, sizeof(float) * oc, n, cudaMemcpyDeviceToHost, st));
     if (depth) CU(cudaMemcpy2DAsync(depth, sizeof(float) * cap, L->dDepth.p, sizeof(float) * oc, sizeof(float) * oc, n, cudaMemcpyDeviceToHost, st));
     if (lr_match) CU(cudaMemcpy2DAsync(lr_match, sizeof(int32_t) * cap, L->dLrMatch.p, sizeof(int32_t) * oc, sizeof(int32_t) * oc, n, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(wait_stream(L, st));
     return VIORB_OK;
 }
 
