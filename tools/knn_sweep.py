@@ -51,7 +51,7 @@ def main():
         if rank == 0:
             print(json.dumps({"workload": f"hamming_knn2_{n}x{n}", "n_gpus": world, "ms": ms, "pairs_per_s": n * n / (ms * 1e-3),
                               "queries_per_s": n / (ms * 1e-3), "checks_ok": ok, "gather_bytes_per_rank": per * 16,
-                              "kernel": os.environ.get("VIORB_KNN", "mma")}), flush=True)
+                              "kernel": os.environ.get("VIORB_KNN", "tc5")}), flush=True)
     if dist is not None:
         dist.destroy_process_group()
 

@@ -14,6 +14,7 @@
 
 #include "kernels_extract.cuh"
 #include "kernels_match.cuh"
+#include "kernels_knn_tc5.cuh"
 #include "kernels_window.cuh"
 #include "kernels_bow.cuh"
 #include "kernels_kb8.cuh"
@@ -539,14 +540,37 @@ int release_partner(viorb_extractor* L, viorb_extractor* R) {
 
 }  // namespace
 
-// Brute-force kNN-2 of a batch of descriptor sets.  Default: the tensor-core kernel (k_knn2_mma, IMMA u8 on
-// {0,1}-expanded bits); VIORB_KNN=popc selects the LOP3/POPC integer-pipe kernel (k_knn2) - both give identical
-// results, the choice is a measured one.
+// Brute-force kNN-2 of a batch of descriptor sets.  Default: k_knn2_tc5 (tcgen05.mma kind::i8, accumulators in
+// tensor memory, kernels_knn_tc5.cuh).  VIORB_KNN=mma selects the warp-level IMMA kernel (k_knn2_mma), VIORB_KNN=popc
+// the LOP3/POPC integer-pipe kernel (k_knn2) - all three give identical results, the choice is a measured one
+// (DESIGN.md section 5).
 static int launch_knn2(const DescSet& Q, const DescSet& T, int maxNq, int nSets, int32_t* dIdx, int32_t* dDist, size_t outStride,
                        cudaStream_t st) {
-    static const bool popc = [] { const char* e = std::getenv("VIORB_KNN"); return e && std::strcmp(e, "popc") == 0; }();
+    static const int mode = [] {
+        const char* e = std::getenv("VIORB_KNN");
+        return !e ? 0 : std::strcmp(e, "popc") == 0 ? 2 : std::strcmp(e, "mma") == 0 ? 1 : 0;
+    }();
+#ifndef VIORB_EMU
+    if (mode == 0) {
+        static int sms[64] = {0};
+        int dev = 0;
+        CU(cudaGetDevice(&dev));
+        if (dev < 64 && sms[dev] == 0) {
+            CU(cudaFuncSetAttribute(tc5::k_knn2_tc5, cudaFuncAttributeMaxDynamicSharedMemorySize, tc5::SMEM_BYTES));
+            CU(cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev));
+        }
+        const int qTiles = (maxNq + tc5::QT - 1) / tc5::QT, nItems = qTiles * nSets;
+        if (nItems > 0) {
+            const int nSm = dev < 64 ? sms[dev] : 148;
+            VIORB_LAUNCH(tc5::k_knn2_tc5, dim3(std::min(nItems, nSm)), dim3(tc5::THREADS), tc5::SMEM_BYTES, st, Q, T, dIdx, dDist,
+                         outStride, qTiles, nItems);
+        }
+        CU(cudaGetLastError());
+        return VIORB_OK;
+    }
+#endif
     const dim3 grid((maxNq + VIORB_KNN_THREADS - 1) / VIORB_KNN_THREADS, nSets), block(VIORB_KNN_THREADS);
-    if (popc) VIORB_LAUNCH(k_knn2, grid, block, 0, st, Q, T, dIdx, dDist, outStride);
+    if (mode == 2) VIORB_LAUNCH(k_knn2, grid, block, 0, st, Q, T, dIdx, dDist, outStride);
     else VIORB_LAUNCH(k_knn2_mma, grid, block, 0, st, Q, T, dIdx, dDist, outStride);
     CU(cudaGetLastError());
     return VIORB_OK;
