@@ -12,18 +12,25 @@
 // and the epilogue is nothing but the running top-2 (min / max / min per pair).  Rows past the end of the train
 // set carry 255 x 255 in a fourth byte and lose against every real key.
 //
-// Shape.  Persistent CTAs of 288 threads, one per SM, work items = (descriptor set, 128-row query tile):
+// Shape.  Persistent CTAs of 416 threads, one per SM, work items = (descriptor set, 128-row query tile):
 //   warps 4-7  producers: expand the query tile (A, 128 x 288 B) and the train tiles (B, 256 x 288 B, two stages)
 //              into the K-major no-swizzle core-matrix layout, fence.proxy.async, arrive on the full barriers
 //   warp 8     one thread issues 9 x tcgen05.mma.cta_group::1.kind::i8 (M 128, N 256, K 32) per train tile into one
 //              of two 256-column accumulators and commits to the barriers that free the stage / publish the tile
-//   warps 0-3  epilogue: thread = TMEM lane = query row; tcgen05.ld 32x32b.x32, top-2 per 64-column group on two
-//              independent chains, merged into (distance' << 22 | train index) keys; writes idx / dist at the end
-// Results are bit-identical to k_knn2 / k_knn2_mma.  grid = min(items, SMs), block 288, dynamic smem 184 KB.
+//   warps 0-3, 9-12  epilogue: thread = TMEM lane = query row, each warp set takes one 128-column half of the
+//              tile.  Every key is below 2^16, so tcgen05.ld ... .pack::16b delivers two columns per register
+//              and the running top-2 of 64 columns is 16 x 3 VIMNMX.U16x2 on two independent chains; the two
+//              survivors become (distance' << 22 | train index) keys; idx / dist are written at the end
+// Results are bit-identical to k_knn2 / k_knn2_mma.  grid = min(items, SMs), block 416, dynamic smem 186 KB.
+// Measured bound (nold / nocomp variants, tools/gpu_tc5_variants.sh): shared-memory bandwidth - per train tile
+// the producers store 72 KB and the tensor core reads 108 KB (A is re-read for every tile) at 128 B / clk.
 #pragma once
 #include "kernels_match.cuh"
 
 #ifndef VIORB_EMU
+#ifndef TC5_DIAG
+#define TC5_DIAG 0
+#endif
 namespace tc5 {
 
 constexpr int QT = 128;                 // query rows per work item (MMA M)
@@ -34,8 +41,9 @@ constexpr int SBO = KCH * 128;          // bytes between 8-row groups
 constexpr int A_BYTES = QT / 8 * SBO;   // 36 864
 constexpr int B_BYTES = TT / 8 * SBO;   // 73 728
 constexpr int NBAR = 10;
-constexpr int SMEM_BYTES = A_BYTES + 2 * B_BYTES + NBAR * 8 + 16;
-constexpr int THREADS = 288;
+constexpr int XCH_OFF = A_BYTES + 2 * B_BYTES + NBAR * 8 + 16;   // uint2[2][QT]: the upper column half's (best, second)
+constexpr int SMEM_BYTES = XCH_OFF + 2 * QT * 8;
+constexpr int THREADS = 416;
 constexpr int PAD_KEY = 255 * 255;      // key contribution of a padding train row
 constexpr uint32_t IDESC = (2u << 4) | ((uint32_t)(TT >> 3) << 17) | ((uint32_t)(QT >> 4) << 24);   // s32 += u8 x u8, K-major A and B
 
@@ -79,6 +87,16 @@ __device__ __forceinline__ void mma_i8(uint32_t d, uint64_t a, uint64_t b, uint3
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, int (&v)[32]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+                   "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+                   "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+                   "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                 : "r"(taddr) : "memory");
+}
+// 64 columns, the low halves of two adjacent columns packed into one register (column 2j in the low half)
+__device__ __forceinline__ void tmem_ld64_pack16(uint32_t taddr, unsigned (&v)[32]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.pack::16b.b32 "
                  "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
                  : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
                    "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
@@ -149,7 +167,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, i
             mbar_init(bar0 + 8 * (BAR_B_FULL + s), 128);
             mbar_init(bar0 + 8 * (BAR_B_EMPTY + s), 1);
             mbar_init(bar0 + 8 * (BAR_D_FULL + s), 1);
-            mbar_init(bar0 + 8 * (BAR_D_EMPTY + s), 128);
+            mbar_init(bar0 + 8 * (BAR_D_EMPTY + s), 256);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -239,53 +257,79 @@ __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, i
         __syncwarp();
     } else {
         // ------------------------------------------------------------------ epilogue: thread = query row = TMEM lane
-        const uint32_t laneBase = tmem + ((uint32_t)(warp * 32) << 16);
-        uint32_t g = 0;
+        // warps 0-3 reduce columns 0-127 of every tile, warps 9-12 columns 128-255 (a warp reaches the 32 lanes
+        // of its SM sub-partition, warp % 4); the two halves of a row meet in shared memory at the end of the item
+        const int half = warp >= 9, quarter = warp & 3, row = quarter * 32 + (tid & 31);
+        const uint32_t laneBase = tmem + ((uint32_t)(quarter * 32) << 16) + half * 128;
+        uint32_t g = 0, it = 0;
         for (int item = blockIdx.x; item < nItems; item += gridDim.x) {
             const int p = item / qTiles, q0 = (item - p * qTiles) * QT;
             const int nq = descset_count(Q, p), nt = descset_count(T, p);
             if (q0 >= nq) continue;
             const int nTiles = (nt + TT - 1) / TT;
-            const int qi = q0 + tid;
-            const uint4* qb = reinterpret_cast<const uint4*>(Q.base + (size_t)p * Q.stride);
-            const int qrow = min(qi, nq - 1);
-            const int pq = popc256(__ldg(qb + (size_t)qrow * 2), __ldg(qb + (size_t)qrow * 2 + 1));
+            const int qi = q0 + row;
             unsigned gb0 = 0xFFFFFFFFu, gb1 = 0xFFFFFFFFu;
             for (int t = 0; t < nTiles; ++t, ++g) {
                 const uint32_t s = g & 1;
                 mbar_wait(bar0 + 8 * (BAR_D_FULL + s), (g >> 1) & 1);
                 tc_fence_after();
-#pragma unroll 1
-                for (int grp = 0; grp < TT / 64; ++grp) {
-                    int v0[32], v1[32];
-                    tmem_ld32(laneBase + s * TT + grp * 64, v0);
-                    tmem_ld32(laneBase + s * TT + grp * 64 + 32, v1);
-                    tmem_ld_wait();
-                    unsigned a0 = 0x7FFFFFFFu, a1 = 0x7FFFFFFFu, c0 = 0x7FFFFFFFu, c1 = 0x7FFFFFFFu;
+                // packed 16-bit keys (every key is below 2^16): two columns per min / max, four chains per 64 columns;
+                // the load of the second 64 columns is in flight while the first 64 are reduced
+                unsigned va[32], vb[32];
+                auto reduce64 = [&](const unsigned (&v)[32], int grp) {
+#if TC5_DIAG != 1
+                    unsigned a0 = 0xFFFFFFFFu, a1 = 0xFFFFFFFFu, c0 = 0xFFFFFFFFu, c1 = 0xFFFFFFFFu;
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        top2(a0, a1, (unsigned)v0[j]);
-                        top2(c0, c1, (unsigned)v1[j]);
+                    for (int j = 0; j < 16; ++j) {
+                        a1 = __vminu2(a1, __vmaxu2(a0, v[j]));
+                        a0 = __vminu2(a0, v[j]);
+                        c1 = __vminu2(c1, __vmaxu2(c0, v[16 + j]));
+                        c0 = __vminu2(c0, v[16 + j]);
                     }
-                    const unsigned base = (unsigned)(t * TT + grp * 64);
-                    const unsigned cand[4] = {a0, a1, c0, c1};
-#pragma unroll
-                    for (int c = 0; c < 4; ++c)
-                        if (cand[c] < (unsigned)PAD_KEY) top2(gb0, gb1, ((cand[c] >> 6) << VIORB_KNN_IDX_BITS) | (base + (cand[c] & 63u)));
-                }
+                    // four chains -> two (packed), even / odd columns -> the two smallest keys of the group
+                    const unsigned m1 = __vminu2(__vminu2(a1, c1), __vmaxu2(a0, c0)), m0 = __vminu2(a0, c0);
+                    const unsigned l0 = m0 & 0xFFFFu, h0 = m0 >> 16, l1 = m1 & 0xFFFFu, h1 = m1 >> 16;
+                    const unsigned x0 = min(l0, h0), x1 = min(max(l0, h0), min(l1, h1));
+                    const unsigned base = (unsigned)(t * TT + half * 128 + grp * 64);
+                    if (x0 < (unsigned)PAD_KEY) top2(gb0, gb1, ((x0 >> 6) << VIORB_KNN_IDX_BITS) | (base + (x0 & 63u)));
+                    if (x1 < (unsigned)PAD_KEY) top2(gb0, gb1, ((x1 >> 6) << VIORB_KNN_IDX_BITS) | (base + (x1 & 63u)));
+#endif
+                };
+                const uint32_t ta = laneBase + s * TT;
+#if TC5_DIAG != 2
+                tmem_ld64_pack16(ta, va);
+                tmem_ld_wait();
+                tmem_ld64_pack16(ta + 64, vb);
+                reduce64(va, 0);
+                tmem_ld_wait();
                 tc_fence_before();
                 mbar_arrive(bar0 + 8 * (BAR_D_EMPTY + s));
+                reduce64(vb, 1);
+#else
+                tc_fence_before();
+                mbar_arrive(bar0 + 8 * (BAR_D_EMPTY + s));
+#endif
             }
-            if (qi < nq) {
+            // the upper half hands its pair to the lower half (double-buffered by item parity; the named barrier
+            // of the next item orders the reuse)
+            uint2* xch = reinterpret_cast<uint2*>(smem + XCH_OFF) + (it & 1) * QT;
+            if (half) xch[row] = make_uint2(gb0, gb1);
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (!half && qi < nq) {
+                const uint2 o = xch[row];
+                top2(gb0, gb1, o.x);
+                top2(gb0, gb1, o.y);
+                const uint4* qb = reinterpret_cast<const uint4*>(Q.base + (size_t)p * Q.stride);
+                const int pq = popc256(__ldg(qb + (size_t)qi * 2), __ldg(qb + (size_t)qi * 2 + 1));
                 const unsigned mask = (1u << VIORB_KNN_IDX_BITS) - 1;
                 int32_t* oi = idx + (size_t)p * outStride * 2 + (size_t)qi * 2;
                 int32_t* od = dist + (size_t)p * outStride * 2 + (size_t)qi * 2;
                 const bool h0 = gb0 != 0xFFFFFFFFu, h1 = gb1 != 0xFFFFFFFFu;
-                oi[0] = h0 ? (int)(gb0 & mask) : -1;
-                od[0] = h0 ? (int)(gb0 >> VIORB_KNN_IDX_BITS) - pq : -1;
-                oi[1] = h1 ? (int)(gb1 & mask) : -1;
-                od[1] = h1 ? (int)(gb1 >> VIORB_KNN_IDX_BITS) - pq : -1;
+                *reinterpret_cast<int2*>(oi) = make_int2(h0 ? (int)(gb0 & mask) : -1, h1 ? (int)(gb1 & mask) : -1);
+                *reinterpret_cast<int2*>(od) = make_int2(h0 ? (int)(gb0 >> VIORB_KNN_IDX_BITS) - pq : -1,
+                                                         h1 ? (int)(gb1 >> VIORB_KNN_IDX_BITS) - pq : -1);
             }
+            ++it;
         }
     }
     tc_fence_before();
