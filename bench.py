@@ -357,14 +357,24 @@ def run_ours(args, rank, world, local_rank):
                 "path_hbm_frac": 2 * B * K * BYTES_EXTRACT_PER_IMAGE / (ms * 1e-3) / 1e9 / peak,
                 "traffic_source": "ncu capture (profiles/r1_ncu_v5.md), per image x images per launch" if traffic else None,
                 "binding_pipe_ncu": pipe}
-    # matcher: brute-force kNN-2 left -> right on the tensor cores; denominator = the IMMA.16832.U8 issue rate measured
-    # on this pool's B200 with tools/probe/imma_probe.cu (574 T u8 MAC/s) / 256 MAC per descriptor pair
+    # matcher: brute-force kNN-2 left -> right on the tensor cores.  Default kernel k_knn2_tc5 (tcgen05.mma kind::i8):
+    # denominator = 148 SMs x 8192 u8 MAC / clk / SM (one M128 N256 K32 instruction per 128 clk, B300_MICROARCH "tcgen05
+    # floor") at the measured max SM clock, 256 algorithmic MAC per descriptor pair (the kernel executes 288: a ninth K
+    # block carries popc(train) and the column).  VIORB_KNN=mma: warp-level IMMA.16832.U8 at the rate measured with
+    # tools/probe/imma_probe.cu (574 T u8 MAC/s).
     pairs = float((res["n_left"].astype(np.float64) ** 2).sum())
-    imma_pairs_peak = 574.2e12 / 256.0
-    match_roofline = {"kernel": "k_knn2_mma", "bound": "tensor (IMMA u8, legacy warp MMA)", "pairs_per_launch": pairs,
-                      "achieved": pairs / (mean["knn2"] * 1e-3), "peak": imma_pairs_peak, "unit": "descriptor pairs/s",
-                      "frac": pairs / (mean["knn2"] * 1e-3) / imma_pairs_peak,
-                      "peak_source": "measured: tools/probe/imma_probe.cu, 574.2 T u8 MAC/s"}
+    knn_mode = os.environ.get("VIORB_KNN", "tc5")
+    if knn_mode == "tc5":
+        sm_mhz = float(json.load(open(peaks_path)).get("sm_max_mhz", 1965.0)) if os.path.exists(peaks_path) else 1965.0
+        pk = 148 * 8192 * sm_mhz * 1e6 / 256.0
+        mk, mb, msrc = "k_knn2_tc5", "tensor (tcgen05.mma kind::i8, TMEM accumulators)", \
+            f"nominal: 148 SM x 8192 u8 MAC/clk x {sm_mhz:.0f} MHz; measured floor of the kernel is shared-memory bandwidth (DESIGN.md section 5)"
+    else:
+        pk = 574.2e12 / 256.0
+        mk, mb, msrc = ("k_knn2_mma", "tensor (IMMA u8, legacy warp MMA)", "measured: tools/probe/imma_probe.cu, 574.2 T u8 MAC/s") \
+            if knn_mode == "mma" else ("k_knn2", "integer pipe (LOP3 / POPC)", "IMMA rate used as the common denominator")
+    match_roofline = {"kernel": mk, "bound": mb, "pairs_per_launch": pairs, "achieved": pairs / (mean["knn2"] * 1e-3), "peak": pk,
+                      "unit": "descriptor pairs/s", "frac": pairs / (mean["knn2"] * 1e-3) / pk, "peak_source": msrc}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",

@@ -261,3 +261,68 @@ def test_knn2_integer_pipe_kernel_matches_too(tmp_path):
         env.pop("VIORB_LIBRARY", None)
         out = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True)
         assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nq,nt", [(1, 1), (1, 2), (5, 0), (127, 255), (128, 256), (129, 257), (300, 63), (64, 65), (2013, 1987),
+                                   (1000, 70000)])
+def test_knn2_tile_edges_and_ties(nq, nt):
+    """Default kernel (k_knn2_tc5, tcgen05): shapes around its 128-row query tile / 256-row train tile / 64-column key
+    group, duplicate train rows (ties -> lower index), all-zero and all-ones rows (distance 0 and 256), empty train set."""
+    from vi_slam_b200 import matcher
+    import oracle
+    q, t = _syn().make_descriptors(nq, max(nt, 1), seed=nq * 7 + nt)
+    t = t[:nt]
+    if nt >= 8:
+        t[nt // 2] = t[1]
+        t[nt - 1] = 0xFF
+        t[0] = 0
+    if nq >= 4:
+        q[1] = 0
+        q[2] = 0xFF
+    idx, dist = matcher.knn_match(q, t)
+    if nt == 0:
+        assert (idx == -1).all() and (dist == -1).all()
+        return
+    oidx, odist = oracle.knn2(q, t, nthreads=4)
+    assert np.array_equal(idx, oidx) and np.array_equal(dist, odist)
+    if nt >= 8 and nq >= 4:
+        assert dist[1, 0] == 0 and idx[1, 0] == 0 and dist[2, 0] == 0 and idx[2, 0] == nt - 1
+
+
+@pytest.mark.gpu
+def test_stereo_batch_with_ragged_and_empty_sets():
+    """viorb_stereo_batch over pairs with very different keypoint counts, including an all-black right image (empty train
+    set), an all-black left image (empty query set) and an all-black pair: the batched kNN-2 + ratio rows of every pair
+    equal the oracle on that pair's own descriptors."""
+    import oracle
+    from vi_slam_b200 import FExtractor, matcher
+    syn = _syn()
+    w, h = 640, 360
+    l0, r0 = syn.make_stereo_pair(5, w, h)
+    l1, r1 = syn.make_stereo_pair(6, w, h)
+    black = np.zeros((h, w), np.uint8)
+    sparse = black.copy()
+    sparse[100:140, 200:260] = 200                       # a handful of corners only
+    lefts = [l0, l1, black, black, sparse, l1]
+    rights = [r0, black, r1, black, r0, sparse]
+    n = len(lefts)
+    gl = FExtractor(1500, max_size=(w, h), max_batch=n)
+    gr = FExtractor(1500, max_size=(w, h), max_batch=n)
+    _, kl, dl = gl.compute_batch(lefts, (0, 0))
+    _, kr, dr = gr.compute_batch(rights, (0, 0))
+    assert len(kl[2]) == 0 and len(kr[1]) == 0 and 0 < len(kl[4]) < 64 and len(kl[0]) > 1000
+    matcher.stereo_batch(gl, gr, n, 386.1448, 0.5372, 0.7)
+    out = matcher.stereo_fetch_all(gl, n)
+    for i in range(n):
+        k = len(kl[i])
+        assert out["n_left"][i] == k
+        want = np.full(k, -1, np.int32)
+        nr = 0
+        if k and len(kr[i]):
+            oidx, odist = oracle.knn2(dl[i], dr[i])
+            om = oracle.ratio_filter(oidx, odist, 0.7, 0)
+            want[om[:, 0]] = om[:, 1]
+            nr = len(om)
+        assert np.array_equal(out["lr_match"][i, :k], want), i
+        assert out["n_ratio"][i] == nr, i
