@@ -342,7 +342,7 @@ def run_ours(args, rank, world, local_rank):
         bound = "hbm"
     achieved = bytes_per_step / (mean[dom] * 1e-3) / 1e9
     # DRAM traffic of the dominant kernel and the pipe that actually bounds it come from the committed ncu capture
-    # (profiles/traffic.json <- profiles/r1_ncu_v5.md), scaled to the images one launch processes here; not live
+    # (profiles/traffic.json <- profiles/r1_ncu_v6.md), scaled to the images one launch processes here; not live
     traffic, pipe = None, None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
@@ -355,7 +355,7 @@ def run_ours(args, rank, world, local_rank):
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "bytes_per_launch": bytes_per_step / launches_per_step, "ms_per_launch": mean[dom] / launches_per_step,
                 "path_hbm_frac": 2 * B * K * BYTES_EXTRACT_PER_IMAGE / (ms * 1e-3) / 1e9 / peak,
-                "traffic_source": "ncu capture (profiles/r1_ncu_v5.md), per image x images per launch" if traffic else None,
+                "traffic_source": "ncu capture (profiles/r1_ncu_v6.md), per image x images per launch" if traffic else None,
                 "binding_pipe_ncu": pipe}
     # matcher: brute-force kNN-2 left -> right on the tensor cores.  Default kernel k_knn2_tc5 (tcgen05.mma kind::i8):
     # denominator = 148 SMs x 8192 u8 MAC / clk / SM (one M128 N256 K32 instruction per 128 clk, B300_MICROARCH "tcgen05
