@@ -348,11 +348,12 @@ struct StereoParams {
 // Row table (frame.cpp:833-850): for every image row the right keypoints whose band
 // [floor(y - 2 s), ceil(y + 2 s)] covers it, as a CSR structure built by one CTA per frame
 // (count, block scan, fill).  Order inside a row is arbitrary; the matcher's winner rule
-// (min over (distance, index)) does not depend on it.  Also packs (x, octave) of the right keypoints.
+// (min over (distance, index)) does not depend on it.  A list entry carries what the coarse matcher filters on
+// (index | octave << 20, x as float bits), so a candidate costs one 8-byte load before the descriptor is touched.
 // grid (nFrames), block 256, dynamic smem 2 * (rows + 1) ints.
 __global__ void __launch_bounds__(256) k_stereo_rows(StereoParams sp, int rows, int listCap, const viorb_keypoint* __restrict__ kr,
                                                      const int* __restrict__ nR, int* __restrict__ rowStart,
-                                                     int* __restrict__ rowList, float2* __restrict__ rmeta, int* __restrict__ status) {
+                                                     int2* __restrict__ rowList, int* __restrict__ status) {
     VIORB_DYN_SMEM(smem);
     __shared__ int warpSums[20];
     int* cnt = reinterpret_cast<int*>(smem);
@@ -368,14 +369,13 @@ __global__ void __launch_bounds__(256) k_stereo_rows(StereoParams sp, int rows, 
         const int maxr = min(__float2int_ru(__fadd_rn(k.y, r)), rows - 1);
         const int minr = max(__float2int_rd(__fsub_rn(k.y, r)), 0);
         for (int y = minr; y <= maxr; ++y) atomicAdd(&cnt[y], 1);
-        rmeta[(size_t)f * sp.outCap + i] = make_float2(k.x, __int_as_float(k.octave));
     }
     __syncthreads();
     const int total = block_excl_scan(cnt, rows + 1, warpSums);      // cnt[y] = start of row y, cnt[rows] = total
     int* RS = rowStart + (size_t)f * (rows + 1);
     for (int i = tid; i <= rows; i += 256) RS[i] = min(cnt[i], listCap);
     if (total > listCap && tid == 0) atomicOr(status, 8);
-    int* RL = rowList + (size_t)f * listCap;
+    int2* RL = rowList + (size_t)f * listCap;
     for (int i = tid; i < nr; i += 256) {
         const viorb_keypoint k = KR[i];
         const float r = __fmul_rn(2.0f, sp.scale[k.octave]);
@@ -383,7 +383,7 @@ __global__ void __launch_bounds__(256) k_stereo_rows(StereoParams sp, int rows, 
         const int minr = max(__float2int_rd(__fsub_rn(k.y, r)), 0);
         for (int y = minr; y <= maxr; ++y) {
             const int pos = cnt[y] + atomicAdd(&cur[y], 1);
-            if (pos < listCap) RL[pos] = i;
+            if (pos < listCap) RL[pos] = make_int2(i | (k.octave << 20), __float_as_int(k.x));
         }
     }
 }
@@ -393,7 +393,7 @@ __global__ void __launch_bounds__(256) k_stereo_rows(StereoParams sp, int rows, 
 __global__ void __launch_bounds__(256) k_stereo_coarse(StereoParams sp, int rows, int listCap, const viorb_keypoint* __restrict__ kl,
                                                        const uint8_t* __restrict__ dl, const int* __restrict__ nL,
                                                        const uint8_t* __restrict__ dr, const int* __restrict__ rowStart,
-                                                       const int* __restrict__ rowList, const float2* __restrict__ rmeta,
+                                                       const int2* __restrict__ rowList,
                                                        int32_t* __restrict__ bestIdx, int32_t* __restrict__ bestDist) {
     const int lane = threadIdx.x & 31, f = blockIdx.y;
     const int iL = blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -401,20 +401,19 @@ __global__ void __launch_bounds__(256) k_stereo_coarse(StereoParams sp, int rows
     const viorb_keypoint k = kl[(size_t)f * sp.outCap + iL];
     const uint4* DL = reinterpret_cast<const uint4*>(dl + (size_t)f * sp.outCap * 32);
     const uint4* DR = reinterpret_cast<const uint4*>(dr + (size_t)f * sp.outCap * 32);
-    const float2* RM = rmeta + (size_t)f * sp.outCap;
     const float uL = k.x, minU = __fsub_rn(k.x, sp.maxD);
     const int row = (int)k.y, levelL = k.octave;
     int best = VIORB_TH_HIGH << 20;
     if (!(uL < 0.f) && row >= 0 && row < rows) {          // maxU = uL - minD, minD = 0 (frame.cpp:872-876)
         const uint4 a0 = DL[(size_t)iL * 2], a1 = DL[(size_t)iL * 2 + 1];
         const int* RS = rowStart + (size_t)f * (rows + 1);
-        const int* RL = rowList + (size_t)f * listCap;
+        const int2* RL = rowList + (size_t)f * listCap;
         const int e = RS[row + 1];
         for (int j = RS[row] + lane; j < e; j += 32) {
-            const int iR = RL[j];
-            const float2 m = RM[iR];
-            const int oc = __float_as_int(m.y);
-            if (oc >= levelL - 1 && oc <= levelL + 1 && m.x >= minU && m.x <= uL) {
+            const int2 m = RL[j];
+            const int iR = m.x & 0xFFFFF, oc = m.x >> 20;
+            const float uR = __int_as_float(m.y);
+            if (oc >= levelL - 1 && oc <= levelL + 1 && uR >= minU && uR <= uL) {
                 const int d = hamming256(a0, a1, DR[(size_t)iR * 2], DR[(size_t)iR * 2 + 1]);
                 best = min(best, (d << 20) | iR);
             }
@@ -464,7 +463,12 @@ __global__ void __launch_bounds__(256) k_stereo_refine(StereoParams sp, ExtractG
             int cR[11], acc[11];
 #pragma unroll
             for (int k = 0; k < 11; ++k) { cR[k] = imR[(size_t)cv * pr + cr + k - 5]; acc[k] = 0; }
-            for (int p = lane; p < 121; p += 32) {
+            // the four passes over the 121 patch pixels are unrolled so that all 48 byte loads of a lane are in flight
+            // together (the kernel is load-latency bound)
+#pragma unroll
+            for (int it = 0; it < 4; ++it) {
+                const int p = min(lane + 32 * it, 120);
+                const bool on = lane + 32 * it < 121;
                 const int dy = p / 11 - 5, dx = p % 11 - 5;
                 const int a = (int)imL[(size_t)(cv + dy) * pl + cu + dx] - cL;
                 const uint8_t* rr = imR + (size_t)(cv + dy) * pr + cr + dx - 5;
@@ -472,7 +476,7 @@ __global__ void __launch_bounds__(256) k_stereo_refine(StereoParams sp, ExtractG
                 for (int k = 0; k < 11; ++k) {
                     const int b = (int)rr[k] - cR[k];
                     const int d = a - b;
-                    acc[k] += d < 0 ? -d : d;
+                    acc[k] += on ? (d < 0 ? -d : d) : 0;
                 }
             }
 #pragma unroll

@@ -138,8 +138,8 @@ struct viorb_extractor {
     // stereo / matching results of the last viorb_stereo_batch on this (left) handle
     DevBuf<int32_t> dBestIdx, dBestDist, dSad, dKnnIdx, dKnnDist, dLrMatch;
     DevBuf<float> dURight, dDepth;
-    DevBuf<int> dNStereo, dNRatio, dRowStart, dRowList;
-    DevBuf<float2> dRMeta;
+    DevBuf<int> dNStereo, dNRatio, dRowStart;
+    DevBuf<int2> dRowList;
     int rowListCap = 0;
     DevBuf<viorb_match> dMatches;
     // pinned staging
@@ -469,7 +469,6 @@ int ensure_match_buffers(viorb_extractor* ex) {
     ex->rowListCap = ex->capOut * span;
     CU(ex->dRowStart.alloc((size_t)ex->prm.max_batch * (ex->prm.max_height + 2)));
     CU(ex->dRowList.alloc((size_t)ex->prm.max_batch * ex->rowListCap));
-    CU(ex->dRMeta.alloc(need));
     return VIORB_OK;
 }
 
@@ -508,9 +507,9 @@ int launch_stereo(viorb_extractor* L, viorb_extractor* R, int n, float bf, float
     if (tm) CU(cudaEventRecord(L->evS[0], st));
     const int rows = L->g.H;
     VIORB_LAUNCH(k_stereo_rows, dim3(n), dim3(256), sizeof(int) * 2 * (rows + 1), st, sp, rows, L->rowListCap, R->dKps.p, R->dNOut.p,
-                 L->dRowStart.p, L->dRowList.p, L->dRMeta.p, L->dStatus.p);
+                 L->dRowStart.p, L->dRowList.p, L->dStatus.p);
     VIORB_LAUNCH(k_stereo_coarse, dim3(gx, n), dim3(256), 0, st, sp, rows, L->rowListCap, L->dKps.p, L->dDesc.p, L->dNOut.p,
-                 R->dDesc.p, L->dRowStart.p, L->dRowList.p, L->dRMeta.p, L->dBestIdx.p, L->dBestDist.p);
+                 R->dDesc.p, L->dRowStart.p, L->dRowList.p, L->dBestIdx.p, L->dBestDist.p);
     if (tm) CU(cudaEventRecord(L->evS[1], st));
     VIORB_LAUNCH(k_stereo_refine, dim3(gx, n), dim3(256), 0, st, sp, L->g, L->src, R->src, L->dKps.p, L->dNOut.p, R->dKps.p,
                  L->dBestIdx.p, L->dBestDist.p, L->dURight.p, L->dDepth.p, L->dSad.p);
@@ -679,7 +678,7 @@ void viorb_extractor_destroy(viorb_extractor* ex) {
     ex->dOrientTab.release(); ex->dSlotLevel.release();
     ex->dBestIdx.release(); ex->dBestDist.release(); ex->dSad.release(); ex->dKnnIdx.release(); ex->dKnnDist.release();
     ex->dLrMatch.release(); ex->dURight.release(); ex->dDepth.release(); ex->dNStereo.release(); ex->dNRatio.release();
-    ex->dMatches.release(); ex->dRowStart.release(); ex->dRowList.release(); ex->dRMeta.release();
+    ex->dMatches.release(); ex->dRowStart.release(); ex->dRowList.release();
     ex->hIn.release(); ex->hDesc.release(); ex->hKps.release(); ex->hCounts.release();
     for (int i = 0; i < 8; ++i) if (ex->evX[i]) cudaEventDestroy(ex->evX[i]);
     for (int i = 0; i < 6; ++i) if (ex->evS[i]) cudaEventDestroy(ex->evS[i]);
