@@ -117,9 +117,15 @@ def test_batch_and_device_resident_paths():
         assert np.array_equal(ex.pyramid_level(0, i), frames[i])
 
 
-def test_chunked_host_batch_matches_single_frames():
+@pytest.mark.parametrize("chunks", [None, "3"])
+def test_chunked_host_batch_matches_single_frames(chunks, monkeypatch):
     """viorb_extract_batch pipelines a large host batch in chunks (H2D / kernels / D2H overlapped): every
-    frame must equal the single-frame result, for pageable and for page-locked buffers, ragged last chunk."""
+    frame must equal the single-frame result, for pageable and for page-locked buffers, ragged last chunk
+    (default: about 80 frames per chunk -> one chunk here; VIORB_CHUNKS=3 -> 28 + 28 + 27)."""
+    if chunks:
+        monkeypatch.setenv("VIORB_CHUNKS", chunks)
+    else:
+        monkeypatch.delenv("VIORB_CHUNKS", raising=False)
     from vi_slam_b200 import FExtractor, pinned_empty
     syn = _syn()
     n, w, h = 83, 640, 360

@@ -820,7 +820,10 @@ int viorb_extract_batch(viorb_extractor* ex, const uint8_t* const* imgs, int n, 
     // The batch is cut into chunks: while the kernels of chunk c run on the handle's stream, the images of
     // chunk c+1 travel host -> device on cpStream and the results of chunk c-1 device -> host on outStream
     // (the three engines of the PCIe / copy path work concurrently).  With stage timing on, one chunk.
-    int nChunks = ex->timing ? 1 : std::min(VIORB_MAX_CHUNKS, std::max(1, n / 40));
+    // 80 frames per chunk: measured with three pipeline workers (tools/e2e_chunks_cmp.sh, 160 frames per call):
+    // 1 / 2 / 3 / 4 / 8 chunks = 39.2k / 40.2k / 37.6k / 37.4k / 34.6k stereo frames/s - smaller chunks leave the
+    // level-synchronous kernels (k_octree, upper pyramid levels) with less than one wave of CTAs.
+    int nChunks = ex->timing ? 1 : std::min(VIORB_MAX_CHUNKS, std::max(1, (n + 40) / 80));
     if (const char* e = std::getenv("VIORB_CHUNKS")) nChunks = std::min(VIORB_MAX_CHUNKS, std::max(1, std::atoi(e)));   // tuning knob
     nChunks = std::min(nChunks, n);
     const int per = (n + nChunks - 1) / nChunks;
