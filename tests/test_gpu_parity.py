@@ -332,3 +332,24 @@ def test_stereo_batch_with_ragged_and_empty_sets():
             nr = len(om)
         assert np.array_equal(out["lr_match"][i, :k], want), i
         assert out["n_ratio"][i] == nr, i
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("split", ["1", "2", "5", "32"])
+def test_knn2_train_range_split(split, monkeypatch):
+    """k_knn2_tc5 cuts a query tile's train range over several CTAs when there are few query tiles (one stereo pair, the
+    row-sharded sweep) and k_knn2_tc5_merge joins the partial pairs: forced split counts, incl. more splits than train tiles."""
+    from vi_slam_b200 import matcher
+    import oracle
+    monkeypatch.setenv("VIORB_KNN_SPLIT", split)
+    for nq, nt in ((300, 5000), (129, 257), (2000, 2000), (5, 1), (64, 0)):
+        q, t = _syn().make_descriptors(nq, max(nt, 1), seed=nq + nt)
+        t = t[:nt]
+        if nt > 600:
+            t[nt - 1] = t[3]              # a tie across two splits: the lower index must win
+        idx, dist = matcher.knn_match(q, t)
+        if nt == 0:
+            assert (idx == -1).all() and (dist == -1).all()
+            continue
+        oidx, odist = oracle.knn2(q, t, nthreads=4)
+        assert np.array_equal(idx, oidx) and np.array_equal(dist, odist), (nq, nt)

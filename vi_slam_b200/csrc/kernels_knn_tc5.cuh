@@ -150,8 +150,35 @@ __device__ __forceinline__ void top2(unsigned& b0, unsigned& b1, unsigned k) {
     b0 = min(b0, k);
 }
 
+// (best, second) keys ((Hamming + popc(query)) << 22 | train index, 0xFFFFFFFF = none) -> idx[2], dist[2] of one query row
+__device__ __forceinline__ void write_knn_row(int32_t* __restrict__ idx, int32_t* __restrict__ dist, size_t rowIdx, unsigned gb0,
+                                              unsigned gb1, int pq) {
+    const unsigned mask = (1u << VIORB_KNN_IDX_BITS) - 1;
+    const bool h0 = gb0 != 0xFFFFFFFFu, h1 = gb1 != 0xFFFFFFFFu;
+    *reinterpret_cast<int2*>(idx + rowIdx * 2) = make_int2(h0 ? (int)(gb0 & mask) : -1, h1 ? (int)(gb1 & mask) : -1);
+    *reinterpret_cast<int2*>(dist + rowIdx * 2) = make_int2(h0 ? (int)(gb0 >> VIORB_KNN_IDX_BITS) - pq : -1,
+                                                            h1 ? (int)(gb1 >> VIORB_KNN_IDX_BITS) - pq : -1);
+}
+
+// Merge of the per-split partial pairs when a query tile's train range was cut over several CTAs (few query tiles,
+// many train rows: a single stereo pair, the row-sharded sweep).  grid (ceil(qTiles * 128 / 256), nSets), block 256.
+__global__ void __launch_bounds__(256) k_knn2_tc5_merge(DescSet Q, const uint2* __restrict__ partial, int32_t* __restrict__ idx,
+                                                        int32_t* __restrict__ dist, size_t outStride, int qTiles, int nSplit) {
+    const int p = blockIdx.y, qi = blockIdx.x * 256 + threadIdx.x;
+    if (qi >= descset_count(Q, p)) return;
+    unsigned gb0 = 0xFFFFFFFFu, gb1 = 0xFFFFFFFFu;
+    for (int j = 0; j < nSplit; ++j) {
+        const uint2 o = partial[((size_t)p * nSplit + j) * ((size_t)qTiles * QT) + qi];
+        top2(gb0, gb1, o.x);
+        top2(gb0, gb1, o.y);
+    }
+    const uint4* qb = reinterpret_cast<const uint4*>(Q.base + (size_t)p * Q.stride);
+    const int pq = popc256(__ldg(qb + (size_t)qi * 2), __ldg(qb + (size_t)qi * 2 + 1));
+    write_knn_row(idx, dist, (size_t)p * outStride + qi, gb0, gb1, pq);
+}
+
 __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, int32_t* __restrict__ idx, int32_t* __restrict__ dist,
-                                                          size_t outStride, int qTiles, int nItems) {
+                                                          size_t outStride, int qTiles, int nItems, int nSplit, uint2* __restrict__ partial) {
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* sA = smem;
     unsigned char* sB = smem + A_BYTES;
@@ -186,12 +213,12 @@ __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, i
         const int rowOff = (pt >> 3) * SBO + (pt & 7) * 16;
         uint32_t g = 0, it = 0;
         for (int item = blockIdx.x; item < nItems; item += gridDim.x) {
-            const int p = item / qTiles, q0 = (item - p * qTiles) * QT;
+            const int js = item % nSplit, rest = item / nSplit, p = rest / qTiles, q0 = (rest - p * qTiles) * QT;
             const int nq = descset_count(Q, p), nt = descset_count(T, p);
             if (q0 >= nq) continue;
             const uint4* qb = reinterpret_cast<const uint4*>(Q.base + (size_t)p * Q.stride);
             const uint4* tb = reinterpret_cast<const uint4*>(T.base + (size_t)p * T.stride);
-            const int nTiles = (nt + TT - 1) / TT;
+            const int nTilesAll = (nt + TT - 1) / TT, tBeg = js * nTilesAll / nSplit, tEnd = (js + 1) * nTilesAll / nSplit;
             uint4 n0[2], n1[2];
             auto fetch = [&](int t) {
 #pragma unroll
@@ -201,7 +228,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, i
                     n1[r] = __ldg(tb + (size_t)row * 2 + 1);
                 }
             };
-            if (nTiles > 0) fetch(0);
+            if (tBeg < tEnd) fetch(tBeg);
             {
                 const int row = min(q0 + pt, nq - 1);
                 const uint4 r0 = __ldg(qb + (size_t)row * 2), r1 = __ldg(qb + (size_t)row * 2 + 1);
@@ -210,10 +237,10 @@ __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, i
                 fence_async_smem();
                 mbar_arrive(bar0 + 8 * BAR_A_FULL);
             }
-            for (int t = 0; t < nTiles; ++t, ++g) {
+            for (int t = tBeg; t < tEnd; ++t, ++g) {
                 const uint32_t s = g & 1;
                 const uint4 c0[2] = {n0[0], n0[1]}, c1[2] = {n1[0], n1[1]};
-                if (t + 1 < nTiles) fetch(t + 1);
+                if (t + 1 < tEnd) fetch(t + 1);
                 mbar_wait(bar0 + 8 * (BAR_B_EMPTY + s), ((g >> 1) & 1) ^ 1);
                 unsigned char* dstB = sB + s * B_BYTES + rowOff;
 #pragma unroll
@@ -233,12 +260,12 @@ __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, i
             const uint64_t descB0 = smem_desc(smem_u32(sB));
             uint32_t g = 0, it = 0;
             for (int item = blockIdx.x; item < nItems; item += gridDim.x) {
-                const int p = item / qTiles, q0 = (item - p * qTiles) * QT;
+                const int js = item % nSplit, rest = item / nSplit, p = rest / qTiles, q0 = (rest - p * qTiles) * QT;
                 const int nq = descset_count(Q, p), nt = descset_count(T, p);
                 if (q0 >= nq) continue;
-                const int nTiles = (nt + TT - 1) / TT;
+                const int nTilesAll = (nt + TT - 1) / TT, tBeg = js * nTilesAll / nSplit, tEnd = (js + 1) * nTilesAll / nSplit;
                 mbar_wait(bar0 + 8 * BAR_A_FULL, it & 1);
-                for (int t = 0; t < nTiles; ++t, ++g) {
+                for (int t = tBeg; t < tEnd; ++t, ++g) {
                     const uint32_t s = g & 1, ph = (g >> 1) & 1;
                     mbar_wait(bar0 + 8 * (BAR_B_FULL + s), ph);
                     mbar_wait(bar0 + 8 * (BAR_D_EMPTY + s), ph ^ 1);
@@ -263,13 +290,13 @@ __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, i
         const uint32_t laneBase = tmem + ((uint32_t)(quarter * 32) << 16) + half * 128;
         uint32_t g = 0, it = 0;
         for (int item = blockIdx.x; item < nItems; item += gridDim.x) {
-            const int p = item / qTiles, q0 = (item - p * qTiles) * QT;
+            const int js = item % nSplit, rest = item / nSplit, p = rest / qTiles, q0 = (rest - p * qTiles) * QT;
             const int nq = descset_count(Q, p), nt = descset_count(T, p);
             if (q0 >= nq) continue;
-            const int nTiles = (nt + TT - 1) / TT;
+            const int nTilesAll = (nt + TT - 1) / TT, tBeg = js * nTilesAll / nSplit, tEnd = (js + 1) * nTilesAll / nSplit;
             const int qi = q0 + row;
             unsigned gb0 = 0xFFFFFFFFu, gb1 = 0xFFFFFFFFu;
-            for (int t = 0; t < nTiles; ++t, ++g) {
+            for (int t = tBeg; t < tEnd; ++t, ++g) {
                 const uint32_t s = g & 1;
                 mbar_wait(bar0 + 8 * (BAR_D_FULL + s), (g >> 1) & 1);
                 tc_fence_after();
@@ -319,15 +346,15 @@ __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, i
                 const uint2 o = xch[row];
                 top2(gb0, gb1, o.x);
                 top2(gb0, gb1, o.y);
-                const uint4* qb = reinterpret_cast<const uint4*>(Q.base + (size_t)p * Q.stride);
-                const int pq = popc256(__ldg(qb + (size_t)qi * 2), __ldg(qb + (size_t)qi * 2 + 1));
-                const unsigned mask = (1u << VIORB_KNN_IDX_BITS) - 1;
-                int32_t* oi = idx + (size_t)p * outStride * 2 + (size_t)qi * 2;
-                int32_t* od = dist + (size_t)p * outStride * 2 + (size_t)qi * 2;
-                const bool h0 = gb0 != 0xFFFFFFFFu, h1 = gb1 != 0xFFFFFFFFu;
-                *reinterpret_cast<int2*>(oi) = make_int2(h0 ? (int)(gb0 & mask) : -1, h1 ? (int)(gb1 & mask) : -1);
-                *reinterpret_cast<int2*>(od) = make_int2(h0 ? (int)(gb0 >> VIORB_KNN_IDX_BITS) - pq : -1,
-                                                         h1 ? (int)(gb1 >> VIORB_KNN_IDX_BITS) - pq : -1);
+                if (nSplit > 1) {
+                    // the train tiles of this query tile are split over nSplit CTAs: raw keys go to the scratch rows
+                    // [set][split][query], k_knn2_tc5_merge finishes
+                    partial[((size_t)p * nSplit + js) * ((size_t)qTiles * QT) + qi] = make_uint2(gb0, gb1);
+                } else {
+                    const uint4* qb = reinterpret_cast<const uint4*>(Q.base + (size_t)p * Q.stride);
+                    const int pq = popc256(__ldg(qb + (size_t)qi * 2), __ldg(qb + (size_t)qi * 2 + 1));
+                    write_knn_row(idx, dist, (size_t)p * outStride + qi, gb0, gb1, pq);
+                }
             }
             ++it;
         }

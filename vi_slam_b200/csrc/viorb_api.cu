@@ -543,8 +543,8 @@ int release_partner(viorb_extractor* L, viorb_extractor* R) {
 // tensor memory, kernels_knn_tc5.cuh).  VIORB_KNN=mma selects the warp-level IMMA kernel (k_knn2_mma), VIORB_KNN=popc
 // the LOP3/POPC integer-pipe kernel (k_knn2) - all three give identical results, the choice is a measured one
 // (DESIGN.md section 5).
-static int launch_knn2(const DescSet& Q, const DescSet& T, int maxNq, int nSets, int32_t* dIdx, int32_t* dDist, size_t outStride,
-                       cudaStream_t st) {
+static int launch_knn2(const DescSet& Q, const DescSet& T, int maxNq, int maxNt, int nSets, int32_t* dIdx, int32_t* dDist,
+                       size_t outStride, cudaStream_t st) {
     static const int mode = [] {
         const char* e = std::getenv("VIORB_KNN");
         return !e ? 0 : std::strcmp(e, "popc") == 0 ? 2 : std::strcmp(e, "mma") == 0 ? 1 : 0;
@@ -556,13 +556,38 @@ static int launch_knn2(const DescSet& Q, const DescSet& T, int maxNq, int nSets,
         CU(cudaGetDevice(&dev));
         if (dev < 64 && sms[dev] == 0) {
             CU(cudaFuncSetAttribute(tc5::k_knn2_tc5, cudaFuncAttributeMaxDynamicSharedMemorySize, tc5::SMEM_BYTES));
+            // the split path takes its scratch rows from the stream-ordered allocator: keep freed blocks in the pool
+            cudaMemPool_t pool;
+            CU(cudaDeviceGetDefaultMemPool(&pool, dev));
+            uint64_t keep = UINT64_MAX;
+            CU(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
             CU(cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev));
         }
-        const int qTiles = (maxNq + tc5::QT - 1) / tc5::QT, nItems = qTiles * nSets;
-        if (nItems > 0) {
+        const int qTiles = (maxNq + tc5::QT - 1) / tc5::QT, nBase = qTiles * nSets;
+        if (nBase > 0) {
             const int nSm = dev < 64 ? sms[dev] : 148;
+            // Few query tiles and a long train set (one stereo pair, the row-sharded sweep) leave SMs idle or a last
+            // wave nearly empty: cut every query tile's train range over nSplit CTAs and merge the partial pairs.
+            // Cost model in train tiles: waves x (tiles per item + ~2 tiles of per-item set-up).
+            const int maxTiles = std::max(1, (maxNt + tc5::TT - 1) / tc5::TT);
+            int nSplit = 1;
+            long best = 0;
+            for (int sp = 1; sp <= std::min(maxTiles, 32); ++sp) {
+                const long cost = (long)((nBase * sp + nSm - 1) / nSm) * ((maxTiles + sp - 1) / sp + 2);
+                if (sp == 1 || cost * 20 < best * 19) { best = cost; nSplit = sp; }      // a split must win by > 5 %
+                if (sp == 1 && cost < 24) break;      // under ~20 us of kernel the merge launch costs more than it saves
+            }
+            if (const char* e = std::getenv("VIORB_KNN_SPLIT")) nSplit = std::max(1, std::min(std::atoi(e), maxTiles));   // tuning knob
+            const int nItems = nBase * nSplit;
+            uint2* partial = nullptr;
+            if (nSplit > 1) CU(cudaMallocAsync((void**)&partial, (size_t)nItems * tc5::QT * sizeof(uint2), st));
             VIORB_LAUNCH(tc5::k_knn2_tc5, dim3(std::min(nItems, nSm)), dim3(tc5::THREADS), tc5::SMEM_BYTES, st, Q, T, dIdx, dDist,
-                         outStride, qTiles, nItems);
+                         outStride, qTiles, nItems, nSplit, partial);
+            if (nSplit > 1) {
+                VIORB_LAUNCH(tc5::k_knn2_tc5_merge, dim3((qTiles * tc5::QT + 255) / 256, nSets), dim3(256), 0, st, Q, partial, dIdx,
+                             dDist, outStride, qTiles, nSplit);
+                CU(cudaFreeAsync(partial, st));
+            }
         }
         CU(cudaGetLastError());
         return VIORB_OK;
@@ -1011,7 +1036,7 @@ int viorb_knn2_device(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, in
     if (((uintptr_t)d_q & 15) || ((uintptr_t)d_t & 15)) return fail(VIORB_E_ARG, "descriptor buffers must be 16-byte aligned");
     if (nq == 0) return VIORB_OK;
     DescSet Q{d_q, 0, nullptr, nq}, T{d_t, 0, nullptr, nt};
-    return launch_knn2(Q, T, nq, 1, d_idx, d_dist, (size_t)nq, (cudaStream_t)stream);
+    return launch_knn2(Q, T, nq, nt, 1, d_idx, d_dist, (size_t)nq, (cudaStream_t)stream);
 }
 
 int viorb_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx, int32_t* dist, int device) {
@@ -1169,7 +1194,7 @@ int viorb_stereo_batch(viorb_extractor* L, viorb_extractor* R, int n, float bf, 
     // fisheye-style brute force kNN-2 + ratio, left -> right (frame.cpp:1167-1170)
     const size_t oc = L->g.outCap;
     DescSet Q{L->dDesc.p, oc * 32, L->dNOut.p, 0}, T{R->dDesc.p, oc * 32, R->dNOut.p, 0};
-    rc = launch_knn2(Q, T, L->g.outCap, n, L->dKnnIdx.p, L->dKnnDist.p, oc, L->stream);
+    rc = launch_knn2(Q, T, L->g.outCap, L->g.outCap, n, L->dKnnIdx.p, L->dKnnDist.p, oc, L->stream);
     if (rc) return rc;
     if (L->timing) CU(cudaEventRecord(L->evS[4], L->stream));
     VIORB_LAUNCH(k_ratio, dim3(n), dim3(256), 0, L->stream, Q, L->dKnnIdx.p, L->dKnnDist.p, oc, ratio, 0, L->dMatches.p, oc,
