@@ -12,8 +12,9 @@
 // and the epilogue is nothing but the running top-2 (min / max / min per pair).  Rows past the end of the train
 // set carry 255 x 255 in a fourth byte and lose against every real key.
 //
-// Shape.  Persistent CTAs of 416 threads, one per SM, work items = (descriptor set, 128-row query tile):
-//   warps 4-7  producers: expand the query tile (A, 128 x 288 B) and the train tiles (B, 256 x 288 B, two stages)
+// Shape.  Persistent CTAs of 416 threads, one per SM, work items = (descriptor set, 128-row query tile), sets
+// fastest, so that the empty trailing tiles of ragged sets (rows past the set's count) all sit at the end of the list:
+//   warps 4-7  producers: expand the query tile (A, 128 x 288 B, double-buffered by item) and the train tiles (B, 256 x 288 B, two stages)
 //              into the K-major no-swizzle core-matrix layout, fence.proxy.async, arrive on the full barriers
 //   warp 8     one thread issues 9 x tcgen05.mma.cta_group::1.kind::i8 (M 128, N 256, K 32) per train tile into one
 //              of two 256-column accumulators and commits to the barriers that free the stage / publish the tile
@@ -21,7 +22,7 @@
 //              tile.  Every key is below 2^16, so tcgen05.ld ... .pack::16b delivers two columns per register
 //              and the running top-2 of 64 columns is 16 x 3 VIMNMX.U16x2 on two independent chains; the two
 //              survivors become (distance' << 22 | train index) keys; idx / dist are written at the end
-// Results are bit-identical to k_knn2 / k_knn2_mma.  grid = min(items, SMs), block 416, dynamic smem 186 KB.
+// Results are bit-identical to k_knn2 / k_knn2_mma.  grid = min(items, SMs), block 416, dynamic smem 222 KB.
 // Measured bound (nold / nocomp variants, tools/gpu_tc5_variants.sh): shared-memory bandwidth - per train tile
 // the producers store 72 KB and the tensor core reads 108 KB (A is re-read for every tile) at 128 B / clk.
 #pragma once
@@ -40,14 +41,14 @@ constexpr int LBO = 128;                // bytes between core matrices adjacent 
 constexpr int SBO = KCH * 128;          // bytes between 8-row groups
 constexpr int A_BYTES = QT / 8 * SBO;   // 36 864
 constexpr int B_BYTES = TT / 8 * SBO;   // 73 728
-constexpr int NBAR = 10;
-constexpr int XCH_OFF = A_BYTES + 2 * B_BYTES + NBAR * 8 + 16;   // uint2[2][QT]: the upper column half's (best, second)
+constexpr int NBAR = 12;
+constexpr int XCH_OFF = 2 * A_BYTES + 2 * B_BYTES + NBAR * 8 + 16;   // uint2[2][QT]: the upper column half's (best, second)
 constexpr int SMEM_BYTES = XCH_OFF + 2 * QT * 8;
 constexpr int THREADS = 416;
 constexpr int PAD_KEY = 255 * 255;      // key contribution of a padding train row
 constexpr uint32_t IDESC = (2u << 4) | ((uint32_t)(TT >> 3) << 17) | ((uint32_t)(QT >> 4) << 24);   // s32 += u8 x u8, K-major A and B
 
-enum { BAR_A_FULL = 0, BAR_A_EMPTY = 1, BAR_B_FULL = 2, BAR_B_EMPTY = 4, BAR_D_FULL = 6, BAR_D_EMPTY = 8 };
+enum { BAR_A_FULL = 0, BAR_A_EMPTY = 2, BAR_B_FULL = 4, BAR_B_EMPTY = 6, BAR_D_FULL = 8, BAR_D_EMPTY = 10 };   // two of each
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint32_t bar, int count) {
@@ -178,19 +179,19 @@ __global__ void __launch_bounds__(256) k_knn2_tc5_merge(DescSet Q, const uint2* 
 }
 
 __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, int32_t* __restrict__ idx, int32_t* __restrict__ dist,
-                                                          size_t outStride, int qTiles, int nItems, int nSplit, uint2* __restrict__ partial) {
+                                                          size_t outStride, int qTiles, int nSets, int nItems, int nSplit, uint2* __restrict__ partial) {
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* sA = smem;
-    unsigned char* sB = smem + A_BYTES;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + A_BYTES + 2 * B_BYTES);
+    unsigned char* sB = smem + 2 * A_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * A_BYTES + 2 * B_BYTES);
     uint32_t* tmemSlot = reinterpret_cast<uint32_t*>(bars + NBAR);
     const uint32_t bar0 = smem_u32(bars);
     const int tid = threadIdx.x, warp = tid >> 5;
 
     if (tid == 0) {
-        mbar_init(bar0 + 8 * BAR_A_FULL, 128);
-        mbar_init(bar0 + 8 * BAR_A_EMPTY, 1);
         for (int s = 0; s < 2; ++s) {
+            mbar_init(bar0 + 8 * (BAR_A_FULL + s), 128);
+            mbar_init(bar0 + 8 * (BAR_A_EMPTY + s), 1);
             mbar_init(bar0 + 8 * (BAR_B_FULL + s), 128);
             mbar_init(bar0 + 8 * (BAR_B_EMPTY + s), 1);
             mbar_init(bar0 + 8 * (BAR_D_FULL + s), 1);
@@ -213,7 +214,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, i
         const int rowOff = (pt >> 3) * SBO + (pt & 7) * 16;
         uint32_t g = 0, it = 0;
         for (int item = blockIdx.x; item < nItems; item += gridDim.x) {
-            const int js = item % nSplit, rest = item / nSplit, p = rest / qTiles, q0 = (rest - p * qTiles) * QT;
+            const int js = item % nSplit, rest = item / nSplit, qt = rest / nSets, p = rest - qt * nSets, q0 = qt * QT;
             const int nq = descset_count(Q, p), nt = descset_count(T, p);
             if (q0 >= nq) continue;
             const uint4* qb = reinterpret_cast<const uint4*>(Q.base + (size_t)p * Q.stride);
@@ -232,10 +233,11 @@ __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, i
             {
                 const int row = min(q0 + pt, nq - 1);
                 const uint4 r0 = __ldg(qb + (size_t)row * 2), r1 = __ldg(qb + (size_t)row * 2 + 1);
-                mbar_wait(bar0 + 8 * BAR_A_EMPTY, (it & 1) ^ 1);
-                expand_query_row(sA + rowOff, r0, r1);
+                // the query tile is double-buffered by item parity: it is expanded while the previous item's MMAs still run
+                mbar_wait(bar0 + 8 * (BAR_A_EMPTY + (it & 1)), ((it >> 1) & 1) ^ 1);
+                expand_query_row(sA + (it & 1) * A_BYTES + rowOff, r0, r1);
                 fence_async_smem();
-                mbar_arrive(bar0 + 8 * BAR_A_FULL);
+                mbar_arrive(bar0 + 8 * (BAR_A_FULL + (it & 1)));
             }
             for (int t = tBeg; t < tEnd; ++t, ++g) {
                 const uint32_t s = g & 1;
@@ -256,15 +258,16 @@ __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, i
     } else if (warp == 8) {
         // ------------------------------------------------------------------ MMA issue (one thread)
         if ((tid & 31) == 0) {
-            const uint64_t descA = smem_desc(smem_u32(sA));
+            const uint64_t descA0 = smem_desc(smem_u32(sA));
             const uint64_t descB0 = smem_desc(smem_u32(sB));
             uint32_t g = 0, it = 0;
             for (int item = blockIdx.x; item < nItems; item += gridDim.x) {
-                const int js = item % nSplit, rest = item / nSplit, p = rest / qTiles, q0 = (rest - p * qTiles) * QT;
+                const int js = item % nSplit, rest = item / nSplit, qt = rest / nSets, p = rest - qt * nSets, q0 = qt * QT;
                 const int nq = descset_count(Q, p), nt = descset_count(T, p);
                 if (q0 >= nq) continue;
                 const int nTilesAll = (nt + TT - 1) / TT, tBeg = js * nTilesAll / nSplit, tEnd = (js + 1) * nTilesAll / nSplit;
-                mbar_wait(bar0 + 8 * BAR_A_FULL, it & 1);
+                mbar_wait(bar0 + 8 * (BAR_A_FULL + (it & 1)), (it >> 1) & 1);
+                const uint64_t descA = descA0 + (uint64_t)(((it & 1) * A_BYTES) >> 4);
                 for (int t = tBeg; t < tEnd; ++t, ++g) {
                     const uint32_t s = g & 1, ph = (g >> 1) & 1;
                     mbar_wait(bar0 + 8 * (BAR_B_FULL + s), ph);
@@ -277,7 +280,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, i
                     tc_commit(bar0 + 8 * (BAR_B_EMPTY + s));
                     tc_commit(bar0 + 8 * (BAR_D_FULL + s));
                 }
-                tc_commit(bar0 + 8 * BAR_A_EMPTY);
+                tc_commit(bar0 + 8 * (BAR_A_EMPTY + (it & 1)));
                 ++it;
             }
         }
@@ -290,7 +293,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_knn2_tc5(DescSet Q, DescSet T, i
         const uint32_t laneBase = tmem + ((uint32_t)(quarter * 32) << 16) + half * 128;
         uint32_t g = 0, it = 0;
         for (int item = blockIdx.x; item < nItems; item += gridDim.x) {
-            const int js = item % nSplit, rest = item / nSplit, p = rest / qTiles, q0 = (rest - p * qTiles) * QT;
+            const int js = item % nSplit, rest = item / nSplit, qt = rest / nSets, p = rest - qt * nSets, q0 = qt * QT;
             const int nq = descset_count(Q, p), nt = descset_count(T, p);
             if (q0 >= nq) continue;
             const int nTilesAll = (nt + TT - 1) / TT, tBeg = js * nTilesAll / nSplit, tEnd = (js + 1) * nTilesAll / nSplit;

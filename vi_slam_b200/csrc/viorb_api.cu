@@ -582,7 +582,7 @@ static int launch_knn2(const DescSet& Q, const DescSet& T, int maxNq, int maxNt,
             uint2* partial = nullptr;
             if (nSplit > 1) CU(cudaMallocAsync((void**)&partial, (size_t)nItems * tc5::QT * sizeof(uint2), st));
             VIORB_LAUNCH(tc5::k_knn2_tc5, dim3(std::min(nItems, nSm)), dim3(tc5::THREADS), tc5::SMEM_BYTES, st, Q, T, dIdx, dDist,
-                         outStride, qTiles, nItems, nSplit, partial);
+                         outStride, qTiles, nSets, nItems, nSplit, partial);
             if (nSplit > 1) {
                 VIORB_LAUNCH(tc5::k_knn2_tc5_merge, dim3((qTiles * tc5::QT + 255) / 256, nSets), dim3(256), 0, st, Q, partial, dIdx,
                              dDist, outStride, qTiles, nSplit);
