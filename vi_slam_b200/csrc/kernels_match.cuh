@@ -434,7 +434,10 @@ __global__ void __launch_bounds__(256) k_stereo_coarse(StereoParams sp, int rows
 // the parabola fit and the disparity / depth arithmetic in float32 without FMA contraction.
 // grid (ceil(outCap/8), nFrames), block 256.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_stereo_refine(StereoParams sp, ExtractGeom g, FrameSrc fsL, FrameSrc fsR,
+#ifndef VIORB_REFINE_MINB
+#define VIORB_REFINE_MINB 5      // <= 51 registers: 0.240 -> 0.218 ms against the unconstrained 64-register build (latency bound: occupancy pays)
+#endif
+__global__ void __launch_bounds__(256, VIORB_REFINE_MINB) k_stereo_refine(StereoParams sp, ExtractGeom g, FrameSrc fsL, FrameSrc fsR,
                                                        const viorb_keypoint* __restrict__ kl, const int* __restrict__ nL,
                                                        const viorb_keypoint* __restrict__ kr, const int32_t* __restrict__ bestIdx,
                                                        const int32_t* __restrict__ bestDist, float* __restrict__ uRight,
