@@ -353,3 +353,28 @@ def test_knn2_train_range_split(split, monkeypatch):
             continue
         oidx, odist = oracle.knn2(q, t, nthreads=4)
         assert np.array_equal(idx, oidx) and np.array_equal(dist, odist), (nq, nt)
+
+
+@pytest.mark.gpu
+def test_knn2_concurrent_callers():
+    """Four host threads call the matcher at once (as the pipeline workers of the end-to-end path do): shapes that take the
+    plain path, the train-range split (stream-ordered scratch) and several waves of the persistent tcgen05 kernel."""
+    import threading
+    import oracle
+    from vi_slam_b200 import matcher
+    shapes = [(2000, 2000), (300, 20000), (20000, 3000), (129, 257)]
+    data = [_syn().make_descriptors(nq, nt, seed=50 + i) for i, (nq, nt) in enumerate(shapes)]
+    want = [oracle.knn2(q, t, nthreads=4) for q, t in data]
+    errs = []
+
+    def work(i):
+        q, t = data[i]
+        for _ in range(6):
+            idx, dist = matcher.knn_match(q, t)
+            if not (np.array_equal(idx, want[i][0]) and np.array_equal(dist, want[i][1])):
+                errs.append(i)
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(len(shapes))]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs
