@@ -181,7 +181,6 @@ def run_ours(args, rank, world, local_rank):
     import torch
     from vi_slam_b200 import FExtractor, matcher
 
-    os.environ.pop("VIORB_LIBRARY", None)            # the product library only
     if args.variant_lib:                             # A/B experiments (tools/variants_bench.sh); flagged in the output
         from vi_slam_b200 import _lib
         _lib.DEFAULT_LIB = os.path.abspath(args.variant_lib)

@@ -131,6 +131,9 @@ int viorb_pyramid_level(viorb_extractor* ex, int frame, int level, uint8_t* dst,
 int viorb_debug_candidates(viorb_extractor* ex, int frame, int level, int32_t* xys, int cap, int* n_out);
 int viorb_debug_kept(viorb_extractor* ex, int frame, int level, int32_t* xys, float* angle, int cap, int* n_out);
 int viorb_debug_blurred(viorb_extractor* ex, int frame, int level, uint8_t* dst, int dst_step);
+/* Test hook of the kNN-2 launcher: force the number of train-range splits per query tile (0 = the cost model decides,
+ * the default).  Process-wide; only the parity tests set it, to reach the split / merge path on small inputs. */
+void viorb_debug_knn_split(int n_split);
 
 /* ---- matching ---------------------------------------------------------------------------- */
 

@@ -50,7 +50,6 @@ def test_no_gpu_means_error_not_fallback(cuda_lib):
     import torch
     if torch.cuda.is_available():
         pytest.skip("GPU present")
-    os.environ.pop("VIORB_LIBRARY", None)
     from vi_slam_b200 import FExtractor, ViorbError, matcher
     import numpy as np
     with pytest.raises(ViorbError):

@@ -13,7 +13,6 @@ pytestmark = pytest.mark.gpu
 
 @pytest.fixture(scope="module", autouse=True)
 def _cuda_lib(oracle_mod):
-    os.environ.pop("VIORB_LIBRARY", None)
     import __graft_entry__ as ge
     assert os.path.exists(ge.LIB), "libviorb.so missing: run __graft_entry__.build()"
     from vi_slam_b200 import _lib
@@ -218,13 +217,31 @@ def test_stereo_golden(golden_dir):
     _, kl, dl = gl.compute(g["left"], None, (0, 0))
     _, kr, dr = gr.compute(g["right"], None, (0, 0))
     ur, dp, _, _ = matcher.compute_stereo_matches(gl, gr, float(g["bf"]), float(g["b"]))
-    if np.array_equal(dl, g["desc_l"]) and np.array_equal(dr, g["desc_r"]):
-        assert np.array_equal(ur.view(np.uint32), g["u_right"].view(np.uint32))
-        assert np.array_equal(dp.view(np.uint32), g["depth"].view(np.uint32))
-        m = matcher.fisheye_ratio_match(dl, dr, 0.7)
-        assert np.array_equal(np.stack([m["query_idx"], m["train_idx"], m["distance"]], 1), g["ratio_matches"])
-    else:
-        assert int((dp > 0).sum()) > 0.95 * int((g["depth"] > 0).sum())
+    # a descriptor row that differs from OpenCV's (sincosf rounding; none observed so far) would make the comparison
+    # below meaningless: report the count and fail instead of weakening the check
+    nd = int((dl != g["desc_l"]).any(axis=1).sum()) + int((dr != g["desc_r"]).any(axis=1).sum())
+    assert nd == 0, f"{nd} descriptor rows differ from the OpenCV golden; the stereo golden cannot be compared"
+    assert np.array_equal(ur.view(np.uint32), g["u_right"].view(np.uint32))
+    assert np.array_equal(dp.view(np.uint32), g["depth"].view(np.uint32))
+    m = matcher.fisheye_ratio_match(dl, dr, 0.7)
+    assert np.array_equal(np.stack([m["query_idx"], m["train_idx"], m["distance"]], 1), g["ratio_matches"])
+
+
+def test_handles_with_different_shared_memory_needs_interleave():
+    """The monocular layout of the reference: a 5 x nFeatures initialiser extractor next to the tracking extractor in one
+    process (tracking.cpp:1087-1093), used alternately.  The kernels' dynamic shared-memory limit is per (function, device);
+    a handle with a small need must not lower it for the other one."""
+    from vi_slam_b200 import FExtractor
+    import oracle
+    syn = _syn()
+    big = FExtractor(10000, max_size=(1241, 376))
+    small = FExtractor(500, max_size=(320, 240))
+    imgs = [syn.make_frame(6000, 1241, 376), syn.make_frame(6001, 320, 240), syn.make_frame(6002, 1241, 376)]
+    ob, osm = oracle.OracleExtractor(10000), oracle.OracleExtractor(500)
+    for ex, ox, img in ((big, ob, imgs[0]), (small, osm, imgs[1]), (big, ob, imgs[2]), (small, osm, imgs[1]), (big, ob, imgs[0])):
+        m, k, d = ex.compute(img, None, (0, 1000))
+        om, ok, od = ox.compute(img, (0, 1000))
+        assert m == om and np.array_equal(k["x"], ok["x"]) and np.array_equal(k["y"], ok["y"]) and np.array_equal(d, od)
 
 
 def test_pinned_buffers_take_the_direct_dma_path():
@@ -248,25 +265,22 @@ def test_pinned_buffers_take_the_direct_dma_path():
 
 
 @pytest.mark.gpu
-def test_knn2_integer_pipe_kernel_matches_too(tmp_path):
-    """k_knn2 (LOP3/POPC, VIORB_KNN=popc) and the default k_knn2_mma (tensor cores) must both equal the oracle; the
-    kernel choice is read once per process, so the integer-pipe kernel runs in a child process."""
-    import subprocess
-    import sys
-    code = ("import numpy as np, oracle\n"
-            "from vi_slam_b200 import matcher, synthetic\n"
-            "for nq, nt in ((2000, 2000), (130, 129), (5, 1), (1, 4000), (3000, 257)):\n"
-            "    q, t = synthetic.make_descriptors(nq, nt, seed=nq + nt)\n"
-            "    i, d = matcher.knn_match(q, t)\n"
-            "    oi, od = oracle.knn2(q, t, nthreads=4)\n"
-            "    assert np.array_equal(i, oi) and np.array_equal(d, od), (nq, nt)\n"
-            "print('ok')\n")
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    for kern in ("popc", "mma"):
-        env = dict(os.environ, VIORB_KNN=kern, PYTHONPATH=root)
-        env.pop("VIORB_LIBRARY", None)
-        out = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True)
-        assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
+@pytest.mark.parametrize("variant,flag", [("knn_popc", "-DVIORB_KNN_VARIANT=2"), ("knn_mma", "-DVIORB_KNN_VARIANT=1")])
+def test_knn2_build_variants_match_too(variant, flag):
+    """The two earlier kNN-2 kernels are BUILD-time variants (the product library holds k_knn2_tc5 only): k_knn2 (LOP3/POPC)
+    and k_knn2_mma (warp-level IMMA) compiled into build_variants/ must equal the oracle as well."""
+    import shutil
+    import __graft_entry__ as ge
+    from vi_slam_b200 import matcher
+    import oracle
+    if shutil.which("nvcc") is None and not os.path.exists("/usr/local/cuda/bin/nvcc"):
+        pytest.skip("no nvcc on this box")
+    lib = ge.build_variant(variant, [flag])
+    for nq, nt in ((2000, 2000), (130, 129), (5, 1), (1, 4000), (3000, 257)):
+        q, t = _syn().make_descriptors(nq, nt, seed=nq + nt)
+        i, d = matcher.knn_match(q, t, lib_path=lib)
+        oi, od = oracle.knn2(q, t, nthreads=4)
+        assert np.array_equal(i, oi) and np.array_equal(d, od), (nq, nt)
 
 
 @pytest.mark.gpu
@@ -335,24 +349,28 @@ def test_stereo_batch_with_ragged_and_empty_sets():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("split", ["1", "2", "5", "32"])
-def test_knn2_train_range_split(split, monkeypatch):
+@pytest.mark.parametrize("split", [1, 2, 5, 32])
+def test_knn2_train_range_split(split):
     """k_knn2_tc5 cuts a query tile's train range over several CTAs when there are few query tiles (one stereo pair, the
     row-sharded sweep) and k_knn2_tc5_merge joins the partial pairs: forced split counts, incl. more splits than train tiles."""
     from vi_slam_b200 import matcher
     import oracle
-    monkeypatch.setenv("VIORB_KNN_SPLIT", split)
-    for nq, nt in ((300, 5000), (129, 257), (2000, 2000), (5, 1), (64, 0)):
-        q, t = _syn().make_descriptors(nq, max(nt, 1), seed=nq + nt)
-        t = t[:nt]
-        if nt > 600:
-            t[nt - 1] = t[3]              # a tie across two splits: the lower index must win
-        idx, dist = matcher.knn_match(q, t)
-        if nt == 0:
-            assert (idx == -1).all() and (dist == -1).all()
-            continue
-        oidx, odist = oracle.knn2(q, t, nthreads=4)
-        assert np.array_equal(idx, oidx) and np.array_equal(dist, odist), (nq, nt)
+    from vi_slam_b200 import _lib
+    _lib.load().viorb_debug_knn_split(split)
+    try:
+        for nq, nt in ((300, 5000), (129, 257), (2000, 2000), (5, 1), (64, 0)):
+            q, t = _syn().make_descriptors(nq, max(nt, 1), seed=nq + nt)
+            t = t[:nt]
+            if nt > 600:
+                t[nt - 1] = t[3]              # a tie across two splits: the lower index must win
+            idx, dist = matcher.knn_match(q, t)
+            if nt == 0:
+                assert (idx == -1).all() and (dist == -1).all()
+                continue
+            oidx, odist = oracle.knn2(q, t, nthreads=4)
+            assert np.array_equal(idx, oidx) and np.array_equal(dist, odist), (nq, nt)
+    finally:
+        _lib.load().viorb_debug_knn_split(0)
 
 
 @pytest.mark.gpu

@@ -164,7 +164,6 @@ def test_emulation_build_equals_reference(name):
 def test_cuda_equals_reference_object_code(name):
     if not ref.available():
         pytest.skip("liborb_ref.so did not travel")
-    os.environ.pop("VIORB_LIBRARY", None)
     from vi_slam_b200 import FExtractor
     make, nf, sf, nl, ini, mn, lap = ref_cases.CASES[name]
     img = make()
@@ -189,7 +188,6 @@ def test_cuda_equals_reference_object_code(name):
 @pytest.mark.gpu
 @pytest.mark.parametrize("name", ref_cases.GOLDEN)
 def test_cuda_equals_committed_reference_fixture(golden_dir, name):
-    os.environ.pop("VIORB_LIBRARY", None)
     from vi_slam_b200 import FExtractor
     make, nf, sf, nl, ini, mn, lap = ref_cases.CASES[name]
     img = make()

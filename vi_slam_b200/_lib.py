@@ -1,9 +1,9 @@
 """Loader for libviorb.so (the C ABI of include/viorb.h).
 
-The product has no CPU path: if the CUDA library is missing this raises.  Tests
-may point ``VIORB_LIBRARY`` at another build of the same ABI (the g++ emulation
-build under tests/cuda_emu) to check host logic without a GPU; nothing in the
-package, bench.py or __graft_entry__.py sets that variable.
+The product has no CPU path: if the CUDA library is missing this raises.  No
+environment variable redirects the loader; tests that check host logic without
+a GPU pass ``lib_path=`` (the g++ emulation build under tests/cuda_emu)
+explicitly to the classes they construct.
 """
 from __future__ import annotations
 
@@ -58,6 +58,7 @@ SYMBOLS = {
     "viorb_debug_candidates": (C.c_int, [C.c_void_p, C.c_int, C.c_int, i32p, C.c_int, i32p]),
     "viorb_debug_kept": (C.c_int, [C.c_void_p, C.c_int, C.c_int, i32p, f32p, C.c_int, i32p]),
     "viorb_debug_blurred": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]),
+    "viorb_debug_knn_split": (None, [C.c_int]),
     "viorb_descriptor_distance": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, i32p, C.c_int]),
     "viorb_knn2": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, i32p, i32p, C.c_int]),
     "viorb_knn2_device": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
@@ -98,7 +99,7 @@ _cache = {}
 
 
 def load(path: str | None = None):
-    path = path or os.environ.get("VIORB_LIBRARY") or DEFAULT_LIB
+    path = path or DEFAULT_LIB
     if path in _cache:
         return _cache[path]
     if not os.path.exists(path):

@@ -5,16 +5,30 @@
 // kernels in kernels_extract.cuh / kernels_match.cuh and fails with VIORB_E_CUDA / VIORB_E_NO_DEVICE
 // if that is impossible.
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
+// kNN-2 kernel of this build: 0 = k_knn2_tc5 (the product), 1 = k_knn2_mma, 2 = k_knn2 (experiments; the CPU
+// emulation build has no tcgen05 and takes 1)
+#ifndef VIORB_KNN_VARIANT
+#ifdef VIORB_EMU
+#define VIORB_KNN_VARIANT 1
+#else
+#define VIORB_KNN_VARIANT 0
+#endif
+#endif
+
 #include "kernels_extract.cuh"
 #include "kernels_match.cuh"
+#if VIORB_KNN_VARIANT == 0
 #include "kernels_knn_tc5.cuh"
+#endif
 #include "kernels_window.cuh"
 #include "kernels_bow.cuh"
 #include "kernels_kb8.cuh"
@@ -141,6 +155,7 @@ struct viorb_extractor {
     DevBuf<int> dNStereo, dNRatio, dRowStart;
     DevBuf<int2> dRowList;
     int rowListCap = 0;
+    bool matchReady = false;
     DevBuf<viorb_match> dMatches;
     // pinned staging
     PinBuf<uint8_t> hIn, hDesc;
@@ -386,10 +401,55 @@ int set_size(viorb_extractor* ex, int W, int H) {
     ex->g.outCap = ex->capOut;
     rc = upload_geometry(ex, tabs);
     if (rc) { ex->g.W = ex->g.H = 0; return rc; }
+    return VIORB_OK;
+}
+
+// ---- once per device ----------------------------------------------------------------------------
+// cudaFuncAttributeMaxDynamicSharedMemorySize belongs to (function, device), not to a handle: it is raised to the
+// opt-in maximum once, so handles with different needs (the monocular initialiser with 5 x nFeatures next to the
+// tracking extractor, tracking.cpp:1087-1093) never lower each other's limit.  The kNN split scratch comes from a
+// pool this library owns (the host application's default pool is left alone).
+struct DeviceState {
+    std::once_flag once;
+    cudaError_t err = cudaSuccess;
+    int sms = 148;
+    int maxSmem = 0;
 #ifndef VIORB_EMU
-    CU(cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->fastSmem));
-    CU(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ex->octSmem));
+    cudaMemPool_t pool = nullptr;
 #endif
+};
+DeviceState g_dev[64];
+std::atomic<int> g_forceKnnSplit{0};      // viorb_debug_knn_split
+
+int device_state(int dev, DeviceState** out) {
+    if (dev < 0 || dev >= 64) return fail(VIORB_E_ARG, "device index out of range");
+    DeviceState& d = g_dev[dev];
+    std::call_once(d.once, [&d, dev] {
+#ifndef VIORB_EMU
+        auto ok = [&d](cudaError_t r) { if (d.err == cudaSuccess) d.err = r; };
+        ok(cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev));
+        ok(cudaDeviceGetAttribute(&d.maxSmem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+        ok(cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, d.maxSmem));
+        ok(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, d.maxSmem));
+#if VIORB_KNN_VARIANT == 0
+        ok(cudaFuncSetAttribute(tc5::k_knn2_tc5, cudaFuncAttributeMaxDynamicSharedMemorySize, tc5::SMEM_BYTES));
+#endif
+        cudaMemPoolProps props{};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = dev;
+        ok(cudaMemPoolCreate(&d.pool, &props));
+        if (d.pool) {
+            uint64_t keep = UINT64_MAX;                 // freed scratch rows stay in OUR pool for the next call
+            ok(cudaMemPoolSetAttribute(d.pool, cudaMemPoolAttrReleaseThreshold, &keep));
+        }
+#else
+        (void)dev;
+        d.maxSmem = 227 * 1024;
+#endif
+    });
+    if (d.err != cudaSuccess) return fail(VIORB_E_CUDA, std::string("per-device initialisation: ") + cudaGetErrorString(d.err));
+    *out = &d;
     return VIORB_OK;
 }
 
@@ -458,7 +518,7 @@ int check_status(viorb_extractor* ex) {
 
 int ensure_match_buffers(viorb_extractor* ex) {
     const size_t need = (size_t)ex->prm.max_batch * ex->capOut;
-    if (ex->dBestIdx.n >= need) return VIORB_OK;
+    if (ex->matchReady) return VIORB_OK;
     CU(ex->dBestIdx.alloc(need)); CU(ex->dBestDist.alloc(need)); CU(ex->dSad.alloc(need));
     CU(ex->dURight.alloc(need)); CU(ex->dDepth.alloc(need)); CU(ex->dLrMatch.alloc(need));
     CU(ex->dKnnIdx.alloc(need * 2)); CU(ex->dKnnDist.alloc(need * 2));
@@ -469,6 +529,7 @@ int ensure_match_buffers(viorb_extractor* ex) {
     ex->rowListCap = ex->capOut * span;
     CU(ex->dRowStart.alloc((size_t)ex->prm.max_batch * (ex->prm.max_height + 2)));
     CU(ex->dRowList.alloc((size_t)ex->prm.max_batch * ex->rowListCap));
+    ex->matchReady = true;           // only once EVERY buffer exists: a failed call is retried from the start
     return VIORB_OK;
 }
 
@@ -539,63 +600,52 @@ int release_partner(viorb_extractor* L, viorb_extractor* R) {
 
 }  // namespace
 
-// Brute-force kNN-2 of a batch of descriptor sets.  Default: k_knn2_tc5 (tcgen05.mma kind::i8, accumulators in
-// tensor memory, kernels_knn_tc5.cuh).  VIORB_KNN=mma selects the warp-level IMMA kernel (k_knn2_mma), VIORB_KNN=popc
-// the LOP3/POPC integer-pipe kernel (k_knn2) - all three give identical results, the choice is a measured one
-// (DESIGN.md section 5).
+// Brute-force kNN-2 of a batch of descriptor sets: k_knn2_tc5 (tcgen05.mma kind::i8, accumulators in tensor memory,
+// kernels_knn_tc5.cuh).  The product library holds this one kernel.  The two earlier kernels (warp-level IMMA k_knn2_mma,
+// LOP3/POPC k_knn2; identical results) are BUILD-time variants for experiments
+// (-DVIORB_KNN_VARIANT=1 / 2, tools/variants.sh); the CPU emulation build of the tests uses the IMMA one.
 static int launch_knn2(const DescSet& Q, const DescSet& T, int maxNq, int maxNt, int nSets, int32_t* dIdx, int32_t* dDist,
                        size_t outStride, cudaStream_t st) {
-    static const int mode = [] {
-        const char* e = std::getenv("VIORB_KNN");
-        return !e ? 0 : std::strcmp(e, "popc") == 0 ? 2 : std::strcmp(e, "mma") == 0 ? 1 : 0;
-    }();
-#ifndef VIORB_EMU
-    if (mode == 0) {
-        static int sms[64] = {0};
-        int dev = 0;
-        CU(cudaGetDevice(&dev));
-        if (dev < 64 && sms[dev] == 0) {
-            CU(cudaFuncSetAttribute(tc5::k_knn2_tc5, cudaFuncAttributeMaxDynamicSharedMemorySize, tc5::SMEM_BYTES));
-            // the split path takes its scratch rows from the stream-ordered allocator: keep freed blocks in the pool
-            cudaMemPool_t pool;
-            CU(cudaDeviceGetDefaultMemPool(&pool, dev));
-            uint64_t keep = UINT64_MAX;
-            CU(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
-            CU(cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev));
+#if VIORB_KNN_VARIANT == 0
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    DeviceState* ds = nullptr;
+    if (int rc = device_state(dev, &ds)) return rc;
+    const int qTiles = (maxNq + tc5::QT - 1) / tc5::QT, nBase = qTiles * nSets;
+    if (nBase > 0) {
+        const int nSm = ds->sms;
+        // Few query tiles and a long train set (one stereo pair, the row-sharded sweep) leave SMs idle or a last
+        // wave nearly empty: cut every query tile's train range over nSplit CTAs and merge the partial pairs.
+        // Cost model in train tiles: waves x (tiles per item + ~2 tiles of per-item set-up).
+        const int maxTiles = std::max(1, (maxNt + tc5::TT - 1) / tc5::TT);
+        int nSplit = 1;
+        long best = 0;
+        for (int sp = 1; sp <= std::min(maxTiles, 32); ++sp) {
+            const long cost = (long)((nBase * sp + nSm - 1) / nSm) * ((maxTiles + sp - 1) / sp + 2);
+            if (sp == 1 || cost * 20 < best * 19) { best = cost; nSplit = sp; }      // a split must win by > 5 %
+            if (sp == 1 && cost < 24) break;      // under ~20 us of kernel the merge launch costs more than it saves
         }
-        const int qTiles = (maxNq + tc5::QT - 1) / tc5::QT, nBase = qTiles * nSets;
-        if (nBase > 0) {
-            const int nSm = dev < 64 ? sms[dev] : 148;
-            // Few query tiles and a long train set (one stereo pair, the row-sharded sweep) leave SMs idle or a last
-            // wave nearly empty: cut every query tile's train range over nSplit CTAs and merge the partial pairs.
-            // Cost model in train tiles: waves x (tiles per item + ~2 tiles of per-item set-up).
-            const int maxTiles = std::max(1, (maxNt + tc5::TT - 1) / tc5::TT);
-            int nSplit = 1;
-            long best = 0;
-            for (int sp = 1; sp <= std::min(maxTiles, 32); ++sp) {
-                const long cost = (long)((nBase * sp + nSm - 1) / nSm) * ((maxTiles + sp - 1) / sp + 2);
-                if (sp == 1 || cost * 20 < best * 19) { best = cost; nSplit = sp; }      // a split must win by > 5 %
-                if (sp == 1 && cost < 24) break;      // under ~20 us of kernel the merge launch costs more than it saves
-            }
-            if (const char* e = std::getenv("VIORB_KNN_SPLIT")) nSplit = std::max(1, std::min(std::atoi(e), maxTiles));   // tuning knob
-            const int nItems = nBase * nSplit;
-            uint2* partial = nullptr;
-            if (nSplit > 1) CU(cudaMallocAsync((void**)&partial, (size_t)nItems * tc5::QT * sizeof(uint2), st));
-            VIORB_LAUNCH(tc5::k_knn2_tc5, dim3(std::min(nItems, nSm)), dim3(tc5::THREADS), tc5::SMEM_BYTES, st, Q, T, dIdx, dDist,
-                         outStride, qTiles, nSets, nItems, nSplit, partial);
-            if (nSplit > 1) {
-                VIORB_LAUNCH(tc5::k_knn2_tc5_merge, dim3((qTiles * tc5::QT + 255) / 256, nSets), dim3(256), 0, st, Q, partial, dIdx,
-                             dDist, outStride, qTiles, nSplit);
-                CU(cudaFreeAsync(partial, st));
-            }
+        if (const int forced = g_forceKnnSplit.load()) nSplit = std::max(1, std::min(forced, maxTiles));     // tests only
+        const int nItems = nBase * nSplit;
+        uint2* partial = nullptr;
+        if (nSplit > 1) CU(cudaMallocFromPoolAsync((void**)&partial, (size_t)nItems * tc5::QT * sizeof(uint2), ds->pool, st));
+        VIORB_LAUNCH(tc5::k_knn2_tc5, dim3(std::min(nItems, nSm)), dim3(tc5::THREADS), tc5::SMEM_BYTES, st, Q, T, dIdx, dDist,
+                     outStride, qTiles, nSets, nItems, nSplit, partial);
+        if (nSplit > 1) {
+            VIORB_LAUNCH(tc5::k_knn2_tc5_merge, dim3((qTiles * tc5::QT + 255) / 256, nSets), dim3(256), 0, st, Q, partial, dIdx,
+                         dDist, outStride, qTiles, nSplit);
+            CU(cudaFreeAsync(partial, st));
         }
-        CU(cudaGetLastError());
-        return VIORB_OK;
     }
-#endif
+#else
     const dim3 grid((maxNq + VIORB_KNN_THREADS - 1) / VIORB_KNN_THREADS, nSets), block(VIORB_KNN_THREADS);
-    if (mode == 2) VIORB_LAUNCH(k_knn2, grid, block, 0, st, Q, T, dIdx, dDist, outStride);
-    else VIORB_LAUNCH(k_knn2_mma, grid, block, 0, st, Q, T, dIdx, dDist, outStride);
+    (void)maxNt;
+#if VIORB_KNN_VARIANT == 2
+    VIORB_LAUNCH(k_knn2, grid, block, 0, st, Q, T, dIdx, dDist, outStride);
+#else
+    VIORB_LAUNCH(k_knn2_mma, grid, block, 0, st, Q, T, dIdx, dDist, outStride);
+#endif
+#endif
     CU(cudaGetLastError());
     return VIORB_OK;
 }
@@ -606,6 +656,7 @@ static int launch_knn2(const DescSet& Q, const DescSet& T, int maxNq, int maxNt,
 extern "C" {
 
 const char* viorb_last_error(void) { return g_err.c_str(); }
+void viorb_debug_knn_split(int n_split) { g_forceKnnSplit.store(n_split < 0 ? 0 : n_split); }
 const char* viorb_version(void) {
 #ifdef VIORB_EMU
     return "viorb 0.1 (cpu emulation build: tests only)";
@@ -625,6 +676,8 @@ int viorb_extractor_create(const viorb_params* params, viorb_extractor** out) {
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= p.device)
         return fail(VIORB_E_NO_DEVICE, "no CUDA device: libviorb has no CPU path");
     CU(cudaSetDevice(p.device));
+    DeviceState* ds = nullptr;
+    if (int rc = device_state(p.device, &ds)) return rc;
     viorb_extractor* ex = new viorb_extractor();
     ex->prm = p;
     std::memset(&ex->g, 0, sizeof(ex->g));
