@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--distinct", type=int, default=8, help="distinct synthetic stereo pairs generated (tiled to --pairs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-knn-sweep", action="store_true", help="skip the row-sharded kNN sweep leg (BASELINE configs[4])")
     ap.add_argument("--no-bind", action="store_true", help="multi-rank runs: do not bind the rank to its GPU's local CPUs")
     ap.add_argument("--variant-lib", default=None, help="experimental build of libviorb.so to measure instead of the product one")
     ap.add_argument("--e2e-workers", type=int, default=3, help="pipeline workers (handle pairs in flight) of the end-to-end leg")
@@ -175,6 +176,53 @@ def run_reference(args, rank):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
+
+
+def knn_sweep(world, rank, dist, sizes=(32768, 200000)):
+    """BASELINE.json configs[4]: brute-force Hamming kNN-2, N x N 256-bit descriptors, query rows sharded over the ranks
+    through the C entry point viorb_knn2_sharded (train set replicated, the kernel writes packed 16-byte rows into its
+    block, ONE in-place NCCL all-gather).  Device time with CUDA events (max over ranks), gather included.  `match`:
+    256 sampled rows of the gathered result equal the single-GPU kernel's rows computed on rank 0."""
+    import ctypes as C
+    import torch
+    from vi_slam_b200 import _lib, sharded, synthetic
+    from vi_slam_b200.extractor import _check
+    lib = _lib.load()
+    m = sharded.ShardedMatcher()
+    out = []
+    for n in sizes:
+        q, t = synthetic.make_descriptors(n, n, seed=n)
+        a, b, per = m.rows(n)
+        dq, dt = torch.from_numpy(q[a:b]).cuda(), torch.from_numpy(t).cuda()
+        res = m.match_device(dq, n, dt)                                    # warm-up (also sizes the scratch pool)
+        torch.cuda.synchronize()
+        reps = 5
+        if dist is not None:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            res = m.match_device(dq, n, dt, out=res)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        if dist is not None:
+            tt = torch.tensor([ms], device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms = float(tt.item())
+        ok = None
+        if rank == 0:
+            full = res.cpu().numpy()
+            rows = np.unique(np.concatenate([np.random.default_rng(n).integers(0, n, 250), [0, per - 1, min(per, n - 1), n - 2, n - 1]]))
+            sq = torch.from_numpy(q[rows]).cuda()
+            one = torch.empty((len(rows), 4), dtype=torch.int32, device="cuda")
+            _check(lib, lib.viorb_knn2_packed_device(sq.data_ptr(), len(rows), dt.data_ptr(), n, one.data_ptr(), None))
+            torch.cuda.synchronize()
+            ok = bool(np.array_equal(full[rows], one.cpu().numpy()) and (full[n:] == -1).all())
+        out.append({"workload": f"hamming_knn2_{n}x{n}", "ms": ms, "pairs_per_s": n * n / (ms * 1e-3), "queries_per_s": n / (ms * 1e-3),
+                    "gather_bytes_per_rank": per * 16 if world > 1 else 0, "match": ok, "rows_checked": 255})
+    m.close()
+    return out
 
 
 def run_ours(args, rank, world, local_rank):
@@ -323,6 +371,8 @@ def run_ours(args, rank, world, local_rank):
         e2e = {"value": world * B * Ke / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                "ms_per_step": 1e3 * dt / Ke, "workers": NWORK, "steps": Ke}
 
+    sweep = None if args.no_knn_sweep else knn_sweep(world, rank, dist)
+
     if rank != 0:
         return
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -390,6 +440,8 @@ def run_ours(args, rank, world, local_rank):
         "stages_ms_per_step": mean,
         "stage_timing": "second pass of K steps, both handles on one stream, CUDA events around each stage", "roofline": roofline,
         "match_roofline": match_roofline,
+        **({"knn_sweep": {"transport": "viorb_knn2_sharded: in-place ncclAllGather of 16 B rows" if world > 1 else "single GPU, no exchange",
+                          "n_gpus": world, "sizes": sweep}} if sweep is not None else {}),
     }
     if world == 1 and not args.no_cpu_baseline:
         cores = host_threads()

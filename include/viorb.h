@@ -147,6 +147,36 @@ int viorb_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
 int viorb_knn2_device(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int32_t* d_idx, int32_t* d_dist,
                       void* stream);
 
+/* Same, one 16-byte row (idx0, idx1, dist0, dist1) per query at d_rows[nq][4]: the row format of the sharded matcher. */
+int viorb_knn2_packed_device(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int32_t* d_rows, void* stream);
+
+/* ---- row-sharded brute-force matcher over the GPUs of one box (BASELINE.json configs[4]) -------------
+ * The reference has no multi-GPU path; this is the partitioning north_star asks for: query rows in contiguous blocks of
+ * rows_per_rank = ceil(nq_total / world), train set replicated, one all-gather of 16-byte result rows.
+ * A viorb_comm is one rank's end of the exchange:
+ *   - viorb_comm_create_nccl: rank 0 calls viorb_comm_unique_id, the host distributes the 128 bytes by its own means,
+ *     every rank then creates the communicator (ncclCommInitRank; collective).  libnccl.so.2 is resolved at run time.
+ *   - viorb_comm_adopt_nccl: wrap an ncclComm_t the host application already owns (not destroyed with the viorb_comm).
+ *   - viorb_comm_create_callback: the host supplies the in-place all-gather itself (d_buf holds world blocks of
+ *     bytes_per_rank; block `rank` is filled; must be stream-ordered or complete on return; 0 = success). */
+typedef struct viorb_comm viorb_comm;
+typedef int (*viorb_allgather_fn)(void* user, void* d_buf, size_t bytes_per_rank, int rank, int world, void* stream);
+int viorb_comm_unique_id(uint8_t id[128]);
+int viorb_comm_create_nccl(const uint8_t id[128], int rank, int world, int device, viorb_comm** out);
+int viorb_comm_adopt_nccl(void* nccl_comm, int rank, int world, int device, viorb_comm** out);
+int viorb_comm_create_callback(viorb_allgather_fn fn, void* user, int rank, int world, int device, viorb_comm** out);
+void viorb_comm_destroy(viorb_comm* comm);
+int viorb_comm_rank(const viorb_comm* comm);
+int viorb_comm_world(const viorb_comm* comm);
+/* The partition every rank must use: rank owns query rows [row0, row0 + rows); rows_per_rank = block size of the result. */
+void viorb_shard_rows(int nq_total, int world, int rank, int* row0, int* rows, int* rows_per_rank);
+/* cv::BFMatcher(NORM_HAMMING).knnMatch(q, t, 2) (frame.cpp:1167) with q sharded by rows.  d_q_local: THIS rank's
+ * `rows` query rows; d_t: all nt train rows; d_out: int32[world * rows_per_rank][4] on the device, complete on every
+ * rank when the stream reaches the end of the call; row r of the full query set is d_out[r] (rows past nq_total: -1).
+ * Collective: every rank of the communicator must call it with the same nq_total / nt. */
+int viorb_knn2_sharded(viorb_comm* comm, const uint8_t* d_q_local, int nq_total, const uint8_t* d_t, int nt,
+                       int32_t* d_out, void* stream);
+
 /* kNN-2 followed by the ratio test, accepted matches in query order.
  * rule 0: frame.cpp:1170   d0 < d1 * ratio (float * double; ratio 0.7 there);
  * rule 1: fmatcher.cpp:220-223 (matchFeatures method 2) (double)d0 < ratio * d1, then with

@@ -19,6 +19,7 @@ class ViorbVocabDesc(C.Structure):
                 ("word_id", C.c_void_p)]
 
 
+ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p)
 u8p = C.POINTER(C.c_uint8)
 i32p = C.POINTER(C.c_int32)
 f32p = C.POINTER(C.c_float)
@@ -62,6 +63,16 @@ SYMBOLS = {
     "viorb_descriptor_distance": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, i32p, C.c_int]),
     "viorb_knn2": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, i32p, i32p, C.c_int]),
     "viorb_knn2_device": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "viorb_knn2_packed_device": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "viorb_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "viorb_comm_create_nccl": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    "viorb_comm_adopt_nccl": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    "viorb_comm_create_callback": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    "viorb_comm_destroy": (None, [C.c_void_p]),
+    "viorb_comm_rank": (C.c_int, [C.c_void_p]),
+    "viorb_comm_world": (C.c_int, [C.c_void_p]),
+    "viorb_shard_rows": (None, [C.c_int, C.c_int, C.c_int, i32p, i32p, i32p]),
+    "viorb_knn2_sharded": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "viorb_match_ratio": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_int,
                                     C.c_void_p, C.c_int, i32p, C.c_int]),
     "viorb_stereo_match": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, f32p, f32p, i32p, i32p,

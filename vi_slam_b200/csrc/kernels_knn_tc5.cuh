@@ -156,9 +156,8 @@ __device__ __forceinline__ void write_knn_row(int32_t* __restrict__ idx, int32_t
                                               unsigned gb1, int pq) {
     const unsigned mask = (1u << VIORB_KNN_IDX_BITS) - 1;
     const bool h0 = gb0 != 0xFFFFFFFFu, h1 = gb1 != 0xFFFFFFFFu;
-    *reinterpret_cast<int2*>(idx + rowIdx * 2) = make_int2(h0 ? (int)(gb0 & mask) : -1, h1 ? (int)(gb1 & mask) : -1);
-    *reinterpret_cast<int2*>(dist + rowIdx * 2) = make_int2(h0 ? (int)(gb0 >> VIORB_KNN_IDX_BITS) - pq : -1,
-                                                            h1 ? (int)(gb1 >> VIORB_KNN_IDX_BITS) - pq : -1);
+    store_knn_row(idx, dist, rowIdx, h0 ? (int)(gb0 & mask) : -1, h1 ? (int)(gb1 & mask) : -1,
+                  h0 ? (int)(gb0 >> VIORB_KNN_IDX_BITS) - pq : -1, h1 ? (int)(gb1 >> VIORB_KNN_IDX_BITS) - pq : -1);
 }
 
 // Merge of the per-split partial pairs when a query tile's train range was cut over several CTAs (few query tiles,

@@ -25,6 +25,19 @@ struct DescSet {
 };
 __device__ __forceinline__ int descset_count(const DescSet& s, int p) { return s.n ? s.n[p] : s.nFixed; }
 
+// One result row of the kNN-2 kernels.  dist != NULL: idx[row][2] and dist[row][2] (cv::DMatch-like pairs).
+// dist == NULL: ONE 16-byte row (idx0, idx1, dist0, dist1) at idx[row][4] - the row format the row-sharded matcher
+// all-gathers (viorb_knn2_sharded), written by the kernel itself so that no packing pass sits before the exchange.
+__device__ __forceinline__ void store_knn_row(int32_t* __restrict__ idx, int32_t* __restrict__ dist, size_t row, int i0, int i1,
+                                              int d0, int d1) {
+    if (dist) {
+        *reinterpret_cast<int2*>(idx + row * 2) = make_int2(i0, i1);
+        *reinterpret_cast<int2*>(dist + row * 2) = make_int2(d0, d1);
+    } else {
+        *reinterpret_cast<int4*>(idx + row * 4) = make_int4(i0, i1, d0, d1);
+    }
+}
+
 __device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) {
     return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
            __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
@@ -87,12 +100,9 @@ __global__ void __launch_bounds__(VIORB_KNN_THREADS) k_knn2(DescSet Q, DescSet T
     }
     if (valid) {
         const unsigned mask = (1u << VIORB_KNN_IDX_BITS) - 1;
-        int32_t* oi = idx + (size_t)p * outStride * 2 + (size_t)qi * 2;
-        int32_t* od = dist + (size_t)p * outStride * 2 + (size_t)qi * 2;
-        oi[0] = best0 == 0xFFFFFFFFu ? -1 : (int)(best0 & mask);
-        od[0] = best0 == 0xFFFFFFFFu ? -1 : (int)(best0 >> VIORB_KNN_IDX_BITS);
-        oi[1] = best1 == 0xFFFFFFFFu ? -1 : (int)(best1 & mask);
-        od[1] = best1 == 0xFFFFFFFFu ? -1 : (int)(best1 >> VIORB_KNN_IDX_BITS);
+        store_knn_row(idx, dist, (size_t)p * outStride + qi, best0 == 0xFFFFFFFFu ? -1 : (int)(best0 & mask),
+                      best1 == 0xFFFFFFFFu ? -1 : (int)(best1 & mask), best0 == 0xFFFFFFFFu ? -1 : (int)(best0 >> VIORB_KNN_IDX_BITS),
+                      best1 == 0xFFFFFFFFu ? -1 : (int)(best1 >> VIORB_KNN_IDX_BITS));
     }
 }
 
@@ -225,14 +235,10 @@ __global__ void __launch_bounds__(VIORB_KNN_THREADS) k_knn2_mma(DescSet Q, DescS
             const int qi = q0 + 32 * warp + 16 * a + g + 8 * h;
             if (t == 0 && qi < nq) {
                 const int mask = (1 << VIORB_KNN_IDX_BITS) - 1;
-                int32_t* oi = idx + (size_t)p * outStride * 2 + (size_t)qi * 2;
-                int32_t* od = dist + (size_t)p * outStride * 2 + (size_t)qi * 2;
                 const bool h0 = b0 < VIORB_KNN_NONE, h1 = b1 < VIORB_KNN_NONE;
                 const int f0 = b0 + pqk[a][h], f1 = b1 + pqk[a][h];
-                oi[0] = h0 ? (f0 & mask) : -1;
-                od[0] = h0 ? (f0 >> VIORB_KNN_IDX_BITS) : -1;
-                oi[1] = h1 ? (f1 & mask) : -1;
-                od[1] = h1 ? (f1 >> VIORB_KNN_IDX_BITS) : -1;
+                store_knn_row(idx, dist, (size_t)p * outStride + qi, h0 ? (f0 & mask) : -1, h1 ? (f1 & mask) : -1,
+                              h0 ? (f0 >> VIORB_KNN_IDX_BITS) : -1, h1 ? (f1 >> VIORB_KNN_IDX_BITS) : -1);
             }
         }
 }

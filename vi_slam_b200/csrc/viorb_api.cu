@@ -1920,4 +1920,6 @@ int viorb_fisheye_stereo_matches(const viorb_kb8_rig* rig, const viorb_keypoint*
     return rc;
 }
 
+#include "host_sharded.inc"
+
 }  // extern "C"
