@@ -210,7 +210,7 @@ def knn_sweep(world, rank, dist, sizes=(32768, 200000)):
             tt = torch.tensor([ms], device="cuda")
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             ms = float(tt.item())
-        ok = None
+        ok, nrows = None, 0
         if rank == 0:
             full = res.cpu().numpy()
             rows = np.unique(np.concatenate([np.random.default_rng(n).integers(0, n, 250), [0, per - 1, min(per, n - 1), n - 2, n - 1]]))
@@ -219,8 +219,9 @@ def knn_sweep(world, rank, dist, sizes=(32768, 200000)):
             _check(lib, lib.viorb_knn2_packed_device(sq.data_ptr(), len(rows), dt.data_ptr(), n, one.data_ptr(), None))
             torch.cuda.synchronize()
             ok = bool(np.array_equal(full[rows], one.cpu().numpy()) and (full[n:] == -1).all())
+            nrows = int(len(rows))
         out.append({"workload": f"hamming_knn2_{n}x{n}", "ms": ms, "pairs_per_s": n * n / (ms * 1e-3), "queries_per_s": n / (ms * 1e-3),
-                    "gather_bytes_per_rank": per * 16 if world > 1 else 0, "match": ok, "rows_checked": 255})
+                    "gather_bytes_per_rank": per * 16 if world > 1 else 0, "match": ok, "rows_checked": nrows})
     m.close()
     return out
 

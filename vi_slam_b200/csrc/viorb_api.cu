@@ -429,8 +429,14 @@ int device_state(int dev, DeviceState** out) {
         auto ok = [&d](cudaError_t r) { if (d.err == cudaSuccess) d.err = r; };
         ok(cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev));
         ok(cudaDeviceGetAttribute(&d.maxSmem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-        ok(cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, d.maxSmem));
-        ok(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, d.maxSmem));
+        // dynamic limit = opt-in maximum minus the kernel's static shared memory
+        auto raise = [&](const void* fn) {
+            cudaFuncAttributes fa{};
+            ok(cudaFuncGetAttributes(&fa, fn));
+            ok(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, d.maxSmem - (int)fa.sharedSizeBytes));
+        };
+        raise((const void*)k_fast);
+        raise((const void*)k_octree);
 #if VIORB_KNN_VARIANT == 0
         ok(cudaFuncSetAttribute(tc5::k_knn2_tc5, cudaFuncAttributeMaxDynamicSharedMemorySize, tc5::SMEM_BYTES));
 #endif
