@@ -244,6 +244,20 @@ int viorb_search_by_projection(int npairs, int cap1, int cap2, const float* uv, 
                                const float* scale_factors, int nlevels, float th, float bf, int direction,
                                int check_orientation, int32_t* assigned, int32_t* nmatches, int device);
 
+/* Frame-to-frame matching between CONSECUTIVE resident frames of the extractor's last batch (the monocular path,
+ * BASELINE.json configs[0]): for p in [0, n - 1), F1 = frame p, F2 = frame p + 1:
+ *   FMatcher::SearchForInitialization(F1, F2, vbPrevMatched = F1 keypoint positions (src/core/tracking.cpp:2286-2288),
+ *   vnMatches12, window_size) (fmatcher.cpp:983-1098), and brute-force kNN-2 + ratio test F1 -> F2 (rule as in
+ *   viorb_match_ratio; matchFeatures method 2, fmatcher.cpp:204-229).  bounds: the frames' grid (NULL = (0, W, 0, H),
+ *   ComputeImageBounds without distortion).  Asynchronous on the handle's stream; results stay on the device. */
+int viorb_f2f_batch(viorb_extractor* ex, int n, const viorb_grid_bounds* bounds, int window_size, float nn_ratio,
+                    int check_orientation, double ratio, int rule);
+/* Read-back: matches12 [npairs][cap] = vnMatches12, nmatches[p] = SearchForInitialization's return value, knn_match
+ * [npairs][cap] = accepted train index per F1 keypoint or -1, n_ratio[p] = accepted count.  cap >= viorb_extractor_capacity().
+ * VIORB_E_CAPACITY if a pair's candidate lists exceeded the handle's budget (that pair reports no window matches). */
+int viorb_f2f_fetch_all(viorb_extractor* ex, int npairs, int32_t* matches12, int32_t* nmatches, int32_t* knn_match,
+                        int32_t* n_ratio, int cap);
+
 /* ---- keypoint undistortion: SURVEY.md section 8 row f-2 ----------------------------------------- */
 
 /* Camera of Frame::UndistortKeyPoints / ComputeImageBounds (src/datastructures/frame.cpp:758-791, 793-821):

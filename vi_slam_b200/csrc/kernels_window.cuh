@@ -35,6 +35,7 @@ struct WinBatch {
     int cap1, cap2;
     const int* n1;
     const int* n2;
+    const int* n1fill;      // optional: source count of the fill pass (0 for a pair whose list did not fit the budget)
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -87,12 +88,15 @@ __global__ void __launch_bounds__(256) k_grid_build(WinBatch wb, GridBounds gb, 
 
 // SearchForInitialization: level-0 keypoints of F1 search a square of half size windowSize around
 // vbPrevMatched[i1], level 0 only (fmatcher.cpp:997-1003).  grid (ceil(cap1/256), nPairs).
-__global__ void k_window_src_ini(WinBatch wb, const viorb_keypoint* __restrict__ kps1, const float* __restrict__ prevMatched,
-                                 float windowSize, WinSrc* __restrict__ src) {
+// initPrev != 0: vbPrevMatched starts as F1's own keypoint positions, as Tracking::MonocularInitialization sets it
+// (src/core/tracking.cpp:2286-2288), and is written to prevMatched first.
+__global__ void k_window_src_ini(WinBatch wb, const viorb_keypoint* __restrict__ kps1, float* __restrict__ prevMatched,
+                                 float windowSize, WinSrc* __restrict__ src, int initPrev) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x, p = blockIdx.y;
     if (i >= wb.n1[p]) return;
     const size_t o = (size_t)p * wb.cap1 + i;
     WinSrc s;
+    if (initPrev) { prevMatched[2 * o] = kps1[o].x; prevMatched[2 * o + 1] = kps1[o].y; }
     s.x = prevMatched[2 * o];
     s.y = prevMatched[2 * o + 1];
     s.r = kps1[o].octave > 0 ? -1.f : windowSize;
@@ -141,7 +145,7 @@ __global__ void __launch_bounds__(256) k_window_list(WinBatch wb, GridBounds gb,
                                                      int* __restrict__ listStart, uint32_t* __restrict__ list, int fill) {
     const int lane = threadIdx.x & 31, p = blockIdx.y;
     const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (i >= wb.n1[p]) return;
+    if (i >= (fill && wb.n1fill ? wb.n1fill[p] : wb.n1[p])) return;
     const size_t o = (size_t)p * wb.cap1 + i;
     const WinSrc s = src[o];
     int total = 0;
@@ -206,6 +210,18 @@ __global__ void __launch_bounds__(256) k_window_scan(WinBatch wb, int* __restric
     const int n1 = wb.n1[p];
     const int total = block_excl_scan(LS, n1, warpSums);
     if (threadIdx.x == 0) { LS[n1] = total; totals[p] = total; }
+}
+// Device-side replacement of the host prefix sum over pairs (resident, asynchronous callers): list offsets of the
+// pairs and the budget check.  A pair whose list does not fit gets n1eff = 0 (it produces no matches) and status bit 4.
+// grid 1, block 1.
+__global__ void k_window_pairbase(int npairs, const int* __restrict__ n1, const int* __restrict__ totals, int* __restrict__ pairBase,
+                                  int* __restrict__ n1eff, size_t listCap, int* __restrict__ status) {
+    size_t sum = 0;
+    for (int p = 0; p < npairs; ++p) {
+        pairBase[p] = (int)sum;
+        if (sum + (size_t)totals[p] > listCap) { n1eff[p] = 0; atomicOr(status, 4); }
+        else { n1eff[p] = n1[p]; sum += (size_t)totals[p]; }
+    }
 }
 __global__ void k_window_rebase(WinBatch wb, int* __restrict__ listStart, const int* __restrict__ pairBase) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x, p = blockIdx.y;

@@ -111,8 +111,28 @@ struct viorb_vocabulary {
     DevBuf<double> weight;
 };
 
+// buffers of viorb_f2f_batch (host_f2f.inc)
+struct viorb_f2f_state {
+    DevBuf<int> cellStart, cellList, listStart, totals, pairBase, n1eff, matchedDist, m21, nMatches;
+    DevBuf<uint32_t> list;
+    DevBuf<WinSrc> src;
+    DevBuf<float> prevMatched;
+    DevBuf<int8_t> binOf;
+    DevBuf<int32_t> matches12;
+    size_t listCap = 0;
+    bool ready = false;
+    int lastPairs = 0;
+    void release() {
+        cellStart.release(); cellList.release(); listStart.release(); totals.release(); pairBase.release(); n1eff.release();
+        matchedDist.release(); m21.release(); nMatches.release(); list.release(); src.release(); prevMatched.release();
+        binOf.release(); matches12.release();
+        ready = false;
+    }
+};
+
 struct viorb_extractor {
     viorb_params prm;
+    viorb_f2f_state* f2f = nullptr;   // buffers of viorb_f2f_batch (host_f2f.inc), created on first use
     // FExtractor ctor tables (fextractor.cpp:401-461)
     float scale[VIORB_MAX_LEVELS], invScale[VIORB_MAX_LEVELS], sigma2[VIORB_MAX_LEVELS], invSigma2[VIORB_MAX_LEVELS];
     int featPerLevel[VIORB_MAX_LEVELS];
@@ -132,7 +152,7 @@ struct viorb_extractor {
     // host-batch pipelining (viorb_extract_batch): images go up on cpStream and results come down on outStream
     // chunk by chunk while the kernels of the neighbouring chunks run on `stream`
     cudaStream_t cpStream = nullptr, outStream = nullptr;
-    cudaEvent_t evIn[VIORB_MAX_CHUNKS] = {}, evDone[VIORB_MAX_CHUNKS] = {}, evEntry = nullptr;
+    cudaEvent_t evIn[VIORB_MAX_CHUNKS] = {}, evDone[VIORB_MAX_CHUNKS] = {}, evCnt[VIORB_MAX_CHUNKS] = {}, evEntry = nullptr;
     cudaEvent_t evJoin = nullptr;     // orders this handle's stream against a partner handle's (stereo)
     cudaEvent_t evBlock = nullptr;    // blocking-sync event: batch calls sleep on it instead of spinning in the driver
     DevBuf<uint8_t> dIn, dPyr, dBlur, dDesc;
@@ -168,6 +188,7 @@ struct viorb_extractor {
     // last run
     FrameSrc src{};
     int lastN = 0;
+    int lastMaxCount = 0;             // largest keypoint count of the last host-batch extraction (0 = not known on the host)
     int inPitch = 0;
 };
 
@@ -734,6 +755,7 @@ int viorb_extractor_create(const viorb_params* params, viorb_extractor** out) {
     for (int i = 0; i < VIORB_MAX_CHUNKS; ++i) {
         ok(cudaEventCreateWithFlags(&ex->evIn[i], cudaEventDisableTiming));
         ok(cudaEventCreateWithFlags(&ex->evDone[i], cudaEventDisableTiming));
+        ok(cudaEventCreateWithFlags(&ex->evCnt[i], cudaEventDisableTiming | cudaEventBlockingSync));
     }
     ok(cudaEventCreateWithFlags(&ex->evEntry, cudaEventDisableTiming));
     ok(cudaEventCreateWithFlags(&ex->evJoin, cudaEventDisableTiming));
@@ -764,11 +786,13 @@ void viorb_extractor_destroy(viorb_extractor* ex) {
     ex->dLrMatch.release(); ex->dURight.release(); ex->dDepth.release(); ex->dNStereo.release(); ex->dNRatio.release();
     ex->dMatches.release(); ex->dRowStart.release(); ex->dRowList.release();
     ex->hIn.release(); ex->hDesc.release(); ex->hKps.release(); ex->hCounts.release();
+    if (ex->f2f) { ex->f2f->release(); delete ex->f2f; }
     for (int i = 0; i < 8; ++i) if (ex->evX[i]) cudaEventDestroy(ex->evX[i]);
     for (int i = 0; i < 6; ++i) if (ex->evS[i]) cudaEventDestroy(ex->evS[i]);
     for (int i = 0; i < VIORB_MAX_CHUNKS; ++i) {
         if (ex->evIn[i]) cudaEventDestroy(ex->evIn[i]);
         if (ex->evDone[i]) cudaEventDestroy(ex->evDone[i]);
+        if (ex->evCnt[i]) cudaEventDestroy(ex->evCnt[i]);
     }
     if (ex->evEntry) cudaEventDestroy(ex->evEntry);
     if (ex->evJoin) cudaEventDestroy(ex->evJoin);
@@ -867,6 +891,7 @@ int viorb_extract_device(viorb_extractor* ex, const uint8_t* d_imgs, int n, int 
     ex->src.l0Stride = frame_stride;
     ex->src.pyr = ex->dPyr.p;
     ex->src.blur = ex->dBlur.p;
+    ex->lastMaxCount = 0;            // counts stay on the device
     return run_pipeline(ex, 0, n, lap0, lap1);
 }
 
@@ -942,30 +967,43 @@ int viorb_extract_batch(viorb_extractor* ex, const uint8_t* const* imgs, int n, 
         if (rc) return rc;
         CU(cudaEventRecord(ex->evDone[c], ex->stream));
         CU(cudaStreamWaitEvent(ex->outStream, ex->evDone[c], 0));
-        cudaStream_t os = ex->outStream;
-        if (pinnedKps && (size_t)cap == oc)
-            CU(cudaMemcpyAsync(kps + (size_t)f0 * cap, ex->dKps.p + f0 * oc, sizeof(viorb_keypoint) * oc * m, cudaMemcpyDeviceToHost, os));
-        else if (pinnedKps)
-            CU(cudaMemcpy2DAsync(kps + (size_t)f0 * cap, sizeof(viorb_keypoint) * cap, ex->dKps.p + f0 * oc, sizeof(viorb_keypoint) * oc,
-                                 sizeof(viorb_keypoint) * rowKp, m, cudaMemcpyDeviceToHost, os));
-        else if (kps)
-            CU(cudaMemcpyAsync(ex->hKps.p + f0 * oc, ex->dKps.p + f0 * oc, sizeof(viorb_keypoint) * oc * m, cudaMemcpyDeviceToHost, os));
-        if (pinnedDesc && (size_t)cap == oc)
-            CU(cudaMemcpyAsync(desc + (size_t)f0 * cap * 32, ex->dDesc.p + f0 * oc * 32, 32 * oc * m, cudaMemcpyDeviceToHost, os));
-        else if (pinnedDesc)
-            CU(cudaMemcpy2DAsync(desc + (size_t)f0 * cap * 32, (size_t)32 * cap, ex->dDesc.p + f0 * oc * 32, 32 * oc, 32 * rowKp, m,
-                                 cudaMemcpyDeviceToHost, os));
-        else if (desc)
-            CU(cudaMemcpyAsync(ex->hDesc.p + f0 * oc * 32, ex->dDesc.p + f0 * oc * 32, 32 * oc * m, cudaMemcpyDeviceToHost, os));
+        // the chunk's counts come down first: the result copies below move only the rows that exist
+        CU(cudaMemcpyAsync(ex->hCounts.p + f0, ex->dNOut.p + f0, sizeof(int) * m, cudaMemcpyDeviceToHost, ex->outStream));
+        CU(cudaMemcpyAsync(ex->hCounts.p + n + f0, ex->dMono.p + f0, sizeof(int) * m, cudaMemcpyDeviceToHost, ex->outStream));
+        CU(cudaEventRecord(ex->evCnt[c], ex->outStream));
     }
-    CU(cudaMemcpyAsync(ex->hCounts.p, ex->dNOut.p, sizeof(int) * n, cudaMemcpyDeviceToHost, ex->outStream));
-    CU(cudaMemcpyAsync(ex->hCounts.p + n, ex->dMono.p, sizeof(int) * n, cudaMemcpyDeviceToHost, ex->outStream));
+    // Device -> host of the results, chunk by chunk as the counts arrive (every chunk's uploads and kernels are already
+    // queued, so the device stays busy while the host waits here).  Rows past the largest count of a chunk are never
+    // copied: the arenas hold viorb_extractor_capacity() slots per frame, a frame fills nfeatures .. nfeatures + ~30.
+    for (int c = 0; c < nChunks; ++c) {
+        const int f0 = c * per, m = std::min(per, n - f0);
+        if (n >= VIORB_BLOCKING_BATCH) CU(cudaEventSynchronize(ex->evCnt[c]));
+        else { cudaError_t q; while ((q = cudaEventQuery(ex->evCnt[c])) == cudaErrorNotReady) {} CU(q); }
+        int maxCnt = 0;
+        for (int i = f0; i < f0 + m; ++i) maxCnt = std::max(maxCnt, ex->hCounts.p[i]);
+        const size_t rows = std::min<size_t>(std::min<size_t>((size_t)maxCnt, oc), rowKp);
+        if (rows == 0) continue;
+        cudaStream_t os = ex->outStream;
+        if (kps) {
+            viorb_keypoint* dst = pinnedKps ? kps + (size_t)f0 * cap : ex->hKps.p + f0 * oc;
+            const size_t dpitch = sizeof(viorb_keypoint) * (pinnedKps ? (size_t)cap : oc);
+            CU(cudaMemcpy2DAsync(dst, dpitch, ex->dKps.p + f0 * oc, sizeof(viorb_keypoint) * oc, sizeof(viorb_keypoint) * rows, m,
+                                 cudaMemcpyDeviceToHost, os));
+        }
+        if (desc) {
+            uint8_t* dst = pinnedDesc ? desc + (size_t)f0 * cap * 32 : ex->hDesc.p + f0 * oc * 32;
+            const size_t dpitch = 32 * (pinnedDesc ? (size_t)cap : oc);
+            CU(cudaMemcpy2DAsync(dst, dpitch, ex->dDesc.p + f0 * oc * 32, 32 * oc, 32 * rows, m, cudaMemcpyDeviceToHost, os));
+        }
+    }
     CU(wait_stream(ex, ex->outStream));
     rc = check_status(ex);          // synchronises the handle's stream
     if (rc) return rc;
     int worst = VIORB_OK;
+    ex->lastMaxCount = 0;
     for (int i = 0; i < n; ++i) {
         const int cnt = ex->hCounts.p[i];
+        ex->lastMaxCount = std::max(ex->lastMaxCount, cnt);
         if (n_out) n_out[i] = cnt;
         if (mono_index_out) mono_index_out[i] = ex->hCounts.p[n + i];
         const int m = std::min(cnt, cap);
@@ -1297,9 +1335,11 @@ int viorb_stereo_fetch_all(viorb_extractor* L, int n, float* u_right, float* dep
     if (n_left) CU(cudaMemcpyAsync(n_left, L->dNOut.p, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
     if (n_stereo) CU(cudaMemcpyAsync(n_stereo, L->dNStereo.p, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
     if (n_ratio) CU(cudaMemcpyAsync(n_ratio, L->dNRatio.p, sizeof(int) * n, cudaMemcpyDeviceToHost, st));
-    if (u_right) CU(cudaMemcpy2DAsync(u_right, sizeof(float) * cap, L->dURight.p, sizeof(float) * oc, sizeof(float) * oc, n, cudaMemcpyDeviceToHost, st));
-    if (depth) CU(cudaMemcpy2DAsync(depth, sizeof(float) * cap, L->dDepth.p, sizeof(float) * oc, sizeof(float) * oc, n, cudaMemcpyDeviceToHost, st));
-    if (lr_match) CU(cudaMemcpy2DAsync(lr_match, sizeof(int32_t) * cap, L->dLrMatch.p, sizeof(int32_t) * oc, sizeof(int32_t) * oc, n, cudaMemcpyDeviceToHost, st));
+    // rows past the largest keypoint count of the batch do not exist: copy them only when the count is not known here
+    const size_t rows = L->lastMaxCount > 0 ? std::min<size_t>((size_t)L->lastMaxCount, oc) : oc;
+    if (u_right) CU(cudaMemcpy2DAsync(u_right, sizeof(float) * cap, L->dURight.p, sizeof(float) * oc, sizeof(float) * rows, n, cudaMemcpyDeviceToHost, st));
+    if (depth) CU(cudaMemcpy2DAsync(depth, sizeof(float) * cap, L->dDepth.p, sizeof(float) * oc, sizeof(float) * rows, n, cudaMemcpyDeviceToHost, st));
+    if (lr_match) CU(cudaMemcpy2DAsync(lr_match, sizeof(int32_t) * cap, L->dLrMatch.p, sizeof(int32_t) * oc, sizeof(int32_t) * rows, n, cudaMemcpyDeviceToHost, st));
     CU(wait_stream(L, st));
     return VIORB_OK;
 }
@@ -1373,7 +1413,7 @@ int window_lists(WindowWork& w, int npairs, int cap1, int cap2, const int32_t* n
                  const float* dURight2) {
     CU(upload(w.n1, n1, npairs));
     CU(upload(w.n2, n2, npairs));
-    w.wb.cap1 = cap1; w.wb.cap2 = cap2; w.wb.n1 = w.n1.p; w.wb.n2 = w.n2.p;
+    w.wb.cap1 = cap1; w.wb.cap2 = cap2; w.wb.n1 = w.n1.p; w.wb.n2 = w.n2.p; w.wb.n1fill = nullptr;
     CU(w.cellStart.alloc((size_t)npairs * (VIORB_GRID_CELLS + 1)));
     CU(w.cellList.alloc((size_t)npairs * cap2));
     CU(w.listStart.alloc((size_t)npairs * (cap1 + 1)));
@@ -1481,9 +1521,9 @@ int viorb_search_for_initialization(int npairs, int cap1, int cap2, const viorb_
         e = upload(tn1, n1, npairs);
         if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
         else {
-            WinBatch wb{cap1, cap2, tn1.p, nullptr};
+            WinBatch wb{cap1, cap2, tn1.p, nullptr, nullptr};
             VIORB_LAUNCH(k_window_src_ini, dim3((cap1 + 255) / 256, npairs), dim3(256), 0, (cudaStream_t)0, wb, dK1.p, dPM.p,
-                         (float)window_size, dS.p);
+                         (float)window_size, dS.p, 0);
             e = cudaDeviceSynchronize();
             if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
         }
@@ -1927,5 +1967,6 @@ int viorb_fisheye_stereo_matches(const viorb_kb8_rig* rig, const viorb_keypoint*
 }
 
 #include "host_sharded.inc"
+#include "host_f2f.inc"
 
 }  // extern "C"

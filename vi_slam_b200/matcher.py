@@ -221,6 +221,25 @@ def search_by_projection(uv, invz, last_octave, last_angle, desc_mp, valid, obse
     return int(nm[0]), out[:len(k2)].copy()
 
 
+def f2f_batch(ex: FExtractor, n: int, bounds=None, window_size=100, nn_ratio=0.9, check_orientation=True, ratio=0.8, rule=1):
+    """Consecutive resident frames p -> p + 1 of ``ex``'s last batch: SearchForInitialization (vbPrevMatched = F1's own
+    keypoints, tracking.cpp:2286-2288) and brute-force kNN-2 + ratio.  Asynchronous; read back with ``f2f_fetch_all``."""
+    b = None if bounds is None else _bounds(bounds)
+    _check(ex._lib, ex._lib.viorb_f2f_batch(ex._h, int(n), None if b is None else b.ctypes.data, int(window_size), float(nn_ratio),
+                                            int(check_orientation), float(ratio), int(rule)))
+
+
+def f2f_fetch_all(ex: FExtractor, npairs: int, out=None):
+    """-> dict(matches12 [npairs, cap], nmatches [npairs], knn_match [npairs, cap], n_ratio [npairs])."""
+    cap = ex.capacity
+    if out is None:
+        out = {"matches12": np.zeros((npairs, cap), np.int32), "nmatches": np.zeros(npairs, np.int32),
+               "knn_match": np.zeros((npairs, cap), np.int32), "n_ratio": np.zeros(npairs, np.int32)}
+    _check(ex._lib, ex._lib.viorb_f2f_fetch_all(ex._h, int(npairs), out["matches12"].ctypes.data, out["nmatches"].ctypes.data,
+                                                out["knn_match"].ctypes.data, out["n_ratio"].ctypes.data, cap))
+    return out
+
+
 def kb8_rig(cam1, cam2, R12, t12, precision=1e-6):
     """viorb_kb8_rig as 29 floats: mpCamera / mpCamera2 parameters (fx fy cx cy k0..k3), mRlr (row-major), mtlr, precision."""
     r = np.concatenate([np.asarray(cam1, np.float32).ravel(), np.asarray(cam2, np.float32).ravel(), np.asarray(R12, np.float32).ravel(),
