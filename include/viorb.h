@@ -229,20 +229,26 @@ int viorb_search_for_initialization(int npairs, int cap1, int cap2, const viorb_
                                     const viorb_grid_bounds* bounds, float* prev_matched, int window_size, float nn_ratio,
                                     int check_orientation, int32_t* matches12, int32_t* nmatches, int device);
 
-/* FMatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (fmatcher.cpp:2471-2688), single-camera branch
- * (Nleft == -1).  Pose, map points and the camera model stay with the caller, which passes per LastFrame keypoint i:
+/* FMatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (fmatcher.cpp:2471-2688), both branches.
+ * Pose, map points and the camera model stay with the caller, which passes per LastFrame keypoint i (i runs over
+ * LastFrame.N, i.e. keypoints_ then keypointsRight_ for a two-camera LastFrame):
  * uv[i][2] = mpCamera->project(Rcw*x3Dw+tcw), invz[i], last_octave[i], last_angle[i] (kpLF.angle), desc_mp[i][32] =
  * pMP->GetDescriptor(), valid[i] = map point present && !mvbOutlier && invz >= 0 && uv inside [mnMinX,mnMaxX]x[mnMinY,mnMaxY]
  * (fmatcher.cpp:2496-2517), observed[i] = pMP->Observations() > 0.  Current frame: kps2 / desc2 / u_right2 (mvuRight, NULL
  * for monocular) / blocked2 (mvpMapPoints[i2] && Observations() > 0; NULL = none).  direction 0: octave window
- * nLastOctave-1..+1, 1: bForward, 2: bBackward.  assigned [npairs][cap2]: -1 untouched, -2 set to NULL by the rotation
- * check, i >= 0: CurrentFrame.mvpMapPoints[i2] = LastFrame.mvpMapPoints[i].  nmatches[p] = return value. */
+ * nLastOctave-1..+1, 1: bForward, 2: bBackward.
+ * Two-camera rigs (CurrentFrame.Nleft != -1, fmatcher.cpp:2593-2660): uv_right[i][2] = mpCamera->project(mTrl * x3Dc) and
+ * nleft2[p] = CurrentFrame.Nleft; kps2 / desc2 / blocked2 / assigned then hold keypoints_ followed by keypointsRight_
+ * (n2 = N) and u_right2 must be NULL.  uv_right == NULL: the single-camera branch.
+ * assigned [npairs][cap2]: -1 untouched, -2 set to NULL by the rotation check, i >= 0: CurrentFrame.mvpMapPoints[i2] =
+ * LastFrame.mvpMapPoints[i].  nmatches[p] = return value. */
 int viorb_search_by_projection(int npairs, int cap1, int cap2, const float* uv, const float* invz, const int32_t* last_octave,
                                const float* last_angle, const uint8_t* desc_mp, const uint8_t* valid, const uint8_t* observed,
                                const int32_t* n1, const viorb_keypoint* kps2, const uint8_t* desc2, const float* u_right2,
                                const uint8_t* blocked2, const int32_t* n2, const viorb_grid_bounds* bounds,
                                const float* scale_factors, int nlevels, float th, float bf, int direction,
-                               int check_orientation, int32_t* assigned, int32_t* nmatches, int device);
+                               int check_orientation, const float* uv_right, const int32_t* nleft2, int32_t* assigned,
+                               int32_t* nmatches, int device);
 
 /* Frame-to-frame matching between CONSECUTIVE resident frames of the extractor's last batch (the monocular path,
  * BASELINE.json configs[0]): for p in [0, n - 1), F1 = frame p, F2 = frame p + 1:

@@ -72,6 +72,8 @@ def lib():
                                                     C.c_float, C.c_int, i32p]
         L.orc_search_by_projection.argtypes = [f32p, f32p, i32p, f32p, u8p, u8p, u8p, C.c_int, C.c_void_p, u8p, f32p, u8p,
                                                C.c_int, f32p, f32p, C.c_float, C.c_float, C.c_int, C.c_int, i32p]
+        L.orc_search_by_projection_rig.argtypes = [f32p, f32p, f32p, i32p, f32p, u8p, u8p, u8p, C.c_int, C.c_void_p, u8p, u8p, C.c_int,
+                                                   C.c_int, f32p, f32p, C.c_float, C.c_int, C.c_int, i32p]
         L.orc_undistort_points.argtypes = [f32p, C.c_int, f32p, f32p, C.c_int, f32p]
         L.orc_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, f32p, f32p, C.c_int, C.c_void_p]
         L.orc_image_bounds.argtypes = [C.c_int, C.c_int, f32p, f32p, C.c_int, f32p]
@@ -306,6 +308,31 @@ def search_by_projection(uv, invz, last_octave, last_angle, desc_mp, valid, obse
                                        k2.ctypes.data, _u8(d2), None if ur is None else _f32(ur),
                                        None if bl is None else _u8(bl), len(k2), _f32(b), _f32(sf), float(th), float(bf),
                                        int(direction), int(check_orientation), _i32(out))
+    return n, out
+
+
+def search_by_projection_rig(uv, uv_right, invz, last_octave, last_angle, desc_mp, valid, observed, k2, d2, nleft2, blocked2, bounds,
+                             scale_factors, th, direction=0, check_orientation=True):
+    """FMatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) for a two-camera rig (CurrentFrame.Nleft != -1,
+    fmatcher.cpp:2471-2688 incl. :2593-2660): k2 / d2 / blocked2 = left keypoints followed by the right ones, nleft2 = Nleft.
+    -> (nmatches, assigned[N])."""
+    uv = np.ascontiguousarray(uv, np.float32)
+    uvr = np.ascontiguousarray(uv_right, np.float32)
+    invz = np.ascontiguousarray(invz, np.float32)
+    lo = np.ascontiguousarray(last_octave, np.int32)
+    la = np.ascontiguousarray(last_angle, np.float32)
+    dm = np.ascontiguousarray(desc_mp, np.uint8)
+    va = np.ascontiguousarray(valid, np.uint8)
+    ob = np.ascontiguousarray(observed, np.uint8)
+    k2 = np.ascontiguousarray(k2)
+    d2 = np.ascontiguousarray(d2, np.uint8)
+    bl = None if blocked2 is None else np.ascontiguousarray(blocked2, np.uint8)
+    b = np.ascontiguousarray(bounds, np.float32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    out = np.full(len(k2), -1, np.int32)
+    n = lib().orc_search_by_projection_rig(_f32(uv), _f32(uvr), _f32(invz), _i32(lo), _f32(la), _u8(dm), _u8(va), _u8(ob), len(lo),
+                                           k2.ctypes.data, _u8(d2), None if bl is None else _u8(bl), len(k2), int(nleft2), _f32(b),
+                                           _f32(sf), float(th), int(direction), int(check_orientation), _i32(out))
     return n, out
 
 

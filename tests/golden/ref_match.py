@@ -203,3 +203,67 @@ def search_by_projection(uv, invz, last_octave, last_angle, desc_mp, valid, obse
                     assigned[idx] = -2
                     nmatches -= 1
     return nmatches, np.array(assigned, np.int32)
+
+
+def search_by_projection_rig(uv, uv_right, invz, last_octave, last_angle, desc_mp, valid, observed, k2, d2, nleft2, blocked2, bounds,
+                             scale_factors, th, direction, check_orientation):
+    """FMatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) with CurrentFrame.Nleft != -1, statement by statement
+    (fmatcher.cpp:2471-2688; the right-camera block is :2593-2660).  k2 / d2 / blocked2: keypoints_ then keypointsRight_."""
+    nl = int(nleft2)
+    grid = Grid(k2[:nl], bounds)                   # mGrid: left keypoints
+    grid_r = Grid(k2[nl:], bounds)                 # mGridRight: indices relative to keypointsRight_
+    nmatches = 0
+    assigned = [-1] * len(k2)
+    blocked = [0] * len(k2) if blocked2 is None else [int(b) for b in blocked2]
+    rot_hist = [[] for _ in range(HISTO_LENGTH)]
+
+    def window(g, x, y, radius, octv):
+        if direction == 1:
+            return g.in_area(x, y, radius, octv, -1)
+        if direction == 2:
+            return g.in_area(x, y, radius, 0, octv)
+        return g.in_area(x, y, radius, octv - 1, octv + 1)
+
+    for i in range(len(last_octave)):
+        if not valid[i]:
+            continue
+        octv = int(last_octave[i])
+        radius = F(F(th) * F(scale_factors[octv]))
+        ind = window(grid, F(uv[i, 0]), F(uv[i, 1]), radius, octv)
+        if not ind:
+            continue                               # :2534 — skips the right-camera block as well
+        best, best_idx = 256, -1
+        for i2 in ind:
+            if blocked[i2]:
+                continue
+            dist = descriptor_distance(desc_mp[i], d2[i2])      # the `er` test is guarded by Nleft == -1 (:2548)
+            if dist < best:
+                best, best_idx = dist, i2
+        if best <= TH_HIGH:
+            assigned[best_idx] = i
+            blocked[best_idx] = int(observed[i])
+            nmatches += 1
+            if check_orientation:
+                rot_hist[rot_bin(last_angle[i], k2["angle"][best_idx])].append(best_idx)
+        ind = window(grid_r, F(uv_right[i, 0]), F(uv_right[i, 1]), radius, octv)
+        best, best_idx = 256, -1
+        for i2 in ind:
+            if blocked[i2 + nl]:
+                continue
+            dist = descriptor_distance(desc_mp[i], d2[i2 + nl])
+            if dist < best:
+                best, best_idx = dist, i2
+        if best <= TH_HIGH:
+            assigned[best_idx + nl] = i
+            blocked[best_idx + nl] = int(observed[i])
+            nmatches += 1
+            if check_orientation:
+                rot_hist[rot_bin(last_angle[i], k2["angle"][best_idx + nl])].append(best_idx + nl)
+    if check_orientation:
+        keep = three_maxima([len(h) for h in rot_hist])
+        for i in range(HISTO_LENGTH):
+            if i not in keep:
+                for idx in rot_hist[i]:
+                    assigned[idx] = -2
+                    nmatches -= 1
+    return nmatches, np.array(assigned, np.int32)

@@ -103,9 +103,109 @@ def _check_edges(lib):
         assert nm[p] == on and np.array_equal(ms[p], om) and np.array_equal(pms[p], opm)
 
 
+def _check_rig_golden(golden_dir, lib):
+    """Two-camera SearchByProjection (CurrentFrame.Nleft != -1, fmatcher.cpp:2593-2660) against the transliteration golden."""
+    g = np.load(os.path.join(golden_dir, "window_rig.npz"))
+    for tag in "abcd":
+        th, direction, chk, ub = g[f"rig_{tag}_args"]
+        n, asg = matcher.search_by_projection(g["uv"], g["invz"], g["octave"], g["angle"], g["dmp"], g["valid"], g["observed"], g["k2"],
+                                              g["d2"], None, g["blocked2"] if ub else None, g["bounds"], g["sf"], th, 0.0, int(direction),
+                                              bool(chk), lib_path=lib, uv_right=g["uv_right"], nleft2=int(g["nleft2"]))
+        assert n == int(g[f"rig_{tag}_n"]) and np.array_equal(asg, g[f"rig_{tag}_asg"]), tag
+        nl = int(g["nleft2"])
+        assert (asg[:nl] >= 0).sum() > 100 and (asg[nl:] >= 0).sum() > 100          # both cameras matched
+
+
+def _kb8_rig_case(seed, n_pts=1500):
+    """A synthetic fisheye rig (the KB8 pair of tests/test_kb8.py): 3D points seen by the LastFrame are projected into the
+    CurrentFrame's left camera and, through mTrl, into its right camera (what the caller of the ABI does); the current
+    frame's keypoints are those projections with pixel noise plus clutter."""
+    from tests.golden import ref_kb8
+    from tests.golden.make_kb8_golden import PRM1, PRM2, rig_pose
+    rng = np.random.default_rng(seed)
+    R12, t12 = rig_pose()
+    R21 = R12.T.astype(np.float64)
+    t21 = -R21 @ t12.astype(np.float64)
+    d = np.exp(rng.uniform(np.log(0.5), np.log(20.0), n_pts))
+    ang, th = rng.uniform(0, 2 * np.pi, n_pts), rng.uniform(0, 1.1, n_pts)
+    X1 = np.stack([np.sin(th) * np.cos(ang), np.sin(th) * np.sin(ang), np.cos(th)], 1) * d[:, None]
+    X2 = X1 @ R21.T + t21
+    uv = np.array([ref_kb8.project(x, PRM1) for x in X1], np.float32)
+    uvr = np.array([ref_kb8.project(x, PRM2) for x in X2], np.float32)
+    octave = rng.integers(0, 8, n_pts).astype(np.int32)
+    angle = rng.uniform(0, 360, n_pts).astype(np.float32)
+    dmp = rng.integers(0, 256, (n_pts, 32), dtype=np.uint8)
+
+    def camera(proj, n_clutter):
+        seen = rng.random(n_pts) < 0.7
+        k = np.zeros(int(seen.sum()) + n_clutter, oracle.KP_DTYPE)
+        m = int(seen.sum())
+        k["x"][:m], k["y"][:m] = proj[seen, 0] + rng.normal(0, 1.5, m), proj[seen, 1] + rng.normal(0, 1.5, m)
+        k["octave"][:m] = np.clip(octave[seen] + rng.integers(-1, 2, m), 0, 7)
+        k["angle"][:m] = (angle[seen] + np.where(rng.random(m) < 0.2, 140.0, rng.normal(0, 3, m))) % 360
+        k["x"][m:], k["y"][m:] = rng.uniform(0, 512, n_clutter), rng.uniform(0, 512, n_clutter)
+        k["octave"][m:], k["angle"][m:] = rng.integers(0, 8, n_clutter), rng.uniform(0, 360, n_clutter)
+        k["size"], k["class_id"] = 31, -1
+        dd = rng.integers(0, 256, (len(k), 32), dtype=np.uint8)
+        noisy = dmp[seen].copy()
+        for i in range(m):
+            for bit in rng.choice(256, int(rng.integers(0, 80)), replace=False):
+                noisy[i, bit >> 3] ^= 1 << (bit & 7)
+        dd[:m] = noisy
+        perm = rng.permutation(len(k))
+        return k[perm], dd[perm]
+
+    kl, dl = camera(uv, 400)
+    kr, dr = camera(uvr, 300)
+    k2, d2 = np.concatenate([kl, kr]), np.concatenate([dl, dr])
+    invz = (1.0 / X1[:, 2]).astype(np.float32)
+    valid = ((rng.random(n_pts) < 0.9) & (uv[:, 0] >= 0) & (uv[:, 0] <= 512) & (uv[:, 1] >= 0) & (uv[:, 1] <= 512)).astype(np.uint8)
+    return {"uv": uv, "uv_right": uvr, "invz": invz, "octave": octave, "angle": angle, "dmp": dmp, "valid": valid,
+            "observed": (rng.random(n_pts) < 0.6).astype(np.uint8), "k2": k2, "d2": d2, "nleft2": len(kl),
+            "blocked2": (rng.random(len(k2)) < 0.1).astype(np.uint8), "bounds": np.array([0, 512, 0, 512], np.float32)}
+
+
+def _check_rig_vs_oracle(lib, seed):
+    c = _kb8_rig_case(seed)
+    for th, direction, chk, bl in ((15.0, 0, True, c["blocked2"]), (7.0, 1, True, None), (25.0, 2, False, c["blocked2"])):
+        on, oa = oracle.search_by_projection_rig(c["uv"], c["uv_right"], c["invz"], c["octave"], c["angle"], c["dmp"], c["valid"],
+                                                 c["observed"], c["k2"], c["d2"], c["nleft2"], bl, c["bounds"], SF, th, direction, chk)
+        n, a = matcher.search_by_projection(c["uv"], c["invz"], c["octave"], c["angle"], c["dmp"], c["valid"], c["observed"], c["k2"], c["d2"],
+                                            None, bl, c["bounds"], SF, th, 0.0, direction, chk, lib_path=lib, uv_right=c["uv_right"],
+                                            nleft2=c["nleft2"])
+        assert n == on and np.array_equal(a, oa)
+        assert (oa[:c["nleft2"]] >= 0).sum() > 50 and (oa[c["nleft2"]:] >= 0).sum() > 50
+    # Nleft = 0 / Nleft = N: one camera of the rig without keypoints
+    for nl in (0, len(c["k2"])):
+        on, oa = oracle.search_by_projection_rig(c["uv"], c["uv_right"], c["invz"], c["octave"], c["angle"], c["dmp"], c["valid"],
+                                                 c["observed"], c["k2"], c["d2"], nl, None, c["bounds"], SF, 15.0, 0, True)
+        n, a = matcher.search_by_projection(c["uv"], c["invz"], c["octave"], c["angle"], c["dmp"], c["valid"], c["observed"], c["k2"], c["d2"],
+                                            None, None, c["bounds"], SF, 15.0, 0.0, 0, True, lib_path=lib, uv_right=c["uv_right"], nleft2=nl)
+        assert n == on and np.array_equal(a, oa)
+
+
 @pytest.fixture(scope="module")
 def emu(oracle_mod):
     return ge.build_emu()
+
+
+def test_window_rig_golden_emulation(emu, golden_dir):
+    _check_rig_golden(golden_dir, emu)
+
+
+def test_window_rig_vs_oracle_emulation(emu):
+    _check_rig_vs_oracle(emu, 31)
+
+
+@pytest.mark.gpu
+def test_window_rig_golden_cuda(oracle_mod, golden_dir):
+    _check_rig_golden(golden_dir, None)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", [32, 33])
+def test_window_rig_vs_oracle_cuda(oracle_mod, seed):
+    _check_rig_vs_oracle(None, seed)
 
 
 def test_window_golden_emulation(emu, golden_dir):

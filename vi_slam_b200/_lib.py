@@ -88,8 +88,8 @@ SYMBOLS = {
                                                   i32p, C.c_int]),
     "viorb_search_by_projection": (C.c_int, [C.c_int, C.c_int, C.c_int, f32p, f32p, i32p, f32p, C.c_void_p, C.c_void_p,
                                              C.c_void_p, i32p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, i32p,
-                                             C.c_void_p, f32p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, i32p, i32p,
-                                             C.c_int]),
+                                             C.c_void_p, f32p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                             i32p, i32p, C.c_int]),
     "viorb_f2f_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_double, C.c_int]),
     "viorb_f2f_fetch_all": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
     "viorb_extractor_set_camera": (C.c_int, [C.c_void_p, f32p, f32p, C.c_int]),

@@ -36,7 +36,10 @@ struct WinBatch {
     const int* n1;
     const int* n2;
     const int* n1fill;      // optional: source count of the fill pass (0 for a pair whose list did not fit the budget)
+    const int* off2;        // optional: first target row of the pair inside its cap2 rows (the right camera of a two-camera
+                            // frame: keypointsRight_ follow keypoints_, offset Nleft; indices stay relative to it, frame.cpp:409)
 };
+__device__ __forceinline__ size_t winbatch_base2(const WinBatch& wb, int p) { return (size_t)p * wb.cap2 + (wb.off2 ? wb.off2[p] : 0); }
 
 // ---------------------------------------------------------------------------------------------
 // Grid: CSR table over the 64x48 cells, cell id = ix * 48 + iy (so the cells of one column are
@@ -50,7 +53,7 @@ __global__ void __launch_bounds__(256) k_grid_build(WinBatch wb, GridBounds gb, 
     __shared__ int warpSums[20];
     const int tid = threadIdx.x, p = blockIdx.x;
     const int n2 = wb.n2[p];
-    const viorb_keypoint* K = kps2 + (size_t)p * wb.cap2;
+    const viorb_keypoint* K = kps2 + winbatch_base2(wb, p);
     int* CS = cellStart + (size_t)p * (VIORB_GRID_CELLS + 1);
     int* CL = cellList + (size_t)p * wb.cap2;
     for (int i = tid; i <= VIORB_GRID_CELLS; i += 256) cnt[i] = 0;
@@ -161,8 +164,8 @@ __global__ void __launch_bounds__(256) k_window_list(WinBatch wb, GridBounds gb,
             const bool check = s.minLevel > 0 || s.maxLevel >= 0;
             const int* CS = cellStart + (size_t)p * (VIORB_GRID_CELLS + 1);
             const int* CL = cellList + (size_t)p * wb.cap2;
-            const viorb_keypoint* K = kps2 + (size_t)p * wb.cap2;
-            const uint4* D2 = reinterpret_cast<const uint4*>(desc2 + (size_t)p * wb.cap2 * 32);
+            const viorb_keypoint* K = kps2 + winbatch_base2(wb, p);
+            const uint4* D2 = reinterpret_cast<const uint4*>(desc2 + winbatch_base2(wb, p) * 32);
             uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
             if (fill && desc1) {
                 const uint4* q = reinterpret_cast<const uint4*>(desc1 + o * 32);
@@ -345,61 +348,76 @@ __global__ void __launch_bounds__(32) k_resolve_ini(WinBatch wb, const viorb_key
     if (lane == 0) nMatches[p] = nm;
 }
 
-// SearchByProjection(CurrentFrame, LastFrame) (fmatcher.cpp:2471-2688, single-camera branch).
+// SearchByProjection(CurrentFrame, LastFrame) (fmatcher.cpp:2471-2688).
 // blocked [cap2]: in: current keypoint already holds an observed map point; updated as matches are made.
 // assigned [cap2]: -1 untouched, -2 cleared by the rotation check, >= 0 the source index now held.
-// pushIdx / pushBin: per-pair scratch of cap1 entries (the rotHist lists).  grid (nPairs), block 32.
+// pushIdx / pushBin: per-pair scratch of 2 * cap1 entries (the rotHist lists).
+// Two-camera frames (CurrentFrame.Nleft != -1, :2593-2660): listStartR / listR are the candidate lists of the SAME sources
+// in the right camera's grid (indices relative to keypointsRight_), nleft[p] = Nleft.  Per source, in the reference's
+// order: the left window (an EMPTY left window skips the right one too: the `continue` at :2534 precedes the right
+// block), then the right window with indices, blocked flags and the rotation histogram offset by Nleft.
+// grid (nPairs), block 32.
 __global__ void __launch_bounds__(32) k_resolve_proj(WinBatch wb, const float* __restrict__ lastAngle,
                                                      const uint8_t* __restrict__ observed, const viorb_keypoint* __restrict__ kps2,
                                                      const int* __restrict__ listStart, const uint32_t* __restrict__ list,
+                                                     const int* __restrict__ listStartR, const uint32_t* __restrict__ listR,
+                                                     const int* __restrict__ nleft, int n2cap,
                                                      int checkOrientation, uint8_t* __restrict__ blocked,
                                                      int* __restrict__ pushIdx, int8_t* __restrict__ pushBin,
-                                                     int32_t* __restrict__ assigned, int* __restrict__ nMatches) {
+                                                     int32_t* __restrict__ assigned, int* __restrict__ nMatches,
+                                                     const int* __restrict__ n2total) {
     __shared__ int hist[VIORB_HISTO_LENGTH];
     __shared__ int keep[3];
     const int lane = threadIdx.x, p = blockIdx.x;
-    const int n1 = wb.n1[p], n2 = wb.n2[p];
+    const int n1 = wb.n1[p], n2 = n2total ? n2total[p] : wb.n2[p];
+    const bool rig = listStartR != nullptr;
+    const int nL = rig ? nleft[p] : 0;
     const int* LS = listStart + (size_t)p * (wb.cap1 + 1);
-    uint8_t* BL = blocked + (size_t)p * wb.cap2;
-    int32_t* AS = assigned + (size_t)p * wb.cap2;
-    int* PI = pushIdx + (size_t)p * wb.cap1;
-    int8_t* PB = pushBin + (size_t)p * wb.cap1;
-    const viorb_keypoint* K2 = kps2 + (size_t)p * wb.cap2;
+    const int* LSR = rig ? listStartR + (size_t)p * (wb.cap1 + 1) : nullptr;
+    uint8_t* BL = blocked + (size_t)p * n2cap;
+    int32_t* AS = assigned + (size_t)p * n2cap;
+    int* PI = pushIdx + (size_t)p * wb.cap1 * 2;
+    int8_t* PB = pushBin + (size_t)p * wb.cap1 * 2;
+    const viorb_keypoint* K2 = kps2 + (size_t)p * n2cap;
     for (int i = lane; i < n2; i += 32) AS[i] = -1;
     if (lane < VIORB_HISTO_LENGTH) hist[lane] = 0;
     __syncwarp();
     int nPush = 0;
-    int s0 = LS[0];
-    for (int i = 0; i < n1; ++i) {
-        const int s1 = LS[i + 1];
-        const int cnt = s1 - s0;
-        if (cnt > 0) {
-            unsigned b1 = VIORB_WIN_EMPTY;
-            for (int j = lane; j < cnt; j += 32) {
-                const uint32_t e = list[s0 + j];
-                if (BL[e & 0xFFFF]) continue;                               // fmatcher.cpp:2545-2547
-                b1 = min(b1, (e & 0xFFFF0000u) | (unsigned)j);
-            }
-            b1 = __reduce_min_sync(0xffffffffu, b1);
-            if (b1 != VIORB_WIN_EMPTY && (int)(b1 >> 16) <= VIORB_TH_HIGH) {
-                const int bestIdx2 = (int)(list[s0 + (int)(b1 & 0xFFFF)] & 0xFFFF);
-                if (lane == 0) {
-                    const size_t o = (size_t)p * wb.cap1 + i;
-                    AS[bestIdx2] = i;
-                    BL[bestIdx2] = observed[o];
-                    int bin = 0;
-                    if (checkOrientation) {
-                        bin = rot_bin_dev(lastAngle[o], K2[bestIdx2].angle);
-                        hist[bin] += 1;
-                    }
-                    PI[nPush] = bestIdx2;
-                    PB[nPush] = (int8_t)bin;
-                }
-                ++nPush;
-                __syncwarp();
-            }
+    // best unblocked candidate of one list; on acceptance lane 0 records it.  off: index offset of this camera.
+    auto pass = [&](const uint32_t* L, int s0, int cnt, int off, int i) {
+        unsigned b1 = VIORB_WIN_EMPTY;
+        for (int j = lane; j < cnt; j += 32) {
+            const uint32_t e = L[s0 + j];
+            if (BL[(e & 0xFFFF) + off]) continue;                           // fmatcher.cpp:2545-2547 / :2621-2623
+            b1 = min(b1, (e & 0xFFFF0000u) | (unsigned)j);
         }
-        s0 = s1;
+        b1 = __reduce_min_sync(0xffffffffu, b1);
+        if (b1 != VIORB_WIN_EMPTY && (int)(b1 >> 16) <= VIORB_TH_HIGH) {
+            const int bestIdx2 = (int)(L[s0 + (int)(b1 & 0xFFFF)] & 0xFFFF) + off;
+            if (lane == 0) {
+                const size_t o = (size_t)p * wb.cap1 + i;
+                AS[bestIdx2] = i;
+                BL[bestIdx2] = observed[o];
+                int bin = 0;
+                if (checkOrientation) {
+                    bin = rot_bin_dev(lastAngle[o], K2[bestIdx2].angle);
+                    hist[bin] += 1;
+                }
+                PI[nPush] = bestIdx2;
+                PB[nPush] = (int8_t)bin;
+            }
+            ++nPush;
+            __syncwarp();
+        }
+    };
+    for (int i = 0; i < n1; ++i) {
+        const int s0 = LS[i], cnt = LS[i + 1] - s0;
+        if (cnt <= 0) continue;                                             // vIndices2.empty(): next map point
+        pass(list, s0, cnt, 0, i);
+        if (rig) {
+            const int r0 = LSR[i], rc = LSR[i + 1] - r0;
+            if (rc > 0) pass(listR, r0, rc, nL, i);
+        }
     }
     __syncwarp();
     int removed = 0;

@@ -1410,10 +1410,10 @@ struct WindowWork {
 
 int window_lists(WindowWork& w, int npairs, int cap1, int cap2, const int32_t* n1, const int32_t* n2, const GridBounds& gb,
                  const WinSrc* dSrc, const uint8_t* dDesc1, const viorb_keypoint* dKps2, const uint8_t* dDesc2,
-                 const float* dURight2) {
+                 const float* dURight2, const int* dOff2 = nullptr) {
     CU(upload(w.n1, n1, npairs));
     CU(upload(w.n2, n2, npairs));
-    w.wb.cap1 = cap1; w.wb.cap2 = cap2; w.wb.n1 = w.n1.p; w.wb.n2 = w.n2.p; w.wb.n1fill = nullptr;
+    w.wb.cap1 = cap1; w.wb.cap2 = cap2; w.wb.n1 = w.n1.p; w.wb.n2 = w.n2.p; w.wb.n1fill = nullptr; w.wb.off2 = dOff2;
     CU(w.cellStart.alloc((size_t)npairs * (VIORB_GRID_CELLS + 1)));
     CU(w.cellList.alloc((size_t)npairs * cap2));
     CU(w.listStart.alloc((size_t)npairs * (cap1 + 1)));
@@ -1549,10 +1549,16 @@ int viorb_search_by_projection(int npairs, int cap1, int cap2, const float* uv, 
                                const int32_t* n1, const viorb_keypoint* kps2, const uint8_t* desc2, const float* u_right2,
                                const uint8_t* blocked2, const int32_t* n2, const viorb_grid_bounds* bounds,
                                const float* scale_factors, int nlevels, float th, float bf, int direction,
-                               int check_orientation, int32_t* assigned, int32_t* nmatches, int device) {
+                               int check_orientation, const float* uv_right, const int32_t* nleft2, int32_t* assigned,
+                               int32_t* nmatches, int device) {
     if (npairs < 1 || cap1 < 0 || cap2 < 0 || !n1 || !n2 || !bounds || !assigned || !scale_factors || nlevels < 1 ||
         nlevels > VIORB_MAX_LEVELS || direction < 0 || direction > 2)
         return fail(VIORB_E_ARG, "bad argument");
+    const bool rig = uv_right != nullptr;           // CurrentFrame.Nleft != -1 (fmatcher.cpp:2593-2660)
+    if (rig && !nleft2) return fail(VIORB_E_ARG, "uv_right needs nleft2 (CurrentFrame.Nleft per pair)");
+    if (rig && u_right2) return fail(VIORB_E_ARG, "two-camera frames have no mvuRight (the predicate is guarded by Nleft == -1)");
+    if (rig) for (int p = 0; p < npairs; ++p)
+        if (nleft2[p] < 0 || nleft2[p] > n2[p]) return fail(VIORB_E_ARG, "nleft2 outside [0, n2]");
     if (cap2 >= 65536) return fail(VIORB_E_ARG, "more than 65535 keypoints per frame are not supported");
     for (int p = 0; p < npairs; ++p)
         if (n1[p] < 0 || n1[p] > cap1 || n2[p] < 0 || n2[p] > cap2) return fail(VIORB_E_ARG, "n1 / n2 outside [0, cap]");
@@ -1572,10 +1578,18 @@ int viorb_search_by_projection(int npairs, int cap1, int cap2, const float* uv, 
     DevBuf<uint8_t> dDM, dVA, dOB, dD2, dBL;
     DevBuf<int8_t> dPB;
     DevBuf<viorb_keypoint> dK2;
-    DevBuf<WinSrc> dS;
-    WindowWork w;
+    DevBuf<WinSrc> dS, dSR;
+    DevBuf<float> dUVR;
+    DevBuf<int> dNLeft, dN2;
+    WindowWork w, wR;
     const bool have1 = cap1 > 0;
+    std::vector<int32_t> nL(npairs), nR(npairs);
+    for (int p = 0; p < npairs; ++p) { nL[p] = rig ? nleft2[p] : n2[p]; nR[p] = n2[p] - nL[p]; }
     cudaError_t e = upload(dUV, have1 ? uv : nullptr, N1 * 2);
+    if (e == cudaSuccess && rig) e = upload(dUVR, have1 ? uv_right : nullptr, N1 * 2);
+    if (e == cudaSuccess && rig) e = upload(dNLeft, nL.data(), npairs);
+    if (e == cudaSuccess && rig) e = dSR.alloc(N1);
+    if (e == cudaSuccess) e = upload(dN2, n2, npairs);
     if (e == cudaSuccess) e = upload(dIZ, have1 ? invz : nullptr, N1);
     if (e == cudaSuccess) e = upload(dLA, have1 ? last_angle : nullptr, N1);
     if (e == cudaSuccess) e = upload(dLO, have1 ? last_octave : nullptr, N1);
@@ -1589,8 +1603,8 @@ int viorb_search_by_projection(int npairs, int cap1, int cap2, const float* uv, 
     if (e == cudaSuccess && !blocked2) e = cudaMemset(dBL.p, 0, N2);
     if (e == cudaSuccess) e = dS.alloc(N1);
     if (e == cudaSuccess) e = dAS.alloc(N2);
-    if (e == cudaSuccess) e = dPI.alloc(N1);
-    if (e == cudaSuccess) e = dPB.alloc(N1);
+    if (e == cudaSuccess) e = dPI.alloc(N1 * 2);
+    if (e == cudaSuccess) e = dPB.alloc(N1 * 2);
     if (e == cudaSuccess) e = dNM.alloc(npairs);
     rc = e == cudaSuccess ? VIORB_OK : fail(VIORB_E_CUDA, cudaGetErrorString(e));
     if (!rc && have1) {
@@ -1601,15 +1615,20 @@ int viorb_search_by_projection(int npairs, int cap1, int cap2, const float* uv, 
             WinBatch wb{cap1, cap2, tn1.p, nullptr};
             VIORB_LAUNCH(k_window_src_proj, dim3((cap1 + 255) / 256, npairs), dim3(256), 0, (cudaStream_t)0, wb, pp, dUV.p, dIZ.p, dLO.p,
                          dVA.p, dS.p);
+            // the same map points projected into the right camera: same radius and octave window (:2596-2611)
+            if (rig) VIORB_LAUNCH(k_window_src_proj, dim3((cap1 + 255) / 256, npairs), dim3(256), 0, (cudaStream_t)0, wb, pp, dUVR.p,
+                                  dIZ.p, dLO.p, dVA.p, dSR.p);
             e = cudaDeviceSynchronize();
             if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
         }
         tn1.release();
     }
-    if (!rc) rc = window_lists(w, npairs, cap1, cap2, n1, n2, gb, dS.p, dDM.p, dK2.p, dD2.p, u_right2 ? dUR.p : nullptr);
+    if (!rc) rc = window_lists(w, npairs, cap1, cap2, n1, nL.data(), gb, dS.p, dDM.p, dK2.p, dD2.p, u_right2 ? dUR.p : nullptr);
+    if (!rc && rig) rc = window_lists(wR, npairs, cap1, cap2, n1, nR.data(), gb, dSR.p, dDM.p, dK2.p, dD2.p, nullptr, dNLeft.p);
     if (!rc) {
         VIORB_LAUNCH(k_resolve_proj, dim3(npairs), dim3(32), 0, (cudaStream_t)0, w.wb, dLA.p, dOB.p, dK2.p, w.listStart.p, w.list.p,
-                     check_orientation, dBL.p, dPI.p, dPB.p, dAS.p, dNM.p);
+                     rig ? wR.listStart.p : (const int*)nullptr, rig ? wR.list.p : (const uint32_t*)nullptr,
+                     rig ? dNLeft.p : (const int*)nullptr, cap2, check_orientation, dBL.p, dPI.p, dPB.p, dAS.p, dNM.p, dN2.p);
         e = cudaGetLastError();
         if (e == cudaSuccess) e = cudaMemcpy(assigned, dAS.p, sizeof(int32_t) * N2, cudaMemcpyDeviceToHost);
         if (e == cudaSuccess && nmatches) e = cudaMemcpy(nmatches, dNM.p, sizeof(int32_t) * npairs, cudaMemcpyDeviceToHost);
@@ -1617,6 +1636,7 @@ int viorb_search_by_projection(int npairs, int cap1, int cap2, const float* uv, 
     }
     dUV.release(); dIZ.release(); dLA.release(); dUR.release(); dLO.release(); dAS.release(); dNM.release(); dPI.release();
     dDM.release(); dVA.release(); dOB.release(); dD2.release(); dBL.release(); dPB.release(); dK2.release(); dS.release(); w.release();
+    dSR.release(); dUVR.release(); dNLeft.release(); dN2.release(); wR.release();
     return rc;
 }
 

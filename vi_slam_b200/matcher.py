@@ -191,8 +191,10 @@ def search_for_initialization_batch(k1s, d1s, k2s, d2s, bounds, prev_matched, wi
 
 
 def search_by_projection(uv, invz, last_octave, last_angle, desc_mp, valid, observed, k2, d2, u_right2, blocked2, bounds,
-                         scale_factors, th, bf, direction=0, check_orientation=True, device=0, lib_path=None):
-    """FMatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono), single-camera branch; the caller projects.
+                         scale_factors, th, bf, direction=0, check_orientation=True, device=0, lib_path=None, uv_right=None,
+                         nleft2=None):
+    """FMatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono); the caller projects.  ``uv_right`` / ``nleft2``
+    select the two-camera branch (CurrentFrame.Nleft != -1): k2 / d2 / blocked2 = keypoints_ then keypointsRight_.
     -> (nmatches, assigned[n2]) with assigned: -1 untouched, -2 cleared by the rotation check, i >= 0 matched source."""
     lib = _lib.load(lib_path)
     uv = np.ascontiguousarray(uv, np.float32)
@@ -210,6 +212,8 @@ def search_by_projection(uv, invz, last_octave, last_angle, desc_mp, valid, obse
     b = _bounds(bounds)
     n1 = np.array([len(lo)], np.int32)
     n2 = np.array([len(k2)], np.int32)
+    uvr = None if uv_right is None else np.ascontiguousarray(uv_right, np.float32)
+    nl2 = None if uv_right is None else np.array([int(nleft2)], np.int32)
     out = np.full(max(len(k2), 1), -1, np.int32)
     nm = np.zeros(1, np.int32)
     _check(lib, lib.viorb_search_by_projection(
@@ -217,7 +221,8 @@ def search_by_projection(uv, invz, last_octave, last_angle, desc_mp, valid, obse
         la.ctypes.data_as(_lib.f32p), dm.ctypes.data, va.ctypes.data, ob.ctypes.data, n1.ctypes.data_as(_lib.i32p),
         k2.ctypes.data, d2.ctypes.data, None if ur is None else ur.ctypes.data, None if bl is None else bl.ctypes.data,
         n2.ctypes.data_as(_lib.i32p), b.ctypes.data, sf.ctypes.data_as(_lib.f32p), len(sf), float(th), float(bf),
-        int(direction), int(check_orientation), out.ctypes.data_as(_lib.i32p), nm.ctypes.data_as(_lib.i32p), device))
+        int(direction), int(check_orientation), None if uvr is None else uvr.ctypes.data, None if nl2 is None else nl2.ctypes.data,
+        out.ctypes.data_as(_lib.i32p), nm.ctypes.data_as(_lib.i32p), device))
     return int(nm[0]), out[:len(k2)].copy()
 
 
