@@ -26,6 +26,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <stdexcept>
 #include <vector>
 
 typedef unsigned char uchar;
@@ -33,6 +34,7 @@ typedef unsigned char uchar;
 #define CV_8U 0
 #define CV_8UC1 0
 #define CV_PI 3.1415926535897932384626433832795
+#define CV_Assert(expr) do { if (!(expr)) throw std::runtime_error("CV_Assert failed: " #expr); } while (0)
 
 // cvRound: OpenCV's x86-64 build uses cvtss2si / cvtsd2si, i.e. the current rounding mode
 // (nearest-even).  lrintf/lrint do the same.
@@ -216,6 +218,21 @@ inline void Mat::copyTo(OutputArray dst) const {
     for (int y = 0; y < rows; ++y)
         if (d.ptr(y) != ptr(y)) std::memmove(d.ptr(y), ptr(y), (size_t)cols);
 }
+
+// opencv2/core/types.hpp: class DMatch; opencv2/core/mat.hpp: Mat1b = Mat_<uchar>
+struct DMatch {
+    int queryIdx, trainIdx, imgIdx;
+    float distance;
+    DMatch() : queryIdx(-1), trainIdx(-1), imgIdx(-1), distance(3.402823466e+38f) {}
+    DMatch(int q, int t, float d) : queryIdx(q), trainIdx(t), imgIdx(-1), distance(d) {}
+    DMatch(int q, int t, int i, float d) : queryIdx(q), trainIdx(t), imgIdx(i), distance(d) {}
+};
+class Mat1b : public Mat {
+public:
+    Mat1b() {}
+    Mat1b(const Mat& m) : Mat(m) {}
+    Mat1b(int r, int c) : Mat(r, c, CV_8UC1) {}
+};
 
 // opencv2/features2d.hpp: KeyPointsFilter::retainBest — keep the n_points strongest, plus every
 // keypoint tied with the weakest kept one (only ComputeKeyPointsOld, which compute() never calls, uses it).

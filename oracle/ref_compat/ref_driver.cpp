@@ -226,4 +226,11 @@ int orb_ref_level_keypoints(void* h, int l, int32_t* xys, float* angle, int cap)
 }
 long orb_ref_arena_fallbacks() { return g_fallbacks.load(); }
 
+// For programs that use vi_slam::geometry::FExtractor from this library DIRECTLY (tests/cpp/dropin_driver.cpp): switch
+// the calling thread to the allocation-ordered arena for the rest of the process (nothing is recycled).
+void orb_ref_monotone(int on) {
+    if (on) arena_init();
+    t_monotone = on != 0;
+}
+
 }  // extern "C"
