@@ -1,7 +1,7 @@
 #!/bin/bash
 # ncu evidence: launch list of a short bench run, then a full capture of selected kernels.
 mkdir -p gpurun_out
-CMD="python bench.py --steps 2 --warmup 3 --pairs 64 --no-cpu-baseline --no-e2e"
+CMD="python bench.py --steps 2 --warmup 3 --pairs 64 --no-cpu-baseline --no-e2e --no-knn-sweep ${BENCH_ARGS}"
 $CMD > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launch.log 2>&1
 echo "launches rc $?"

@@ -58,6 +58,9 @@ __device__ __forceinline__ int2 hamming256_csa(const uint4& a0, const uint4& a1,
     return make_int2(__popc(s2) + __popc(x7), __popc(c0) + __popc(c1) + __popc(c2));
 }
 
+// The two kernels below are build-time variants (VIORB_KNN_VARIANT 2 / 1; viorb_api.cu): the product library holds
+// k_knn2_tc5 only.
+#if VIORB_KNN_VARIANT == 2
 // ---------------------------------------------------------------------------------------------
 // Brute-force Hamming 2-NN.  One thread = one query row (256 bits in 8 registers); train rows are
 // staged 128 at a time in shared memory and read as warp-wide broadcasts (2 x LDS.128 per row).
@@ -105,7 +108,9 @@ __global__ void __launch_bounds__(VIORB_KNN_THREADS) k_knn2(DescSet Q, DescSet T
                       best1 == 0xFFFFFFFFu ? -1 : (int)(best1 >> VIORB_KNN_IDX_BITS));
     }
 }
+#endif  // VIORB_KNN_VARIANT == 2
 
+#if VIORB_KNN_VARIANT == 1
 // ---------------------------------------------------------------------------------------------
 // Brute-force Hamming 2-NN on the tensor cores.  Hamming(a, b) = popc(a) + popc(b) - 2 a.b, and the dot product
 // of two 256-bit rows is an integer GEMM once the bits are expanded to {0,1} bytes.  sm_100a has no native
@@ -242,6 +247,7 @@ __global__ void __launch_bounds__(VIORB_KNN_THREADS) k_knn2_mma(DescSet Q, DescS
             }
         }
 }
+#endif  // VIORB_KNN_VARIANT == 1
 
 // ---------------------------------------------------------------------------------------------
 // Ratio test + ordered compaction.  One CTA per set; accepted matches are written in query order.
