@@ -147,6 +147,17 @@ int viorb_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx,
 int viorb_knn2_device(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int32_t* d_idx, int32_t* d_dist,
                       void* stream);
 
+/* viorb_knn2_device without ANY allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same inputs, outputs and results as viorb_knn2_device.  The scratch rows of the kernel's train-range split live in a
+ * file-scope device array of 4 MiB that every GPU loading the library holds until the process exits; the call makes no
+ * cudaMalloc / cudaFree / pool allocation (the first call on a device does one-time set-up: make it before a capture).
+ * Limit: nq <= VIORB_KNN2_STATIC_MAX_QUERIES rows per call, larger calls fail with VIORB_E_CAPACITY and a message (nt is
+ * bounded by 2^22 - 1 as everywhere).  All calls share the array: calls that overlap on the GPU (different streams, or
+ * several host threads) race - serialise them on one stream.  Nothing in the array needs clearing between calls. */
+#define VIORB_KNN2_STATIC_MAX_QUERIES 16384
+int viorb_knn2_device_static(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int32_t* d_idx, int32_t* d_dist,
+                             void* stream);
 /* Same, one 16-byte row (idx0, idx1, dist0, dist1) per query at d_rows[nq][4]: the row format of the sharded matcher. */
 int viorb_knn2_packed_device(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int32_t* d_rows, void* stream);
 

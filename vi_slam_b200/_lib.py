@@ -63,6 +63,7 @@ SYMBOLS = {
     "viorb_descriptor_distance": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, i32p, C.c_int]),
     "viorb_knn2": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, i32p, i32p, C.c_int]),
     "viorb_knn2_device": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "viorb_knn2_device_static": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "viorb_knn2_packed_device": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "viorb_comm_unique_id": (C.c_int, [C.c_void_p]),
     "viorb_comm_create_nccl": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),

@@ -1990,3 +1990,80 @@ int viorb_fisheye_stereo_matches(const viorb_kb8_rig* rig, const viorb_keypoint*
 #include "host_f2f.inc"
 
 }  // extern "C"
+
+// =================================================================================================
+// viorb_knn2_device_static: kNN-2 on device buffers WITHOUT any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops,
+// harnesses that forbid it).  The only scratch the kNN-2 path uses - the partial (best, second) key rows of a query tile
+// whose train range is cut over several CTAs (k_knn2_tc5 -> k_knn2_tc5_merge) - lives in the file-scope device array
+// below instead of the stream-ordered pool of launch_knn2.  Every GPU that loads the library holds these 4 MiB until the
+// process exits.  Nothing in it has to start at zero: every row k_knn2_tc5_merge reads was written by k_knn2_tc5 in the
+// same call.  All calls share the array, so two calls that overlap on the GPU (different streams) race.
+// =================================================================================================
+#define VIORB_STATIC_KNN_MAX_QUERIES VIORB_KNN2_STATIC_MAX_QUERIES   /* query rows per call (include/viorb.h) */
+#define VIORB_STATIC_KNN_MAX_SPLIT 32                        /* CTAs per query tile, as in launch_knn2 */
+#if VIORB_KNN_VARIANT == 0
+#define VIORB_STATIC_KNN_ROWS ((VIORB_STATIC_KNN_MAX_QUERIES / 128) * VIORB_STATIC_KNN_MAX_SPLIT * 128)     /* 524 288 uint2 = 4 MiB */
+static __device__ __align__(256) uint2 g_knnStaticScratch[VIORB_STATIC_KNN_ROWS];
+
+namespace {
+struct StaticKnnState {
+    std::once_flag once;
+    cudaError_t err = cudaSuccess;
+    int sms = 148;
+    uint2* scratch = nullptr;         // DEVICE address of g_knnStaticScratch on this device (the name itself is a host-side stand-in)
+};
+StaticKnnState g_staticKnn[64];
+}  // namespace
+#endif
+
+extern "C" int viorb_knn2_device_static(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int32_t* d_idx, int32_t* d_dist,
+                                        void* stream) {
+    if (nq < 0 || nt < 0 || (nq > 0 && (!d_q || !d_idx || !d_dist))) return fail(VIORB_E_ARG, "bad argument");
+    if (nq > VIORB_STATIC_KNN_MAX_QUERIES)
+        return fail(VIORB_E_CAPACITY, "viorb_knn2_device_static: nq = " + std::to_string(nq) + " exceeds the static scratch limit of " +
+                                          std::to_string(VIORB_STATIC_KNN_MAX_QUERIES) + " query rows per call (use viorb_knn2_device, or split the queries)");
+    if (nt >= (1 << VIORB_KNN_IDX_BITS)) return fail(VIORB_E_ARG, "train set larger than 2^22 rows");
+    if (((uintptr_t)d_q & 15) || ((uintptr_t)d_t & 15)) return fail(VIORB_E_ARG, "descriptor buffers must be 16-byte aligned");
+    if (nq == 0) return VIORB_OK;
+#if VIORB_KNN_VARIANT == 0
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(VIORB_E_ARG, "device index out of range");
+    StaticKnnState& S = g_staticKnn[dev];
+    std::call_once(S.once, [&S, dev] {                       // set-up, once per device, with that device current
+        auto ok = [&S](cudaError_t r) { if (S.err == cudaSuccess) S.err = r; };
+        ok(cudaDeviceGetAttribute(&S.sms, cudaDevAttrMultiProcessorCount, dev));
+        ok(cudaFuncSetAttribute(tc5::k_knn2_tc5, cudaFuncAttributeMaxDynamicSharedMemorySize, tc5::SMEM_BYTES));
+        ok(cudaGetSymbolAddress((void**)&S.scratch, g_knnStaticScratch));
+    });
+    if (S.err != cudaSuccess || !S.scratch)
+        return fail(VIORB_E_CUDA, std::string("viorb_knn2_device_static set-up: ") + cudaGetErrorString(S.err));
+    cudaStream_t st = (cudaStream_t)stream;
+    DescSet Q{d_q, 0, nullptr, nq}, T{d_t, 0, nullptr, nt};
+    const int qTiles = (nq + tc5::QT - 1) / tc5::QT;
+    // the train-range split of launch_knn2 (same cost model), bounded by what the static rows hold
+    const int maxTiles = std::max(1, (nt + tc5::TT - 1) / tc5::TT);
+    int nSplit = 1;
+    long best = 0;
+    for (int sp = 1; sp <= std::min(maxTiles, VIORB_STATIC_KNN_MAX_SPLIT); ++sp) {
+        const long cost = (long)((qTiles * sp + S.sms - 1) / S.sms) * ((maxTiles + sp - 1) / sp + 2);
+        if (sp == 1 || cost * 20 < best * 19) { best = cost; nSplit = sp; }
+        if (sp == 1 && cost < 24) break;
+    }
+    if (const int forced = g_forceKnnSplit.load()) nSplit = std::max(1, std::min(std::min(forced, maxTiles), VIORB_STATIC_KNN_MAX_SPLIT));
+    const int nItems = qTiles * nSplit;
+    if ((size_t)nItems * tc5::QT > (size_t)VIORB_STATIC_KNN_ROWS) return fail(VIORB_E_CAPACITY, "viorb_knn2_device_static: scratch rows exceeded");
+    uint2* partial = nSplit > 1 ? S.scratch : nullptr;
+    VIORB_LAUNCH(tc5::k_knn2_tc5, dim3(std::min(nItems, S.sms)), dim3(tc5::THREADS), tc5::SMEM_BYTES, st, Q, T, d_idx, d_dist, (size_t)nq,
+                 qTiles, 1, nItems, nSplit, partial);
+    if (nSplit > 1)
+        VIORB_LAUNCH(tc5::k_knn2_tc5_merge, dim3((qTiles * tc5::QT + 255) / 256, 1), dim3(256), 0, st, Q, partial, d_idx, d_dist, (size_t)nq,
+                     qTiles, nSplit);
+    CU(cudaGetLastError());
+    return VIORB_OK;
+#else
+    (void)stream;
+    return fail(VIORB_E_NO_DEVICE, "viorb_knn2_device_static exists only in the sm_100a build with the tcgen05 kNN-2 kernel");
+#endif
+}
