@@ -431,22 +431,32 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
 // The reference breaks (size) ties by heap pointer; here, as in the oracle, by creation order
 // (later created first), which for nodes of one round equals "smaller list index first".
 // Final pick per node: max response, first in cell-major raster order wins ties          (:735-751).
-// grid (nlevels, B), block 512, dynamic smem = octree_smem_bytes(maxNodes).
+// grid (B, nlevels), block 512, dynamic smem = octree_smem_bytes(maxNodes).
 // ---------------------------------------------------------------------------------------------
 #ifndef VIORB_OCT_THREADS
-#define VIORB_OCT_THREADS 512
+#define VIORB_OCT_THREADS 1024
+#endif
+#ifndef VIORB_OCT_MIN_THREADS
+#define VIORB_OCT_MIN_THREADS 256
+#endif
+#ifndef VIORB_OCT_KEYS_PER_THREAD
+#define VIORB_OCT_KEYS_PER_THREAD 8
+#endif
+#ifndef VIORB_OCT_AGG
+#define VIORB_OCT_AGG 0
 #endif
 
 struct OctBounds { short ulx, uly, brx, bry; };
 
 __host__ __device__ inline size_t octree_smem_bytes(int nc) {
-    // bounds[2][nc] (8 B) + cnt[2][nc] + child[4 nc] + rank[nc] + aux0[nc] + aux1[nc] + newIdx[nc]
-    return (size_t)nc * (16 + 8 + 16 + 4 + 4 + 4 + 4) + 64;
+    // bounds[2][nc] (8 B) + cnt[2][nc] + child[4 nc] + rank[nc] + aux0[nc] + aux1[nc] + newIdx[nc] + child2[4 nc]
+    return (size_t)nc * (16 + 8 + 16 + 4 + 4 + 4 + 4 + 16) + 64;
 }
 
 // exclusive scan of a[0..m) in place by the whole CTA; returns the total (all threads).
-__device__ __forceinline__ int block_excl_scan(int* a, int m, int* warpSums /* >= 17 ints */) {
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nth = blockDim.x;
+// nthOverride: number of participating threads when the trailing warps of the CTA have already exited (k_octree)
+__device__ __forceinline__ int block_excl_scan(int* a, int m, int* warpSums /* >= 33 ints */, int nthOverride = 0) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nth = nthOverride ? nthOverride : (int)blockDim.x;
     const int chunk = (m + nth - 1) / nth;
     const int st = min(tid * chunk, m), en = min(st + chunk, m);
     int sum = 0;
@@ -468,12 +478,12 @@ __device__ __forceinline__ int block_excl_scan(int* a, int m, int* warpSums /* >
             if (lane >= d) vi += t;
         }
         if (lane < (nth >> 5)) warpSums[lane] = vi - v;
-        if (lane == 31) warpSums[16] = vi;
+        if (lane == 31) warpSums[32] = vi;
     }
     __syncthreads();
     int run = warpSums[wid] + inc - sum;
     for (int i = st; i < en; ++i) { int t = a[i]; a[i] = run; run += t; }
-    const int total = warpSums[16];
+    const int total = warpSums[32];
     __syncthreads();
     return total;
 }
@@ -483,13 +493,21 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
                                                               KeptKp* __restrict__ kept, int* __restrict__ keptCount,
                                                               int* __restrict__ status) {
     VIORB_DYN_SMEM(smem);
-    __shared__ int warpSums[20];
+    __shared__ int warpSums[36];
     __shared__ int sh_live, sh_nExp, sh_cut, sh_remap[64];
-    const int tid = threadIdx.x, nth = VIORB_OCT_THREADS;
-    const int l = blockIdx.x, f = blockIdx.y + g.frame0;
+    const int tid = threadIdx.x;
+    // grid (frames, levels): the CTAs of level 0 - the ones with the most keys - are dispatched first and the short ones
+    // of the upper levels fill the tail (longest job first)
+    const int l = blockIdx.y, f = blockIdx.x + g.frame0;
     const LevelGeom& L = g.lv[l];
     const int NC = g.maxNodes;
     const int n = min(candCount[f * g.nlevels + l], L.candCap);
+    // The CTA is launched with VIORB_OCT_THREADS threads, but only as many warps as this (level, frame) has work for
+    // stay: a typical level holds a few thousand candidates, a noise-like frame 50 times as many, and the kernel ends
+    // with its longest CTA.  The other warps exit here (an exited warp counts as arrived at every later barrier), so the
+    // many light CTAs pay short barriers and the few heavy ones get all 32 warps.
+    const int nth = min(VIORB_OCT_THREADS, max(VIORB_OCT_MIN_THREADS, ((n + VIORB_OCT_KEYS_PER_THREAD * 32 - 1) / (VIORB_OCT_KEYS_PER_THREAD * 32)) * 32));
+    if (tid >= nth) return;
     const uint32_t* keys = cand + (size_t)f * g.candPerFrame + L.candOff;
     uint16_t* kn = keyNode + (size_t)f * g.candPerFrame + L.candOff;
     KeptKp* out = kept + (size_t)f * g.keptPerFrame + L.keptOff;
@@ -508,7 +526,20 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
     int* aux0 = rankv + NC;            // scans
     int* aux1 = aux0 + NC;
     int* newIdx = aux1 + NC;           // new index of an unsplit node
+    int* child2 = newIdx + NC;         // [4 NC] child key counts of the NEXT round, filled while the keys move
     const int N = L.nWant;
+    const int lane = tid & 31;
+    // one shared-memory atomic per distinct counter of a warp (neighbouring candidates fall into the same node, and on
+    // dense frames a node holds hundreds of keys: unaggregated, the 32 lanes serialise on one address)
+    auto warp_add = [&](int* ctr, int c) {
+#if VIORB_OCT_AGG
+        const unsigned m = __match_any_sync(0xffffffffu, c);
+        if (c >= 0 && lane == __ffs(m) - 1) atomicAdd(&ctr[c], __popc(m));
+#else
+        (void)lane;
+        if (c >= 0) atomicAdd(&ctr[c], 1);
+#endif
+    };
 
     // ---- roots (:535-578)
     const int nIni = L.nIni;
@@ -523,12 +554,15 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
         cnt[0][i] = 0;
     }
     __syncthreads();
-    for (int k = tid; k < n; k += nth) {
-        const int x = keys[k] & 0xFFF;
-        int r = (int)__fdiv_rn((float)x, hX);
-        r = min(r, nIni - 1);
-        kn[k] = (uint16_t)r;
-        atomicAdd(&cnt[0][r], 1);
+    for (int base = 0; base < n; base += nth) {
+        const int k = base + tid;
+        int r = -1;
+        if (k < n) {
+            const int x = keys[k] & 0xFFF;
+            r = min((int)__fdiv_rn((float)x, hX), nIni - 1);
+            kn[k] = (uint16_t)r;
+        }
+        warp_add(cnt[0], r);
     }
     __syncthreads();
     if (tid == 0) {
@@ -540,10 +574,28 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
         sh_live = m;
     }
     __syncthreads();
-    for (int k = tid; k < n; k += nth) kn[k] = (uint16_t)sh_remap[kn[k]];
     int cur = 1;
     int live = sh_live;
     bool careful = false;
+    // child key counts of the root nodes; for every later round they are counted while the keys move (step 4)
+    for (int i = tid; i < 4 * live; i += nth) child[i] = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += nth) {
+        const int k = base + tid;
+        int c = -1;
+        if (k < n) {
+            const uint32_t e = keys[k];
+            const int nd = sh_remap[kn[k]];
+            kn[k] = (uint16_t)nd;
+            if (cnt[1][nd] > 1) {
+                const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
+                const OctBounds b = bnd[1][nd];
+                const int mx = b.ulx + ((b.brx - b.ulx + 1) >> 1), my = b.uly + ((b.bry - b.uly + 1) >> 1);
+                c = nd * 4 + (x < mx ? 0 : 1) + (y < my ? 0 : 2);
+            }
+        }
+        warp_add(child, c);
+    }
     __syncthreads();
 
     for (int round = 0; round < 64; ++round) {
@@ -552,26 +604,13 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
         OctBounds* B2 = bnd[cur ^ 1];
         int* Cn2 = cnt[cur ^ 1];
         const int prevSize = live;
-        // 1. child key counts of every expandable node
-        for (int i = tid; i < 4 * live; i += nth) child[i] = 0;
-        __syncthreads();
-        for (int k = tid; k < n; k += nth) {
-            const int nd = kn[k];
-            if (Cn[nd] > 1) {
-                const uint32_t e = keys[k];
-                const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
-                const OctBounds b = B[nd];
-                const int mx = b.ulx + ((b.brx - b.ulx + 1) >> 1), my = b.uly + ((b.bry - b.uly + 1) >> 1);
-                atomicAdd(&child[nd * 4 + (x < mx ? 0 : 1) + (y < my ? 0 : 2)], 1);
-            }
-        }
-        __syncthreads();
+        // 1. child[4 i ..] = child key counts of every expandable node i (counted when the keys moved into it)
         // 2. push rank of the nodes to split
         int nSplit;
         if (!careful) {
             for (int i = tid; i < live; i += nth) aux0[i] = Cn[i] > 1 ? 1 : 0;
             __syncthreads();
-            nSplit = block_excl_scan(aux0, live, warpSums);
+            nSplit = block_excl_scan(aux0, live, warpSums, nth);
             for (int i = tid; i < live; i += nth) rankv[i] = Cn[i] > 1 ? aux0[i] : -1;
             __syncthreads();
         } else {
@@ -605,7 +644,7 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
             __syncthreads();
             nE = sh_nExp;                           // number of expandable nodes
             __syncthreads();
-            block_excl_scan(aux0, nE, warpSums);    // aux0[r] = gain of ranks < r
+            block_excl_scan(aux0, nE, warpSums, nth);    // aux0[r] = gain of ranks < r
             for (int r = tid; r < nE; r += nth) {
                 // inclusive gain after splitting rank r = aux0[r+1] (or total); recompute from neighbours
                 const int before = live + aux0[r];
@@ -632,10 +671,10 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
                 aux0[rankv[i]] = (ch[0] > 0) + (ch[1] > 0) + (ch[2] > 0) + (ch[3] > 0);
             }
         __syncthreads();
-        const int P = block_excl_scan(aux0, nSplit, warpSums);      // aux0[rank] = first push position
+        const int P = block_excl_scan(aux0, nSplit, warpSums, nth);      // aux0[rank] = first push position
         for (int i = tid; i < live; i += nth) aux1[i] = rankv[i] < 0 ? 1 : 0;
         __syncthreads();
-        const int nKeep = block_excl_scan(aux1, live, warpSums);    // aux1[i] = #unsplit before i
+        const int nKeep = block_excl_scan(aux1, live, warpSums, nth);    // aux1[i] = #unsplit before i
         const int newLive = P + nKeep;
         if (newLive > NC) {                 // cannot happen for maxNodes = max(N+3, 4 nIni); guard anyway
             if (tid == 0) atomicOr(status, 2);
@@ -665,6 +704,7 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
                         Cn2[ni] = c;
                         myExp += c > 1;
                         ch[q] = ni;
+                        child2[4 * ni] = 0; child2[4 * ni + 1] = 0; child2[4 * ni + 2] = 0; child2[4 * ni + 3] = 0;
                     }
                 }
             } else {
@@ -676,21 +716,33 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
         }
         if (myExp) atomicAdd(&sh_nExp, myExp);
         __syncthreads();
-        // 4. move the keys
-        for (int k = tid; k < n; k += nth) {
-            const int nd = kn[k];
-            if (rankv[nd] >= 0) {
-                const uint32_t e = keys[k];
-                const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
-                const OctBounds b = B[nd];
-                const int mx = b.ulx + ((b.brx - b.ulx + 1) >> 1), my = b.uly + ((b.bry - b.uly + 1) >> 1);
-                kn[k] = (uint16_t)child[nd * 4 + (x < mx ? 0 : 1) + (y < my ? 0 : 2)];
-            } else {
-                kn[k] = (uint16_t)newIdx[nd];
+        // 4. move the keys; a key that lands in a node with more than one key is counted for that node's next split
+        for (int base = 0; base < n; base += nth) {
+            const int k = base + tid;
+            int c = -1;
+            if (k < n) {
+                const int nd = kn[k];
+                if (rankv[nd] >= 0) {
+                    const uint32_t e = keys[k];
+                    const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
+                    const OctBounds b = B[nd];
+                    const int mx = b.ulx + ((b.brx - b.ulx + 1) >> 1), my = b.uly + ((b.bry - b.uly + 1) >> 1);
+                    const int ni = child[nd * 4 + (x < mx ? 0 : 1) + (y < my ? 0 : 2)];
+                    kn[k] = (uint16_t)ni;
+                    if (Cn2[ni] > 1) {
+                        const OctBounds nb = B2[ni];
+                        const int mx2 = nb.ulx + ((nb.brx - nb.ulx + 1) >> 1), my2 = nb.uly + ((nb.bry - nb.uly + 1) >> 1);
+                        c = ni * 4 + (x < mx2 ? 0 : 1) + (y < my2 ? 0 : 2);
+                    }
+                } else {
+                    kn[k] = (uint16_t)newIdx[nd];
+                }
             }
+            warp_add(child2, c);
         }
         const int nToExpand = sh_nExp;
         __syncthreads();
+        { int* t = child; child = child2; child2 = t; }
         cur ^= 1;
         live = newLive;
         // 5. termination (:655-662, :724-725)
@@ -699,12 +751,21 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
     }
 
     // ---- best key per node (:735-751): max score, ties -> first in (cell row, cell col, y, x) order
+    // two steps: the node's best score with a native 32-bit atomic, then only the keys that hold that score compete for
+    // "first in the reference's order" with the 64-bit one
     unsigned long long* best = reinterpret_cast<unsigned long long*>(child);
-    for (int i = tid; i < live; i += nth) best[i] = 0ull;
+    int* bestScore = aux0;
+    for (int i = tid; i < live; i += nth) { best[i] = 0ull; bestScore[i] = 0; }
+    __syncthreads();
+    for (int k = tid; k < n; k += nth) {
+        const int sc = (int)(keys[k] >> 24), nd = kn[k];
+        if (sc > bestScore[nd]) atomicMax(&bestScore[nd], sc);
+    }
     __syncthreads();
     const unsigned long long OMASK = (1ull << 40) - 1;
     for (int k = tid; k < n; k += nth) {
         const uint32_t e = keys[k];
+        if ((int)(e >> 24) != bestScore[kn[k]]) continue;
         const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
         const unsigned long long sc = e >> 24;
         const int cj = min(max(x - 3, 0) / L.wCell, L.lastCol);

@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(256) k_stereo_rows(StereoParams sp, int rows, 
                                                      const int* __restrict__ nR, int* __restrict__ rowStart,
                                                      int2* __restrict__ rowList, int* __restrict__ status) {
     VIORB_DYN_SMEM(smem);
-    __shared__ int warpSums[20];
+    __shared__ int warpSums[36];
     int* cnt = reinterpret_cast<int*>(smem);
     int* cur = cnt + rows + 1;
     const int tid = threadIdx.x, f = blockIdx.x;

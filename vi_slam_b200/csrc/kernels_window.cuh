@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(256) k_grid_build(WinBatch wb, GridBounds gb, 
                                                     int* __restrict__ cellStart, int* __restrict__ cellList) {
     __shared__ int cnt[VIORB_GRID_CELLS + 1];
     __shared__ int cur[VIORB_GRID_CELLS];
-    __shared__ int warpSums[20];
+    __shared__ int warpSums[36];
     const int tid = threadIdx.x, p = blockIdx.x;
     const int n2 = wb.n2[p];
     const viorb_keypoint* K = kps2 + winbatch_base2(wb, p);
@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(256) k_window_list(WinBatch wb, GridBounds gb,
 // exclusive scan of the per-source counts of one pair -> list offsets relative to the pair's base, which
 // is pairBase[p] (filled by the host from the totals).  grid (nPairs), block 256.
 __global__ void __launch_bounds__(256) k_window_scan(WinBatch wb, int* __restrict__ listStart, int* __restrict__ totals) {
-    __shared__ int warpSums[20];
+    __shared__ int warpSums[36];
     const int p = blockIdx.x;
     int* LS = listStart + (size_t)p * (wb.cap1 + 1);
     const int n1 = wb.n1[p];

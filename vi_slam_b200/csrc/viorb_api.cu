@@ -501,7 +501,7 @@ int run_pipeline(viorb_extractor* ex, int f0, int n, int lap0, int lap1) {
                      ex->dCand.p, ex->dCandCount.p, ex->dStatus.p);
     }
     if (tm) CU(cudaEventRecord(ex->evX[2], st));
-    VIORB_LAUNCH(k_octree, dim3(g.nlevels, n), dim3(VIORB_OCT_THREADS), ex->octSmem, st, g, ex->dCand.p, ex->dCandCount.p,
+    VIORB_LAUNCH(k_octree, dim3(n, g.nlevels), dim3(VIORB_OCT_THREADS), ex->octSmem, st, g, ex->dCand.p, ex->dCandCount.p,
                  ex->dKeyNode.p, ex->dKept.p, ex->dKeptCount.p, ex->dStatus.p);
     if (tm) CU(cudaEventRecord(ex->evX[3], st));
     VIORB_LAUNCH(k_orient, dim3((g.keptPerFrame + 7) / 8, n), dim3(256), 0, st, g, fs, ex->dOrientTab.p, ex->dSlotLevel.p, ex->dKept.p,
