@@ -1,11 +1,24 @@
 #!/bin/bash
-# 8-GPU box: 1-GPU kNN sweep, 8-GPU sharded kNN sweep (config 5), then the bench at 2 / 4 / 8 GPUs as the driver launches it.
+# 8-GPU box: the bench as the driver launches it at N = 1, 2, 4, 8 (default workload: weak scaling; knn_sweep = configs[4]
+# rides along), then the 4096-frame strong-scaling batch (configs[3]) at N = 1 and 8.
 mkdir -p gpurun_out
-timeout 300 python tools/knn_sweep.py 2000 8000 32000 100000 200000 > gpurun_out/knn_sweep_1gpu_v8.jsonl 2> gpurun_out/knn_sweep_1gpu_v8.err
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511 tools/knn_sweep.py 2000 8000 32000 100000 200000 > gpurun_out/knn_sweep_8gpu_v8.jsonl 2> gpurun_out/knn_sweep_8gpu_v8.err
-for n in 2 4 8; do
-  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2952$n bench.py --gpus $n --steps 5 --warmup 3 > gpurun_out/bench_${n}gpu_v8.json 2> gpurun_out/bench_${n}gpu_v8.err
-  tail -c 600 gpurun_out/bench_${n}gpu_v8.json | head -c 300; echo
-done
-timeout 900 python tools/cpu_baselines.py > gpurun_out/cpu_baselines_v8.jsonl 2> gpurun_out/cpu_baselines_v8.err; cat gpurun_out/cpu_baselines_v8.jsonl | cut -c1-200
-cat gpurun_out/knn_sweep_1gpu_v8.jsonl gpurun_out/knn_sweep_8gpu_v8.jsonl | cut -c1-140
+run() {  # N workload tag
+  local n=$1 w=$2 tag=$3
+  if [ "$n" = 1 ]; then
+    timeout 600 python bench.py --gpus 1 --workload $w --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/bench_${tag}_1gpu.json 2> gpurun_out/bench_${tag}_1gpu.err
+  else
+    timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2952$n bench.py --gpus $n --workload $w --steps 10 --warmup 3 > gpurun_out/bench_${tag}_${n}gpu.json 2> gpurun_out/bench_${tag}_${n}gpu.err
+  fi
+  python - <<PY
+import json
+try:
+    d = json.loads(open("gpurun_out/bench_${tag}_${n}gpu.json").read().strip().splitlines()[-1])
+    ks = d.get("knn_sweep", {}).get("sizes", [])
+    print("$tag N=$n", round(d["value"]), "e2e", round(d["e2e"]["value"]), "ms/step", round(d["ms_per_step"], 3),
+          "knn", [(s["workload"][13:], round(s["ms"], 3), s["match"]) for s in ks])
+except Exception as e:
+    print("$tag N=$n: no line:", e)
+PY
+}
+for n in ${NS:-1 2 4 8}; do run $n kitti_stereo stereo; done
+for n in ${NS2:-1 8}; do run $n kitti_batch_4096 batch4096; done
