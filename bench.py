@@ -676,7 +676,7 @@ def run_ours(args, wl, rank, world, local_rank):
                    "distinct_frames": min(args.distinct, B), "frame_classes": {c: classes.count(c) for c in sorted(set(classes))}, **stats},
         **({"variant_lib": args.variant_lib} if args.variant_lib else {}),
         "host": host, "clocks": clk, "e2e": e2e,
-        "gpu_launches": K * (calls * (NLEVELS - 1 + 6) + (5 if stereo else 10 if kind == "mono_f2f" else 0)),
+        "gpu_launches": K * (calls * (NLEVELS - 1 + 7) + (5 if stereo else 10 if kind == "mono_f2f" else 0)),
         "stages_ms_per_step": mean,
         "stage_timing": "second pass of K steps, every handle on one stream, CUDA events around each stage", "roofline": roofline,
     }

@@ -431,13 +431,20 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
 // The reference breaks (size) ties by heap pointer; here, as in the oracle, by creation order
 // (later created first), which for nodes of one round equals "smaller list index first".
 // Final pick per node: max response, first in cell-major raster order wins ties          (:735-751).
-// grid (B, nlevels), block 512, dynamic smem = octree_smem_bytes(maxNodes).
+// grid (B, nlevels), two launches (k_octree / k_octree_dense, below), dynamic smem = octree_smem_bytes(maxNodes, cells).
 // ---------------------------------------------------------------------------------------------
+// Two launches share the work by candidate count n of the (level, frame):
+//   k_octree        n <= VIORB_OCT_DENSE_KEYS   256-thread CTAs, several per SM: the many light jobs are barrier-latency
+//                                               bound, what they need is CTAs in flight;
+//   k_octree_dense  n >  VIORB_OCT_DENSE_KEYS   1024-thread CTAs (as many warps as n needs stay): a noise-like frame holds
+//                                               50 times the candidates of a textured one and the launch ends with it.
+// A CTA whose job belongs to the other launch exits at once.
 #ifndef VIORB_OCT_THREADS
 #define VIORB_OCT_THREADS 1024
 #endif
-#ifndef VIORB_OCT_MIN_THREADS
-#define VIORB_OCT_MIN_THREADS 256
+#define VIORB_OCT_LIGHT_THREADS 256
+#ifndef VIORB_OCT_DENSE_KEYS
+#define VIORB_OCT_DENSE_KEYS 4096
 #endif
 #ifndef VIORB_OCT_KEYS_PER_THREAD
 #define VIORB_OCT_KEYS_PER_THREAD 8
@@ -445,12 +452,20 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
 #ifndef VIORB_OCT_AGG
 #define VIORB_OCT_AGG 0
 #endif
+// count pyramid: per root a full 4-ary tree of key counts down to depth D0, D0 the largest depth with
+// nIni * 4^D0 <= min(cells of the launch, n / VIORB_OCT_KEYS_PER_CELL); all levels together stay below 4/3 of the cells
+#ifndef VIORB_OCT_KEYS_PER_CELL
+#define VIORB_OCT_KEYS_PER_CELL 8
+#endif
+#define VIORB_OCT_PYR_CELLS 4096
+#define VIORB_OCT_LIGHT_PYR_CELLS 512
 
 struct OctBounds { short ulx, uly, brx, bry; };
 
-__host__ __device__ inline size_t octree_smem_bytes(int nc) {
-    // bounds[2][nc] (8 B) + cnt[2][nc] + child[4 nc] + rank[nc] + aux0[nc] + aux1[nc] + newIdx[nc] + child2[4 nc]
-    return (size_t)nc * (16 + 8 + 16 + 4 + 4 + 4 + 4 + 16) + 64;
+__host__ __device__ inline size_t octree_smem_bytes(int nc, int pyrCells) {
+    // bounds[2][nc] (8 B) + cnt[2][nc] + child[4 nc] + rank[nc] + aux0[nc] + aux1[nc] + newIdx[nc] + child2[4 nc] + code[2][nc]
+    // + the count pyramid (VIORB_OCT_PYR_INTS)
+    return (size_t)nc * (16 + 8 + 16 + 4 + 4 + 4 + 4 + 16 + 8) + 64 + (size_t)(pyrCells * 4 / 3 + 8) * 4;
 }
 
 // exclusive scan of a[0..m) in place by the whole CTA; returns the total (all threads).
@@ -488,13 +503,15 @@ __device__ __forceinline__ int block_excl_scan(int* a, int m, int* warpSums /* >
     return total;
 }
 
-__global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, const uint32_t* __restrict__ cand,
-                                                              const int* __restrict__ candCount, uint16_t* __restrict__ keyNode,
-                                                              KeptKp* __restrict__ kept, int* __restrict__ keptCount,
-                                                              int* __restrict__ status) {
+template <int THREADS, int PYR_CELLS>
+__device__ __forceinline__ void octree_body(const ExtractGeom& g, const uint32_t* __restrict__ cand,
+                                            const int* __restrict__ candCount, uint16_t* __restrict__ keyNode,
+                                            KeptKp* __restrict__ kept, int* __restrict__ keptCount,
+                                            int* __restrict__ status, int nLo, int nHi) {
     VIORB_DYN_SMEM(smem);
     __shared__ int warpSums[36];
-    __shared__ int sh_live, sh_nExp, sh_cut, sh_remap[64];
+    __shared__ int sh_live, sh_nExp, sh_cut;
+    __shared__ OctBounds sh_rootB[64];
     const int tid = threadIdx.x;
     // grid (frames, levels): the CTAs of level 0 - the ones with the most keys - are dispatched first and the short ones
     // of the upper levels fill the tail (longest job first)
@@ -502,11 +519,10 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
     const LevelGeom& L = g.lv[l];
     const int NC = g.maxNodes;
     const int n = min(candCount[f * g.nlevels + l], L.candCap);
-    // The CTA is launched with VIORB_OCT_THREADS threads, but only as many warps as this (level, frame) has work for
-    // stay: a typical level holds a few thousand candidates, a noise-like frame 50 times as many, and the kernel ends
-    // with its longest CTA.  The other warps exit here (an exited warp counts as arrived at every later barrier), so the
-    // many light CTAs pay short barriers and the few heavy ones get all 32 warps.
-    const int nth = min(VIORB_OCT_THREADS, max(VIORB_OCT_MIN_THREADS, ((n + VIORB_OCT_KEYS_PER_THREAD * 32 - 1) / (VIORB_OCT_KEYS_PER_THREAD * 32)) * 32));
+    if (n < nLo || n > nHi) return;                        // the other launch's job
+    // Of a dense CTA only as many warps as the job has work for stay; the others exit here (an exited warp counts as
+    // arrived at every later barrier).
+    const int nth = min(THREADS, max(VIORB_OCT_LIGHT_THREADS, ((n + VIORB_OCT_KEYS_PER_THREAD * 32 - 1) / (VIORB_OCT_KEYS_PER_THREAD * 32)) * 32));
     if (tid >= nth) return;
     const uint32_t* keys = cand + (size_t)f * g.candPerFrame + L.candOff;
     uint16_t* kn = keyNode + (size_t)f * g.candPerFrame + L.candOff;
@@ -527,6 +543,10 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
     int* aux1 = aux0 + NC;
     int* newIdx = aux1 + NC;           // new index of an unsplit node
     int* child2 = newIdx + NC;         // [4 NC] child key counts of the NEXT round, filled while the keys move
+    int* code[2];                      // per node: depth << 24 | root << 16 | path (2 bits per level), while depth <= D0
+    code[0] = child2 + 4 * NC;
+    code[1] = code[0] + NC;
+    int* pyr = code[1] + NC;           // count pyramid; later the (depth, root, path) -> node table
     const int N = L.nWant;
     const int lane = tid & 31;
     // one shared-memory atomic per distinct counter of a warp (neighbouring candidates fall into the same node, and on
@@ -544,59 +564,95 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
     // ---- roots (:535-578)
     const int nIni = L.nIni;
     const float hX = L.hX;
+    // The first D0 rounds never touch the keys.  Every expandable node of round r was created in round r - 1, so it has
+    // depth r, and its children's key counts are entries of a count pyramid built ONCE: each key walks D0 levels down
+    // from its root (the same ceil-half comparisons as DivideNode, :474-475, :506-517) and counts itself in its depth-D0
+    // cell; the upper levels are sums.  Only if the tree must grow below depth D0 (sparse, clustered levels - few keys)
+    // do the keys get their node and the per-round key passes start.  A dense level (tens of thousands of keys, a few
+    // hundred nodes) finishes within the pyramid: 3 passes over the keys instead of 2 + one per round.
+    // The pyramid's fixed cost (clearing, summing, the node table) is proportional to its cells: its depth follows the
+    // key count, so that a light level (a few hundred keys) pays next to nothing and switches to key passes early.
+    const int cellCap = min(PYR_CELLS, max(nIni, n / VIORB_OCT_KEYS_PER_CELL));
+    int D0 = 0;
+    while (D0 < 6 && (nIni << (2 * (D0 + 1))) <= cellCap) ++D0;
+    auto lvl_off = [&](int d) { return nIni * (((1 << (2 * d)) - 1) / 3); };                 // nIni * (4^d - 1) / 3
+    auto cell_idx = [&](int d, int r, int pth) { return lvl_off(d) + (r << (2 * d)) + pth; };
+    const int pyrTotal = lvl_off(D0 + 1);
     for (int i = tid; i < nIni; i += nth) {
         OctBounds b;
         b.ulx = (short)(int)__fmul_rn(hX, (float)i);
         b.brx = (short)(int)__fmul_rn(hX, (float)(i + 1));
         b.uly = 0;
         b.bry = (short)(L.maxBY - VIORB_MINB);
-        bnd[0][i] = b;
-        cnt[0][i] = 0;
+        sh_rootB[i] = b;
     }
-    __syncthreads();
-    for (int base = 0; base < n; base += nth) {
-        const int k = base + tid;
-        int r = -1;
-        if (k < n) {
-            const int x = keys[k] & 0xFFF;
-            r = min((int)__fdiv_rn((float)x, hX), nIni - 1);
-            kn[k] = (uint16_t)r;
-        }
-        warp_add(cnt[0], r);
-    }
-    __syncthreads();
-    if (tid == 0) {
-        int m = 0;
-        for (int i = 0; i < nIni; ++i) {
-            if (cnt[0][i] > 0) { sh_remap[i] = m; bnd[1][m] = bnd[0][i]; cnt[1][m] = cnt[0][i]; ++m; }
-            else sh_remap[i] = -1;
-        }
-        sh_live = m;
-    }
-    __syncthreads();
-    int cur = 1;
-    int live = sh_live;
-    bool careful = false;
-    // child key counts of the root nodes; for every later round they are counted while the keys move (step 4)
-    for (int i = tid; i < 4 * live; i += nth) child[i] = 0;
+    for (int i = tid; i < pyrTotal; i += nth) pyr[i] = 0;
     __syncthreads();
     for (int base = 0; base < n; base += nth) {
         const int k = base + tid;
         int c = -1;
         if (k < n) {
             const uint32_t e = keys[k];
-            const int nd = sh_remap[kn[k]];
-            kn[k] = (uint16_t)nd;
-            if (cnt[1][nd] > 1) {
-                const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
-                const OctBounds b = bnd[1][nd];
-                const int mx = b.ulx + ((b.brx - b.ulx + 1) >> 1), my = b.uly + ((b.bry - b.uly + 1) >> 1);
-                c = nd * 4 + (x < mx ? 0 : 1) + (y < my ? 0 : 2);
+            const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
+            const int r = min((int)__fdiv_rn((float)x, hX), nIni - 1);
+            const OctBounds b = sh_rootB[r];
+            int ulx = b.ulx, brx = b.brx, uly = b.uly, bry = b.bry, pth = 0;
+            for (int d = 0; d < D0; ++d) {
+                const int mx = ulx + ((brx - ulx + 1) >> 1), my = uly + ((bry - uly + 1) >> 1);
+                int q = 0;
+                if (x < mx) brx = mx; else { ulx = mx; q = 1; }
+                if (y < my) bry = my; else { uly = my; q += 2; }
+                pth = pth * 4 + q;
             }
+            c = cell_idx(D0, r, pth);
         }
-        warp_add(child, c);
+        warp_add(pyr, c);
     }
     __syncthreads();
+    for (int d = D0 - 1; d >= 0; --d) {
+        const int cells = nIni << (2 * d), o = lvl_off(d), oc = lvl_off(d + 1);
+        for (int c = tid; c < cells; c += nth) pyr[o + c] = pyr[oc + 4 * c] + pyr[oc + 4 * c + 1] + pyr[oc + 4 * c + 2] + pyr[oc + 4 * c + 3];
+        __syncthreads();
+    }
+    if (tid == 0) {
+        int m = 0;
+        for (int i = 0; i < nIni; ++i)
+            if (pyr[i] > 0) { bnd[1][m] = sh_rootB[i]; cnt[1][m] = pyr[i]; code[1][m] = i << 16; ++m; }
+        sh_live = m;
+    }
+    __syncthreads();
+    int cur = 1;
+    int live = sh_live;
+    bool careful = false;
+    bool usePyr = true;
+    // (depth, root, path) -> node table over the pyramid's cells (-1 = split further), then every key walks down to its node
+    auto assign_keys = [&](const OctBounds* /*B*/, const int* codes, int nLive) {
+        for (int i = tid; i < pyrTotal; i += nth) pyr[i] = -1;
+        __syncthreads();
+        for (int i = tid; i < nLive; i += nth) {
+            const int c = codes[i];
+            pyr[cell_idx(c >> 24, (c >> 16) & 0xFF, c & 0xFFFF)] = i;
+        }
+        __syncthreads();
+        for (int k = tid; k < n; k += nth) {
+            const uint32_t e = keys[k];
+            const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
+            const int r = min((int)__fdiv_rn((float)x, hX), nIni - 1);
+            const OctBounds b = sh_rootB[r];
+            int ulx = b.ulx, brx = b.brx, uly = b.uly, bry = b.bry, pth = 0, d = 0, t;
+            while ((t = pyr[cell_idx(d, r, pth)]) < 0 && d < D0) {
+                const int mx = ulx + ((brx - ulx + 1) >> 1), my = uly + ((bry - uly + 1) >> 1);
+                int q = 0;
+                if (x < mx) brx = mx; else { ulx = mx; q = 1; }
+                if (y < my) bry = my; else { uly = my; q += 2; }
+                pth = pth * 4 + q;
+                ++d;
+            }
+            if (t < 0) { atomicOr(status, 8); t = 0; }          // cannot happen: the leaves partition the keys
+            kn[k] = (uint16_t)t;
+        }
+        __syncthreads();
+    };
 
     for (int round = 0; round < 64; ++round) {
         const OctBounds* B = bnd[cur];
@@ -604,7 +660,35 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
         OctBounds* B2 = bnd[cur ^ 1];
         int* Cn2 = cnt[cur ^ 1];
         const int prevSize = live;
-        // 1. child[4 i ..] = child key counts of every expandable node i (counted when the keys moved into it)
+        // 1. child[4 i ..] = child key counts of every expandable node i: read from the count pyramid while the nodes
+        //    are not deeper than D0, counted when the keys moved into the node afterwards
+        if (usePyr && round == D0) {
+            // the tree grows below the pyramid: give the keys their nodes and count the children of the expandable ones
+            assign_keys(B, code[cur], live);
+            usePyr = false;
+            for (int i = tid; i < 4 * live; i += nth) child[i] = 0;
+            __syncthreads();
+            for (int k = tid; k < n; k += nth) {
+                const int nd = kn[k];
+                if (Cn[nd] > 1) {
+                    const uint32_t e = keys[k];
+                    const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
+                    const OctBounds b = B[nd];
+                    const int mx = b.ulx + ((b.brx - b.ulx + 1) >> 1), my = b.uly + ((b.bry - b.uly + 1) >> 1);
+                    atomicAdd(&child[nd * 4 + (x < mx ? 0 : 1) + (y < my ? 0 : 2)], 1);
+                }
+            }
+            __syncthreads();
+        } else if (usePyr) {
+            const int* cd = code[cur];
+            for (int i = tid; i < live; i += nth)
+                if (Cn[i] > 1) {
+                    const int c = cd[i], d = c >> 24;
+                    const int o = lvl_off(d + 1) + 4 * ((((c >> 16) & 0xFF) << (2 * d)) + (c & 0xFFFF));
+                    child[4 * i] = pyr[o]; child[4 * i + 1] = pyr[o + 1]; child[4 * i + 2] = pyr[o + 2]; child[4 * i + 3] = pyr[o + 3];
+                }
+            __syncthreads();
+        }
         // 2. push rank of the nodes to split
         int nSplit;
         if (!careful) {
@@ -689,6 +773,7 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
                 const int mx = b.ulx + ((b.brx - b.ulx + 1) >> 1), my = b.uly + ((b.bry - b.uly + 1) >> 1);
                 int pp = aux0[rankv[i]];
                 int* ch = child + 4 * i;
+                const int cdi = code[cur][i];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int c = ch[q];
@@ -702,6 +787,7 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
                         nb.bry = (q & 2) ? b.bry : (short)my;
                         B2[ni] = nb;
                         Cn2[ni] = c;
+                        code[cur ^ 1][ni] = (((cdi >> 24) + 1) << 24) | (cdi & 0xFF0000) | (((cdi & 0xFFFF) << 2) + q);
                         myExp += c > 1;
                         ch[q] = ni;
                         child2[4 * ni] = 0; child2[4 * ni + 1] = 0; child2[4 * ni + 2] = 0; child2[4 * ni + 3] = 0;
@@ -711,13 +797,15 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
                 const int ni = P + aux1[i];
                 B2[ni] = B[i];
                 Cn2[ni] = Cn[i];
+                code[cur ^ 1][ni] = code[cur][i];
                 newIdx[i] = ni;
             }
         }
         if (myExp) atomicAdd(&sh_nExp, myExp);
         __syncthreads();
-        // 4. move the keys; a key that lands in a node with more than one key is counted for that node's next split
-        for (int base = 0; base < n; base += nth) {
+        // 4. (below the pyramid only) move the keys; a key that lands in a node with more than one key is counted for that
+        //    node's next split
+        for (int base = 0; !usePyr && base < n; base += nth) {
             const int k = base + tid;
             int c = -1;
             if (k < n) {
@@ -742,7 +830,7 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
         }
         const int nToExpand = sh_nExp;
         __syncthreads();
-        { int* t = child; child = child2; child2 = t; }
+        if (!usePyr) { int* t = child; child = child2; child2 = t; }
         cur ^= 1;
         live = newLive;
         // 5. termination (:655-662, :724-725)
@@ -751,6 +839,7 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
     }
 
     // ---- best key per node (:735-751): max score, ties -> first in (cell row, cell col, y, x) order
+    if (usePyr) assign_keys(bnd[cur], code[cur], live);
     // two steps: the node's best score with a native 32-bit atomic, then only the keys that hold that score compete for
     // "first in the reference's order" with the 64-bit one
     unsigned long long* best = reinterpret_cast<unsigned long long*>(child);
@@ -789,6 +878,19 @@ __global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree(ExtractGeom g, con
         if (live > L.keptCap) atomicOr(status, 4);
         keptCount[f * g.nlevels + l] = min(live, L.keptCap);
     }
+}
+
+__global__ void __launch_bounds__(VIORB_OCT_LIGHT_THREADS, 4) k_octree(ExtractGeom g, const uint32_t* __restrict__ cand,
+                                                                       const int* __restrict__ candCount, uint16_t* __restrict__ keyNode,
+                                                                       KeptKp* __restrict__ kept, int* __restrict__ keptCount,
+                                                                       int* __restrict__ status) {
+    octree_body<VIORB_OCT_LIGHT_THREADS, VIORB_OCT_LIGHT_PYR_CELLS>(g, cand, candCount, keyNode, kept, keptCount, status, 0, VIORB_OCT_DENSE_KEYS);
+}
+__global__ void __launch_bounds__(VIORB_OCT_THREADS) k_octree_dense(ExtractGeom g, const uint32_t* __restrict__ cand,
+                                                                    const int* __restrict__ candCount, uint16_t* __restrict__ keyNode,
+                                                                    KeptKp* __restrict__ kept, int* __restrict__ keptCount,
+                                                                    int* __restrict__ status) {
+    octree_body<VIORB_OCT_THREADS, VIORB_OCT_PYR_CELLS>(g, cand, candCount, keyNode, kept, keptCount, status, VIORB_OCT_DENSE_KEYS + 1, 0x7fffffff);
 }
 
 // ---------------------------------------------------------------------------------------------

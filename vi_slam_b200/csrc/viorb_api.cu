@@ -142,7 +142,7 @@ struct viorb_extractor {
     BlurTiles blurTiles;
     int totalBlurTiles = 0;
     std::vector<CellDesc> cells;
-    size_t fastSmem = 0, octSmem = 0;
+    size_t fastSmem = 0, octSmem = 0, octSmemDense = 0;
     // limits the arenas were sized for
     size_t capArena = 0, capCand = 0, capKept = 0, capCells = 0, capXTab = 0, capYTab = 0;
     int capOut = 0;
@@ -152,6 +152,8 @@ struct viorb_extractor {
     // host-batch pipelining (viorb_extract_batch): images go up on cpStream and results come down on outStream
     // chunk by chunk while the kernels of the neighbouring chunks run on `stream`
     cudaStream_t cpStream = nullptr, outStream = nullptr;
+    cudaStream_t sideOct = nullptr;                       // k_octree_dense runs here, beside k_octree on `stream`
+    cudaEvent_t evOctFork = nullptr, evOctJoin = nullptr;
     cudaEvent_t evIn[VIORB_MAX_CHUNKS] = {}, evDone[VIORB_MAX_CHUNKS] = {}, evCnt[VIORB_MAX_CHUNKS] = {}, evEntry = nullptr;
     cudaEvent_t evJoin = nullptr;     // orders this handle's stream against a partner handle's (stereo)
     cudaEvent_t evBlock = nullptr;    // blocking-sync event: batch calls sleep on it instead of spinning in the driver
@@ -380,8 +382,9 @@ int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
     g.maxNodes = maxNodes;
     g.arenaStride = off;
     ex->fastSmem = fast_smem_bytes(g.tileW, g.tileH);
-    ex->octSmem = octree_smem_bytes(maxNodes);
-    if (ex->octSmem > 220 * 1024) return fail(VIORB_E_ARG, "nfeatures too large for the quadtree's shared memory");
+    ex->octSmem = octree_smem_bytes(maxNodes, VIORB_OCT_LIGHT_PYR_CELLS);
+    ex->octSmemDense = octree_smem_bytes(maxNodes, VIORB_OCT_PYR_CELLS);
+    if (ex->octSmemDense > 220 * 1024) return fail(VIORB_E_ARG, "nfeatures too large for the quadtree's shared memory");
     if (maxRW > 511 || maxRH > 127) return fail(VIORB_E_ARG, "FAST cell larger than supported");
     return VIORB_OK;
 }
@@ -458,6 +461,9 @@ int device_state(int dev, DeviceState** out) {
         };
         raise((const void*)k_fast);
         raise((const void*)k_octree);
+        raise((const void*)k_octree_dense);
+        // several ~40 KB CTAs of k_octree per SM: without this hint the driver picks a carveout that holds one
+        ok(cudaFuncSetAttribute(k_octree, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
 #if VIORB_KNN_VARIANT == 0
         ok(cudaFuncSetAttribute(tc5::k_knn2_tc5, cudaFuncAttributeMaxDynamicSharedMemorySize, tc5::SMEM_BYTES));
 #endif
@@ -501,8 +507,23 @@ int run_pipeline(viorb_extractor* ex, int f0, int n, int lap0, int lap1) {
                      ex->dCand.p, ex->dCandCount.p, ex->dStatus.p);
     }
     if (tm) CU(cudaEventRecord(ex->evX[2], st));
-    VIORB_LAUNCH(k_octree, dim3(n, g.nlevels), dim3(VIORB_OCT_THREADS), ex->octSmem, st, g, ex->dCand.p, ex->dCandCount.p,
-                 ex->dKeyNode.p, ex->dKept.p, ex->dKeptCount.p, ex->dStatus.p);
+    // the dense jobs (few, long) run beside the light ones on the handle's side stream; with the stage timers on, in line
+    {
+        cudaStream_t sd = st;
+        if (!tm && ex->sideOct) {
+            CU(cudaEventRecord(ex->evOctFork, st));
+            CU(cudaStreamWaitEvent(ex->sideOct, ex->evOctFork, 0));
+            sd = ex->sideOct;
+        }
+        VIORB_LAUNCH(k_octree_dense, dim3(n, g.nlevels), dim3(VIORB_OCT_THREADS), ex->octSmemDense, sd, g, ex->dCand.p, ex->dCandCount.p,
+                     ex->dKeyNode.p, ex->dKept.p, ex->dKeptCount.p, ex->dStatus.p);
+        VIORB_LAUNCH(k_octree, dim3(n, g.nlevels), dim3(VIORB_OCT_LIGHT_THREADS), ex->octSmem, st, g, ex->dCand.p, ex->dCandCount.p,
+                     ex->dKeyNode.p, ex->dKept.p, ex->dKeptCount.p, ex->dStatus.p);
+        if (sd != st) {
+            CU(cudaEventRecord(ex->evOctJoin, sd));
+            CU(cudaStreamWaitEvent(st, ex->evOctJoin, 0));
+        }
+    }
     if (tm) CU(cudaEventRecord(ex->evX[3], st));
     VIORB_LAUNCH(k_orient, dim3((g.keptPerFrame + 7) / 8, n), dim3(256), 0, st, g, fs, ex->dOrientTab.p, ex->dSlotLevel.p, ex->dKept.p,
                  ex->dKeptCount.p);
@@ -751,6 +772,9 @@ int viorb_extractor_create(const viorb_params* params, viorb_extractor** out) {
     ok(ex->hDesc.alloc(B * ex->capOut * 32));
     ok(ex->hCounts.alloc(B * 2 + 8));
     ok(cudaStreamCreateWithFlags(&ex->cpStream, cudaStreamNonBlocking));
+    ok(cudaStreamCreateWithFlags(&ex->sideOct, cudaStreamNonBlocking));
+    ok(cudaEventCreateWithFlags(&ex->evOctFork, cudaEventDisableTiming));
+    ok(cudaEventCreateWithFlags(&ex->evOctJoin, cudaEventDisableTiming));
     ok(cudaStreamCreateWithFlags(&ex->outStream, cudaStreamNonBlocking));
     for (int i = 0; i < VIORB_MAX_CHUNKS; ++i) {
         ok(cudaEventCreateWithFlags(&ex->evIn[i], cudaEventDisableTiming));
@@ -798,6 +822,9 @@ void viorb_extractor_destroy(viorb_extractor* ex) {
     if (ex->evJoin) cudaEventDestroy(ex->evJoin);
     if (ex->evBlock) cudaEventDestroy(ex->evBlock);
     if (ex->cpStream) { cudaStreamSynchronize(ex->cpStream); cudaStreamDestroy(ex->cpStream); }
+    if (ex->sideOct) { cudaStreamSynchronize(ex->sideOct); cudaStreamDestroy(ex->sideOct); }
+    if (ex->evOctFork) cudaEventDestroy(ex->evOctFork);
+    if (ex->evOctJoin) cudaEventDestroy(ex->evOctJoin);
     if (ex->outStream) { cudaStreamSynchronize(ex->outStream); cudaStreamDestroy(ex->outStream); }
     if (ex->ownStream && ex->stream) cudaStreamDestroy(ex->stream);
     delete ex;
