@@ -113,7 +113,8 @@ struct viorb_vocabulary {
 
 // buffers of viorb_f2f_batch (host_f2f.inc)
 struct viorb_f2f_state {
-    DevBuf<int> cellStart, cellList, listStart, totals, pairBase, n1eff, matchedDist, m21, nMatches;
+    DevBuf<int> cellStart, cellList, listStart, totals, pairBase, n1eff, matchedDist, m21, nMatches, accepted;
+    DevBuf<float4> cellKp;
     DevBuf<uint32_t> list;
     DevBuf<WinSrc> src;
     DevBuf<float> prevMatched;
@@ -123,8 +124,8 @@ struct viorb_f2f_state {
     bool ready = false;
     int lastPairs = 0;
     void release() {
-        cellStart.release(); cellList.release(); listStart.release(); totals.release(); pairBase.release(); n1eff.release();
-        matchedDist.release(); m21.release(); nMatches.release(); list.release(); src.release(); prevMatched.release();
+        cellStart.release(); cellList.release(); cellKp.release(); listStart.release(); totals.release(); pairBase.release(); n1eff.release();
+        matchedDist.release(); m21.release(); nMatches.release(); accepted.release(); list.release(); src.release(); prevMatched.release();
         binOf.release(); matches12.release();
         ready = false;
     }
@@ -462,6 +463,8 @@ int device_state(int dev, DeviceState** out) {
         raise((const void*)k_fast);
         raise((const void*)k_octree);
         raise((const void*)k_octree_dense);
+        raise((const void*)k_resolve_ini);
+        raise((const void*)k_resolve_proj);
         // several ~40 KB CTAs of k_octree per SM: without this hint the driver picks a carveout that holds one
         ok(cudaFuncSetAttribute(k_octree, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
 #if VIORB_KNN_VARIANT == 0
@@ -1427,10 +1430,11 @@ GridBounds make_bounds(const viorb_grid_bounds& b) {
 // list filled.  desc1 may be null (distance 0: plain GetFeaturesInArea).
 struct WindowWork {
     DevBuf<int> cellStart, cellList, listStart, totals, pairBase, n1, n2;
+    DevBuf<float4> cellKp;
     DevBuf<uint32_t> list;
     WinBatch wb{};
     void release() {
-        cellStart.release(); cellList.release(); listStart.release(); totals.release(); pairBase.release();
+        cellStart.release(); cellList.release(); cellKp.release(); listStart.release(); totals.release(); pairBase.release();
         n1.release(); n2.release(); list.release();
     }
 };
@@ -1443,13 +1447,14 @@ int window_lists(WindowWork& w, int npairs, int cap1, int cap2, const int32_t* n
     w.wb.cap1 = cap1; w.wb.cap2 = cap2; w.wb.n1 = w.n1.p; w.wb.n2 = w.n2.p; w.wb.n1fill = nullptr; w.wb.off2 = dOff2;
     CU(w.cellStart.alloc((size_t)npairs * (VIORB_GRID_CELLS + 1)));
     CU(w.cellList.alloc((size_t)npairs * cap2));
+    CU(w.cellKp.alloc((size_t)npairs * std::max(cap2, 1)));
     CU(w.listStart.alloc((size_t)npairs * (cap1 + 1)));
     CU(w.totals.alloc(npairs));
     CU(w.pairBase.alloc(npairs));
     cudaStream_t st = 0;
-    VIORB_LAUNCH(k_grid_build, dim3(npairs), dim3(256), 0, st, w.wb, gb, dKps2, w.cellStart.p, w.cellList.p);
+    VIORB_LAUNCH(k_grid_build, dim3(npairs), dim3(256), 0, st, w.wb, gb, dKps2, w.cellStart.p, w.cellList.p, w.cellKp.p);
     const dim3 gl((cap1 + 7) / 8, npairs);
-    VIORB_LAUNCH(k_window_list, gl, dim3(256), 0, st, w.wb, gb, dSrc, dDesc1, dKps2, dDesc2, dURight2, w.cellStart.p, w.cellList.p,
+    VIORB_LAUNCH(k_window_list, gl, dim3(256), 0, st, w.wb, gb, dSrc, dDesc1, dKps2, dDesc2, dURight2, w.cellStart.p, w.cellKp.p,
                  w.listStart.p, (uint32_t*)nullptr, 0);
     VIORB_LAUNCH(k_window_scan, dim3(npairs), dim3(256), 0, st, w.wb, w.listStart.p, w.totals.p);
     std::vector<int> tot(npairs), base(npairs);
@@ -1460,17 +1465,21 @@ int window_lists(WindowWork& w, int npairs, int cap1, int cap2, const int32_t* n
     CU(cudaMemcpy(w.pairBase.p, base.data(), sizeof(int) * npairs, cudaMemcpyHostToDevice));
     VIORB_LAUNCH(k_window_rebase, dim3((cap1 + 256) / 256, npairs), dim3(256), 0, st, w.wb, w.listStart.p, w.pairBase.p);
     CU(w.list.alloc(sum));
-    VIORB_LAUNCH(k_window_list, gl, dim3(256), 0, st, w.wb, gb, dSrc, dDesc1, dKps2, dDesc2, dURight2, w.cellStart.p, w.cellList.p,
+    VIORB_LAUNCH(k_window_list, gl, dim3(256), 0, st, w.wb, gb, dSrc, dDesc1, dKps2, dDesc2, dURight2, w.cellStart.p, w.cellKp.p,
                  w.listStart.p, w.list.p, 1);
     CU(cudaGetLastError());
     return VIORB_OK;
 }
 
+// dynamic shared memory of k_resolve_ini: vMatchedDistance + vnMatches21 of the target frame (0 = keep them in global memory)
+size_t resolve_ini_smem(int cap2) { return (size_t)cap2 * 8 <= 200 * 1024 ? (size_t)cap2 * 8 : 0; }
+
 int need_device(int device) {
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= device) return fail(VIORB_E_NO_DEVICE, "no CUDA device: libviorb has no CPU path");
     CU(cudaSetDevice(device));
-    return VIORB_OK;
+    DeviceState* ds = nullptr;
+    return device_state(device, &ds);          // kernel attributes (dynamic shared-memory limits) are set once per device
 }
 
 }  // namespace
@@ -1528,10 +1537,11 @@ int viorb_search_for_initialization(int npairs, int cap1, int cap2, const viorb_
     DevBuf<uint8_t> dD1, dD2;
     DevBuf<float> dPM;
     DevBuf<WinSrc> dS;
-    DevBuf<int> dMD, dM21, dM12, dNM;
+    DevBuf<int> dMD, dM21, dM12, dNM, dAcc;
     DevBuf<int8_t> dBin;
     WindowWork w;
     cudaError_t e = upload(dK1, kps1, N1);
+    if (e == cudaSuccess) e = dAcc.alloc(N1);
     if (e == cudaSuccess) e = upload(dD1, desc1, N1 * 32);
     if (e == cudaSuccess) e = upload(dK2, cap2 ? kps2 : nullptr, N2);
     if (e == cudaSuccess) e = upload(dD2, cap2 ? desc2 : nullptr, N2 * 32);
@@ -1558,8 +1568,9 @@ int viorb_search_for_initialization(int npairs, int cap1, int cap2, const viorb_
     }
     if (!rc) rc = window_lists(w, npairs, cap1, cap2, n1, n2, gb, dS.p, dD1.p, dK2.p, dD2.p, nullptr);
     if (!rc) {
-        VIORB_LAUNCH(k_resolve_ini, dim3(npairs), dim3(32), 0, (cudaStream_t)0, w.wb, dK1.p, dK2.p, w.listStart.p, w.list.p, nn_ratio,
-                     check_orientation, dMD.p, dM21.p, dBin.p, dM12.p, dPM.p, dNM.p);
+        const int useSmem = resolve_ini_smem(cap2) ? 1 : 0;
+        VIORB_LAUNCH(k_resolve_ini, dim3(npairs), dim3(32), resolve_ini_smem(cap2), (cudaStream_t)0, w.wb, dK1.p, dK2.p, w.listStart.p,
+                     w.list.p, nn_ratio, check_orientation, dMD.p, dM21.p, dBin.p, dAcc.p, dM12.p, dPM.p, dNM.p, useSmem);
         e = cudaGetLastError();
         if (e == cudaSuccess) e = cudaMemcpy(matches12, dM12.p, sizeof(int32_t) * N1, cudaMemcpyDeviceToHost);
         if (e == cudaSuccess) e = cudaMemcpy(prev_matched, dPM.p, sizeof(float) * 2 * N1, cudaMemcpyDeviceToHost);
@@ -1567,7 +1578,7 @@ int viorb_search_for_initialization(int npairs, int cap1, int cap2, const viorb_
         if (e != cudaSuccess) rc = fail(VIORB_E_CUDA, cudaGetErrorString(e));
     }
     dK1.release(); dK2.release(); dD1.release(); dD2.release(); dPM.release(); dS.release(); dMD.release(); dM21.release();
-    dM12.release(); dBin.release(); dNM.release(); w.release();
+    dM12.release(); dBin.release(); dNM.release(); dAcc.release(); w.release();
     return rc;
 }
 
@@ -1630,7 +1641,7 @@ int viorb_search_by_projection(int npairs, int cap1, int cap2, const float* uv, 
     if (e == cudaSuccess && !blocked2) e = cudaMemset(dBL.p, 0, N2);
     if (e == cudaSuccess) e = dS.alloc(N1);
     if (e == cudaSuccess) e = dAS.alloc(N2);
-    if (e == cudaSuccess) e = dPI.alloc(N1 * 2);
+    if (e == cudaSuccess) e = dPI.alloc(N1 * 4);
     if (e == cudaSuccess) e = dPB.alloc(N1 * 2);
     if (e == cudaSuccess) e = dNM.alloc(npairs);
     rc = e == cudaSuccess ? VIORB_OK : fail(VIORB_E_CUDA, cudaGetErrorString(e));
@@ -1653,7 +1664,7 @@ int viorb_search_by_projection(int npairs, int cap1, int cap2, const float* uv, 
     if (!rc) rc = window_lists(w, npairs, cap1, cap2, n1, nL.data(), gb, dS.p, dDM.p, dK2.p, dD2.p, u_right2 ? dUR.p : nullptr);
     if (!rc && rig) rc = window_lists(wR, npairs, cap1, cap2, n1, nR.data(), gb, dSR.p, dDM.p, dK2.p, dD2.p, nullptr, dNLeft.p);
     if (!rc) {
-        VIORB_LAUNCH(k_resolve_proj, dim3(npairs), dim3(32), 0, (cudaStream_t)0, w.wb, dLA.p, dOB.p, dK2.p, w.listStart.p, w.list.p,
+        VIORB_LAUNCH(k_resolve_proj, dim3(npairs), dim3(32), (size_t)cap2, (cudaStream_t)0, w.wb, dLA.p, dOB.p, dK2.p, w.listStart.p, w.list.p,
                      rig ? wR.listStart.p : (const int*)nullptr, rig ? wR.list.p : (const uint32_t*)nullptr,
                      rig ? dNLeft.p : (const int*)nullptr, cap2, check_orientation, dBL.p, dPI.p, dPB.p, dAS.p, dNM.p, dN2.p);
         e = cudaGetLastError();
