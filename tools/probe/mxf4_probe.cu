@@ -1,0 +1,309 @@
+// mxf4_probe.cu — semantics probe for tcgen05.mma kind::mxf4.block_scale (packed e2m1 operands, ue8m0 block-32
+// scales in tensor memory) on sm_100a.  Answers, on the GPU, the questions the fp4 Hamming kNN kernel depends on:
+//   T1  does a K-major no-swizzle descriptor with 16-byte core-matrix rows address packed 4-bit operands as it does bytes?
+//   T2  which nibble of a byte is the even K element?
+//   T3  which bytes of the scale-factor word do a_sf_id / b_sf_id select?
+//   T4  is the sum (2^23-sized constant) + (64 * Hamming) + (column index) accumulated EXACTLY in fp32?
+//   T5  the same with the constant written to the accumulator beforehand (tcgen05.st) instead of coming from the MMA
+// build: nvcc -gencode arch=compute_100a,code=sm_100a -O2 -o mxf4_probe mxf4_probe.cu ; run: ./mxf4_probe
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+constexpr int M = 128, N = 256, MAXS = 6;
+constexpr int LBO = 128;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, int sbo) {
+    return (uint64_t)((addr & 0x3FFFF) >> 4) | ((uint64_t)(LBO >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) | (1ull << 46);
+}
+
+// A: [S][128][32] bytes, B: [S][256][32] bytes (row-major, 32 bytes = 64 e2m1 elements of one K step)
+__global__ void __launch_bounds__(128) k_probe(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B, uint32_t sfaWord,
+                                               uint32_t sfbWord, const int* __restrict__ ids, int S, int prefill, float prefillVal,
+                                               float* __restrict__ D) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tmemSlot;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int KCH = 2 * S, SBO = KCH * 128;
+    unsigned char* sA = smem;
+    unsigned char* sB = smem + (M / 8) * SBO;
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&bar)), "r"(1));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmemSlot)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    for (int s = 0; s < S; ++s) {
+        for (int i = tid; i < M * 2; i += 128) {
+            const int r = i >> 1, c = i & 1;
+            *reinterpret_cast<uint4*>(sA + (r >> 3) * SBO + (r & 7) * 16 + (2 * s + c) * LBO) =
+                *reinterpret_cast<const uint4*>(A + ((size_t)s * M + r) * 32 + c * 16);
+        }
+        for (int i = tid; i < N * 2; i += 128) {
+            const int r = i >> 1, c = i & 1;
+            *reinterpret_cast<uint4*>(sB + (r >> 3) * SBO + (r & 7) * 16 + (2 * s + c) * LBO) =
+                *reinterpret_cast<const uint4*>(B + ((size_t)s * N + r) * 32 + c * 16);
+        }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = tmemSlot;
+    const uint32_t lane0 = tmem + ((uint32_t)(warp * 32) << 16);
+    // scale factors: the same word in every lane and column of the SFA (4 columns) and SFB (8 columns) regions
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1,%1,%1,%1};" ::"r"(lane0 + 256), "r"(sfaWord) : "memory");
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(lane0 + 272), "r"(sfbWord) : "memory");
+    if (prefill) {
+        const uint32_t pv = __float_as_uint(prefillVal);
+        for (int c = 0; c < N; c += 8)
+            asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(lane0 + c), "r"(pv) : "memory");
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    if (tid == 0) {
+        const uint64_t dA = smem_desc(smem_u32(sA), SBO), dB = smem_desc(smem_u32(sB), SBO);
+        for (int s = 0; s < S; ++s) {
+            // e2m1 x e2m1 (format 1), ue8m0 scales, K-major, N >> 3, M >> 4, scale-factor byte ids, K = 64
+            const uint32_t idesc = ((uint32_t)(ids[2 * s + 1] & 3) << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | (1u << 23) |
+                                   ((uint32_t)(M >> 4) << 24) | ((uint32_t)(ids[2 * s] & 3) << 29);
+            const uint32_t acc = (s > 0 || prefill) ? 1u : 0u;
+            asm volatile(
+                "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%5], [%6], p;\n\t}"
+                ::"r"(tmem), "l"(dA + (uint64_t)((s * 2 * LBO) >> 4)), "l"(dB + (uint64_t)((s * 2 * LBO) >> 4)), "r"(idesc), "r"(acc),
+                  "r"(tmem + 256), "r"(tmem + 272) : "memory");
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)) : "memory");
+    }
+    {
+        uint32_t done = 0;
+        long spins = 0;
+        while (!done) {
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                         : "=r"(done) : "r"(smem_u32(&bar)), "r"(0) : "memory");
+            if (++spins > (1l << 26)) __trap();
+        }
+    }
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const int row = warp * 32 + (tid & 31);
+    for (int c = 0; c < N; c += 8) {
+        uint32_t v[8];
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                     : "r"(lane0 + c) : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        for (int j = 0; j < 8; ++j) D[(size_t)row * N + c + j] = __uint_as_float(v[j]);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+    }
+}
+
+// ------------------------------------------------------------------------------------------- host
+static const float kE2M1[16] = {0.f, .5f, 1.f, 1.5f, 2.f, 3.f, 4.f, 6.f, -0.f, -.5f, -1.f, -1.5f, -2.f, -3.f, -4.f, -6.f};
+
+struct Case {
+    int S = 1;
+    std::vector<uint8_t> A, B;        // nibble codes, [S][rows][64]
+    uint32_t sfa = 0x7f7f7f7fu, sfb = 0x7f7f7f7fu;
+    int ids[2 * MAXS] = {0};
+    int prefill = 0;
+    float prefillVal = 0.f;
+    explicit Case(int s) : S(s), A((size_t)s * M * 64, 0), B((size_t)s * N * 64, 0) {}
+    uint8_t& a(int s, int r, int k) { return A[((size_t)s * M + r) * 64 + k]; }
+    uint8_t& b(int s, int r, int k) { return B[((size_t)s * N + r) * 64 + k]; }
+};
+
+static std::vector<uint8_t> pack(const std::vector<uint8_t>& codes, bool lowFirst) {
+    std::vector<uint8_t> out(codes.size() / 2);
+    for (size_t i = 0; i < out.size(); ++i)
+        out[i] = lowFirst ? (uint8_t)(codes[2 * i] | (codes[2 * i + 1] << 4)) : (uint8_t)(codes[2 * i + 1] | (codes[2 * i] << 4));
+    return out;
+}
+
+static std::vector<float> run(const Case& c, bool lowFirst) {
+    std::vector<uint8_t> a = pack(c.A, lowFirst), b = pack(c.B, lowFirst);
+    uint8_t *dA, *dB;
+    int* dIds;
+    float* dD;
+    cudaMalloc(&dA, a.size());
+    cudaMalloc(&dB, b.size());
+    cudaMalloc(&dIds, sizeof(c.ids));
+    cudaMalloc(&dD, sizeof(float) * M * N);
+    cudaMemcpy(dA, a.data(), a.size(), cudaMemcpyHostToDevice);
+    cudaMemcpy(dB, b.data(), b.size(), cudaMemcpyHostToDevice);
+    cudaMemcpy(dIds, c.ids, sizeof(c.ids), cudaMemcpyHostToDevice);
+    cudaMemset(dD, 0xff, sizeof(float) * M * N);
+    const int smem = (M / 8 + N / 8) * 2 * c.S * 128;
+    cudaFuncSetAttribute(k_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    k_probe<<<1, 128, smem>>>(dA, dB, c.sfa, c.sfb, dIds, c.S, c.prefill, c.prefillVal, dD);
+    cudaError_t e = cudaDeviceSynchronize();
+    std::vector<float> D((size_t)M * N, NAN);
+    if (e != cudaSuccess) {
+        printf("  kernel failed: %s\n", cudaGetErrorString(e));
+        exit(1);
+    }
+    cudaMemcpy(D.data(), dD, sizeof(float) * M * N, cudaMemcpyDeviceToHost);
+    cudaFree(dA); cudaFree(dB); cudaFree(dIds); cudaFree(dD);
+    return D;
+}
+
+// expected value with scale bytes chosen by (byte index of block 0, byte index of block 1) per step
+static double expect(const Case& c, int r, int n, const int (*selA)[2], const int (*selB)[2]) {
+    double acc = c.prefill ? c.prefillVal : 0.0;
+    for (int s = 0; s < c.S; ++s)
+        for (int blk = 0; blk < 2; ++blk) {
+            const int ea = (int)((c.sfa >> (8 * selA[s][blk])) & 0xff) - 127, eb = (int)((c.sfb >> (8 * selB[s][blk])) & 0xff) - 127;
+            double sum = 0;
+            for (int k = 32 * blk; k < 32 * blk + 32; ++k)
+                sum += (double)kE2M1[c.A[((size_t)s * M + r) * 64 + k]] * (double)kE2M1[c.B[((size_t)s * N + n) * 64 + k]];
+            acc += std::ldexp(sum, ea + eb);
+        }
+    return acc;
+}
+
+static long compare(const Case& c, const std::vector<float>& D, const int (*selA)[2], const int (*selB)[2], bool verbose) {
+    long bad = 0;
+    for (int r = 0; r < M; ++r)
+        for (int n = 0; n < N; ++n) {
+            const double e = expect(c, r, n, selA, selB);
+            if ((double)D[(size_t)r * N + n] != e) {
+                if (verbose && bad < 6) printf("    D[%d][%d] = %.3f expected %.3f\n", r, n, D[(size_t)r * N + n], e);
+                ++bad;
+            }
+        }
+    return bad;
+}
+
+static uint32_t rng = 12345u;
+static uint32_t rnd() { rng = rng * 1664525u + 1013904223u; return rng >> 8; }
+
+int main() {
+    const int sel0[MAXS][2] = {{0, 1}, {0, 1}, {0, 1}, {0, 1}, {0, 1}, {0, 1}};
+    // T1: all ones
+    {
+        Case c(1);
+        std::fill(c.A.begin(), c.A.end(), 2);
+        std::fill(c.B.begin(), c.B.end(), 2);
+        std::vector<float> D = run(c, true);
+        printf("T1 all-ones K64: D[0][0] = %.1f D[127][255] = %.1f mismatches vs 64: %ld\n", D[0], D[(size_t)127 * N + 255],
+               compare(c, D, sel0, sel0, true));
+    }
+    // T2: nibble order / K order / row-column addressing
+    bool lowFirst = true;
+    {
+        Case c(2);
+        for (int s = 0; s < 2; ++s) {
+            for (int r = 0; r < M; ++r) c.a(s, r, (r * 7 + s * 3) % 64) = 2;                       // one 1.0 per row and step
+            for (int n = 0; n < N; ++n)
+                for (int k = 0; k < 64; ++k) c.b(s, n, k) = (uint8_t)(1 + (k + n + s) % 7);       // value depends on k, n and the step
+        }
+        for (int lf = 1; lf >= 0; --lf) {
+            std::vector<float> D = run(c, lf != 0);
+            const long bad = compare(c, D, sel0, sel0, false);
+            printf("T2 element order, %s nibble = even K: mismatches %ld\n", lf ? "low" : "high", bad);
+            if (bad == 0) lowFirst = lf != 0;
+        }
+    }
+    // T3: which scale bytes does sf_id select (A side, then B side)
+    for (int side = 0; side < 2; ++side)
+        for (int id = 0; id < 4; id += 2) {
+            Case c(1);
+            std::fill(c.A.begin(), c.A.end(), 2);
+            std::fill(c.B.begin(), c.B.end(), 2);
+            // block 0 only / block 1 only / both, to see each block's scale
+            float got[3];
+            for (int mode = 0; mode < 3; ++mode) {
+                Case d = c;
+                for (int r = 0; r < M; ++r)
+                    for (int k = 0; k < 64; ++k)
+                        if ((mode == 0 && k >= 32) || (mode == 1 && k < 32)) d.a(0, r, k) = 0;
+                (side ? d.sfb : d.sfa) = 0x7f7f7f7fu + 0x04030201u * 1u;       // bytes 128, 129, 130, 131 -> x2, x4, x8, x16
+                d.ids[side] = id;
+                std::vector<float> D = run(d, lowFirst);
+                got[mode] = D[(size_t)77 * N + 131];
+            }
+            printf("T3 %s sf_id %d: block0 sum %.1f (scale %.1f) block1 sum %.1f (scale %.1f) both %.1f\n", side ? "B" : "A", id, got[0],
+                   got[0] / 32, got[1], got[1] / 32, got[2]);
+        }
+    // T4 / T5: the kNN key arithmetic on random 256-bit rows
+    for (int variant = 0; variant < 3; ++variant) {
+        // variant 0: key step last, 1: key step first, 2: constant pre-stored in the accumulator (key step carries only the column)
+        Case c(5);
+        std::vector<uint32_t> qa((size_t)M * 8), tb((size_t)N * 8);
+        for (auto& w : qa) w = rnd() ^ (rnd() << 12);
+        for (auto& w : tb) w = rnd() ^ (rnd() << 12);
+        for (int i = 0; i < 8; ++i) { tb[8 * 5 + i] = qa[8 * 3 + i]; tb[8 * 9 + i] = ~qa[8 * 4 + i]; }   // Hamming 0 and 256
+        const int keyStep = variant == 1 ? 0 : 4, main0 = variant == 1 ? 1 : 0;
+        for (int r = 0; r < M; ++r)
+            for (int k = 0; k < 256; ++k) c.a(main0 + k / 64, r, k % 64) = ((qa[(size_t)r * 8 + k / 32] >> (k % 32)) & 1) ? 0x2 : 0xA;
+        for (int n = 0; n < N; ++n) {
+            const bool pad = n >= 250;
+            for (int k = 0; k < 256; ++k)
+                c.b(main0 + k / 64, n, k % 64) = pad ? 0 : (((tb[(size_t)n * 8 + k / 32] >> (k % 32)) & 1) ? 0xA : 0x2);
+            const int col = n & 63, d0 = col & 3, d1 = (col >> 2) & 3, d2 = col >> 4;
+            const uint8_t small[4] = {0, 2, 4, 5};                 // codes of 0, 1, 2, 3
+            const uint8_t x2[4] = {0, 6, 6, 7}, y2[4] = {0, 0, 6, 7};   // x + y = 4 d2
+            c.b(keyStep, n, 0) = small[d0];
+            c.b(keyStep, n, 1) = small[d1];
+            c.b(keyStep, n, 2) = x2[d2];
+            c.b(keyStep, n, 3) = y2[d2];
+            if (variant != 2) {
+                for (int k = 32; k < 36; ++k) c.b(keyStep, n, k) = 7;
+                c.b(keyStep, n, 36) = 1;
+            }
+            c.b(keyStep, n, 37) = pad ? 2 : 0;
+        }
+        for (int r = 0; r < M; ++r) {
+            c.a(keyStep, r, 0) = 2;
+            c.a(keyStep, r, 1) = 6;
+            c.a(keyStep, r, 2) = 6;
+            c.a(keyStep, r, 3) = 6;
+            for (int k = 32; k < 36; ++k) c.a(keyStep, r, k) = 7;
+            c.a(keyStep, r, 36) = 1;
+            c.a(keyStep, r, 37) = 1;
+        }
+        // scale bytes: main steps use bytes (0, 1) = 2^5, the key step bytes (2, 3) = 2^0 and 2^16
+        c.sfa = 132u | (132u << 8) | (127u << 16) | (143u << 24);
+        int selA[MAXS][2];
+        for (int s = 0; s < 5; ++s) {
+            c.ids[2 * s] = s == keyStep ? 2 : 0;
+            selA[s][0] = s == keyStep ? 2 : 0;
+            selA[s][1] = s == keyStep ? 3 : 1;
+        }
+        if (variant == 2) { c.prefill = 1; c.prefillVal = 9453568.f; }
+        std::vector<float> D = run(c, lowFirst);
+        const long bad = compare(c, D, selA, sel0, true);
+        // and the decoded key: low 16 bits of the fp32 pattern = 8192 + 64 Hamming + column
+        long badKey = 0;
+        for (int r = 0; r < M; ++r)
+            for (int n = 0; n < 250; ++n) {
+                int h = 0;
+                for (int i = 0; i < 8; ++i) h += __builtin_popcount(qa[(size_t)r * 8 + i] ^ tb[(size_t)n * 8 + i]);
+                uint32_t bits;
+                std::memcpy(&bits, &D[(size_t)r * N + n], 4);
+                if ((bits & 0xFFFFu) != (uint32_t)(8192 + 64 * h + (n & 63))) ++badKey;
+            }
+        uint32_t padBits;
+        std::memcpy(&padBits, &D[(size_t)5 * N + 251], 4);
+        printf("T%d key arithmetic (%s): value mismatches %ld, key mismatches %ld of %d, D[3][5] = %.1f (Hamming 0), D[4][9] = %.1f (256), pad low16 = %u\n",
+               variant == 2 ? 5 : 4, variant == 0 ? "key step last" : variant == 1 ? "key step first" : "constant pre-stored", bad, badKey,
+               M * 250, D[(size_t)3 * N + 5], D[(size_t)4 * N + 9], padBits & 0xFFFFu);
+    }
+    return 0;
+}
