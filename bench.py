@@ -681,17 +681,18 @@ def run_ours(args, wl, rank, world, local_rank):
         "stage_timing": "second pass of K steps, every handle on one stream, CUDA events around each stage", "roofline": roofline,
     }
     if stereo:
-        # matcher: brute-force kNN-2 left -> right on the tensor cores, k_knn2_tc5 (tcgen05.mma kind::i8): denominator =
-        # 148 SMs x 8192 u8 MAC / clk / SM (one M128 N256 K32 instruction per 128 clk) at the measured max SM clock, 256
-        # algorithmic MAC per descriptor pair (the kernel executes 288: a ninth K block carries popc(train) and the column)
+        # matcher: brute-force kNN-2 left -> right on the tensor cores, k_knn2_f4 (tcgen05.mma kind::mxf4.block_scale):
+        # denominator = 148 SMs x 16384 4-bit MAC / clk / SM (one M128 N256 K64 instruction per 128 clk) at the measured max
+        # SM clock, 256 algorithmic MAC per descriptor pair (the kernel executes 320: a fifth K step carries the column and
+        # the constant that turns the fp32 accumulator into a 16-bit sort key)
         sm_mhz = float(json.load(open(peaks_path)).get("sm_max_mhz", 1965.0)) if os.path.exists(peaks_path) else 1965.0
-        pk = 148 * 8192 * sm_mhz * 1e6 / 256.0
+        pk = 148 * 16384 * sm_mhz * 1e6 / 256.0
+        ach = knn_pairs / (mean["knn2"] * 1e-3)
         line["match_roofline"] = {
-            "kernel": "k_knn2_tc5", "bound": "tensor (tcgen05.mma kind::i8, TMEM accumulators)", "pairs_per_launch": knn_pairs,
-            "achieved": knn_pairs / (mean["knn2"] * 1e-3), "peak": pk, "unit": "descriptor pairs/s",
-            "frac": knn_pairs / (mean["knn2"] * 1e-3) / pk,
-            "peak_source": f"nominal: 148 SM x 8192 u8 MAC/clk x {sm_mhz:.0f} MHz; measured floor of the kernel is shared-memory "
-                           "bandwidth (DESIGN.md section 5)"}
+            "kernel": "k_knn2_f4", "bound": "tensor (tcgen05.mma kind::mxf4.block_scale, TMEM accumulators)", "pairs_per_launch": knn_pairs,
+            "achieved": ach, "peak": pk, "unit": "descriptor pairs/s", "frac": ach / pk, "frac_of_i8_peak": ach / (pk / 2),
+            "peak_source": f"nominal: 148 SM x 16384 e2m1 MAC/clk x {sm_mhz:.0f} MHz (kind::i8, the round-1 kernel's pipe, is half "
+                           "of that); measured floors of the kernel in DESIGN.md section 5"}
     if sweep is not None:
         line["knn_sweep"] = {"transport": "viorb_knn2_sharded: in-place ncclAllGather of 16 B rows" if world > 1 else "single GPU, no exchange",
                              "n_gpus": world, "sizes": sweep}

@@ -265,10 +265,11 @@ def test_pinned_buffers_take_the_direct_dma_path():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("variant,flag", [("knn_popc", "-DVIORB_KNN_VARIANT=2"), ("knn_mma", "-DVIORB_KNN_VARIANT=1")])
+@pytest.mark.parametrize("variant,flag", [("knn_popc", "-DVIORB_KNN_VARIANT=2"), ("knn_mma", "-DVIORB_KNN_VARIANT=1"),
+                                          ("knn_i8", "-DVIORB_KNN_VARIANT=3")])
 def test_knn2_build_variants_match_too(variant, flag):
-    """The two earlier kNN-2 kernels are BUILD-time variants (the product library holds k_knn2_tc5 only): k_knn2 (LOP3/POPC)
-    and k_knn2_mma (warp-level IMMA) compiled into build_variants/ must equal the oracle as well."""
+    """The earlier kNN-2 kernels are BUILD-time variants (the product library holds k_knn2_f4 only): k_knn2 (LOP3/POPC),
+    k_knn2_mma (warp-level IMMA) and k_knn2_tc5 (tcgen05 kind::i8) compiled into build_variants/ must equal the oracle as well."""
     import shutil
     import __graft_entry__ as ge
     from vi_slam_b200 import matcher
@@ -276,7 +277,7 @@ def test_knn2_build_variants_match_too(variant, flag):
     if shutil.which("nvcc") is None and not os.path.exists("/usr/local/cuda/bin/nvcc"):
         pytest.skip("no nvcc on this box")
     lib = ge.build_variant(variant, [flag])
-    for nq, nt in ((2000, 2000), (130, 129), (5, 1), (1, 4000), (3000, 257)):
+    for nq, nt in ((2000, 2000), (130, 129), (5, 1), (1, 4000), (3000, 257), (300, 70000)):
         q, t = _syn().make_descriptors(nq, nt, seed=nq + nt)
         i, d = matcher.knn_match(q, t, lib_path=lib)
         oi, od = oracle.knn2(q, t, nthreads=4)
@@ -285,10 +286,11 @@ def test_knn2_build_variants_match_too(variant, flag):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("nq,nt", [(1, 1), (1, 2), (5, 0), (127, 255), (128, 256), (129, 257), (300, 63), (64, 65), (2013, 1987),
-                                   (1000, 70000)])
+                                   (1000, 70000), (127, 239), (128, 240), (129, 241), (260, 191), (33, 193), (250, 479), (130, 481)])
 def test_knn2_tile_edges_and_ties(nq, nt):
-    """Default kernel (k_knn2_tc5, tcgen05): shapes around its 128-row query tile / 256-row train tile / 64-column key
-    group, duplicate train rows (ties -> lower index), all-zero and all-ones rows (distance 0 and 256), empty train set."""
+    """Default kernel (k_knn2_f4, tcgen05 kind::mxf4): shapes around its 128-row query tile / 240-row train tile / 64- and
+    48-column key groups (and the 256-row tile of the kind::i8 variant), duplicate train rows (ties -> lower index),
+    all-zero and all-ones rows (distance 0 and 256), empty train set."""
     from vi_slam_b200 import matcher
     import oracle
     q, t = _syn().make_descriptors(nq, max(nt, 1), seed=nq * 7 + nt)
@@ -351,7 +353,7 @@ def test_stereo_batch_with_ragged_and_empty_sets():
 @pytest.mark.gpu
 @pytest.mark.parametrize("split", [1, 2, 5, 32])
 def test_knn2_train_range_split(split):
-    """k_knn2_tc5 cuts a query tile's train range over several CTAs when there are few query tiles (one stereo pair, the
+    """k_knn2_f4 cuts a query tile's train range over several CTAs when there are few query tiles (one stereo pair, the
     row-sharded sweep) and k_knn2_tc5_merge joins the partial pairs: forced split counts, incl. more splits than train tiles."""
     from vi_slam_b200 import matcher
     import oracle

@@ -13,6 +13,10 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from vi_slam_b200 import sharded, synthetic  # noqa: E402
 
+if os.environ.get("VIORB_TOOL_LIB"):      # A/B of a build variant (tools/variants.sh); the package itself has no such knob
+    from vi_slam_b200 import _lib  # noqa: E402
+    _lib.DEFAULT_LIB = os.path.abspath(os.environ["VIORB_TOOL_LIB"])
+
 
 def main():
     sizes = [int(a) for a in sys.argv[1:]] or [2000, 8000, 32000, 100000, 200000]
@@ -23,21 +27,20 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    sm = sharded.ShardedMatcher(device=local)
     for n in sizes:
         q, t = synthetic.make_descriptors(n, n, seed=n)
-        a, b, per = sharded.row_shard(n, world, rank)
-        qpad = np.zeros((per, 32), np.uint8)
-        qpad[: b - a] = q[a:b]
-        dq, dt = torch.from_numpy(qpad).cuda(), torch.from_numpy(t).cuda()
-        reps = 1 if n >= 100000 else 5
-        sharded.knn_match_sharded_device(dq, dt)                      # warm-up
+        a, b, per = sm.rows(n)
+        dq, dt = torch.from_numpy(np.ascontiguousarray(q[a:b])).cuda(), torch.from_numpy(t).cuda()
+        reps = 3 if n >= 100000 else 10
+        sm.match_device(dq, n, dt)                                    # warm-up
         torch.cuda.synchronize()
         if dist is not None:
             dist.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(reps):
-            out = sharded.knn_match_sharded_device(dq, dt)
+            out = sm.match_device(dq, n, dt)
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / reps
@@ -51,7 +54,7 @@ def main():
         if rank == 0:
             print(json.dumps({"workload": f"hamming_knn2_{n}x{n}", "n_gpus": world, "ms": ms, "pairs_per_s": n * n / (ms * 1e-3),
                               "queries_per_s": n / (ms * 1e-3), "checks_ok": ok, "gather_bytes_per_rank": per * 16,
-                              "kernel": os.environ.get("VIORB_KNN", "tc5")}), flush=True)
+                              "lib": os.path.basename(os.environ.get("VIORB_TOOL_LIB", "libviorb.so"))}), flush=True)
     if dist is not None:
         dist.destroy_process_group()
 

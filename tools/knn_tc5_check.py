@@ -12,6 +12,10 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import oracle  # noqa: E402
 from vi_slam_b200 import matcher, synthetic  # noqa: E402
 
+if os.environ.get("VIORB_TOOL_LIB"):      # A/B of a build variant (tools/variants.sh); the package itself has no such knob
+    from vi_slam_b200 import _lib  # noqa: E402
+    _lib.DEFAULT_LIB = os.path.abspath(os.environ["VIORB_TOOL_LIB"])
+
 
 def main():
     shapes = [(1, 1), (1, 2), (5, 0), (127, 255), (128, 256), (129, 257), (300, 63), (64, 65), (2000, 2000), (2013, 1987),
@@ -34,7 +38,7 @@ def main():
             oi, od = oracle.knn2(q, t, nthreads=8)
             ok = bool(np.array_equal(idx, oi) and np.array_equal(dist, od))
         bad += not ok
-        print(json.dumps({"nq": nq, "nt": nt, "ok": ok, "kernel": os.environ.get("VIORB_KNN", "tc5")}), flush=True)
+        print(json.dumps({"nq": nq, "nt": nt, "ok": ok, "lib": os.path.basename(os.environ.get("VIORB_TOOL_LIB", "libviorb.so"))}), flush=True)
         if not ok and nt:
             w = np.argwhere((idx != oi) | (dist != od))[:5]
             print("  first mismatches (row, k):", w.tolist(), idx[w[:, 0]].tolist(), oi[w[:, 0]].tolist(), dist[w[:, 0]].tolist(), od[w[:, 0]].tolist())

@@ -14,8 +14,9 @@
 #include <string>
 #include <vector>
 
-// kNN-2 kernel of this build: 0 = k_knn2_tc5 (the product), 1 = k_knn2_mma, 2 = k_knn2 (experiments; the CPU
-// emulation build has no tcgen05 and takes 1)
+// kNN-2 kernel of this build: 0 = k_knn2_f4 (the product: tcgen05.mma kind::mxf4), 1 = k_knn2_mma, 2 = k_knn2,
+// 3 = k_knn2_tc5 (tcgen05.mma kind::i8, the round-1 product); 1-3 are experiments, the CPU emulation build has no
+// tcgen05 and takes 1
 #ifndef VIORB_KNN_VARIANT
 #ifdef VIORB_EMU
 #define VIORB_KNN_VARIANT 1
@@ -27,8 +28,13 @@
 #include "kernels_extract.cuh"
 #include "kernels_match.cuh"
 #if VIORB_KNN_VARIANT == 0
+#include "kernels_knn_f4.cuh"
+#define VIORB_KNN_TC_KERNEL tc5::k_knn2_f4
+#elif VIORB_KNN_VARIANT == 3
 #include "kernels_knn_tc5.cuh"
+#define VIORB_KNN_TC_KERNEL tc5::k_knn2_tc5
 #endif
+#define VIORB_KNN_TENSOR (VIORB_KNN_VARIANT == 0 || VIORB_KNN_VARIANT == 3)
 #include "kernels_window.cuh"
 #include "kernels_bow.cuh"
 #include "kernels_kb8.cuh"
@@ -467,8 +473,8 @@ int device_state(int dev, DeviceState** out) {
         raise((const void*)k_resolve_proj);
         // several ~40 KB CTAs of k_octree per SM: without this hint the driver picks a carveout that holds one
         ok(cudaFuncSetAttribute(k_octree, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
-#if VIORB_KNN_VARIANT == 0
-        ok(cudaFuncSetAttribute(tc5::k_knn2_tc5, cudaFuncAttributeMaxDynamicSharedMemorySize, tc5::SMEM_BYTES));
+#if VIORB_KNN_TENSOR
+        ok(cudaFuncSetAttribute(VIORB_KNN_TC_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, tc5::SMEM_BYTES));
 #endif
         cudaMemPoolProps props{};
         props.allocType = cudaMemAllocationTypePinned;
@@ -651,13 +657,13 @@ int release_partner(viorb_extractor* L, viorb_extractor* R) {
 
 }  // namespace
 
-// Brute-force kNN-2 of a batch of descriptor sets: k_knn2_tc5 (tcgen05.mma kind::i8, accumulators in tensor memory,
-// kernels_knn_tc5.cuh).  The product library holds this one kernel.  The two earlier kernels (warp-level IMMA k_knn2_mma,
-// LOP3/POPC k_knn2; identical results) are BUILD-time variants for experiments
-// (-DVIORB_KNN_VARIANT=1 / 2, tools/variants.sh); the CPU emulation build of the tests uses the IMMA one.
+// Brute-force kNN-2 of a batch of descriptor sets: k_knn2_f4 (tcgen05.mma kind::mxf4.block_scale, accumulators in tensor
+// memory, kernels_knn_f4.cuh).  The product library holds this one kernel.  The earlier kernels (kind::i8 k_knn2_tc5,
+// warp-level IMMA k_knn2_mma, LOP3/POPC k_knn2; identical results) are BUILD-time variants for
+// experiments (-DVIORB_KNN_VARIANT=3 / 1 / 2, tools/variants.sh); the CPU emulation build of the tests uses the IMMA one.
 static int launch_knn2(const DescSet& Q, const DescSet& T, int maxNq, int maxNt, int nSets, int32_t* dIdx, int32_t* dDist,
                        size_t outStride, cudaStream_t st) {
-#if VIORB_KNN_VARIANT == 0
+#if VIORB_KNN_TENSOR
     int dev = 0;
     CU(cudaGetDevice(&dev));
     DeviceState* ds = nullptr;
@@ -680,7 +686,7 @@ static int launch_knn2(const DescSet& Q, const DescSet& T, int maxNq, int maxNt,
         const int nItems = nBase * nSplit;
         uint2* partial = nullptr;
         if (nSplit > 1) CU(cudaMallocFromPoolAsync((void**)&partial, (size_t)nItems * tc5::QT * sizeof(uint2), ds->pool, st));
-        VIORB_LAUNCH(tc5::k_knn2_tc5, dim3(std::min(nItems, nSm)), dim3(tc5::THREADS), tc5::SMEM_BYTES, st, Q, T, dIdx, dDist,
+        VIORB_LAUNCH(VIORB_KNN_TC_KERNEL, dim3(std::min(nItems, nSm)), dim3(tc5::THREADS), tc5::SMEM_BYTES, st, Q, T, dIdx, dDist,
                      outStride, qTiles, nSets, nItems, nSplit, partial);
         if (nSplit > 1) {
             VIORB_LAUNCH(tc5::k_knn2_tc5_merge, dim3((qTiles * tc5::QT + 255) / 256, nSets), dim3(256), 0, st, Q, partial, dIdx,
@@ -2040,7 +2046,7 @@ int viorb_fisheye_stereo_matches(const viorb_kb8_rig* rig, const viorb_keypoint*
 // =================================================================================================
 #define VIORB_STATIC_KNN_MAX_QUERIES VIORB_KNN2_STATIC_MAX_QUERIES   /* query rows per call (include/viorb.h) */
 #define VIORB_STATIC_KNN_MAX_SPLIT 32                        /* CTAs per query tile, as in launch_knn2 */
-#if VIORB_KNN_VARIANT == 0
+#if VIORB_KNN_TENSOR
 #define VIORB_STATIC_KNN_ROWS ((VIORB_STATIC_KNN_MAX_QUERIES / 128) * VIORB_STATIC_KNN_MAX_SPLIT * 128)     /* 524 288 uint2 = 4 MiB */
 static __device__ __align__(256) uint2 g_knnStaticScratch[VIORB_STATIC_KNN_ROWS];
 
@@ -2064,7 +2070,7 @@ extern "C" int viorb_knn2_device_static(const uint8_t* d_q, int nq, const uint8_
     if (nt >= (1 << VIORB_KNN_IDX_BITS)) return fail(VIORB_E_ARG, "train set larger than 2^22 rows");
     if (((uintptr_t)d_q & 15) || ((uintptr_t)d_t & 15)) return fail(VIORB_E_ARG, "descriptor buffers must be 16-byte aligned");
     if (nq == 0) return VIORB_OK;
-#if VIORB_KNN_VARIANT == 0
+#if VIORB_KNN_TENSOR
     int dev = 0;
     CU(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) return fail(VIORB_E_ARG, "device index out of range");
@@ -2072,7 +2078,7 @@ extern "C" int viorb_knn2_device_static(const uint8_t* d_q, int nq, const uint8_
     std::call_once(S.once, [&S, dev] {                       // set-up, once per device, with that device current
         auto ok = [&S](cudaError_t r) { if (S.err == cudaSuccess) S.err = r; };
         ok(cudaDeviceGetAttribute(&S.sms, cudaDevAttrMultiProcessorCount, dev));
-        ok(cudaFuncSetAttribute(tc5::k_knn2_tc5, cudaFuncAttributeMaxDynamicSharedMemorySize, tc5::SMEM_BYTES));
+        ok(cudaFuncSetAttribute(VIORB_KNN_TC_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, tc5::SMEM_BYTES));
         ok(cudaGetSymbolAddress((void**)&S.scratch, g_knnStaticScratch));
     });
     if (S.err != cudaSuccess || !S.scratch)
@@ -2093,7 +2099,7 @@ extern "C" int viorb_knn2_device_static(const uint8_t* d_q, int nq, const uint8_
     const int nItems = qTiles * nSplit;
     if ((size_t)nItems * tc5::QT > (size_t)VIORB_STATIC_KNN_ROWS) return fail(VIORB_E_CAPACITY, "viorb_knn2_device_static: scratch rows exceeded");
     uint2* partial = nSplit > 1 ? S.scratch : nullptr;
-    VIORB_LAUNCH(tc5::k_knn2_tc5, dim3(std::min(nItems, S.sms)), dim3(tc5::THREADS), tc5::SMEM_BYTES, st, Q, T, d_idx, d_dist, (size_t)nq,
+    VIORB_LAUNCH(VIORB_KNN_TC_KERNEL, dim3(std::min(nItems, S.sms)), dim3(tc5::THREADS), tc5::SMEM_BYTES, st, Q, T, d_idx, d_dist, (size_t)nq,
                  qTiles, 1, nItems, nSplit, partial);
     if (nSplit > 1)
         VIORB_LAUNCH(tc5::k_knn2_tc5_merge, dim3((qTiles * tc5::QT + 255) / 256, 1), dim3(256), 0, st, Q, partial, d_idx, d_dist, (size_t)nq,
