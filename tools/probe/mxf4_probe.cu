@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <vector>
 
 constexpr int M = 128, N = 256, MAXS = 6;
@@ -114,6 +115,105 @@ __global__ void __launch_bounds__(128) k_probe(const uint8_t* __restrict__ A, co
     }
 }
 
+// MMA issue rate: one CTA per SM (grid = nCta) issues `reps` x `steps` MMAs of one kind back to back on resident operands
+// (steps = K steps per accumulator pass, alternating between two accumulators like the kNN kernel) and reports the
+// clocks per MMA seen by the issuing thread between the first issue and the arrival of the last commit.
+// kind 0: mxf4 block32 (K 64), kind 1: i8 (K 32).  Operand contents are irrelevant.
+__global__ void __launch_bounds__(128) k_rate(int kind, int n, int steps, int reps, int layoutArg, int offA, int gapB, long long* __restrict__ out) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tmemSlot;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int inter = layoutArg >> 1, layout = layoutArg & 1;
+    const int KCH = 2 * steps, SBO = KCH * 128;
+    unsigned char* sA = smem + ((1024u - (smem_u32(smem) & 1023u)) & 1023u) + offA;      // swizzle atoms are 1024-byte aligned
+    unsigned char* sB = sA + (M / 8) * SBO + gapB;
+    const int bytes = layout ? (M + 256) * 128 * ((steps + 3) / 4) : (M / 8 + 256 / 8) * SBO;
+    for (int i = tid; i < bytes / 4; i += 128) reinterpret_cast<uint32_t*>(sA)[i] = 0x22222222u;
+    if (layout) sB = sA + M * 128 * ((steps + 3) / 4) + gapB;
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&bar)), "r"(1));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmemSlot)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = tmemSlot;
+    const uint32_t lane0 = tmem + ((uint32_t)(warp * 32) << 16);
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1,%1,%1,%1};" ::"r"(lane0 + 240), "r"(0x7f7f7f7fu) : "memory");
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(lane0 + 244), "r"(0x7f7f7f7fu) : "memory");
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    if (tid == 0) {
+        const uint64_t dA = smem_desc(smem_u32(sA), SBO), dB = smem_desc(smem_u32(sB), SBO);
+        const uint32_t idF4 = (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | (1u << 23) | ((uint32_t)(M >> 4) << 24);
+        const uint32_t idI8 = (2u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+        const int nacc = n <= 240 ? 2 : 1;                  // kind 0 needs the scale-factor columns: one accumulator at N = 256
+        const long long t0 = clock64();
+        for (int i = 0; i < reps * steps; ++i) {
+            // inter: the K steps of two tiles alternate between the two accumulators (no two consecutive MMAs accumulate into the same one)
+            int r = i / steps, s = i % steps;
+            if (inter) { const int w = i % (2 * steps); r = i / (2 * steps) * 2 + (w & 1); s = w >> 1; }
+            const uint32_t d = tmem + ((kind == 0 ? (r % nacc) : (r & 1)) * 256);
+            {
+                uint64_t a = dA + (uint64_t)((s * 2 * LBO) >> 4), b = dB + (uint64_t)((s * 2 * LBO) >> 4);
+                if (layout) {
+                    // K-major SWIZZLE_128B: rows of 128 B, 8-row groups of 1024 B; a K step advances the start address by 32 B,
+                    // every fourth step moves to the next 128-byte-wide operand block
+                    const uint32_t offA = (uint32_t)(s / 4) * M * 128 + (s % 4) * 32, offB = (uint32_t)(s / 4) * 256 * 128 + (s % 4) * 32;
+                    a = (uint64_t)(((smem_u32(sA) + offA) & 0x3FFFF) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+                    b = (uint64_t)(((smem_u32(sB) + offB) & 0x3FFFF) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+                }
+                const uint32_t acc = s > 0;
+                if (kind == 0)
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                 "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%5], [%6], p;\n\t}"
+                                 ::"r"(d), "l"(a), "l"(b), "r"(idF4), "r"(acc), "r"(tmem + 240), "r"(tmem + 244) : "memory");
+                else
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                                 ::"r"(d), "l"(a), "l"(b), "r"(idI8), "r"(acc) : "memory");
+            }
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)) : "memory");
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                         : "=r"(done) : "r"(smem_u32(&bar)), "r"(0) : "memory");
+        out[blockIdx.x] = clock64() - t0;
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+    }
+}
+
+static void rate(int kind, int n, int steps, int nCta, int layout = 0, int offA = 0, int gapB = 0) {
+    const int reps = 400;
+    const int inter = layout >> 1;
+    long long* d;
+    cudaMalloc(&d, sizeof(long long) * nCta);
+    const int smem = ((layout & 1) ? (M + 256) * 128 * ((steps + 3) / 4) : (M / 8 + 256 / 8) * 2 * steps * 128) + 1024 + 4096;
+    cudaFuncSetAttribute(k_rate, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    k_rate<<<nCta, 128, smem>>>(kind, n, steps, reps, layout, offA, gapB, d);
+    if (cudaDeviceSynchronize() != cudaSuccess) { printf("  rate kernel failed\n"); exit(1); }
+    std::vector<long long> h(nCta);
+    cudaMemcpy(h.data(), d, sizeof(long long) * nCta, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    long long mx = 0;
+    for (long long v : h) mx = std::max(mx, v);
+    printf("RATE %s %s offA %4d gapB %4d N %3d K-steps %d CTAs %3d: %.1f clk per MMA (%.2f clk per train row and tile of %d steps)\n", kind ? "i8   K32" : "mxf4 K64", (layout & 1) ? (inter ? "swizzle-128B-interleaved" : "swizzle-128B") : (inter ? "no-swizzle-interleaved" : "no-swizzle  "), offA, gapB,
+           n, steps, nCta, (double)mx / (reps * steps), (double)mx / reps / n, steps);
+}
+
 // ------------------------------------------------------------------------------------------- host
 static const float kE2M1[16] = {0.f, .5f, 1.f, 1.5f, 2.f, 3.f, 4.f, 6.f, -0.f, -.5f, -1.f, -1.5f, -2.f, -3.f, -4.f, -6.f};
 
@@ -193,7 +293,25 @@ static long compare(const Case& c, const std::vector<float>& D, const int (*selA
 static uint32_t rng = 12345u;
 static uint32_t rnd() { rng = rng * 1664525u + 1013904223u; return rng >> 8; }
 
-int main() {
+int main(int argc, char** argv) {
+    if (argc > 1 && !strcmp(argv[1], "rate")) {
+        for (int n : {64, 128, 240}) {
+            rate(0, n, 5, 148, 0);
+            rate(0, n, 5, 148, 2);
+            rate(0, n, 4, 148, 1);
+            rate(0, n, 4, 148, 3);
+        }
+        for (int nCta : {148}) {
+            for (int n : {128, 192, 208, 240}) rate(0, n, 5, nCta);
+            rate(0, 256, 5, nCta);
+            rate(0, 240, 4, nCta);
+            for (int n : {128, 240, 256}) rate(1, n, 9, nCta);
+            for (int n : {64, 128, 192, 240, 256}) rate(0, n, 4, nCta, 1);
+            rate(0, 240, 5, nCta, 1);
+            for (int n : {128, 256}) rate(1, n, 8, nCta, 1);
+        }
+        return 0;
+    }
     const int sel0[MAXS][2] = {{0, 1}, {0, 1}, {0, 1}, {0, 1}, {0, 1}, {0, 1}};
     // T1: all ones
     {
