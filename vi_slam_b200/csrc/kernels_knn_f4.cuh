@@ -126,9 +126,17 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 
 // One descriptor word -> one 16-byte chunk of e2m1 nibbles: nibble j of output word s holds bit 4 j + 3 - s of w as the
 // sign of 1.0 (0x2 / 0xA).  Query and train rows use the same position map, which is all the dot product needs.
+// multipliers 1, 2, 4, 8 read from constant memory: ptxas cannot turn the multiply-add into a shift-add on the ALU pipe
+__constant__ unsigned c_nibbleShift[4] = {1u, 2u, 4u, 8u};
+__device__ __forceinline__ unsigned mad_u32(unsigned a, unsigned b, unsigned c) {
+    unsigned d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+// (the AND runs on the ALU pipe, shift + OR as one multiply-add on the FMA pipe: the ALU pipe is this kernel's busiest)
 __device__ __forceinline__ uint4 sign_nibbles(unsigned w) {
-    return make_uint4((w & 0x88888888u) | 0x22222222u, ((w << 1) & 0x88888888u) | 0x22222222u, ((w << 2) & 0x88888888u) | 0x22222222u,
-                      ((w << 3) & 0x88888888u) | 0x22222222u);
+    return make_uint4(mad_u32(w & 0x88888888u, c_nibbleShift[0], 0x22222222u), mad_u32(w & 0x44444444u, c_nibbleShift[1], 0x22222222u),
+                      mad_u32(w & 0x22222222u, c_nibbleShift[2], 0x22222222u), mad_u32(w & 0x11111111u, c_nibbleShift[3], 0x22222222u));
 }
 
 // nibble codes of the column index of a train row inside its 64-column group (block X): 1 * d0 + 4 * d1 + 4 * x + 4 * y
