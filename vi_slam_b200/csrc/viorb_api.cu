@@ -931,6 +931,8 @@ int viorb_extract_device(viorb_extractor* ex, const uint8_t* d_imgs, int n, int 
     return run_pipeline(ex, 0, n, lap0, lap1);
 }
 
+static std::atomic<int> g_batchCalls{0};      // viorb_extract_batch calls in flight in this process
+
 int viorb_extract_batch(viorb_extractor* ex, const uint8_t* const* imgs, int n, int width, int height, int step, int lap0,
                         int lap1, viorb_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_index_out) {
     if (!ex) return fail(VIORB_E_ARG, "null handle");
@@ -968,7 +970,15 @@ int viorb_extract_batch(viorb_extractor* ex, const uint8_t* const* imgs, int n, 
     // 80 frames per chunk: measured with three pipeline workers (tools/e2e_chunks_cmp.sh, 160 frames per call):
     // 1 / 2 / 3 / 4 / 8 chunks = 39.2k / 40.2k / 37.6k / 37.4k / 34.6k stereo frames/s - smaller chunks leave the
     // level-synchronous kernels (k_octree, upper pyramid levels) with less than one wave of CTAs.
-    int nChunks = ex->timing ? 1 : std::min(VIORB_MAX_CHUNKS, std::max(1, (n + 40) / 80));
+    // With several batch calls in flight (pipeline workers, each with its own handles: more than one left / right pair)
+    // the calls' copies already run under each other's kernels and whole-batch launches are the better use of the GPU:
+    // 1 / 2 / 4 chunks = 39.8k / 38.3k / 34.6k with three workers and the pointer tables prebuilt.
+    struct InFlight {
+        InFlight() { now = ++g_batchCalls; }
+        ~InFlight() { --g_batchCalls; }
+        int now;
+    } inflight;
+    int nChunks = (ex->timing || inflight.now > 2) ? 1 : std::min(VIORB_MAX_CHUNKS, std::max(1, (n + 40) / 80));
     if (const char* e = std::getenv("VIORB_CHUNKS")) nChunks = std::min(VIORB_MAX_CHUNKS, std::max(1, std::atoi(e)));   // tuning knob
     nChunks = std::min(nChunks, n);
     const int per = (n + nChunks - 1) / nChunks;

@@ -50,6 +50,26 @@ def _check(lib, rc):
         raise ViorbError(rc, lib.viorb_last_error().decode())
 
 
+class HostBatch:
+    """Pointer table of n equally sized CV_8UC1 host images (fextractor.cpp:1041) as viorb_extract_batch takes it."""
+
+    def __init__(self, images):
+        n = len(images)
+        h, w = images[0].shape
+        step = images[0].strides[0]
+        self.keep = []
+        self.ptrs = (C.c_void_p * n)()
+        for i, im in enumerate(images):
+            assert im.dtype == np.uint8 and im.ndim == 2 and im.shape == (h, w)
+            if im.strides[1] != 1 or im.strides[0] != step:
+                im = np.ascontiguousarray(im)
+                assert im.strides[0] == step or n == 1
+                step = im.strides[0]
+            self.keep.append(im)
+            self.ptrs[i] = im.ctypes.data
+        self.n, self.w, self.h, self.step = n, w, h, step
+
+
 class FExtractor:
     """FExtractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST) — fextractor.cpp:401-461.
 
@@ -121,36 +141,36 @@ class FExtractor:
         return {"kps": mk((n, cap), KP_DTYPE), "desc": mk((n, cap, 32), np.uint8), "count": np.zeros(n, np.int32),
                 "mono": np.zeros(n, np.int32)}
 
-    def compute_batch(self, images, vLappingArea=(0, 0), out=None):
-        """Batch form of ``compute``.  With ``out`` (from ``alloc_outputs``) results are written in place and the
-        return value holds views (rows beyond count[i] are undefined) instead of fresh copies."""
-        n = len(images)
-        h, w = images[0].shape
-        step = images[0].strides[0]
-        keep = []
-        ptrs = (C.c_void_p * n)()
-        for i, im in enumerate(images):
-            assert im.dtype == np.uint8 and im.ndim == 2 and im.shape == (h, w)   # CV_8UC1 (fextractor.cpp:1041)
-            if im.strides[1] != 1 or im.strides[0] != step:
-                im = np.ascontiguousarray(im)
-                assert im.strides[0] == step or n == 1
-                step = im.strides[0]
-            keep.append(im)
-            ptrs[i] = im.ctypes.data
+    def host_batch(self, images):
+        """Pointer table of a list of equally sized uint8 images for ``compute_batch`` - build it once when the same host
+        buffers (a capture ring, page-locked staging memory) are handed over repeatedly."""
+        return HostBatch(images)
+
+    def compute_batch(self, images, vLappingArea=(0, 0), out=None, views=True):
+        """Batch form of ``compute``; ``images`` is a list of arrays or a ``HostBatch``.  With ``out`` (from
+        ``alloc_outputs``) results are written in place and the return value holds views (rows beyond count[i] are
+        undefined) instead of fresh copies; ``views=False`` returns only (mono, count) and leaves slicing to the caller."""
+        hb = images if isinstance(images, HostBatch) else HostBatch(images)
+        n, w, h, step = hb.n, hb.w, hb.h, hb.step
         cap = self.capacity
         if out is None:
             kps = np.zeros((n, cap), KP_DTYPE)
             desc = np.zeros((n, cap, 32), np.uint8)
             cnt = np.zeros(n, np.int32)
             mono = np.zeros(n, np.int32)
+            addr = (kps.ctypes.data, desc.ctypes.data, cnt.ctypes.data_as(_lib.i32p), mono.ctypes.data_as(_lib.i32p))
         else:
             kps, desc, cnt, mono = out["kps"], out["desc"], out["count"], out["mono"]
             assert kps.shape[0] >= n and kps.shape[1] == cap
+            addr = out.get("_addr")
+            if addr is None:
+                addr = out["_addr"] = (kps.ctypes.data, desc.ctypes.data, cnt.ctypes.data_as(_lib.i32p), mono.ctypes.data_as(_lib.i32p))
         _check(self._lib, self._lib.viorb_extract_batch(
-            self._h, ptrs, n, w, h, step, int(vLappingArea[0]), int(vLappingArea[1]), kps.ctypes.data,
-            desc.ctypes.data, cap, cnt.ctypes.data_as(_lib.i32p), mono.ctypes.data_as(_lib.i32p)))
+            self._h, hb.ptrs, n, w, h, step, int(vLappingArea[0]), int(vLappingArea[1]), addr[0], addr[1], cap, addr[2], addr[3]))
         self._last_n = n
         if out is not None:
+            if not views:
+                return mono[:n], cnt[:n]
             return mono[:n], [kps[i, :cnt[i]] for i in range(n)], [desc[i, :cnt[i]] for i in range(n)]
         return ([int(m) for m in mono], [kps[i, :cnt[i]].copy() for i in range(n)],
                 [desc[i, :cnt[i]].copy() for i in range(n)])
