@@ -21,6 +21,7 @@ from __future__ import annotations
 
 import argparse
 import concurrent.futures as cf
+import ctypes as C
 import json
 import os
 import sys
@@ -69,6 +70,7 @@ def parse_args():
     ap.add_argument("--no-knn-sweep", action="store_true", help="skip the row-sharded kNN sweep leg (BASELINE configs[4])")
     ap.add_argument("--no-bind", action="store_true", help="multi-rank runs: do not bind the rank to its GPU's local CPUs")
     ap.add_argument("--variant-lib", default=None, help="experimental build of libviorb.so to measure instead of the product one")
+    ap.add_argument("--e2e-diag", default="", help="diagnostics only (the line is flagged): nod2h | noh2d | nofetch")
     ap.add_argument("--e2e-workers", type=int, default=3, help="pipeline workers (handles in flight) of the end-to-end leg")
     return ap.parse_args()
 
@@ -568,6 +570,8 @@ def run_ours(args, wl, rank, world, local_rank):
         hbr = HostBatch(hr) if stereo else None
         hbc = {f0: HostBatch(hl[f0:f0 + chunk]) for f0 in range(0, B, chunk)} if kind == "mono_batch" else None
 
+        TRACE = [] if os.environ.get("BENCH_TRACE") else None
+
         class Worker:
             def __init__(self):
                 self.pool = ThreadPoolExecutor(1) if stereo else None      # the right camera's call runs beside the left one's
@@ -575,6 +579,9 @@ def run_ours(args, wl, rank, world, local_rank):
                 self.er = mk() if stereo else None
                 self.outs = [self.el.alloc_outputs(chunk)] + ([self.er.alloc_outputs(chunk)] if stereo else [])
                 self.out = [None, None]
+                if args.e2e_diag == "nod2h":
+                    for o in self.outs:
+                        o["_addr"] = (None, None, o["count"].ctypes.data_as(C.POINTER(C.c_int32)), o["mono"].ctypes.data_as(C.POINTER(C.c_int32)))
                 cap = self.el.capacity
                 if stereo:
                     self.buf = {"u_right": pinned_empty((B, cap), np.float32), "depth": pinned_empty((B, cap), np.float32),
@@ -585,12 +592,25 @@ def run_ours(args, wl, rank, world, local_rank):
                                 "knn_match": pinned_empty((B - 1, cap), np.int32), "n_ratio": np.zeros(B - 1, np.int32)}
 
             def step(self, f0=0):
-                if stereo:
-                    fr = self.pool.submit(self.er.compute_batch, hbr, LAP, self.outs[1], False)
-                    self.el.compute_batch(hbl, LAP, self.outs[0], False)
-                    fr.result()
+                if stereo and args.e2e_diag == "noh2d":
+                    self.el.extract_device(dl.data_ptr(), B, W, H, PITCH, fstride, LAP)
+                    self.er.extract_device(dr.data_ptr(), B, W, H, PITCH, fstride, LAP)
                     matcher.stereo_batch(self.el, self.er, B, BF, BB, 0.7)
                     matcher.stereo_fetch_all(self.el, B, self.buf)
+                elif stereo:
+                    t0 = time.perf_counter()
+                    fr = self.pool.submit(self.er.compute_batch, hbr, LAP, self.outs[1], False)
+                    self.el.compute_batch(hbl, LAP, self.outs[0], False)
+                    t1 = time.perf_counter()
+                    fr.result()
+                    t2 = time.perf_counter()
+                    matcher.stereo_batch(self.el, self.er, B, BF, BB, 0.7)
+                    t3 = time.perf_counter()
+                    if args.e2e_diag != "nofetch":
+                        matcher.stereo_fetch_all(self.el, B, self.buf)
+                    t4 = time.perf_counter()
+                    if TRACE is not None:
+                        TRACE.append((id(self) % 1000, t0, t1, t2, t3, t4))
                 elif kind == "mono_f2f":
                     self.el.compute_batch(hbl, LAP, self.outs[0], False)
                     matcher.f2f_batch(self.el, B, None, 100, 0.9, True, 0.8, 1)
@@ -623,6 +643,9 @@ def run_ours(args, wl, rank, world, local_rank):
             t = torch.tensor([dt], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
+        if TRACE:
+            for w, a, b, c, d_, e in sorted(TRACE, key=lambda r: r[1])[-24:]:
+                print(f"TRACE w{w:03d} start {1e3 * (a - t0):8.2f} L {1e3 * (b - a):6.2f} R+ {1e3 * (c - b):6.2f} stereo {1e3 * (d_ - c):6.2f} fetch {1e3 * (e - d_):6.2f} total {1e3 * (e - a):6.2f}", file=sys.stderr)
         nimg = (2 if stereo else 1) * B
         h2d = nimg * W * H
         kp_rows = stats["keypoints_per_frame"]            # rows that exist are what viorb_extract_batch copies (chunk maximum)
@@ -632,7 +655,7 @@ def run_ours(args, wl, rank, world, local_rank):
         elif kind == "mono_f2f":
             d2h += int((B - 1) * kp_rows * 8) + 2 * (B - 1) * 4
         e2e = {"value": total_units * Ke / dt, "unit": wl["unit"], "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-               "ms_per_step": 1e3 * dt / Ke, "workers": NWORK, "steps": Ke,
+               "ms_per_step": 1e3 * dt / Ke, "workers": NWORK, "steps": Ke, **({"diag": args.e2e_diag} if args.e2e_diag else {}),
                "host_side": "page-locked input ring with its pointer tables built once, results into reused page-locked buffers, "
                             "left / right calls from two host threads per worker",
                "d2h_note": "counted from the mean keypoint count: result rows are copied up to the largest count of a chunk, not the arena capacity"}

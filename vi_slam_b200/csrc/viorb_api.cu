@@ -448,6 +448,13 @@ struct DeviceState {
 #ifndef VIORB_EMU
     cudaMemPool_t pool = nullptr;
 #endif
+    // ONE host -> device copy stream per device, shared by every handle's viorb_extract_batch: uploads of concurrent
+    // calls (pipeline workers, left / right cameras) run in issue order at full link rate each, so the first caller's
+    // kernels start after ITS images arrived - with one copy stream per handle the copy engines interleave all
+    // uploads, every call's images arrive at the same late moment and the workers fall into lockstep
+    // (all copy, then all compute: measured 13 ms cycles of three workers, 4.4 ms per step instead of 3.6).
+    cudaStream_t h2d = nullptr;
+    std::mutex h2dMu;                         // copy + event record of one chunk stay adjacent in the stream
 };
 DeviceState g_dev[64];
 std::atomic<int> g_forceKnnSplit{0};      // viorb_debug_knn_split
@@ -476,6 +483,13 @@ int device_state(int dev, DeviceState** out) {
 #if VIORB_KNN_TENSOR
         ok(cudaFuncSetAttribute(VIORB_KNN_TC_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, tc5::SMEM_BYTES));
 #endif
+        {
+            int cur = 0;
+            ok(cudaGetDevice(&cur));
+            ok(cudaSetDevice(dev));
+            ok(cudaStreamCreateWithFlags(&d.h2d, cudaStreamNonBlocking));
+            ok(cudaSetDevice(cur));
+        }
         cudaMemPoolProps props{};
         props.allocType = cudaMemAllocationTypePinned;
         props.location.type = cudaMemLocationTypeDevice;
@@ -983,31 +997,42 @@ int viorb_extract_batch(viorb_extractor* ex, const uint8_t* const* imgs, int n, 
     nChunks = std::min(nChunks, n);
     const int per = (n + nChunks - 1) / nChunks;
     nChunks = (n + per - 1) / per;
+    // Uploads go through the device's shared copy stream (DeviceState::h2d) when nothing is pending on this handle -
+    // the normal case of the synchronous calls; otherwise through the handle's own copy stream behind the pending work,
+    // so that one busy handle never blocks the other handles' uploads.
+    DeviceState* ds = nullptr;
+    if (int drc = device_state(ex->prm.device, &ds)) return drc;
+    const bool sharedUp = ds->h2d && !ex->timing && cudaStreamQuery(ex->stream) == cudaSuccess;
+    cudaStream_t up = sharedUp ? ds->h2d : ex->cpStream;
     CU(cudaEventRecord(ex->evEntry, ex->stream));              // earlier work on the handle may still read the arenas
-    CU(cudaStreamWaitEvent(ex->cpStream, ex->evEntry, 0));
+    if (!sharedUp) CU(cudaStreamWaitEvent(ex->cpStream, ex->evEntry, 0));
     CU(cudaStreamWaitEvent(ex->outStream, ex->evEntry, 0));
     for (int c = 0; c < nChunks; ++c) {
         const int f0 = c * per, m = std::min(per, n - f0);
+        if (!pinnedIn)
+            for (int i = f0; i < f0 + m; ++i)
+                for (int y = 0; y < height; ++y)
+                    std::memcpy(ex->hIn.p + i * fstride + (size_t)y * pitch, imgs[i] + (size_t)y * step, width);
+        std::unique_lock<std::mutex> upLock(ds->h2dMu, std::defer_lock);
+        if (sharedUp) upLock.lock();
         if (pinnedIn) {
             bool contiguous = true;
             for (int i = f0 + 1; i < f0 + m && contiguous; ++i) contiguous = imgs[i] == imgs[i - 1] + (size_t)step * height;
             if (contiguous && step == pitch) {
                 // same row stride on both sides: one linear DMA (the bytes between width and step of a row belong
                 // to the caller's rows; the copy stops after the last pixel of the last row)
-                CU(cudaMemcpyAsync(ex->dIn.p + f0 * fstride, imgs[f0], ((size_t)height * m - 1) * step + width, cudaMemcpyHostToDevice, ex->cpStream));
+                CU(cudaMemcpyAsync(ex->dIn.p + f0 * fstride, imgs[f0], ((size_t)height * m - 1) * step + width, cudaMemcpyHostToDevice, up));
             } else if (contiguous) {
-                CU(cudaMemcpy2DAsync(ex->dIn.p + f0 * fstride, pitch, imgs[f0], step, width, (size_t)height * m, cudaMemcpyHostToDevice, ex->cpStream));
+                CU(cudaMemcpy2DAsync(ex->dIn.p + f0 * fstride, pitch, imgs[f0], step, width, (size_t)height * m, cudaMemcpyHostToDevice, up));
             } else {
                 for (int i = f0; i < f0 + m; ++i)
-                    CU(cudaMemcpy2DAsync(ex->dIn.p + i * fstride, pitch, imgs[i], step, width, height, cudaMemcpyHostToDevice, ex->cpStream));
+                    CU(cudaMemcpy2DAsync(ex->dIn.p + i * fstride, pitch, imgs[i], step, width, height, cudaMemcpyHostToDevice, up));
             }
         } else {
-            for (int i = f0; i < f0 + m; ++i)
-                for (int y = 0; y < height; ++y)
-                    std::memcpy(ex->hIn.p + i * fstride + (size_t)y * pitch, imgs[i] + (size_t)y * step, width);
-            CU(cudaMemcpyAsync(ex->dIn.p + f0 * fstride, ex->hIn.p + f0 * fstride, fstride * m, cudaMemcpyHostToDevice, ex->cpStream));
+            CU(cudaMemcpyAsync(ex->dIn.p + f0 * fstride, ex->hIn.p + f0 * fstride, fstride * m, cudaMemcpyHostToDevice, up));
         }
-        CU(cudaEventRecord(ex->evIn[c], ex->cpStream));
+        CU(cudaEventRecord(ex->evIn[c], up));
+        if (sharedUp) upLock.unlock();
         CU(cudaStreamWaitEvent(ex->stream, ex->evIn[c], 0));
         rc = run_pipeline(ex, f0, m, lap0, lap1);
         if (rc) return rc;
