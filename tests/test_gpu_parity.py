@@ -398,3 +398,64 @@ def test_knn2_concurrent_callers():
     [t.start() for t in th]
     [t.join() for t in th]
     assert not errs, errs
+
+
+@pytest.mark.gpu
+def test_concurrent_host_batches_share_the_upload_stream():
+    """Six viorb_extract_batch calls in flight from six host threads (three pipeline workers x left / right handles, the shape
+    of bench.py's end-to-end leg): uploads go through the device's one copy stream in call order, calls beyond a left / right
+    pair take one chunk.  Every call must return exactly the rows of a lone call on the same images, repeatedly, with
+    prebuilt pointer tables (HostBatch) and views=False."""
+    import threading
+    from vi_slam_b200 import FExtractor, pinned_empty
+    from vi_slam_b200.extractor import HostBatch
+    syn = _syn()
+    n, w, h, nthreads = 12, 640, 360, 6
+    sets = []
+    for t in range(nthreads):
+        pin = pinned_empty((n, h, 640), np.uint8)
+        for i in range(n):
+            pin[i] = syn.make_frame(7000 + 31 * t + i, w, h)
+        sets.append(pin)
+    ref_ex = FExtractor(1000, max_size=(w, h), max_batch=n)
+    want = [ref_ex.compute_batch([p[i] for i in range(n)], (0, 0)) for p in sets]
+    exs = [FExtractor(1000, max_size=(w, h), max_batch=n) for _ in range(nthreads)]
+    outs = [e.alloc_outputs(n, pinned=True) for e in exs]
+    batches = [HostBatch([p[i] for i in range(n)]) for p in sets]
+    errors = []
+
+    def run(t):
+        try:
+            for _ in range(5):
+                mono, cnt = exs[t].compute_batch(batches[t], (0, 0), out=outs[t], views=False)
+                wm, wk, wd = want[t]
+                for i in range(n):
+                    c = int(cnt[i])
+                    assert mono[i] == wm[i] and c == len(wk[i])
+                    assert np.array_equal(outs[t]["kps"][i, :c], wk[i]) and np.array_equal(outs[t]["desc"][i, :c], wd[i])
+        except Exception as e:          # noqa: BLE001
+            errors.append((t, repr(e)))
+
+    th = [threading.Thread(target=run, args=(t,)) for t in range(nthreads)]
+    [x.start() for x in th]
+    [x.join() for x in th]
+    assert not errors, errors
+
+
+@pytest.mark.gpu
+def test_knn2_random_shapes():
+    """40 random (query rows, train rows) shapes up to 3000 x 6000 with planted duplicates against the oracle: the fp4 kernel's
+    240-row tiles, 64- / 48-column key groups, train-range splits and the epilogue's early exit all meet their edges here."""
+    from vi_slam_b200 import matcher
+    import oracle
+    rng = np.random.default_rng(20261105)
+    for case in range(40):
+        nq, nt = int(rng.integers(1, 3001)), int(rng.integers(1, 6001))
+        q, t = _syn().make_descriptors(nq, nt, seed=9000 + case)
+        ndup = int(rng.integers(0, 1 + min(nq, nt) // 4))
+        if ndup:
+            t[rng.integers(0, nt, ndup)] = q[rng.integers(0, nq, ndup)]           # exact matches, some of them repeated
+            t[rng.integers(0, nt, ndup)] = t[rng.integers(0, nt, ndup)]           # duplicate train rows: ties -> lower index
+        idx, dist = matcher.knn_match(q, t)
+        oidx, odist = oracle.knn2(q, t, nthreads=8)
+        assert np.array_equal(idx, oidx) and np.array_equal(dist, odist), (case, nq, nt)
