@@ -630,9 +630,9 @@ def run_ours(args, wl, rank, world, local_rank):
             [t.join() for t in th]
 
         run_steps(NWORK * max(1, min(Wm, 2)) if kind != "mono_batch" else 1)
-        # every worker runs at least four steps inside the timed region, so that the fill and drain of the pipeline (first
+        # at least 32 steps inside the timed region (about ten per worker), so that the fill and drain of the pipeline (first
         # images up, last results down) do not dominate; disclosed as e2e.steps
-        Ke = max(K, 4 * NWORK) if kind != "mono_batch" else max(K, 3)
+        Ke = max(K, 32) if kind != "mono_batch" else max(K, 3)
         barrier()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
