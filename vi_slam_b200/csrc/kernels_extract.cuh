@@ -443,6 +443,9 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
 #define VIORB_OCT_THREADS 1024
 #endif
 #define VIORB_OCT_LIGHT_THREADS 256
+#ifndef VIORB_OCT_LIGHT_MINB
+#define VIORB_OCT_LIGHT_MINB 4
+#endif
 #ifndef VIORB_OCT_DENSE_KEYS
 #define VIORB_OCT_DENSE_KEYS 4096
 #endif
@@ -880,7 +883,7 @@ __device__ __forceinline__ void octree_body(const ExtractGeom& g, const uint32_t
     }
 }
 
-__global__ void __launch_bounds__(VIORB_OCT_LIGHT_THREADS, 4) k_octree(ExtractGeom g, const uint32_t* __restrict__ cand,
+__global__ void __launch_bounds__(VIORB_OCT_LIGHT_THREADS, VIORB_OCT_LIGHT_MINB) k_octree(ExtractGeom g, const uint32_t* __restrict__ cand,
                                                                        const int* __restrict__ candCount, uint16_t* __restrict__ keyNode,
                                                                        KeptKp* __restrict__ kept, int* __restrict__ keptCount,
                                                                        int* __restrict__ status) {
