@@ -10,16 +10,41 @@ CXX ?= g++
 # (no FMA) and keeps the float index math of computeOrbDescriptor uncontracted elsewhere.
 CXXFLAGS ?= -O3 -std=c++14 -fPIC -pthread -ffp-contract=off -w
 OUT := _ref/liborb_ref.so
-SRC := $(REF)/src/geometry/fextractor.cpp ref_compat/cv_compat.cpp ref_compat/ref_driver.cpp orb_oracle.cpp
+FRAME_CPP := $(REF)/src/datastructures/frame.cpp
+FMATCHER_CPP := $(REF)/src/geometry/fmatcher.cpp
+PINHOLE_CPP := $(REF)/src/geometry/cameramodels/pinhole.cpp
+SRC := $(REF)/src/geometry/fextractor.cpp ref_compat/cv_compat.cpp ref_compat/ref_driver.cpp ref_compat/ref_slices.cpp orb_oracle.cpp \
+       $(FRAME_CPP) $(FMATCHER_CPP) $(PINHOLE_CPP)
 
 all: $(OUT)
 
-$(OUT): $(SRC) ref_compat/cv_compat.hpp ../vi_slam_b200/csrc/orb_pattern.inc
-	mkdir -p _ref
-	$(CXX) $(CXXFLAGS) -Iref_compat -I$(REF)/include -shared -Wl,-Bsymbolic -o $@ \
-	    $(REF)/src/geometry/fextractor.cpp ref_compat/cv_compat.cpp ref_compat/ref_driver.cpp \
+# Function definitions of frame.cpp / fmatcher.cpp cut out by line range (those translation units need Eigen, Sophus, g2o,
+# DBoW3 ... and cannot be compiled whole; ref_compat/ref_slices.cpp says what the slices are compiled against).
+# slice <file> <first> <last> <name> <text the first line must contain>
+define slice
+	@sed -n '$(2)p' $(1) | grep -q -F '$(5)' || { echo "ref.mk: $(1):$(2) is not '$(5)' - the reference changed" >&2; exit 1; }
+	@sed -n '$(3)p' $(1) | grep -q '^        }' || { echo "ref.mk: $(1):$(3) does not close a function" >&2; exit 1; }
+	sed -n '$(2),$(3)p' $(1) > _ref/gen/$(4)_$(2)_$(3).inc
+endef
+
+$(OUT): $(SRC) ref_compat/cv_compat.hpp ../vi_slam_b200/csrc/orb_pattern.inc ref.mk
+	mkdir -p _ref/gen
+	$(call slice,$(FRAME_CPP),386,414,frame,void Frame::AssignFeaturesToGrid)
+	$(call slice,$(FRAME_CPP),678,744,frame,Frame::GetFeaturesInArea)
+	$(call slice,$(FRAME_CPP),746,756,frame,bool Frame::PosInGrid)
+	$(call slice,$(FRAME_CPP),823,997,frame,void Frame::ComputeStereoMatches)
+	$(call slice,$(FMATCHER_CPP),313,319,fmatcher,const int FMatcher::TH_HIGH = 100;)
+	$(call slice,$(FMATCHER_CPP),983,1098,fmatcher,int FMatcher::SearchForInitialization)
+	$(call slice,$(FMATCHER_CPP),2813,2854,fmatcher,void FMatcher::ComputeThreeMaxima)
+	$(call slice,$(FMATCHER_CPP),2859,2875,fmatcher,int FMatcher::DescriptorDistance)
+	$(call slice,$(FMATCHER_CPP),2471,2687,fmatcher,const Frame &LastFrame)
+	$(call slice,$(PINHOLE_CPP),13,16,pinhole,const cv::Point3f &p3D)
+	$(call slice,$(PINHOLE_CPP),22,26,pinhole,const cv::Mat &m3D)
+	$(CXX) $(CXXFLAGS) -Iref_compat -I_ref -I$(REF)/include -shared -Wl,-Bsymbolic -o $@ \
+	    $(REF)/src/geometry/fextractor.cpp ref_compat/cv_compat.cpp ref_compat/ref_driver.cpp ref_compat/ref_slices.cpp \
 	    -x c++ -std=c++17 orb_oracle.cpp
-	sha256sum $(REF)/src/geometry/fextractor.cpp $(REF)/include/vi_slam/geometry/fextractor.h > _ref/SOURCES.sha256
+	sha256sum $(REF)/src/geometry/fextractor.cpp $(REF)/include/vi_slam/geometry/fextractor.h $(FRAME_CPP) $(FMATCHER_CPP) $(PINHOLE_CPP) > _ref/SOURCES.sha256
+	rm -rf _ref/gen          # the slices are build intermediates: only the library stays
 
 clean:
 	rm -rf _ref

@@ -25,7 +25,8 @@ def build(force: bool = False) -> str | None:
     reference checkout is absent (GPU box) and no prebuilt library travelled."""
     if os.path.exists(REF_SOURCE):
         deps = [REF_SOURCE, os.path.join(_HERE, "orb_oracle.cpp"), os.path.join(_HERE, "ref.mk")] + \
-               [os.path.join(_HERE, "ref_compat", f) for f in ("cv_compat.hpp", "cv_compat.cpp", "ref_driver.cpp")]
+               [os.path.join(_HERE, "ref_compat", f) for f in ("cv_compat.hpp", "cv_compat.cpp", "ref_driver.cpp", "ref_slices.cpp")] + \
+               [os.path.join(REFERENCE, "src", "datastructures", "frame.cpp"), os.path.join(REFERENCE, "src", "geometry", "fmatcher.cpp")]
         stale = not os.path.exists(LIB_PATH) or any(os.path.getmtime(d) > os.path.getmtime(LIB_PATH) for d in deps)
         if force or stale:
             subprocess.run(["make", "-C", _HERE, "-f", "ref.mk", "-s", "REF=" + REFERENCE] + (["-B"] if force else []), check=True)
@@ -58,6 +59,16 @@ def lib():
         L.orb_ref_level_candidates.argtypes = [C.c_void_p, C.c_int, i32p, C.c_int]
         L.orb_ref_level_keypoints.argtypes = [C.c_void_p, C.c_int, i32p, f32p, C.c_int]
         L.orb_ref_arena_fallbacks.restype = C.c_long
+        # ref_slices.cpp: function bodies of frame.cpp / fmatcher.cpp
+        L.orb_refs_descriptor_distance.argtypes = [u8p, u8p]
+        L.orb_refs_stereo.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, u8p, C.c_void_p, C.c_int, u8p, C.c_float, C.c_float,
+                                      f32p, f32p]
+        L.orb_refs_features_in_area.argtypes = [C.c_void_p, C.c_int, f32p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, i32p, C.c_int]
+        L.orb_refs_search_for_initialization.argtypes = [C.c_void_p, C.c_int, u8p, C.c_void_p, C.c_int, u8p, f32p, f32p, C.c_int,
+                                                         C.c_float, C.c_int, i32p]
+        L.orb_refs_search_by_projection.argtypes = [C.c_int, C.c_void_p, f32p, u8p, u8p, u8p, C.c_void_p, C.c_int, u8p, f32p, u8p, C.c_int,
+                                                    f32p, f32p, f32p, f32p, f32p, f32p, C.c_int, C.c_float, C.c_int, C.c_float, C.c_float,
+                                                    C.c_float, C.c_int, i32p, f32p, f32p, f32p, u8p, i32p]
         _lib = L
     return _lib
 
@@ -138,3 +149,81 @@ class RefExtractor:
 
 def arena_fallbacks() -> int:
     return lib().orb_ref_arena_fallbacks()
+
+
+# ---- the reference's own matcher functions (oracle/ref_compat/ref_slices.cpp) -------------------------------------------
+
+def descriptor_distance(a: np.ndarray, b: np.ndarray) -> int:
+    """FMatcher::DescriptorDistance (fmatcher.cpp:2859-2875), the reference's own text."""
+    a = np.ascontiguousarray(a, np.uint8).reshape(32)
+    b = np.ascontiguousarray(b, np.uint8).reshape(32)
+    return int(lib().orb_refs_descriptor_distance(_p(a, C.c_uint8), _p(b, C.c_uint8)))
+
+
+def stereo_match(ref_l: RefExtractor, ref_r: RefExtractor, kl, dl, kr, dr, bf: float, b: float):
+    """Frame::ComputeStereoMatches (frame.cpp:823-997), the reference's own text, on the pyramids the two reference
+    extractors hold after their compute() calls -> (mvuRight, mvDepth).  The caller must make sure at least one match
+    survives (the reference reads an empty vector otherwise, frame.cpp:984)."""
+    kl = np.ascontiguousarray(kl, KP_DTYPE); kr = np.ascontiguousarray(kr, KP_DTYPE)
+    dl = np.ascontiguousarray(dl, np.uint8).reshape(-1, 32); dr = np.ascontiguousarray(dr, np.uint8).reshape(-1, 32)
+    ur = np.zeros(len(kl), np.float32)
+    dp = np.zeros(len(kl), np.float32)
+    rc = lib().orb_refs_stereo(ref_l._h, ref_r._h, kl.ctypes.data, len(kl), _p(dl, C.c_uint8), kr.ctypes.data, len(kr), _p(dr, C.c_uint8),
+                               float(bf), float(b), _p(ur, C.c_float), _p(dp, C.c_float))
+    assert rc == 0
+    return ur, dp
+
+
+def features_in_area(kps, bounds, x, y, r, min_level=-1, max_level=-1):
+    """Frame::GetFeaturesInArea (frame.cpp:678-744) on the grid Frame::AssignFeaturesToGrid (:386-414) builds."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    bd = np.ascontiguousarray(bounds, np.float32)
+    out = np.zeros(max(len(kps), 1), np.int32)
+    n = lib().orb_refs_features_in_area(kps.ctypes.data, len(kps), _p(bd, C.c_float), float(x), float(y), float(r), int(min_level),
+                                        int(max_level), _p(out, C.c_int32), len(out))
+    return out[:n].copy()
+
+
+def search_for_initialization(k1, d1, k2, d2, bounds, prev_matched, window_size=100, nn_ratio=0.9, check_orientation=True):
+    """FMatcher(nn_ratio, check_orientation).SearchForInitialization (fmatcher.cpp:983-1098 with :2813-2854, :2859-2875 and
+    the frame grid of frame.cpp:386-414, 678-756) -> (nmatches, vnMatches12, vbPrevMatched)."""
+    k1 = np.ascontiguousarray(k1, KP_DTYPE); k2 = np.ascontiguousarray(k2, KP_DTYPE)
+    d1 = np.ascontiguousarray(d1, np.uint8).reshape(-1, 32); d2 = np.ascontiguousarray(d2, np.uint8).reshape(-1, 32)
+    bd = np.ascontiguousarray(bounds, np.float32)
+    prev = np.ascontiguousarray(prev_matched, np.float32).reshape(-1, 2).copy()
+    m12 = np.zeros(len(k1), np.int32)
+    n = lib().orb_refs_search_for_initialization(k1.ctypes.data, len(k1), _p(d1, C.c_uint8), k2.ctypes.data, len(k2), _p(d2, C.c_uint8),
+                                                 _p(bd, C.c_float), _p(prev, C.c_float), int(window_size), float(nn_ratio),
+                                                 int(bool(check_orientation)), _p(m12, C.c_int32))
+    return int(n), m12, prev
+
+
+def search_by_projection(k_last, xw, desc_mp, outlier, observed, k2, d2, u_right2, blocked2, nleft2, bounds, tcw_cur, tcw_last, trl, cam,
+                         scale_factors, th, mono, bf, b, check_orientation=True):
+    """FMatcher(0.9, check_orientation).SearchByProjection(CurrentFrame, LastFrame, th, bMono) (fmatcher.cpp:2471-2687, the
+    reference's own text incl. the two-camera branch :2593-2660) on a synthetic scene: last-frame keypoints with world points
+    `xw` (NaN = no map point), world -> camera poses (4x4), a pinhole camera (Pinhole::project, pinhole.cpp:13-26), `nleft2` < 0
+    for one camera or Nleft of a rig with `trl` (3x4).  Returns (nmatches, assigned[n2], host) where `host` holds what the
+    caller of the device API computes on the host - uv, uv_right, invz, valid, direction - as the reference's own
+    expressions evaluate them."""
+    kl = np.ascontiguousarray(k_last, KP_DTYPE); k2 = np.ascontiguousarray(k2, KP_DTYPE)
+    n1, n2 = len(kl), len(k2)
+    f = lambda a: np.ascontiguousarray(a, np.float32)
+    u = lambda a: np.ascontiguousarray(a, np.uint8)
+    xw, dmp, d2 = f(xw).reshape(n1, 3), u(desc_mp).reshape(n1, 32), u(d2).reshape(n2, 32)
+    out, obs = u(outlier), u(observed)
+    ur = None if u_right2 is None else f(u_right2)
+    bl = None if blocked2 is None else u(blocked2)
+    bd, tc, tl, cm, sf = f(bounds), f(tcw_cur).reshape(16), f(tcw_last).reshape(16), f(cam), f(scale_factors)
+    tr = None if trl is None else f(trl).reshape(12)
+    asg = np.zeros(n2, np.int32)
+    uv, uvr, invz = np.zeros((n1, 2), np.float32), np.zeros((n1, 2), np.float32), np.zeros(n1, np.float32)
+    valid = np.zeros(n1, np.uint8)
+    direction = C.c_int32(0)
+    n = lib().orb_refs_search_by_projection(
+        n1, kl.ctypes.data, _p(xw, C.c_float), _p(dmp, C.c_uint8), _p(out, C.c_uint8), _p(obs, C.c_uint8), k2.ctypes.data, n2,
+        _p(d2, C.c_uint8), None if ur is None else _p(ur, C.c_float), None if bl is None else _p(bl, C.c_uint8), int(nleft2),
+        _p(bd, C.c_float), _p(tc, C.c_float), _p(tl, C.c_float), None if tr is None else _p(tr, C.c_float), _p(cm, C.c_float),
+        _p(sf, C.c_float), len(sf), float(th), int(bool(mono)), float(bf), float(b), 0.9, int(bool(check_orientation)),
+        _p(asg, C.c_int32), _p(uv, C.c_float), _p(uvr, C.c_float), _p(invz, C.c_float), _p(valid, C.c_uint8), C.byref(direction))
+    return int(n), asg, {"uv": uv, "uv_right": uvr, "invz": invz, "valid": valid, "direction": int(direction.value)}

@@ -33,6 +33,8 @@ typedef unsigned char uchar;
 
 #define CV_8U 0
 #define CV_8UC1 0
+#define CV_32F 5
+#define CV_32FC1 5
 #define CV_PI 3.1415926535897932384626433832795
 #define CV_Assert(expr) do { if (!(expr)) throw std::runtime_error("CV_Assert failed: " #expr); } while (0)
 
@@ -68,6 +70,13 @@ template <typename T> static inline Point_<T>& operator*=(Point_<T>& a, int b) {
 typedef Point_<int> Point2i;
 typedef Point2i Point;
 typedef Point_<float> Point2f;
+template <typename T>
+struct Point3_ {
+    T x, y, z;
+    Point3_() : x(0), y(0), z(0) {}
+    Point3_(T x_, T y_, T z_) : x(x_), y(y_), z(z_) {}
+};
+typedef Point3_<float> Point3f;
 
 struct Size {
     int width, height;
@@ -104,7 +113,9 @@ class _OutputArray;
 typedef const _InputArray& InputArray;
 typedef const _OutputArray& OutputArray;
 
-// CV_8UC1 matrices only.  A Mat is a view (data, rows, cols, step) into a shared whole buffer.
+// CV_8UC1 matrices (everything fextractor.cpp touches) and single-channel CV_32F ones (the 11 x 11 correlation patches of
+// Frame::ComputeStereoMatches, oracle/ref_compat/ref_slices.cpp).  A Mat is a view (data, rows, cols, step in bytes) into
+// a shared whole buffer.
 class Mat {
 public:
     struct Whole { uchar* base; int rows, cols; size_t step; bool owned; ~Whole() { if (owned) std::free(base); } };
@@ -113,36 +124,46 @@ public:
     uchar* data;
     MatStep step;
     std::shared_ptr<Whole> whole;
+    int tp = CV_8UC1;
+    size_t esz() const { return tp == CV_32F ? 4 : 1; }
 
     Mat() : rows(0), cols(0), data(nullptr) {}
     Mat(int r, int c, int type) : rows(0), cols(0), data(nullptr) { create(r, c, type); }
     Mat(Size s, int type) : rows(0), cols(0), data(nullptr) { create(s.height, s.width, type); }
     // header over caller memory (no copy), like cv::Mat(rows, cols, type, void* data, size_t step)
-    Mat(int r, int c, int type, void* ptr, size_t stp = 0) : rows(r), cols(c), data((uchar*)ptr), step(stp ? stp : (size_t)c) {
-        assert(type == CV_8UC1); (void)type;
+    Mat(int r, int c, int type, void* ptr, size_t stp = 0) : rows(r), cols(c), data((uchar*)ptr), tp(type) {
+        assert(type == CV_8UC1 || type == CV_32F);
+        step = stp ? stp : (size_t)c * esz();
         whole = std::shared_ptr<Whole>(new Whole{(uchar*)ptr, r, c, (size_t)step, false});
     }
 
     void create(int r, int c, int type) {
-        assert(type == CV_8UC1); (void)type;
-        if (data && rows == r && cols == c) return;          // Mat::create keeps a matching buffer
-        rows = r; cols = c; step = (size_t)c;
-        size_t bytes = (size_t)r * c;
+        assert(type == CV_8UC1 || type == CV_32F);
+        if (data && rows == r && cols == c && tp == type) return;          // Mat::create keeps a matching buffer
+        tp = type;
+        rows = r; cols = c; step = (size_t)c * esz();
+        size_t bytes = (size_t)r * c * esz();
         uchar* p = (uchar*)std::calloc(bytes ? bytes : 1, 1);
-        whole = std::shared_ptr<Whole>(new Whole{p, r, c, (size_t)c, true});
+        whole = std::shared_ptr<Whole>(new Whole{p, r, c, (size_t)step, true});
         data = p;
     }
     void create(Size s, int type) { create(s.height, s.width, type); }
     void release() { rows = cols = 0; data = nullptr; step = 0; whole.reset(); }
 
-    static Mat zeros(int r, int c, int type) { Mat m; m.create(r, c, type); std::memset(m.data, 0, (size_t)r * c); return m; }
+    static Mat zeros(int r, int c, int type) { Mat m; m.create(r, c, type); std::memset(m.data, 0, (size_t)r * c * m.esz()); return m; }
+    static Mat ones(int r, int c, int type) {
+        Mat m; m.create(r, c, type);
+        for (int y = 0; y < r; ++y)
+            for (int x = 0; x < c; ++x) { if (type == CV_32F) m.at<float>(y, x) = 1.f; else m.at<uchar>(y, x) = 1; }
+        return m;
+    }
 
-    int type() const { return CV_8UC1; }
+    int type() const { return tp; }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
     Size size() const { return Size(cols, rows); }
     size_t step1(int = 0) const { return step; }
     size_t total() const { return (size_t)rows * cols; }
-    bool isContinuous() const { return rows == 1 || (size_t)step == (size_t)cols; }
+    bool isContinuous() const { return rows == 1 || (size_t)step == (size_t)cols * esz(); }
     bool isSubmatrix() const { return whole && (rows != whole->rows || cols != whole->cols); }
 
     uchar* ptr(int i = 0) { return data + (size_t)i * step; }
@@ -151,11 +172,20 @@ public:
     template <typename T> const T* ptr(int i = 0) const { return (const T*)(data + (size_t)i * step); }
     template <typename T> T& at(int r, int c) { return ((T*)(data + (size_t)r * step))[c]; }
     template <typename T> const T& at(int r, int c) const { return ((const T*)(data + (size_t)r * step))[c]; }
+    // Mat::at(i0): element i0 of a row vector / a continuous matrix, row i0 of a column vector
+    template <typename T> T& at(int i) { return cols == 1 ? at<T>(i, 0) : at<T>(i / cols, i % cols); }
+    template <typename T> const T& at(int i) const { return cols == 1 ? at<T>(i, 0) : at<T>(i / cols, i % cols); }
+    Mat t() const {
+        assert(tp == CV_32F);
+        Mat o; o.create(cols, rows, CV_32F);
+        for (int y = 0; y < rows; ++y) for (int x = 0; x < cols; ++x) o.at<float>(x, y) = at<float>(y, x);
+        return o;
+    }
 
     Mat operator()(const Rect& r) const {
         assert(r.x >= 0 && r.y >= 0 && r.x + r.width <= cols && r.y + r.height <= rows);
         Mat m(*this);
-        m.data = data + (size_t)r.y * step + r.x; m.rows = r.height; m.cols = r.width;
+        m.data = data + (size_t)r.y * step + (size_t)r.x * esz(); m.rows = r.height; m.cols = r.width;
         return m;
     }
     Mat rowRange(int a, int b) const { return (*this)(Rect(0, a, cols, b - a)); }
@@ -166,26 +196,80 @@ public:
     // Mat::locateROI / adjustROI, used by copyMakeBorder without BORDER_ISOLATED
     void locateROI(Size& wholeSize, Point& ofs) const {
         size_t d = (size_t)(data - whole->base);
-        ofs.y = (int)(d / whole->step); ofs.x = (int)(d % whole->step);
+        ofs.y = (int)(d / whole->step); ofs.x = (int)((d % whole->step) / esz());
         wholeSize = Size(whole->cols, whole->rows);
     }
     Mat& adjustROI(int dtop, int dbottom, int dleft, int dright) {
         Size ws; Point ofs; locateROI(ws, ofs);
         int r1 = std::max(ofs.y - dtop, 0), r2 = std::min(ofs.y + rows + dbottom, ws.height);
         int c1 = std::max(ofs.x - dleft, 0), c2 = std::min(ofs.x + cols + dright, ws.width);
-        data = whole->base + (size_t)r1 * whole->step + c1; rows = r2 - r1; cols = c2 - c1;
+        data = whole->base + (size_t)r1 * whole->step + (size_t)c1 * esz(); rows = r2 - r1; cols = c2 - c1;
         return *this;
     }
 
     Mat clone() const {
         Mat m;
         if (empty()) return m;
-        m.create(rows, cols, CV_8UC1);
-        for (int y = 0; y < rows; ++y) std::memcpy(m.ptr(y), ptr(y), (size_t)cols);
+        m.create(rows, cols, tp);
+        for (int y = 0; y < rows; ++y) std::memcpy(m.ptr(y), ptr(y), (size_t)cols * esz());
         return m;
     }
     inline void copyTo(OutputArray dst) const;
+    // Mat::convertTo without scaling: 8U -> 32F (exact) or a same-type copy.  `dst` may be *this (the reference converts a
+    // ROI view in place): a new buffer is made first, the source buffer is never written.
+    void convertTo(Mat& dst, int rtype) const {
+        Mat out;
+        out.create(rows, cols, rtype);
+        for (int y = 0; y < rows; ++y)
+            for (int x = 0; x < cols; ++x) {
+                const float v = tp == CV_32F ? at<float>(y, x) : (float)at<uchar>(y, x);
+                if (rtype == CV_32F) out.at<float>(y, x) = v; else out.at<uchar>(y, x) = (uchar)v;
+            }
+        dst = out;
+    }
 };
+
+// the matrix expressions of frame.cpp:921-937: (float) * Mat::ones(...), Mat - Mat, norm(a, b, NORM_L1) on CV_32F patches
+enum NormTypes { NORM_INF = 1, NORM_L1 = 2, NORM_L2 = 4 };
+static inline Mat operator*(float s, const Mat& m) {
+    assert(m.type() == CV_32F);
+    Mat o; o.create(m.rows, m.cols, CV_32F);
+    for (int y = 0; y < m.rows; ++y) for (int x = 0; x < m.cols; ++x) o.at<float>(y, x) = s * m.at<float>(y, x);
+    return o;
+}
+static inline Mat operator*(const Mat& m, float s) { return s * m; }
+static inline Mat operator-(const Mat& a, const Mat& b) {
+    assert(a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);
+    Mat o; o.create(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) o.at<float>(y, x) = a.at<float>(y, x) - b.at<float>(y, x);
+    return o;
+}
+// the pose algebra of fmatcher.cpp:2481-2505 on small CV_32F matrices: -A, A * B (gemm: float products accumulated in
+// double per element like OpenCV's 32F GEMM kernel for small sizes, rounded once), A + B
+static inline Mat operator-(const Mat& a) { return -1.f * a; }
+static inline Mat operator+(const Mat& a, const Mat& b) {
+    assert(a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);
+    Mat o; o.create(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) o.at<float>(y, x) = a.at<float>(y, x) + b.at<float>(y, x);
+    return o;
+}
+static inline Mat operator*(const Mat& a, const Mat& b) {
+    assert(a.type() == CV_32F && b.type() == CV_32F && a.cols == b.rows);
+    Mat o; o.create(a.rows, b.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < b.cols; ++x) {
+            double s = 0;
+            for (int k = 0; k < a.cols; ++k) s += (double)a.at<float>(y, k) * (double)b.at<float>(k, x);
+            o.at<float>(y, x) = (float)s;
+        }
+    return o;
+}
+static inline double norm(const Mat& a, const Mat& b, int normType) {
+    assert(normType == NORM_L1 && a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols); (void)normType;
+    double s = 0;                       // cv::norm accumulates 32F L1 norms in double
+    for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) s += std::fabs((double)a.at<float>(y, x) - (double)b.at<float>(y, x));
+    return s;
+}
 
 // Proxies with the call shapes fextractor.cpp uses: image.empty()/getMat()/type(), descriptors.create()/
 // release()/getMat().
@@ -213,10 +297,10 @@ public:
 static inline InputArray noArray() { static _OutputArray none; return none; }
 
 inline void Mat::copyTo(OutputArray dst) const {
-    dst.create(rows, cols, CV_8UC1);
+    dst.create(rows, cols, tp);
     Mat d = dst.getMat();
     for (int y = 0; y < rows; ++y)
-        if (d.ptr(y) != ptr(y)) std::memmove(d.ptr(y), ptr(y), (size_t)cols);
+        if (d.ptr(y) != ptr(y)) std::memmove(d.ptr(y), ptr(y), (size_t)cols * esz());
 }
 
 // opencv2/core/types.hpp: class DMatch; opencv2/core/mat.hpp: Mat1b = Mat_<uchar>

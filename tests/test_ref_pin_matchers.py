@@ -1,0 +1,234 @@
+"""Parity pin of the matcher rows against the reference's OWN function bodies.
+
+oracle/_ref/liborb_ref.so also holds Frame::ComputeStereoMatches (frame.cpp:823-997), Frame::AssignFeaturesToGrid /
+GetFeaturesInArea / PosInGrid (frame.cpp:386-414, 678-756), FMatcher::SearchForInitialization (fmatcher.cpp:983-1098),
+ComputeThreeMaxima (:2813-2854) and DescriptorDistance (:2859-2875): oracle/ref.mk cuts those definitions out of the
+reference files by line range at build time and compiles them unmodified against stand-in class declarations
+(oracle/ref_compat/ref_slices.cpp); the pyramids the stereo matcher reads are the reference FExtractor's own.
+Compared here: the oracle (CPU), the emulation build (CPU) and - marked gpu - the CUDA path; committed fixtures
+(tests/golden/refm_*.npz, written by tests/golden/make_ref_matcher_golden.py) let the comparisons run where
+/root/reference is absent."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from oracle import ref
+from tests import ref_matcher_cases as cases
+
+
+
+@pytest.fixture(scope="module")
+def emu_lib(oracle_mod):
+    import __graft_entry__ as ge
+    return ge.build_emu()
+
+
+needs_ref = pytest.mark.skipif(not ref.available(), reason="oracle/_ref/liborb_ref.so not built and /root/reference absent")
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+# --------------------------------------------------------------------------------------------- row a-8
+@needs_ref
+def test_descriptor_distance_reference_text():
+    rng = np.random.default_rng(3)
+    d = rng.integers(0, 256, (400, 32), dtype=np.uint8)
+    d[0] = 0
+    d[1] = 255
+    d[2] = d[3]
+    for i in range(0, 400, 2):
+        want = ref.descriptor_distance(d[i], d[i + 1])
+        assert want == int(np.unpackbits(d[i] ^ d[i + 1]).sum())
+        assert oracle.descriptor_distance(d[i], d[i + 1]) == want
+    assert ref.descriptor_distance(d[0], d[1]) == 256 and ref.descriptor_distance(d[2], d[3]) == 0
+
+
+# --------------------------------------------------------------------------------------------- row a-10
+@needs_ref
+@pytest.mark.parametrize("name", list(cases.STEREO))
+def test_oracle_stereo_equals_reference_text(name):
+    """ComputeStereoMatches: the reference's text on the reference extractor's pyramids == oracle.stereo_match on the
+    oracle's pyramids (which test_ref_pin.py shows to be the same bytes), mvuRight / mvDepth bit for bit."""
+    c = cases.stereo_inputs(name)
+    ur, dp = ref.stereo_match(c["rl"], c["rr"], c["kl"], c["dl"], c["kr"], c["dr"], c["bf"], c["b"])
+    our, odp, _, _ = oracle.stereo_match(c["ol"], c["orr"], c["kl"], c["dl"], c["kr"], c["dr"], c["bf"], c["b"])
+    assert np.array_equal(_bits(ur), _bits(our)) and np.array_equal(_bits(dp), _bits(odp))
+    n = int((dp > 0).sum())
+    print(f"{name}: {len(c['kl'])} left / {len(c['kr'])} right keypoints, {n} stereo matches")
+    assert n > 50
+
+
+def _check_stereo_fixture(golden_dir, name, run):
+    g = np.load(os.path.join(golden_dir, f"refm_stereo_{name}.npz"))
+    ur, dp = run(g)
+    assert np.array_equal(_bits(ur), g["u_right"].view(np.uint32)) and np.array_equal(_bits(dp), g["depth"].view(np.uint32))
+
+
+@pytest.mark.parametrize("name", list(cases.STEREO))
+def test_oracle_stereo_equals_committed_reference_fixture(golden_dir, name):
+    """Runs anywhere: the oracle on the same images must reproduce the reference's committed mvuRight / mvDepth (and, on
+    the way, the reference's keypoints and descriptors)."""
+    def run(g):
+        left, right = cases.stereo_images(name)
+        nf = cases.STEREO[name][1]
+        ol, orr = oracle.OracleExtractor(nf), oracle.OracleExtractor(nf)
+        _, kl, dl = ol.compute(left, (0, 0))
+        _, kr, dr = orr.compute(right, (0, 0))
+        assert np.array_equal(dl, g["dl"]) and np.array_equal(dr, g["dr"]) and np.array_equal(kl["x"], g["klx"])
+        return oracle.stereo_match(ol, orr, kl, dl, kr, dr, float(g["bf"]), float(g["b"]))[:2]
+    _check_stereo_fixture(golden_dir, name, run)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(cases.STEREO))
+def test_cuda_stereo_equals_committed_reference_fixture(golden_dir, name):
+    """The CUDA path (k_stereo_rows / coarse / refine / cut behind viorb_compute_stereo_matches and the batched resident
+    form) against the reference's own ComputeStereoMatches output."""
+    from vi_slam_b200 import FExtractor, matcher
+
+    def run(g):
+        left, right = cases.stereo_images(name)
+        nf = cases.STEREO[name][1]
+        h, w = left.shape
+        gl, gr = FExtractor(nf, max_size=(w, h)), FExtractor(nf, max_size=(w, h))
+        _, kl, dl = gl.compute(left, None, (0, 0))
+        _, kr, dr = gr.compute(right, None, (0, 0))
+        assert np.array_equal(dl, g["dl"]) and np.array_equal(dr, g["dr"]) and np.array_equal(kl["x"], g["klx"])
+        ur, dp, _, _ = matcher.compute_stereo_matches(gl, gr, float(g["bf"]), float(g["b"]))
+        matcher.stereo_batch(gl, gr, 1, float(g["bf"]), float(g["b"]), 0.7)
+        r = matcher.stereo_fetch(gl, 0)
+        assert np.array_equal(_bits(r["u_right"]), _bits(ur)) and np.array_equal(_bits(r["depth"]), _bits(dp))
+        return ur, dp
+    _check_stereo_fixture(golden_dir, name, run)
+
+
+# --------------------------------------------------------------------------------------------- row a-11 / f-1 (grid, initialiser)
+@needs_ref
+def test_features_in_area_reference_text():
+    """GetFeaturesInArea on the AssignFeaturesToGrid grid: same indices in the same order, incl. windows that leave the
+    image, level filters and degenerate radii."""
+    k1, _, k2, _, bounds = cases.ini_inputs("kitti")[:5]
+    rng = np.random.default_rng(11)
+    for i in range(300):
+        x, y = float(rng.uniform(-80, bounds[1] + 80)), float(rng.uniform(-80, bounds[3] + 80))
+        r = float(rng.choice([0.0, 3.0, 15.0, 100.0, 400.0]))
+        lo, hi = [(-1, -1), (0, 0), (2, -1), (1, 3), (0, 7)][i % 5]
+        want = ref.features_in_area(k2, bounds, x, y, r, lo, hi)
+        assert np.array_equal(oracle.features_in_area(k2, bounds, x, y, r, lo, hi), want), (x, y, r, lo, hi)
+
+
+@needs_ref
+@pytest.mark.parametrize("name", list(cases.INI))
+@pytest.mark.parametrize("nn_ratio,check", [(0.9, True), (0.6, False)])
+def test_oracle_search_for_initialization_equals_reference_text(name, nn_ratio, check):
+    k1, d1, k2, d2, bounds, prev, win = cases.ini_inputs(name)
+    n, m12, pm = ref.search_for_initialization(k1, d1, k2, d2, bounds, prev, win, nn_ratio, check)
+    on, om12, opm = oracle.search_for_initialization(k1, d1, k2, d2, bounds, prev, win, nn_ratio, check)
+    assert n == on and np.array_equal(m12, om12) and np.array_equal(_bits(pm), _bits(opm))
+    print(f"{name} nn {nn_ratio} orientation {check}: {n} matches of {len(k1)} keypoints")
+    assert n > 20
+
+
+def _check_ini_fixture(golden_dir, name, run):
+    g = np.load(os.path.join(golden_dir, f"refm_ini_{name}.npz"))
+    n, m12, pm = run(g["k1"], g["d1"], g["k2"], g["d2"], g["bounds"], g["prev"], int(g["window"]))
+    assert n == int(g["nmatches"]) and np.array_equal(m12, g["matches12"]) and np.array_equal(_bits(pm), g["prev_out"].view(np.uint32))
+
+
+@pytest.mark.parametrize("name", list(cases.INI))
+def test_oracle_search_for_initialization_equals_committed_reference_fixture(golden_dir, name):
+    _check_ini_fixture(golden_dir, name, lambda *a: oracle.search_for_initialization(*a, 0.9, True))
+
+
+@pytest.mark.parametrize("name", ["qvga"])
+def test_emulation_search_for_initialization_equals_committed_reference_fixture(golden_dir, emu_lib, name):
+    from vi_slam_b200 import matcher
+    _check_ini_fixture(golden_dir, name, lambda *a: matcher.search_for_initialization(*a, 0.9, True, lib_path=emu_lib))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(cases.INI))
+def test_cuda_search_for_initialization_equals_committed_reference_fixture(golden_dir, name):
+    from vi_slam_b200 import matcher
+    _check_ini_fixture(golden_dir, name, lambda *a: matcher.search_for_initialization(*a, 0.9, True))
+
+
+# --------------------------------------------------------------------------------------------- row f-1 (tracking matcher, both camera branches)
+def _ours_projection(run_single, run_rig, c, host):
+    kl = c["k_last"]
+    if int(c["nleft2"]) < 0:
+        n, a = run_single(host["uv"], host["invz"], kl["octave"], kl["angle"], c["desc_mp"], host["valid"], c["observed"], c["k2"], c["d2"],
+                          c["u_right2"], c["blocked2"], c["bounds"], c["sf"], float(c["th"]), float(c["bf"]), int(host["direction"]),
+                          bool(c["check"]))
+    else:
+        n, a = run_rig(host["uv"], host["uv_right"], host["invz"], kl["octave"], kl["angle"], c["desc_mp"], host["valid"], c["observed"],
+                       c["k2"], c["d2"], int(c["nleft2"]), c["blocked2"], c["bounds"], c["sf"], float(c["th"]), int(host["direction"]),
+                       bool(c["check"]))
+    return int(n), np.where(a >= 0, a, -1)           # -2 (cleared by the rotation check) and -1 are both "no map point"
+
+
+def _ref_projection(c):
+    return ref.search_by_projection(c["k_last"], c["xw"], c["desc_mp"], c["outlier"], c["observed"], c["k2"], c["d2"], c["u_right2"],
+                                    c["blocked2"], c["nleft2"], c["bounds"], c["tcw_cur"], c["tcw_last"], c["trl"], c["cam"], c["sf"],
+                                    c["th"], c["mono"], c["bf"], c["b"], c["check"])
+
+
+@needs_ref
+@pytest.mark.parametrize("name", list(cases.PROJ))
+def test_oracle_search_by_projection_equals_reference_text(name):
+    """SearchByProjection(CurrentFrame, LastFrame) - pose algebra, Pinhole::project, window query, distance loop, the
+    mvuRight predicate, the two-camera pass with its Nleft offsets, the joint rotation histogram - run as the reference's own
+    text; the oracle gets the uv / invz / valid / direction that text computed and must give the same assignment."""
+    c = cases.proj_scene(name)
+    n, asg, host = _ref_projection(c)
+    on, oa = _ours_projection(oracle.search_by_projection, oracle.search_by_projection_rig, c, host)
+    assert n == on and np.array_equal(asg, oa)
+    print(f"{name}: direction {host['direction']}, {int(host['valid'].sum())} projected points, {n} matches")
+    assert n > 300
+    if c["nleft2"] >= 0:
+        assert (asg[:c["nleft2"]] >= 0).sum() > 100 and (asg[c["nleft2"]:] >= 0).sum() > 100
+
+
+def _proj_fixture(golden_dir, name):
+    g = np.load(os.path.join(golden_dir, f"refm_proj_{name}.npz"))
+    c = {k: g[k] for k in g.files}
+    for k in ("u_right2", "blocked2"):
+        if c[k].size == 0:
+            c[k] = None
+    host = {k: g["host_" + k] for k in ("uv", "uv_right", "invz", "valid")}
+    host["direction"] = int(g["host_direction"])
+    return c, host, int(g["nmatches"]), g["assigned"]
+
+
+@pytest.mark.parametrize("name", list(cases.PROJ))
+def test_oracle_search_by_projection_equals_committed_reference_fixture(golden_dir, name):
+    c, host, n, asg = _proj_fixture(golden_dir, name)
+    on, oa = _ours_projection(oracle.search_by_projection, oracle.search_by_projection_rig, c, host)
+    assert on == n and np.array_equal(oa, asg)
+
+
+def _device_runs(lib_path):
+    from vi_slam_b200 import matcher
+    single = lambda *a: matcher.search_by_projection(*a, lib_path=lib_path)
+    rig = lambda uv, uvr, invz, lo, la, dmp, va, ob, k2, d2, nl, bl, bd, sf, th, direction, chk: matcher.search_by_projection(
+        uv, invz, lo, la, dmp, va, ob, k2, d2, None, bl, bd, sf, th, 0.0, direction, chk, lib_path=lib_path, uv_right=uvr, nleft2=nl)
+    return single, rig
+
+
+@pytest.mark.parametrize("name", ["mono", "rig"])
+def test_emulation_search_by_projection_equals_committed_reference_fixture(golden_dir, emu_lib, name):
+    c, host, n, asg = _proj_fixture(golden_dir, name)
+    on, oa = _ours_projection(*_device_runs(emu_lib), c, host)
+    assert on == n and np.array_equal(oa, asg)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(cases.PROJ))
+def test_cuda_search_by_projection_equals_committed_reference_fixture(golden_dir, name):
+    c, host, n, asg = _proj_fixture(golden_dir, name)
+    on, oa = _ours_projection(*_device_runs(None), c, host)
+    assert on == n and np.array_equal(oa, asg)
