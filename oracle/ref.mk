@@ -13,8 +13,10 @@ OUT := _ref/liborb_ref.so
 FRAME_CPP := $(REF)/src/datastructures/frame.cpp
 FMATCHER_CPP := $(REF)/src/geometry/fmatcher.cpp
 PINHOLE_CPP := $(REF)/src/geometry/cameramodels/pinhole.cpp
+DBOW3 := $(REF)/thirdparty/DBoW3/DBoW3/src
 SRC := $(REF)/src/geometry/fextractor.cpp ref_compat/cv_compat.cpp ref_compat/ref_driver.cpp ref_compat/ref_slices.cpp orb_oracle.cpp \
-       $(FRAME_CPP) $(FMATCHER_CPP) $(PINHOLE_CPP)
+       $(FRAME_CPP) $(FMATCHER_CPP) $(PINHOLE_CPP) ref_compat/ref_dbow3.cpp $(DBOW3)/Vocabulary.cpp $(DBOW3)/DescManip.cpp \
+       $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp
 
 all: $(OUT)
 
@@ -23,7 +25,7 @@ all: $(OUT)
 # slice <file> <first> <last> <name> <text the first line must contain>
 define slice
 	@sed -n '$(2)p' $(1) | grep -q -F '$(5)' || { echo "ref.mk: $(1):$(2) is not '$(5)' - the reference changed" >&2; exit 1; }
-	@sed -n '$(3)p' $(1) | grep -q '^        }' || { echo "ref.mk: $(1):$(3) does not close a function" >&2; exit 1; }
+	@sed -n '$(3)p' $(1) | grep -q '^ *}' || { echo "ref.mk: $(1):$(3) does not close a function" >&2; exit 1; }
 	sed -n '$(2),$(3)p' $(1) > _ref/gen/$(4)_$(2)_$(3).inc
 endef
 
@@ -40,10 +42,16 @@ $(OUT): $(SRC) ref_compat/cv_compat.hpp ../vi_slam_b200/csrc/orb_pattern.inc ref
 	$(call slice,$(FMATCHER_CPP),2471,2687,fmatcher,const Frame &LastFrame)
 	$(call slice,$(PINHOLE_CPP),13,16,pinhole,const cv::Point3f &p3D)
 	$(call slice,$(PINHOLE_CPP),22,26,pinhole,const cv::Mat &m3D)
+	$(call slice,$(DBOW3)/Vocabulary.cpp,754,820,Vocabulary,void Vocabulary::transform)
+	$(call slice,$(DBOW3)/Vocabulary.cpp,838,876,Vocabulary,void Vocabulary::transform)
+	$(call slice,$(DBOW3)/DescManip.cpp,92,130,DescManip,double DescManip::distance)
+	@# -include ...: the vendored DBoW3 headers rely on transitive std includes that GCC 13's leaner headers no longer provide
 	$(CXX) $(CXXFLAGS) -Iref_compat -I_ref -I$(REF)/include -shared -Wl,-Bsymbolic -o $@ \
 	    $(REF)/src/geometry/fextractor.cpp ref_compat/cv_compat.cpp ref_compat/ref_driver.cpp ref_compat/ref_slices.cpp \
+	    -I$(DBOW3) -include cstdint -include iostream -include string ref_compat/ref_dbow3.cpp $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp \
 	    -x c++ -std=c++17 orb_oracle.cpp
-	sha256sum $(REF)/src/geometry/fextractor.cpp $(REF)/include/vi_slam/geometry/fextractor.h $(FRAME_CPP) $(FMATCHER_CPP) $(PINHOLE_CPP) > _ref/SOURCES.sha256
+	sha256sum $(REF)/src/geometry/fextractor.cpp $(REF)/include/vi_slam/geometry/fextractor.h $(FRAME_CPP) $(FMATCHER_CPP) $(PINHOLE_CPP) \
+	    $(DBOW3)/Vocabulary.cpp $(DBOW3)/DescManip.cpp $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp > _ref/SOURCES.sha256
 	rm -rf _ref/gen          # the slices are build intermediates: only the library stays
 
 clean:

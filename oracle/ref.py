@@ -25,7 +25,7 @@ def build(force: bool = False) -> str | None:
     reference checkout is absent (GPU box) and no prebuilt library travelled."""
     if os.path.exists(REF_SOURCE):
         deps = [REF_SOURCE, os.path.join(_HERE, "orb_oracle.cpp"), os.path.join(_HERE, "ref.mk")] + \
-               [os.path.join(_HERE, "ref_compat", f) for f in ("cv_compat.hpp", "cv_compat.cpp", "ref_driver.cpp", "ref_slices.cpp")] + \
+               [os.path.join(_HERE, "ref_compat", f) for f in ("cv_compat.hpp", "cv_compat.cpp", "ref_driver.cpp", "ref_slices.cpp", "ref_dbow3.cpp")] + \
                [os.path.join(REFERENCE, "src", "datastructures", "frame.cpp"), os.path.join(REFERENCE, "src", "geometry", "fmatcher.cpp")]
         stale = not os.path.exists(LIB_PATH) or any(os.path.getmtime(d) > os.path.getmtime(LIB_PATH) for d in deps)
         if force or stale:
@@ -69,6 +69,12 @@ def lib():
         L.orb_refs_search_by_projection.argtypes = [C.c_int, C.c_void_p, f32p, u8p, u8p, u8p, C.c_void_p, C.c_int, u8p, f32p, u8p, C.c_int,
                                                     f32p, f32p, f32p, f32p, f32p, f32p, C.c_int, C.c_float, C.c_int, C.c_float, C.c_float,
                                                     C.c_float, C.c_int, i32p, f32p, f32p, f32p, u8p, i32p]
+        # ref_dbow3.cpp: DBoW3's own transform
+        L.orb_refd_vocab_create.restype = C.c_void_p
+        L.orb_refd_vocab_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, i32p, i32p, u8p, C.POINTER(C.c_double), i32p]
+        L.orb_refd_vocab_destroy.argtypes = [C.c_void_p]
+        u32p = C.POINTER(C.c_uint32)
+        L.orb_refd_transform.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int, u32p, C.POINTER(C.c_double), i32p, u32p, i32p, u32p, i32p]
         _lib = L
     return _lib
 
@@ -227,3 +233,31 @@ def search_by_projection(k_last, xw, desc_mp, outlier, observed, k2, d2, u_right
         _p(sf, C.c_float), len(sf), float(th), int(bool(mono)), float(bf), float(b), 0.9, int(bool(check_orientation)),
         _p(asg, C.c_int32), _p(uv, C.c_float), _p(uvr, C.c_float), _p(invz, C.c_float), _p(valid, C.c_uint8), C.byref(direction))
     return int(n), asg, {"uv": uv, "uv_right": uvr, "invz": invz, "valid": valid, "direction": int(direction.value)}
+
+
+class RefVocabulary:
+    """DBoW3::Vocabulary::transform - DBoW3's own text (Vocabulary.cpp:754-876, DescManip.cpp:92-130, BowVector.cpp and
+    FeatureVector.cpp whole; oracle/ref_compat/ref_dbow3.cpp) on a tree given as flat arrays (synthetic.make_vocabulary)."""
+
+    def __init__(self, voc):
+        self._keep = [np.ascontiguousarray(voc["child_start"], np.int32), np.ascontiguousarray(voc["children"], np.int32),
+                      np.ascontiguousarray(voc["descriptors"], np.uint8), np.ascontiguousarray(voc["weight"], np.float64),
+                      np.ascontiguousarray(voc["word_id"], np.int32)]
+        cs, ch, de, we, wi = self._keep
+        self._h = lib().orb_refd_vocab_create(len(we), int(voc["levels"]), int(voc["weighting"]), int(voc["scoring"]), _p(cs, C.c_int32),
+                                              _p(ch, C.c_int32), _p(de, C.c_uint8), _p(we, C.c_double), _p(wi, C.c_int32))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orb_refd_vocab_destroy(self._h)
+            self._h = None
+
+    def transform(self, desc, levelsup=4):
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(desc)
+        bw, bv = np.zeros(n + 1, np.uint32), np.zeros(n + 1, np.float64)
+        fn, fs, ff = np.zeros(n + 1, np.uint32), np.zeros(n + 2, np.int32), np.zeros(n + 1, np.uint32)
+        nb, nf = C.c_int32(), C.c_int32()
+        lib().orb_refd_transform(self._h, _p(desc, C.c_uint8), n, int(levelsup), _p(bw, C.c_uint32), _p(bv, C.c_double), C.byref(nb),
+                                 _p(fn, C.c_uint32), _p(fs, C.c_int32), _p(ff, C.c_uint32), C.byref(nf))
+        return bw[:nb.value].copy(), bv[:nb.value].copy(), fn[:nf.value].copy(), fs[:nf.value + 1].copy(), ff[:fs[nf.value]].copy()

@@ -126,6 +126,7 @@ public:
     std::shared_ptr<Whole> whole;
     int tp = CV_8UC1;
     size_t esz() const { return tp == CV_32F ? 4 : 1; }
+    size_t elemSize() const { return esz(); }
 
     Mat() : rows(0), cols(0), data(nullptr) {}
     Mat(int r, int c, int type) : rows(0), cols(0), data(nullptr) { create(r, c, type); }

@@ -232,3 +232,54 @@ def test_cuda_search_by_projection_equals_committed_reference_fixture(golden_dir
     c, host, n, asg = _proj_fixture(golden_dir, name)
     on, oa = _ours_projection(*_device_runs(None), c, host)
     assert on == n and np.array_equal(oa, asg)
+
+
+# --------------------------------------------------------------------------------------------- row f-3 (DBoW3 transform)
+def _same_bow(a, b):
+    for x, y in zip(a, b):
+        x, y = np.ascontiguousarray(x), np.ascontiguousarray(y)
+        assert x.shape == y.shape and np.array_equal(x.view(np.uint8), y.view(np.uint8))
+
+
+@needs_ref
+def test_dbow3_own_transform_equals_committed_golden(golden_dir):
+    """DBoW3's own Vocabulary::transform / BowVector / FeatureVector / DescManip::distance (compiled from thirdparty/DBoW3)
+    reproduce tests/golden/bow.npz - the fixture the oracle, the emulation build and the CUDA kernels are held to in
+    tests/test_bow.py (it was written by the Python transliteration tests/golden/ref_bow.py): word ids, node ids, feature
+    lists and the double values bit for bit, every weighting and every normalisation."""
+    from tests.golden.make_bow_golden import CASES
+    from vi_slam_b200 import synthetic
+    g = np.load(os.path.join(golden_dir, "bow.npz"))
+    for tag, (kw, levelsup, _) in CASES.items():
+        rv = ref.RefVocabulary(synthetic.make_vocabulary(**kw))
+        got = rv.transform(g[tag + "_desc"], levelsup)
+        _same_bow(got, (g[tag + "_bow_word"], g[tag + "_bow_value"], g[tag + "_fv_node"], g[tag + "_fv_start"], g[tag + "_fv_feature"]))
+        assert len(got[0]) > 30, tag
+
+
+@needs_ref
+@pytest.mark.parametrize("k,levels,n,seed,prune", [(10, 4, 1500, 5, 0.0), (6, 5, 800, 6, 0.2), (40, 2, 600, 7, 0.0), (3, 6, 400, 8, 0.3)])
+def test_oracle_bow_equals_dbow3_own_transform(k, levels, n, seed, prune):
+    from vi_slam_b200 import synthetic
+    for weighting in range(4):
+        for scoring in (0, 1, 5):                       # L1, L2, dot product (no normalisation)
+            v = synthetic.make_vocabulary(seed, k=k, levels=levels, weighting=weighting, scoring=scoring, stop_fraction=0.03, prune=prune)
+            rv, ov = ref.RefVocabulary(v), oracle.OracleVocabulary(v)
+            rng = np.random.default_rng(seed)
+            for d in (synthetic.descriptors_near_words(v, n, seed + 1, 20), rng.integers(0, 256, (n // 3, 32), dtype=np.uint8),
+                      np.repeat(synthetic.descriptors_near_words(v, 3, seed + 3), 40, axis=0), np.zeros((0, 32), np.uint8)):
+                for levelsup in (0, 2, levels, levels + 3):
+                    a, b = rv.transform(d, levelsup), ov.transform(d, levelsup)
+                    if prune == 0.0:
+                        _same_bow(a, b)
+                        continue
+                    # An irregular tree has leaves above level L - levelsup: DBoW3 then never writes *nid (Vocabulary.cpp:868)
+                    # and the FeatureVector gets whatever the stack held - the one place where the reference is undefined
+                    # (DESIGN.md section 2; the oracle and the kernels report node 0).  BowVector: identical; FeatureVector:
+                    # identical on every feature whose node is defined.
+                    _same_bow(a[:2], b[:2])
+                    node_of = lambda r: {int(f): int(r[2][k]) for k in range(len(r[2])) for f in r[4][r[3][k]:r[3][k + 1]]}
+                    na, nb = node_of(a), node_of(b)
+                    assert na.keys() == nb.keys()
+                    undefined = [f for f in nb if nb[f] == 0 and levelsup < levels]
+                    assert all(na[f] == nb[f] for f in nb if f not in set(undefined))
