@@ -274,6 +274,73 @@ def cpu_pass(wl, nthreads, units, seed0=5000):
     return units / dt, dt
 
 
+def ref_available():
+    """oracle/_ref/liborb_ref.so: the reference's own extractor and matcher code (built here from /root/reference, prebuilt on
+    the GPU box)."""
+    try:
+        from oracle import ref
+        return ref.available()
+    except Exception:
+        return False
+
+
+REF_PARTS = ("FExtractor::compute, Frame::ComputeStereoMatches, FMatcher::SearchForInitialization = the reference's own code "
+             "(oracle/_ref: fextractor.cpp whole, the other two cut out of frame.cpp / fmatcher.cpp) on a scalar OpenCV stand-in; "
+             "BFMatcher.knnMatch + ratio = the oracle's restatement (OpenCV itself is not linkable here)")
+
+
+def ref_pass(wl, nthreads, units, seed0=5000):
+    """cpu_pass on the reference's OWN code (oracle/_ref) -> (units/s, seconds): one reference FExtractor per camera and host
+    thread, frames dealt to a thread pool (ctypes calls release the GIL)."""
+    import oracle
+    from oracle import ref
+    W, H, nf = wl["W"], wl["H"], wl["nfeat"]
+    tl = threading.local()
+
+    def exs():
+        if not hasattr(tl, "ex"):
+            tl.ex = (ref.RefExtractor(nf, SCALE, NLEVELS, INI_TH, MIN_TH, monotone=False),
+                     ref.RefExtractor(nf, SCALE, NLEVELS, INI_TH, MIN_TH, monotone=False))
+        return tl.ex
+
+    if wl["kind"] == "stereo":
+        left, right, _ = make_stereo(wl, units, 4, seed0)
+        b = float(np.float32(wl["bf"]) / np.float32(wl["fx"]))
+
+        def pair(i):
+            el, er = exs()
+            _, kl, dl = el.compute_plain(left[i, :, :W], (0, 0))
+            _, kr, dr = er.compute_plain(right[i, :, :W], (0, 0))
+            if len(kl) and len(kr):
+                ref.stereo_match(el, er, kl, dl, kr, dr, wl["bf"], b)
+                oi, od = oracle.knn2(dl, dr)
+                oracle.ratio_filter(oi, od, 0.7, 0)
+
+        work, n = pair, units
+    elif wl["kind"] == "mono_batch":
+        frames = make_mono(wl, units, 4, seed0)[0]
+        work, n = (lambda i: exs()[0].compute_plain(frames[i, :, :W], wl["lap"])), units
+    else:
+        frames = make_mono(wl, units, 4, seed0, sequences=True)[0]
+        work, n = None, units
+    t0 = time.perf_counter()
+    with cf.ThreadPoolExecutor(nthreads) as pool:
+        if work is not None:
+            list(pool.map(work, range(n)))
+        else:
+            res = list(pool.map(lambda i: exs()[0].compute_plain(frames[i, :, :W], wl["lap"]), range(units)))
+
+            def match(p):
+                (_, k1, d1), (_, k2, d2) = res[p], res[p + 1]
+                pm = np.stack([k1["x"], k1["y"]], 1)
+                ref.search_for_initialization(k1, d1, k2, d2, (0.0, float(W), 0.0, float(H)), pm, 100, 0.9, True)
+                oi, od = oracle.knn2(d1, d2)
+                oracle.ratio_filter(oi, od, 0.8, 1)
+            list(pool.map(match, range(units - 1)))
+    dt = time.perf_counter() - t0
+    return units / dt, dt
+
+
 def cpu_sample_units(wl, cores):
     u = max(2 * cores, 8)
     if wl["W"] * wl["H"] > 600_000:
@@ -281,20 +348,29 @@ def cpu_sample_units(wl, cores):
     return u
 
 
-def cpu_sample_text(wl, units, cores):
+def cpu_sample_text(wl, units, cores, kind="port"):
     what = {"stereo": "stereo frames", "mono_f2f": "consecutive mono frames", "mono_batch": "mono frames"}[wl["kind"]]
-    return f"{units} synthetic {wl['W']}x{wl['H']} {what} per pass, oracle/orb_oracle.cpp (-O3, no -march) on {cores} threads"
+    code = "oracle/_ref/liborb_ref.so (the reference's own sources, -O3, no -march)" if kind == "reference" else \
+        "oracle/orb_oracle.cpp (-O3, no -march)"
+    return f"{units} synthetic {wl['W']}x{wl['H']} {what} per pass, {code} on {cores} threads"
+
+
+def cpu_arm(wl):
+    """(pass function, kind): the reference's own code when oracle/_ref is there, else the oracle port."""
+    return (ref_pass, "reference") if ref_available() else (cpu_pass, "port")
 
 
 def run_reference(args, wl, rank):
-    """--impl reference: the reference's CPU path (restated: oracle/) on all host threads.  Rank 0 only."""
+    """--impl reference: the reference's CPU path on all host threads - its own code from oracle/_ref when that library is
+    present (built here from /root/reference, prebuilt on the GPU box), else the oracle port.  Rank 0 only."""
     if rank != 0:
         return
     cores = host_threads()
     units = cpu_sample_units(wl, cores)
+    run_pass, kind = cpu_arm(wl)
     for _ in range(args.warmup):
-        cpu_pass(wl, cores, units)
-    t = [cpu_pass(wl, cores, units)[1] for _ in range(args.steps)]
+        run_pass(wl, cores, units)
+    t = [run_pass(wl, cores, units)[1] for _ in range(args.steps)]
     total = sum(t)
     value = units * args.steps / total
     print(json.dumps({
@@ -302,7 +378,8 @@ def run_reference(args, wl, rank):
         "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": wl["scaling"],
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": wl["tag"], "units_per_step": units, "device": "cpu"},
-        "cpu_baseline": {"value": value, "unit": wl["unit"], "cores": cores, "kind": "port", "sample": cpu_sample_text(wl, units, cores)},
+        "cpu_baseline": {"value": value, "unit": wl["unit"], "cores": cores, "kind": kind, "sample": cpu_sample_text(wl, units, cores, kind),
+                         **({"parts": REF_PARTS} if kind == "reference" else {})},
         "e2e": {"value": value, "unit": wl["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
@@ -730,14 +807,18 @@ def run_ours(args, wl, rank, world, local_rank):
     if world == 1 and not args.no_cpu_baseline:
         cores = host_threads()
         cu = cpu_sample_units(wl, cores)
-        cpu_pass(wl, cores, min(cu, 8))          # warm
-        v, dt = cpu_pass(wl, cores, cu)
+        run_pass, kind = cpu_arm(wl)
+        run_pass(wl, cores, min(cu, 8))          # warm
+        v, dt = run_pass(wl, cores, cu)
         reps = max(1, int(10.0 / max(dt, 1e-3)))
         if reps > 1:
-            tt = [cpu_pass(wl, cores, cu)[1] for _ in range(min(reps, 6))]
+            tt = [run_pass(wl, cores, cu)[1] for _ in range(min(reps, 6))]
             v = cu * len(tt) / sum(tt)
-        line["cpu_baseline"] = {"value": v, "unit": wl["unit"], "cores": cores, "kind": "port", "sample": cpu_sample_text(wl, cu, cores),
+        line["cpu_baseline"] = {"value": v, "unit": wl["unit"], "cores": cores, "kind": kind, "sample": cpu_sample_text(wl, cu, cores, kind),
                                 "cv2_floor": cv2_floor(wl, cores, cu)}
+        if kind == "reference":              # the scalar port beside it, one pass
+            line["cpu_baseline"]["parts"] = REF_PARTS
+            line["cpu_baseline"]["port_value"] = cpu_pass(wl, cores, cu)[0]
     print(json.dumps(line))
 
 

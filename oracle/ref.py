@@ -53,6 +53,7 @@ def lib():
         L.orb_ref_tables.argtypes = [C.c_void_p, f32p, f32p, f32p, f32p, i32p, i32p]
         L.orb_ref_compute.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, u8p,
                                       C.c_int, i32p, C.c_int]
+        L.orb_ref_compute_plain.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, u8p, C.c_int, i32p]
         L.orb_ref_consistent.argtypes = [C.c_void_p]
         L.orb_ref_level_size.argtypes = [C.c_void_p, C.c_int, i32p, i32p]
         L.orb_ref_level_image.argtypes = [C.c_void_p, C.c_int, u8p]
@@ -125,6 +126,17 @@ class RefExtractor:
                                   kps.ctypes.data, _p(desc, C.c_uint8), cap, C.byref(mono), int(self.monotone))
         assert 0 <= n <= cap
         return mono.value, kps[:n].copy(), desc[:n].copy()
+
+    def compute_plain(self, image: np.ndarray, lapping=(0, 0)):
+        """FExtractor::compute only (no probes, glibc malloc, thread-safe across instances): the timed CPU baseline."""
+        h, w = image.shape
+        cap = self.nfeatures + 64
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        mono = C.c_int32(0)
+        n = lib().orb_ref_compute_plain(self._h, _p(image, C.c_uint8), w, h, image.strides[0], int(lapping[0]), int(lapping[1]),
+                                        kps.ctypes.data, _p(desc, C.c_uint8), cap, C.byref(mono))
+        return mono.value, kps[:n], desc[:n]
 
     @property
     def consistent(self):

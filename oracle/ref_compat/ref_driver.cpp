@@ -199,6 +199,27 @@ int orb_ref_compute(void* h, const uint8_t* img, int W, int H, int step, int lap
     return n;
 }
 
+// FExtractor::compute and nothing else (no FAST trace, no second probing pass, glibc malloc): the timed CPU baseline of
+// bench.py.  Thread-safe across handles.  Returns the keypoint count, -1 on an empty image.
+int orb_ref_compute_plain(void* h, const uint8_t* img, int W, int H, int step, int lap0, int lap1, cv::KeyPoint* kps, uint8_t* desc,
+                          int cap, int* mono) {
+    Probe* e = (Probe*)h;
+    cv::Mat image = (img && W > 0 && H > 0) ? cv::Mat(H, W, CV_8UC1, (void*)img, (size_t)step) : cv::Mat();
+    std::vector<cv::KeyPoint> k;
+    cv::Mat d, mask;
+    std::vector<int> lap = {lap0, lap1};
+    cv_compat::fast_trace_enable(false);
+    const int m = e->compute(image, mask, k, d, lap);
+    if (mono) *mono = m;
+    if (m < 0) return -1;
+    const int n = (int)k.size();
+    for (int i = 0; i < std::min(n, cap); ++i) {
+        kps[i] = k[i];
+        std::memcpy(desc + (size_t)32 * i, d.ptr(i), 32);
+    }
+    return n;
+}
+
 int orb_ref_consistent(void* h) { return ((Probe*)h)->consistent ? 1 : 0; }
 
 int orb_ref_level_size(void* h, int l, int* w, int* hh) {

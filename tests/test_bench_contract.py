@@ -37,7 +37,8 @@ def test_reference_arm_prints_the_contract_line(workload, oracle_mod):
     assert d["impl"] == "reference" and d["metric"] == wl["metric"] and d["unit"] == wl["unit"] and d["value"] > 0
     assert d["higher_is_better"] is True and d["config"]["workload"] == wl["tag"] and d["gpu_launches"] == 0
     c = d["cpu_baseline"]
-    assert c["kind"] == "port" and c["cores"] >= 1 and c["value"] == d["value"] and c["sample"]
+    # the reference's own code when oracle/_ref is there (this container, and prebuilt on the GPU box), else the port
+    assert c["kind"] == ("reference" if bench.ref_available() else "port") and c["cores"] >= 1 and c["value"] == d["value"] and c["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
 
 
