@@ -290,53 +290,26 @@ REF_PARTS = ("FExtractor::compute, Frame::ComputeStereoMatches, FMatcher::Search
 
 
 def ref_pass(wl, nthreads, units, seed0=5000):
-    """cpu_pass on the reference's OWN code (oracle/_ref) -> (units/s, seconds): one reference FExtractor per camera and host
-    thread, frames dealt to a thread pool (ctypes calls release the GIL)."""
-    import oracle
+    """cpu_pass on the reference's OWN code (oracle/_ref) -> (units/s, seconds): std::threads inside the library, one
+    reference FExtractor per camera and thread."""
     from oracle import ref
     W, H, nf = wl["W"], wl["H"], wl["nfeat"]
-    tl = threading.local()
-
-    def exs():
-        if not hasattr(tl, "ex"):
-            tl.ex = (ref.RefExtractor(nf, SCALE, NLEVELS, INI_TH, MIN_TH, monotone=False),
-                     ref.RefExtractor(nf, SCALE, NLEVELS, INI_TH, MIN_TH, monotone=False))
-        return tl.ex
-
     if wl["kind"] == "stereo":
         left, right, _ = make_stereo(wl, units, 4, seed0)
+        frames = np.empty((2 * units, H, W), np.uint8)
+        frames[0::2] = left[:, :, :W]
+        frames[1::2] = right[:, :, :W]
         b = float(np.float32(wl["bf"]) / np.float32(wl["fx"]))
-
-        def pair(i):
-            el, er = exs()
-            _, kl, dl = el.compute_plain(left[i, :, :W], (0, 0))
-            _, kr, dr = er.compute_plain(right[i, :, :W], (0, 0))
-            if len(kl) and len(kr):
-                ref.stereo_match(el, er, kl, dl, kr, dr, wl["bf"], b)
-                oi, od = oracle.knn2(dl, dr)
-                oracle.ratio_filter(oi, od, 0.7, 0)
-
-        work, n = pair, units
+        t0 = time.perf_counter()
+        ref.bench_frames(frames, nf, SCALE, NLEVELS, INI_TH, MIN_TH, (0, 0), 1, wl["bf"], b, nthreads)
     elif wl["kind"] == "mono_batch":
-        frames = make_mono(wl, units, 4, seed0)[0]
-        work, n = (lambda i: exs()[0].compute_plain(frames[i, :, :W], wl["lap"])), units
+        frames = np.ascontiguousarray(make_mono(wl, units, 4, seed0)[0][:, :, :W])
+        t0 = time.perf_counter()
+        ref.bench_frames(frames, nf, SCALE, NLEVELS, INI_TH, MIN_TH, wl["lap"], 0, 0.0, 0.0, nthreads)
     else:
-        frames = make_mono(wl, units, 4, seed0, sequences=True)[0]
-        work, n = None, units
-    t0 = time.perf_counter()
-    with cf.ThreadPoolExecutor(nthreads) as pool:
-        if work is not None:
-            list(pool.map(work, range(n)))
-        else:
-            res = list(pool.map(lambda i: exs()[0].compute_plain(frames[i, :, :W], wl["lap"]), range(units)))
-
-            def match(p):
-                (_, k1, d1), (_, k2, d2) = res[p], res[p + 1]
-                pm = np.stack([k1["x"], k1["y"]], 1)
-                ref.search_for_initialization(k1, d1, k2, d2, (0.0, float(W), 0.0, float(H)), pm, 100, 0.9, True)
-                oi, od = oracle.knn2(d1, d2)
-                oracle.ratio_filter(oi, od, 0.8, 1)
-            list(pool.map(match, range(units - 1)))
+        frames = np.ascontiguousarray(make_mono(wl, units, 4, seed0, sequences=True)[0][:, :, :W])
+        t0 = time.perf_counter()
+        ref.bench_frames(frames, nf, SCALE, NLEVELS, INI_TH, MIN_TH, wl["lap"], 2, 0.0, 0.0, nthreads)
     dt = time.perf_counter() - t0
     return units / dt, dt
 

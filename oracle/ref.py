@@ -70,6 +70,9 @@ def lib():
         L.orb_refs_search_by_projection.argtypes = [C.c_int, C.c_void_p, f32p, u8p, u8p, u8p, C.c_void_p, C.c_int, u8p, f32p, u8p, C.c_int,
                                                     f32p, f32p, f32p, f32p, f32p, f32p, C.c_int, C.c_float, C.c_int, C.c_float, C.c_float,
                                                     C.c_float, C.c_int, i32p, f32p, f32p, f32p, u8p, i32p]
+        L.orb_refs_bench_frames.restype = C.c_long
+        L.orb_refs_bench_frames.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                            C.c_int, C.c_float, C.c_float, C.c_int, C.POINTER(C.c_long)]
         # ref_dbow3.cpp: DBoW3's own transform
         L.orb_refd_vocab_create.restype = C.c_void_p
         L.orb_refd_vocab_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, i32p, i32p, u8p, C.POINTER(C.c_double), i32p]
@@ -273,3 +276,16 @@ class RefVocabulary:
         lib().orb_refd_transform(self._h, _p(desc, C.c_uint8), n, int(levelsup), _p(bw, C.c_uint32), _p(bv, C.c_double), C.byref(nb),
                                  _p(fn, C.c_uint32), _p(fs, C.c_int32), _p(ff, C.c_uint32), C.byref(nf))
         return bw[:nb.value].copy(), bv[:nb.value].copy(), fn[:nf.value].copy(), fs[:nf.value + 1].copy(), ff[:fs[nf.value]].copy()
+
+
+def bench_frames(frames: np.ndarray, nfeatures=2000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, lapping=(0, 0), mode=0,
+                 bf=386.1448, b=0.5371657, nthreads=1):
+    """Timed CPU baseline body on the reference's own code, std::threads inside the library: mode 0 extraction per frame,
+    1 stereo pairs (frames 2i, 2i+1: compute x 2 + ComputeStereoMatches + kNN-2 / 0.7), 2 consecutive frames (compute +
+    SearchForInitialization + kNN-2 / 0.8 per pair).  -> (total keypoints, matches)."""
+    frames = np.ascontiguousarray(frames)
+    n, h, w = frames.shape
+    nm = C.c_long(0)
+    tot = lib().orb_refs_bench_frames(nfeatures, scale_factor, nlevels, ini_th, min_th, _p(frames, C.c_uint8), n, w, h, int(lapping[0]),
+                                      int(lapping[1]), int(mode), bf, b, nthreads, C.byref(nm))
+    return tot, nm.value

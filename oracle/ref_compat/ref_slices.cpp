@@ -23,8 +23,13 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <thread>
 #include <utility>
 #include <vector>
+
+// the oracle's brute-force kNN-2 + ratio (orb_oracle.cpp, same library): OpenCV's BFMatcher is not linkable here
+extern "C" void orc_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx, int32_t* dist, int nthreads);
+extern "C" int orc_ratio_filter(const int32_t* idx, const int32_t* dist, int nq, double ratio, int rule, int32_t* out);
 
 // reference include/vi_slam/datastructures/frame.h:42-43
 #define FRAME_GRID_ROWS 48
@@ -305,6 +310,91 @@ int orb_refs_search_by_projection(int nLast, const cv::KeyPoint* kLast, const fl
     const int n = matcher.SearchByProjection(Cur, Last, th, bMono != 0);
     for (int i = 0; i < n2; ++i) assigned[i] = Cur.mvpMapPoints[i] ? Cur.mvpMapPoints[i]->index : -1;
     return n;
+}
+
+// Timed CPU baseline of bench.py (cpu_baseline / --impl reference): `n` frames (stereo: left / right interleaved) dealt to
+// `nthreads` std::threads, every thread with its own reference FExtractor per camera on glibc malloc.
+//   mode 0  FExtractor::compute per frame
+//   mode 1  stereo pairs: compute x 2, Frame::ComputeStereoMatches, kNN-2 + 0.7 ratio
+//   mode 2  consecutive frames: compute, then FMatcher::SearchForInitialization + kNN-2 + 0.8 ratio per pair
+// Returns the total number of keypoints.
+long orb_refs_bench_frames(int nf, float sf, int nl, int ini, int mn, const uint8_t* imgs, int n, int W, int H, int lap0, int lap1, int mode,
+                           float bf, float b, int nthreads, long* nMatches) {
+    std::vector<long> tot(nthreads, 0), mt(nthreads, 0);
+    const size_t fsz = (size_t)W * H;
+    struct Out { std::vector<cv::KeyPoint> k; cv::Mat d; };
+    std::vector<Out> kept(mode == 2 ? n : 0);
+    auto extract = [&](FExtractor& e, const uint8_t* img, std::vector<cv::KeyPoint>& k, cv::Mat& d) {
+        cv::Mat image(H, W, CV_8UC1, (void*)img, (size_t)W), mask;
+        std::vector<int> lap = {lap0, lap1};
+        e.compute(image, mask, k, d, lap);
+    };
+    auto knn_ratio = [&](const cv::Mat& dq, int nq, const cv::Mat& dt, int nt, double ratio, int rule) -> long {
+        if (nq == 0 || nt == 0) return 0;
+        std::vector<int32_t> idx(2 * (size_t)nq), dist(2 * (size_t)nq), out(3 * (size_t)nq);
+        orc_knn2(dq.ptr(0), nq, dt.ptr(0), nt, idx.data(), dist.data(), 1);
+        return orc_ratio_filter(idx.data(), dist.data(), nq, ratio, rule, out.data());
+    };
+    auto work = [&](int tid) {
+        FExtractor eL(nf, sf, nl, ini, mn), eR(nf, sf, nl, ini, mn);
+        if (mode == 1) {
+            for (int i = tid; i < n / 2; i += nthreads) {
+                Frame F;
+                extract(eL, imgs + (size_t)(2 * i) * fsz, F.keypoints_, F.descriptors_);
+                extract(eR, imgs + (size_t)(2 * i + 1) * fsz, F.keypointsRight_, F.descriptorsRight_);
+                F.N = (int)F.keypoints_.size();
+                tot[tid] += F.N + (long)F.keypointsRight_.size();
+                if (F.N == 0 || F.keypointsRight_.empty()) continue;
+                F.mpORBextractorLeft = &eL;
+                F.mpORBextractorRight = &eR;
+                F.mvScaleFactors = eL.GetScaleFactors();
+                F.mvInvScaleFactors = eL.GetInverseScaleFactors();
+                F.mbf = bf;
+                F.mb = b;
+                F.ComputeStereoMatches();
+                for (float v : F.mvDepth) mt[tid] += v > 0;
+                mt[tid] += knn_ratio(F.descriptors_, F.N, F.descriptorsRight_, (int)F.keypointsRight_.size(), 0.7, 0);
+            }
+        } else {
+            for (int i = tid; i < n; i += nthreads) {
+                std::vector<cv::KeyPoint> k;
+                cv::Mat d;
+                extract(eL, imgs + (size_t)i * fsz, k, d);
+                tot[tid] += (long)k.size();
+                if (mode == 2) { kept[i].k.swap(k); kept[i].d = d.clone(); }
+            }
+        }
+    };
+    auto match = [&](int tid) {
+        const float bounds[4] = {0.f, (float)W, 0.f, (float)H};
+        for (int p = tid; p + 1 < n; p += nthreads) {
+            Out &a = kept[p], &c = kept[p + 1];
+            if (a.k.empty() || c.k.empty()) continue;
+            Frame F1, F2;
+            fill_frame(F1, a.k.data(), (int)a.k.size(), a.d.ptr(0), bounds);
+            fill_frame(F2, c.k.data(), (int)c.k.size(), c.d.ptr(0), bounds);
+            std::vector<cv::Point2f> prev(a.k.size());
+            for (size_t i = 0; i < a.k.size(); ++i) prev[i] = a.k[i].pt;
+            std::vector<int> m12;
+            FMatcher matcher(0.9f, true);
+            mt[tid] += matcher.SearchForInitialization(F1, F2, prev, m12, 100);
+            mt[tid] += knn_ratio(a.d, (int)a.k.size(), c.d, (int)c.k.size(), 0.8, 1);
+        }
+    };
+    {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nthreads; ++t) th.emplace_back(work, t);
+        for (auto& x : th) x.join();
+    }
+    if (mode == 2) {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nthreads; ++t) th.emplace_back(match, t);
+        for (auto& x : th) x.join();
+    }
+    long s = 0, m = 0;
+    for (int t = 0; t < nthreads; ++t) { s += tot[t]; m += mt[t]; }
+    if (nMatches) *nMatches = m;
+    return s;
 }
 
 }  // extern "C"

@@ -283,3 +283,23 @@ def test_oracle_bow_equals_dbow3_own_transform(k, levels, n, seed, prune):
                     assert na.keys() == nb.keys()
                     undefined = [f for f in nb if nb[f] == 0 and levelsup < levels]
                     assert all(na[f] == nb[f] for f in nb if f not in set(undefined))
+
+
+# --------------------------------------------------------------------------------------------- the timed CPU baseline body
+@needs_ref
+def test_reference_bench_body_does_the_same_work_as_the_port():
+    """bench.py's CPU arm (oracle/_ref, std::threads, glibc malloc) against the oracle port on the same frames: keypoint and
+    match totals agree up to the reference's own pointer tie-breaks (a few keypoints per frame)."""
+    from vi_slam_b200 import synthetic
+    left = np.stack([synthetic.make_stereo_pair(70 + i, 640, 360)[0] for i in range(4)])
+    right = np.stack([synthetic.make_stereo_pair(70 + i, 640, 360)[1] for i in range(4)])
+    frames = np.empty((8, 360, 640), np.uint8)
+    frames[0::2], frames[1::2] = left, right
+    rt, rm = ref.bench_frames(frames, 1000, mode=1, bf=120.0, b=0.24, nthreads=3)
+    ot, om = oracle.bench_frames(frames, 1000, stereo=True, bf=120.0, b=0.24, nthreads=3)
+    assert abs(rt - ot) <= 0.01 * ot and abs(rm - om) <= 0.03 * om and rm > 500
+    rt, _ = ref.bench_frames(frames, 1000, lapping=(0, 1000), mode=0, nthreads=2)
+    ot, _ = oracle.bench_frames(frames, 1000, lapping=(0, 1000), stereo=False, nthreads=2)
+    assert abs(rt - ot) <= 0.01 * ot
+    rt, rm = ref.bench_frames(frames[0::2], 1000, lapping=(0, 1000), mode=2, nthreads=2)
+    assert rt > 3000 and rm > 0
