@@ -27,6 +27,13 @@ sf = (np.float32(1.2) ** np.arange(8)).astype(np.float32)
 n1 = len(k1)
 print('proj', matcher.search_by_projection(pm, np.full(n1, 0.1, np.float32), k1['octave'], k1['angle'], d1, np.ones(n1, np.uint8), np.ones(n1, np.uint8),
                                            k2, d2, None, None, b, sf, 15.0, 386.0, 0, True, lib_path=LIB)[0])
+nl2 = len(k2) // 2
+print('proj rig', matcher.search_by_projection(pm, np.full(n1, 0.1, np.float32), k1['octave'], k1['angle'], d1, np.ones(n1, np.uint8), np.zeros(n1, np.uint8),
+                                               k2, d2, None, (np.arange(len(k2)) % 9 == 0).astype(np.uint8), b, sf, 15.0, 0.0, 1, True, lib_path=LIB,
+                                               uv_right=pm + np.float32(3.0), nleft2=nl2)[0])
+matcher.f2f_batch(el, 3, None, 60, 0.9, True, 0.8, 1)
+ff = matcher.f2f_fetch_all(el, 2)
+print('f2f', [int(x) for x in ff['nmatches']], [int(x) for x in ff['n_ratio']])
 print('area', len(matcher.features_in_area(k2, b, 100, 100, 50, -1, -1, lib_path=LIB)))
 v = synthetic.make_vocabulary(3, k=5, levels=3, stop_fraction=0.05, prune=0.2)
 voc = bow.Vocabulary(v, lib_path=LIB)
