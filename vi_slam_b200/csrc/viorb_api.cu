@@ -1357,17 +1357,32 @@ int viorb_stereo_batch(viorb_extractor* L, viorb_extractor* R, int n, float bf, 
     if (rc) return rc;
     rc = join_streams(L, R);
     if (rc) return rc;
-    rc = launch_stereo(L, R, n, bf, b);
-    if (rc) return rc;
-    // fisheye-style brute force kNN-2 + ratio, left -> right (frame.cpp:1167-1170)
+    // fisheye-style brute force kNN-2 + ratio, left -> right (frame.cpp:1167-1170).  It needs nothing from the rectified
+    // matcher, whose kernels are bound by load latency: outside stage timing it runs beside them on the handle's side stream.
     const size_t oc = L->g.outCap;
     DescSet Q{L->dDesc.p, oc * 32, L->dNOut.p, 0}, T{R->dDesc.p, oc * 32, R->dNOut.p, 0};
-    rc = launch_knn2(Q, T, L->g.outCap, L->g.outCap, n, L->dKnnIdx.p, L->dKnnDist.p, oc, L->stream);
+    const bool fork = !L->timing && L->sideOct != nullptr;
+    if (fork) {
+        CU(cudaEventRecord(L->evOctFork, L->stream));
+        CU(cudaStreamWaitEvent(L->sideOct, L->evOctFork, 0));
+        rc = launch_knn2(Q, T, L->g.outCap, L->g.outCap, n, L->dKnnIdx.p, L->dKnnDist.p, oc, L->sideOct);
+        if (rc) return rc;
+        VIORB_LAUNCH(k_ratio, dim3(n), dim3(256), 0, L->sideOct, Q, L->dKnnIdx.p, L->dKnnDist.p, oc, ratio, 0, L->dMatches.p, oc,
+                     L->dNRatio.p, L->dLrMatch.p);
+        CU(cudaEventRecord(L->evOctJoin, L->sideOct));
+    }
+    rc = launch_stereo(L, R, n, bf, b);
     if (rc) return rc;
-    if (L->timing) CU(cudaEventRecord(L->evS[4], L->stream));
-    VIORB_LAUNCH(k_ratio, dim3(n), dim3(256), 0, L->stream, Q, L->dKnnIdx.p, L->dKnnDist.p, oc, ratio, 0, L->dMatches.p, oc,
-                 L->dNRatio.p, L->dLrMatch.p);
-    if (L->timing) { CU(cudaEventRecord(L->evS[5], L->stream)); L->haveS = true; }
+    if (fork) {
+        CU(cudaStreamWaitEvent(L->stream, L->evOctJoin, 0));
+    } else {
+        rc = launch_knn2(Q, T, L->g.outCap, L->g.outCap, n, L->dKnnIdx.p, L->dKnnDist.p, oc, L->stream);
+        if (rc) return rc;
+        if (L->timing) CU(cudaEventRecord(L->evS[4], L->stream));
+        VIORB_LAUNCH(k_ratio, dim3(n), dim3(256), 0, L->stream, Q, L->dKnnIdx.p, L->dKnnDist.p, oc, ratio, 0, L->dMatches.p, oc,
+                     L->dNRatio.p, L->dLrMatch.p);
+        if (L->timing) { CU(cudaEventRecord(L->evS[5], L->stream)); L->haveS = true; }
+    }
     CU(cudaGetLastError());
     return release_partner(L, R);
 }
