@@ -14,9 +14,10 @@ FRAME_CPP := $(REF)/src/datastructures/frame.cpp
 FMATCHER_CPP := $(REF)/src/geometry/fmatcher.cpp
 PINHOLE_CPP := $(REF)/src/geometry/cameramodels/pinhole.cpp
 DBOW3 := $(REF)/thirdparty/DBoW3/DBoW3/src
+KB8_CPP := $(REF)/src/geometry/cameramodels/kannalabrandt8.cpp
 SRC := $(REF)/src/geometry/fextractor.cpp ref_compat/cv_compat.cpp ref_compat/ref_driver.cpp ref_compat/ref_slices.cpp orb_oracle.cpp \
        $(FRAME_CPP) $(FMATCHER_CPP) $(PINHOLE_CPP) ref_compat/ref_dbow3.cpp $(DBOW3)/Vocabulary.cpp $(DBOW3)/DescManip.cpp \
-       $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp
+       $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp ref_compat/ref_kb8.cpp $(KB8_CPP)
 
 all: $(OUT)
 
@@ -35,6 +36,8 @@ $(OUT): $(SRC) ref_compat/cv_compat.hpp ../vi_slam_b200/csrc/orb_pattern.inc ref
 	$(call slice,$(FRAME_CPP),678,744,frame,Frame::GetFeaturesInArea)
 	$(call slice,$(FRAME_CPP),746,756,frame,bool Frame::PosInGrid)
 	$(call slice,$(FRAME_CPP),823,997,frame,void Frame::ComputeStereoMatches)
+	$(call slice,$(FRAME_CPP),758,791,frame,void Frame::UndistortKeyPoints)
+	$(call slice,$(FRAME_CPP),793,821,frame,void Frame::ComputeImageBounds)
 	$(call slice,$(FMATCHER_CPP),313,319,fmatcher,const int FMatcher::TH_HIGH = 100;)
 	$(call slice,$(FMATCHER_CPP),983,1098,fmatcher,int FMatcher::SearchForInitialization)
 	$(call slice,$(FMATCHER_CPP),2813,2854,fmatcher,void FMatcher::ComputeThreeMaxima)
@@ -45,13 +48,20 @@ $(OUT): $(SRC) ref_compat/cv_compat.hpp ../vi_slam_b200/csrc/orb_pattern.inc ref
 	$(call slice,$(DBOW3)/Vocabulary.cpp,754,820,Vocabulary,void Vocabulary::transform)
 	$(call slice,$(DBOW3)/Vocabulary.cpp,838,876,Vocabulary,void Vocabulary::transform)
 	$(call slice,$(DBOW3)/DescManip.cpp,92,130,DescManip,double DescManip::distance)
+	$(call slice,$(KB8_CPP),11,27,kannalabrandt8,KannalaBrandt8::project)
+	$(call slice,$(KB8_CPP),33,37,kannalabrandt8,KannalaBrandt8::project)
+	$(call slice,$(KB8_CPP),70,74,kannalabrandt8,KannalaBrandt8::unprojectMat)
+	$(call slice,$(KB8_CPP),82,109,kannalabrandt8,KannalaBrandt8::unproject)
+	$(call slice,$(KB8_CPP),324,393,kannalabrandt8,KannalaBrandt8::TriangulateMatches)
+	$(call slice,$(KB8_CPP),485,498,kannalabrandt8,void KannalaBrandt8::Triangulate)
+	$(call slice,$(FRAME_CPP),1149,1189,frame,void Frame::ComputeStereoFishEyeMatches)
 	@# -include ...: the vendored DBoW3 headers rely on transitive std includes that GCC 13's leaner headers no longer provide
 	$(CXX) $(CXXFLAGS) -Iref_compat -I_ref -I$(REF)/include -shared -Wl,-Bsymbolic -o $@ \
 	    $(REF)/src/geometry/fextractor.cpp ref_compat/cv_compat.cpp ref_compat/ref_driver.cpp ref_compat/ref_slices.cpp \
-	    -I$(DBOW3) -include cstdint -include iostream -include string ref_compat/ref_dbow3.cpp $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp \
+	    ref_compat/ref_kb8.cpp -I$(DBOW3) -include cstdint -include iostream -include string ref_compat/ref_dbow3.cpp $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp \
 	    -x c++ -std=c++17 orb_oracle.cpp
 	sha256sum $(REF)/src/geometry/fextractor.cpp $(REF)/include/vi_slam/geometry/fextractor.h $(FRAME_CPP) $(FMATCHER_CPP) $(PINHOLE_CPP) \
-	    $(DBOW3)/Vocabulary.cpp $(DBOW3)/DescManip.cpp $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp > _ref/SOURCES.sha256
+	    $(DBOW3)/Vocabulary.cpp $(DBOW3)/DescManip.cpp $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp $(KB8_CPP) > _ref/SOURCES.sha256
 	rm -rf _ref/gen          # the slices are build intermediates: only the library stays
 
 clean:

@@ -25,7 +25,7 @@ def build(force: bool = False) -> str | None:
     reference checkout is absent (GPU box) and no prebuilt library travelled."""
     if os.path.exists(REF_SOURCE):
         deps = [REF_SOURCE, os.path.join(_HERE, "orb_oracle.cpp"), os.path.join(_HERE, "ref.mk")] + \
-               [os.path.join(_HERE, "ref_compat", f) for f in ("cv_compat.hpp", "cv_compat.cpp", "ref_driver.cpp", "ref_slices.cpp", "ref_dbow3.cpp")] + \
+               [os.path.join(_HERE, "ref_compat", f) for f in ("cv_compat.hpp", "cv_compat.cpp", "ref_driver.cpp", "ref_slices.cpp", "ref_dbow3.cpp", "ref_kb8.cpp")] + \
                [os.path.join(REFERENCE, "src", "datastructures", "frame.cpp"), os.path.join(REFERENCE, "src", "geometry", "fmatcher.cpp")]
         stale = not os.path.exists(LIB_PATH) or any(os.path.getmtime(d) > os.path.getmtime(LIB_PATH) for d in deps)
         if force or stale:
@@ -73,6 +73,12 @@ def lib():
         L.orb_refs_bench_frames.restype = C.c_long
         L.orb_refs_bench_frames.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                             C.c_int, C.c_float, C.c_float, C.c_int, C.POINTER(C.c_long)]
+        L.orb_refs_undistort_keypoints.argtypes = [C.c_void_p, C.c_int, f32p, f32p, C.c_int, C.c_void_p]
+        L.orb_refs_image_bounds.argtypes = [C.c_int, C.c_int, f32p, f32p, C.c_int, f32p]
+        # ref_kb8.cpp: KannalaBrandt8 / fisheye stereo
+        L.orb_refk_triangulate.argtypes = [f32p, f32p, f32p, f32p, f32p, C.c_int, f32p, f32p]
+        L.orb_refk_fisheye_matches.argtypes = [f32p, C.c_void_p, u8p, C.c_int, C.c_int, C.c_void_p, u8p, C.c_int, C.c_int, f32p, C.c_int,
+                                               i32p, i32p, f32p, f32p]
         # ref_dbow3.cpp: DBoW3's own transform
         L.orb_refd_vocab_create.restype = C.c_void_p
         L.orb_refd_vocab_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, i32p, i32p, u8p, C.POINTER(C.c_double), i32p]
@@ -289,3 +295,47 @@ def bench_frames(frames: np.ndarray, nfeatures=2000, scale_factor=1.2, nlevels=8
     tot = lib().orb_refs_bench_frames(nfeatures, scale_factor, nlevels, ini_th, min_th, _p(frames, C.c_uint8), n, w, h, int(lapping[0]),
                                       int(lapping[1]), int(mode), bf, b, nthreads, C.byref(nm))
     return tot, nm.value
+
+
+def kb8_triangulate(rig, pt1, pt2, sigma1, sigma2):
+    """KannalaBrandt8::TriangulateMatches (kannalabrandt8.cpp:324-393 with :11-27, 33-37, 70-74, 82-109, 485-498), the
+    reference's own text; cv::SVD::compute is the oracle's Jacobi stand-in.  -> (depth, p3d)."""
+    f = lambda a: np.ascontiguousarray(a, np.float32)
+    rig, pt1, pt2, s1, s2 = f(rig), f(pt1).reshape(-1, 2), f(pt2).reshape(-1, 2), f(sigma1), f(sigma2)
+    n = len(pt1)
+    depth, p3d = np.zeros(n, np.float32), np.zeros((n, 3), np.float32)
+    lib().orb_refk_triangulate(_p(rig, C.c_float), _p(pt1, C.c_float), _p(pt2, C.c_float), _p(s1, C.c_float), _p(s2, C.c_float), n,
+                               _p(depth, C.c_float), _p(p3d, C.c_float))
+    return depth, p3d
+
+
+def stereo_fisheye_matches(rig, kps_left, desc_left, mono_left, kps_right, desc_right, mono_right, level_sigma2):
+    """Frame::ComputeStereoFishEyeMatches (frame.cpp:1149-1189), the reference's own text (BFMatcher.knnMatch = the oracle's kNN-2)."""
+    kl = np.ascontiguousarray(kps_left, KP_DTYPE); kr = np.ascontiguousarray(kps_right, KP_DTYPE)
+    dl = np.ascontiguousarray(desc_left, np.uint8).reshape(-1, 32); dr = np.ascontiguousarray(desc_right, np.uint8).reshape(-1, 32)
+    rig = np.ascontiguousarray(rig, np.float32)
+    sig = np.ascontiguousarray(level_sigma2, np.float32)
+    nl, nr = len(kl), len(kr)
+    l2r, r2l = np.zeros(nl, np.int32), np.zeros(max(nr, 1), np.int32)
+    depth, p3d = np.zeros(nl, np.float32), np.zeros((nl, 3), np.float32)
+    lib().orb_refk_fisheye_matches(_p(rig, C.c_float), kl.ctypes.data, _p(dl, C.c_uint8), nl, int(mono_left), kr.ctypes.data,
+                                   _p(dr, C.c_uint8), nr, int(mono_right), _p(sig, C.c_float), len(sig), _p(l2r, C.c_int32),
+                                   _p(r2l, C.c_int32), _p(depth, C.c_float), _p(p3d, C.c_float))
+    return {"left_to_right": l2r, "right_to_left": r2l[:nr], "depth": depth, "p3d": p3d}
+
+
+def undistort_keypoints(kps, cam, dist):
+    """Frame::UndistortKeyPoints (frame.cpp:758-791), the reference's own text; cv::undistortPoints = the oracle's restatement."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    cam, dist = np.ascontiguousarray(cam, np.float32), np.ascontiguousarray(dist, np.float32)
+    out = np.zeros_like(kps)
+    lib().orb_refs_undistort_keypoints(kps.ctypes.data, len(kps), _p(cam, C.c_float), _p(dist, C.c_float), len(dist), out.ctypes.data)
+    return out
+
+
+def image_bounds(cols, rows, cam, dist):
+    """Frame::ComputeImageBounds (frame.cpp:793-821), the reference's own text -> (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+    cam, dist = np.ascontiguousarray(cam, np.float32), np.ascontiguousarray(dist, np.float32)
+    out = np.zeros(4, np.float32)
+    lib().orb_refs_image_bounds(int(cols), int(rows), _p(cam, C.c_float), _p(dist, C.c_float), len(dist), _p(out, C.c_float))
+    return out

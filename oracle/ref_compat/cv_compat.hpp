@@ -110,6 +110,7 @@ struct MatStep {
 
 class _InputArray;
 class _OutputArray;
+class MatExpr;
 typedef const _InputArray& InputArray;
 typedef const _OutputArray& OutputArray;
 
@@ -176,6 +177,18 @@ public:
     // Mat::at(i0): element i0 of a row vector / a continuous matrix, row i0 of a column vector
     template <typename T> T& at(int i) { return cols == 1 ? at<T>(i, 0) : at<T>(i / cols, i % cols); }
     template <typename T> const T& at(int i) const { return cols == 1 ? at<T>(i, 0) : at<T>(i / cols, i % cols); }
+    // A = <matrix expression>: OpenCV evaluates the expression INTO an already allocated destination of the right size and
+    // type - which is how `A.row(0) = p1.x*Tcw1.row(2)-Tcw1.row(0)` (kannalabrandt8.cpp:489-492) fills a row of A
+    inline Mat& operator=(const MatExpr& e);
+    double dot(const Mat& b) const {                // Mat::dot on CV_32F: products accumulated in double
+        assert(tp == CV_32F && b.tp == CV_32F && rows * cols == b.rows * b.cols);
+        double s = 0;
+        for (int i = 0; i < rows * cols; ++i) s += (double)at<float>(i) * (double)b.at<float>(i);
+        return s;
+    }
+    // Mat::reshape(cn): the N x 2 one-channel <-> N x 1 two-channel views of frame.cpp:778-780 share one memory layout
+    // (N rows of x, y); this stand-in keeps the N x 2 header and cv::undistortPoints below reads rows as points
+    Mat reshape(int) const { return *this; }
     Mat t() const {
         assert(tp == CV_32F);
         Mat o; o.create(cols, rows, CV_32F);
@@ -230,31 +243,55 @@ public:
     }
 };
 
-// the matrix expressions of frame.cpp:921-937: (float) * Mat::ones(...), Mat - Mat, norm(a, b, NORM_L1) on CV_32F patches
-enum NormTypes { NORM_INF = 1, NORM_L1 = 2, NORM_L2 = 4 };
-static inline Mat operator*(float s, const Mat& m) {
+// Result of a matrix expression: a value that converts to Mat, and that Mat::operator= copies into an existing destination.
+class MatExpr {
+public:
+    Mat m;
+    MatExpr() {}
+    explicit MatExpr(const Mat& v) : m(v) {}
+    operator Mat() const { return m; }
+    template <typename T> const T& at(int i) const { return m.at<T>(i); }
+    Mat t() const { return m.t(); }
+};
+inline Mat& Mat::operator=(const MatExpr& e) {
+    if (data && rows == e.m.rows && cols == e.m.cols && tp == e.m.tp) {
+        for (int y = 0; y < rows; ++y) std::memcpy(ptr(y), e.m.ptr(y), (size_t)cols * esz());
+        return *this;
+    }
+    return *this = e.m;
+}
+
+// the matrix expressions of frame.cpp:921-937 ((float) * Mat::ones(...), Mat - Mat, norm(a, b, NORM_L1) on CV_32F patches), the
+// pose algebra of fmatcher.cpp:2481-2505 (-A, A * B as gemm with float products accumulated in double per element, A + B)
+// and kannalabrandt8.cpp:324-393, 485-498 (A / s, hconcat, dot, norm, Mat_<float>(r, c) << a, b, ...)
+enum NormTypes { NORM_INF = 1, NORM_L1 = 2, NORM_L2 = 4, NORM_HAMMING = 6 };
+static inline MatExpr operator*(float s, const Mat& m) {
     assert(m.type() == CV_32F);
     Mat o; o.create(m.rows, m.cols, CV_32F);
     for (int y = 0; y < m.rows; ++y) for (int x = 0; x < m.cols; ++x) o.at<float>(y, x) = s * m.at<float>(y, x);
-    return o;
+    return MatExpr(o);
 }
-static inline Mat operator*(const Mat& m, float s) { return s * m; }
-static inline Mat operator-(const Mat& a, const Mat& b) {
+static inline MatExpr operator*(const Mat& m, float s) { return s * m; }
+static inline MatExpr operator/(const Mat& m, float s) {
+    assert(m.type() == CV_32F);
+    Mat o; o.create(m.rows, m.cols, CV_32F);
+    for (int y = 0; y < m.rows; ++y) for (int x = 0; x < m.cols; ++x) o.at<float>(y, x) = m.at<float>(y, x) / s;
+    return MatExpr(o);
+}
+static inline MatExpr operator-(const Mat& a, const Mat& b) {
     assert(a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);
     Mat o; o.create(a.rows, a.cols, CV_32F);
     for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) o.at<float>(y, x) = a.at<float>(y, x) - b.at<float>(y, x);
-    return o;
+    return MatExpr(o);
 }
-// the pose algebra of fmatcher.cpp:2481-2505 on small CV_32F matrices: -A, A * B (gemm: float products accumulated in
-// double per element like OpenCV's 32F GEMM kernel for small sizes, rounded once), A + B
-static inline Mat operator-(const Mat& a) { return -1.f * a; }
-static inline Mat operator+(const Mat& a, const Mat& b) {
+static inline MatExpr operator-(const Mat& a) { return -1.f * a; }
+static inline MatExpr operator+(const Mat& a, const Mat& b) {
     assert(a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);
     Mat o; o.create(a.rows, a.cols, CV_32F);
     for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) o.at<float>(y, x) = a.at<float>(y, x) + b.at<float>(y, x);
-    return o;
+    return MatExpr(o);
 }
-static inline Mat operator*(const Mat& a, const Mat& b) {
+static inline MatExpr operator*(const Mat& a, const Mat& b) {
     assert(a.type() == CV_32F && b.type() == CV_32F && a.cols == b.rows);
     Mat o; o.create(a.rows, b.cols, CV_32F);
     for (int y = 0; y < a.rows; ++y)
@@ -263,7 +300,53 @@ static inline Mat operator*(const Mat& a, const Mat& b) {
             for (int k = 0; k < a.cols; ++k) s += (double)a.at<float>(y, k) * (double)b.at<float>(k, x);
             o.at<float>(y, x) = (float)s;
         }
-    return o;
+    return MatExpr(o);
+}
+// MatExpr on the left: -R21*t12, (Rlw*twc)+tlw, p1.x*row - row ...
+static inline MatExpr operator*(const MatExpr& a, const Mat& b) { return a.m * b; }
+static inline MatExpr operator+(const MatExpr& a, const Mat& b) { return a.m + b; }
+static inline MatExpr operator-(const MatExpr& a, const Mat& b) { return a.m - b; }
+static inline MatExpr operator-(const Mat& a, const MatExpr& b) { return a - b.m; }
+static inline MatExpr operator/(const MatExpr& a, float s) { return a.m / s; }
+// cv::undistortPoints(src, dst, K, D, R = Mat(), P = K) on an N x 2 CV_32F matrix: forwarded to the oracle's restatement
+// (orb_oracle.cpp), which tests/test_undistort.py pins bit for bit against the real cv2.undistortPoints
+extern "C" void orc_undistort_points(const float* xy, int n, const float* cam, const float* dist, int ndist, float* out);
+static inline void undistortPoints(const Mat& src, Mat& dst, const Mat& K, const Mat& D, const Mat& R, const Mat& P) {
+    assert(src.type() == CV_32F && src.cols == 2 && R.empty() && P.data == K.data); (void)R; (void)P;
+    const float cam[4] = {K.at<float>(0, 0), K.at<float>(1, 1), K.at<float>(0, 2), K.at<float>(1, 2)};
+    float dist[8];
+    const int nd = D.rows * D.cols;
+    for (int i = 0; i < nd && i < 8; ++i) dist[i] = D.at<float>(i);
+    Mat in = src.clone(), out;
+    out.create(src.rows, 2, CV_32F);
+    orc_undistort_points(in.ptr<float>(0), src.rows, cam, dist, nd, out.ptr<float>(0));
+    dst = out;
+}
+static inline double norm(const Mat& a) {            // L2 norm of a CV_32F vector, accumulated in double
+    return std::sqrt(a.dot(a));
+}
+static inline void hconcat(const Mat& a, const Mat& b, Mat& dst) {
+    assert(a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows);
+    Mat o; o.create(a.rows, a.cols + b.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y) {
+        for (int x = 0; x < a.cols; ++x) o.at<float>(y, x) = a.at<float>(y, x);
+        for (int x = 0; x < b.cols; ++x) o.at<float>(y, a.cols + x) = b.at<float>(y, x);
+    }
+    dst = o;
+}
+// cv::Mat_<float>(r, c) << a, b, c ...
+template <typename T> class Mat_ : public Mat {
+public:
+    Mat_(int r, int c) : Mat(r, c, CV_32F) {}
+};
+struct MatCommaInitializer {
+    Mat m; int i;
+    MatCommaInitializer& operator,(float v) { m.at<float>(i / m.cols, i % m.cols) = v; ++i; return *this; }
+    operator Mat() const { return m; }
+};
+template <typename T> static inline MatCommaInitializer operator<<(const Mat_<T>& m, float v) {
+    MatCommaInitializer c{m, 0};
+    return c, v;
 }
 static inline double norm(const Mat& a, const Mat& b, int normType) {
     assert(normType == NORM_L1 && a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols); (void)normType;

@@ -11,6 +11,8 @@
 // reference's own source text:
 //     frame.cpp:386-414      Frame::AssignFeaturesToGrid          frame.cpp:678-744   Frame::GetFeaturesInArea
 //     frame.cpp:746-756      Frame::PosInGrid                     frame.cpp:823-997   Frame::ComputeStereoMatches
+//     frame.cpp:758-791      Frame::UndistortKeyPoints            frame.cpp:793-821   Frame::ComputeImageBounds   (row f-2;
+//                            cv::undistortPoints itself = the oracle's restatement, pinned bit for bit against cv2)
 //     fmatcher.cpp:313-319   TH_HIGH / TH_LOW / HISTO_LENGTH, ctor fmatcher.cpp:983-1098   FMatcher::SearchForInitialization
 //     fmatcher.cpp:2813-2854 FMatcher::ComputeThreeMaxima         fmatcher.cpp:2859-2875   FMatcher::DescriptorDistance
 //     fmatcher.cpp:2471-2687 FMatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono), both camera branches
@@ -72,7 +74,7 @@ public:
 // the members of datastructures::Frame (frame.h) the slices read or write - same names, same types
 class Frame {
 public:
-    cv::Mat T_w_c_, mTrl;
+    cv::Mat T_w_c_, mTrl, mK, mDistCoef;
     geometry::Camera* mpCamera = nullptr;
     std::vector<MapPoint*> mvpMapPoints;
     std::vector<bool> mvbOutlier;
@@ -94,6 +96,8 @@ public:
                                      const bool bRight = false) const;
     bool PosInGrid(const cv::KeyPoint& kp, int& posX, int& posY);
     void ComputeStereoMatches();
+    void UndistortKeyPoints();
+    void ComputeImageBounds(const cv::Mat& imLeft);
 };
 }  // namespace datastructures
 
@@ -130,6 +134,8 @@ namespace datastructures {
 #include "gen/frame_678_744.inc"
 #include "gen/frame_746_756.inc"
 #include "gen/frame_823_997.inc"
+#include "gen/frame_758_791.inc"
+#include "gen/frame_793_821.inc"
 }  // namespace datastructures
 }  // namespace vi_slam
 
@@ -310,6 +316,30 @@ int orb_refs_search_by_projection(int nLast, const cv::KeyPoint* kLast, const fl
     const int n = matcher.SearchByProjection(Cur, Last, th, bMono != 0);
     for (int i = 0; i < n2; ++i) assigned[i] = Cur.mvpMapPoints[i] ? Cur.mvpMapPoints[i]->index : -1;
     return n;
+}
+
+// Frame::UndistortKeyPoints / ComputeImageBounds with mK = (fx, fy, cx, cy), mDistCoef = dist[ndist]
+static void set_camera(Frame& F, const float* cam, const float* dist, int ndist) {
+    F.mK = cv::Mat::zeros(3, 3, CV_32F);
+    F.mK.at<float>(0, 0) = cam[0]; F.mK.at<float>(1, 1) = cam[1]; F.mK.at<float>(0, 2) = cam[2]; F.mK.at<float>(1, 2) = cam[3];
+    F.mK.at<float>(2, 2) = 1.f;
+    F.mDistCoef = cv::Mat::zeros(ndist, 1, CV_32F);
+    for (int i = 0; i < ndist; ++i) F.mDistCoef.at<float>(i) = dist[i];
+}
+void orb_refs_undistort_keypoints(const cv::KeyPoint* kps, int n, const float* cam, const float* dist, int ndist, cv::KeyPoint* out) {
+    Frame F;
+    F.N = n;
+    F.keypoints_.assign(kps, kps + n);
+    set_camera(F, cam, dist, ndist);
+    F.UndistortKeyPoints();
+    for (int i = 0; i < n; ++i) out[i] = F.ukeypoints_[i];
+}
+void orb_refs_image_bounds(int cols, int rows, const float* cam, const float* dist, int ndist, float* bounds) {
+    Frame F;
+    set_camera(F, cam, dist, ndist);
+    cv::Mat im(rows, cols, CV_8UC1);
+    F.ComputeImageBounds(im);
+    bounds[0] = F.mnMinX; bounds[1] = F.mnMaxX; bounds[2] = F.mnMinY; bounds[3] = F.mnMaxY;
 }
 
 // Timed CPU baseline of bench.py (cpu_baseline / --impl reference): `n` frames (stereo: left / right interleaved) dealt to

@@ -303,3 +303,53 @@ def test_reference_bench_body_does_the_same_work_as_the_port():
     assert abs(rt - ot) <= 0.01 * ot
     rt, rm = ref.bench_frames(frames[0::2], 1000, lapping=(0, 1000), mode=2, nthreads=2)
     assert rt > 3000 and rm > 0
+
+
+# --------------------------------------------------------------------------------------------- row f-4 (fisheye stereo epilogue)
+@needs_ref
+@pytest.mark.parametrize("seed", [3, 17])
+def test_oracle_kb8_triangulation_equals_reference_text(seed):
+    """KannalaBrandt8::TriangulateMatches with unproject (Newton), project, Triangulate - the reference's own text - against the
+    oracle: every accept / reject decision, depth and 3D point bit for bit.  (cv::SVD::compute is the same Jacobi stand-in on
+    both sides; the real cv::SVD is pinned with a tolerance through tests/golden/kb8.npz, tests/test_kb8.py.)"""
+    from tests.golden.make_kb8_golden import PRM1, PRM2, make_matches, rig_pose
+    R12, t12 = rig_pose()
+    rig = oracle.kb8_rig(PRM1, PRM2, R12, t12)
+    p1, p2, s1, s2 = make_matches(6000, seed)
+    rd, rp = ref.kb8_triangulate(rig, p1, p2, s1, s2)
+    od, op, _ = oracle.kb8_triangulate(rig, p1, p2, s1, s2)
+    assert np.array_equal(_bits(rd), _bits(od)) and np.array_equal(_bits(rp), _bits(op))
+    assert 0.2 * len(rd) < (rd > 0).sum() < 0.8 * len(rd)            # both outcomes are well represented
+
+
+@needs_ref
+@pytest.mark.parametrize("n,seed,mono_left,mono_right", [(1200, 5, 0, 0), (900, 6, 150, 90)])
+def test_oracle_fisheye_stereo_equals_reference_text(n, seed, mono_left, mono_right):
+    """Frame::ComputeStereoFishEyeMatches - lapping-area slices, knnMatch, the 0.7 rule, TriangulateMatches, the three output
+    vectors (a right keypoint claimed twice keeps the later left index) - as the reference's own text."""
+    from tests.golden.make_kb8_golden import PRM1, PRM2, rig_pose
+    from tests.test_kb8 import SIGMA2, _fisheye_frames
+    R12, t12 = rig_pose()
+    rig = oracle.kb8_rig(PRM1, PRM2, R12, t12)
+    kl, dl, kr, dr = _fisheye_frames(n, seed, mono_left, mono_right)
+    got = ref.stereo_fisheye_matches(rig, kl, dl, mono_left, kr, dr, mono_right, SIGMA2)
+    exp = oracle.stereo_fisheye_matches(rig, kl, dl, mono_left, kr, dr, mono_right, SIGMA2)
+    assert np.array_equal(got["left_to_right"], exp["left_to_right"]) and np.array_equal(got["right_to_left"], exp["right_to_left"])
+    assert np.array_equal(_bits(got["depth"]), _bits(exp["depth"])) and np.array_equal(_bits(got["p3d"]), _bits(exp["p3d"]))
+    assert (got["left_to_right"] >= 0).sum() > n // 10
+
+
+# --------------------------------------------------------------------------------------------- row f-2 (undistortion, image bounds)
+@needs_ref
+@pytest.mark.parametrize("cam,dist", [([500, 510, 320, 240], [-0.28, 0.07, 0.0002, 0.0001]),
+                                      ([500, 510, 320, 240], [0.0, 0.07, 0.0002, 0.0001]),            # k1 == 0: the copy branch (frame.cpp:762)
+                                      ([458.654, 457.296, 367.215, 248.375], [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05, 0.01])])
+def test_oracle_undistortion_equals_reference_text(cam, dist):
+    """Frame::UndistortKeyPoints / ComputeImageBounds as the reference's own text (the k1 == 0 branch, the point matrix, the
+    corner order of the bounds); cv::undistortPoints underneath is the restatement that tests/test_undistort.py pins against cv2."""
+    from vi_slam_b200 import synthetic
+    _, k, _ = oracle.OracleExtractor(1500).compute(synthetic.make_frame(5, 640, 480), (0, 0))
+    a, b = ref.undistort_keypoints(k, cam, dist), oracle.undistort_keypoints(k, cam, dist)
+    for f in a.dtype.names:
+        assert np.array_equal(a[f].view(np.uint32), b[f].view(np.uint32)), f
+    assert np.array_equal(_bits(ref.image_bounds(640, 480, cam, dist)), _bits(oracle.image_bounds(640, 480, cam, dist)))
