@@ -17,7 +17,7 @@ DBOW3 := $(REF)/thirdparty/DBoW3/DBoW3/src
 KB8_CPP := $(REF)/src/geometry/cameramodels/kannalabrandt8.cpp
 SRC := $(REF)/src/geometry/fextractor.cpp ref_compat/cv_compat.cpp ref_compat/ref_driver.cpp ref_compat/ref_slices.cpp orb_oracle.cpp \
        $(FRAME_CPP) $(FMATCHER_CPP) $(PINHOLE_CPP) ref_compat/ref_dbow3.cpp $(DBOW3)/Vocabulary.cpp $(DBOW3)/DescManip.cpp \
-       $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp ref_compat/ref_kb8.cpp $(KB8_CPP)
+       $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp ref_compat/ref_kb8.cpp ref_compat/ref_matchfeatures.cpp $(KB8_CPP)
 
 all: $(OUT)
 
@@ -42,6 +42,8 @@ $(OUT): $(SRC) ref_compat/cv_compat.hpp ../vi_slam_b200/csrc/orb_pattern.inc ref
 	$(call slice,$(FMATCHER_CPP),983,1098,fmatcher,int FMatcher::SearchForInitialization)
 	$(call slice,$(FMATCHER_CPP),2813,2854,fmatcher,void FMatcher::ComputeThreeMaxima)
 	$(call slice,$(FMATCHER_CPP),2859,2875,fmatcher,int FMatcher::DescriptorDistance)
+	$(call slice,$(FMATCHER_CPP),132,245,fmatcher,void matchFeatures)
+	$(call slice,$(FMATCHER_CPP),247,266,fmatcher,void removeDuplicatedMatches)
 	$(call slice,$(FMATCHER_CPP),2471,2687,fmatcher,const Frame &LastFrame)
 	$(call slice,$(PINHOLE_CPP),13,16,pinhole,const cv::Point3f &p3D)
 	$(call slice,$(PINHOLE_CPP),22,26,pinhole,const cv::Mat &m3D)
@@ -58,7 +60,7 @@ $(OUT): $(SRC) ref_compat/cv_compat.hpp ../vi_slam_b200/csrc/orb_pattern.inc ref
 	@# -include ...: the vendored DBoW3 headers rely on transitive std includes that GCC 13's leaner headers no longer provide
 	$(CXX) $(CXXFLAGS) -Iref_compat -I_ref -I$(REF)/include -shared -Wl,-Bsymbolic -o $@ \
 	    $(REF)/src/geometry/fextractor.cpp ref_compat/cv_compat.cpp ref_compat/ref_driver.cpp ref_compat/ref_slices.cpp \
-	    ref_compat/ref_kb8.cpp -I$(DBOW3) -include cstdint -include iostream -include string ref_compat/ref_dbow3.cpp $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp \
+	    ref_compat/ref_kb8.cpp ref_compat/ref_matchfeatures.cpp -I$(DBOW3) -include cstdint -include iostream -include string ref_compat/ref_dbow3.cpp $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp \
 	    -x c++ -std=c++17 orb_oracle.cpp
 	sha256sum $(REF)/src/geometry/fextractor.cpp $(REF)/include/vi_slam/geometry/fextractor.h $(FRAME_CPP) $(FMATCHER_CPP) $(PINHOLE_CPP) \
 	    $(DBOW3)/Vocabulary.cpp $(DBOW3)/DescManip.cpp $(DBOW3)/BowVector.cpp $(DBOW3)/FeatureVector.cpp $(KB8_CPP) > _ref/SOURCES.sha256

@@ -25,7 +25,7 @@ def build(force: bool = False) -> str | None:
     reference checkout is absent (GPU box) and no prebuilt library travelled."""
     if os.path.exists(REF_SOURCE):
         deps = [REF_SOURCE, os.path.join(_HERE, "orb_oracle.cpp"), os.path.join(_HERE, "ref.mk")] + \
-               [os.path.join(_HERE, "ref_compat", f) for f in ("cv_compat.hpp", "cv_compat.cpp", "ref_driver.cpp", "ref_slices.cpp", "ref_dbow3.cpp", "ref_kb8.cpp")] + \
+               [os.path.join(_HERE, "ref_compat", f) for f in ("cv_compat.hpp", "cv_compat.cpp", "ref_driver.cpp", "ref_slices.cpp", "ref_dbow3.cpp", "ref_kb8.cpp", "ref_matchfeatures.cpp")] + \
                [os.path.join(REFERENCE, "src", "datastructures", "frame.cpp"), os.path.join(REFERENCE, "src", "geometry", "fmatcher.cpp")]
         stale = not os.path.exists(LIB_PATH) or any(os.path.getmtime(d) > os.path.getmtime(LIB_PATH) for d in deps)
         if force or stale:
@@ -295,6 +295,18 @@ def bench_frames(frames: np.ndarray, nfeatures=2000, scale_factor=1.2, nlevels=8
     tot = lib().orb_refs_bench_frames(nfeatures, scale_factor, nlevels, ini_th, min_th, _p(frames, C.c_uint8), n, w, h, int(lapping[0]),
                                       int(lapping[1]), int(mode), bf, b, nthreads, C.byref(nm))
     return tot, nm.value
+
+
+def match_features(desc1, desc2, lowe_ratio_as_int=1):
+    """geometry::matchFeatures method 2 + removeDuplicatedMatches (fmatcher.cpp:132-245, 247-266), the reference's own
+    text; knnMatch is the oracle's kNN-2.  The reference reads the ratio with Config::get<int> and caches it in a
+    function-local static, so the FIRST call of a process fixes it.  desc2 needs >= 2 rows (the reference indexes
+    knn_matches[i][1] unconditionally).  -> int32[n][3] (queryIdx, trainIdx, distance), sorted by trainIdx; which of
+    several matches onto one trainIdx survives follows std::sort (unstable beyond 16 elements)."""
+    a, b = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32), np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+    out = np.zeros((max(len(a), 1), 3), np.int32)
+    n = lib().orb_refm_match_features(_p(a, C.c_uint8), len(a), _p(b, C.c_uint8), len(b), int(lowe_ratio_as_int), _p(out, C.c_int32))
+    return out[:n].copy()
 
 
 def kb8_triangulate(rig, pt1, pt2, sigma1, sigma2):

@@ -40,6 +40,12 @@ def main():
                             host_uv_right=host["uv_right"], host_invz=host["invz"], host_valid=host["valid"],
                             host_direction=np.int32(host["direction"]), sources_sha256=sha, **keep)
         print(name, "projection:", n, "matches, direction", host["direction"])
+    # row a-9: matchFeatures method 2 + removeDuplicatedMatches (fmatcher.cpp:132-266), ratio as the reference reads it (int 1)
+    from tests.test_ref_pin_matchers import _match_features_case
+    q, t = _match_features_case(11, 700, 500)
+    m = ref.match_features(q, t, 1)
+    np.savez_compressed(os.path.join(OUT, "refm_matchfeatures.npz"), q=q, t=t, matches=m, sources_sha256=sha)
+    print("matchFeatures:", len(m), "matches of", len(q))
 
 
 if __name__ == "__main__":

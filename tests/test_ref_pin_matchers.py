@@ -2,7 +2,8 @@
 
 oracle/_ref/liborb_ref.so also holds Frame::ComputeStereoMatches (frame.cpp:823-997), Frame::AssignFeaturesToGrid /
 GetFeaturesInArea / PosInGrid (frame.cpp:386-414, 678-756), FMatcher::SearchForInitialization (fmatcher.cpp:983-1098),
-ComputeThreeMaxima (:2813-2854) and DescriptorDistance (:2859-2875): oracle/ref.mk cuts those definitions out of the
+ComputeThreeMaxima (:2813-2854), DescriptorDistance (:2859-2875) and the free matchFeatures / removeDuplicatedMatches
+(:132-266): oracle/ref.mk cuts those definitions out of the
 reference files by line range at build time and compiles them unmodified against stand-in class declarations
 (oracle/ref_compat/ref_slices.cpp); the pyramids the stereo matcher reads are the reference FExtractor's own.
 Compared here: the oracle (CPU), the emulation build (CPU) and - marked gpu - the CUDA path; committed fixtures
@@ -45,6 +46,74 @@ def test_descriptor_distance_reference_text():
         assert want == int(np.unpackbits(d[i] ^ d[i + 1]).sum())
         assert oracle.descriptor_distance(d[i], d[i + 1]) == want
     assert ref.descriptor_distance(d[0], d[1]) == 256 and ref.descriptor_distance(d[2], d[3]) == 0
+
+
+# --------------------------------------------------------------------------------------------- row a-9 (matchFeatures method 2)
+def _match_features_case(seed, nq, nt):
+    """queries = noisy copies of train rows, several per train row, plus unrelated rows: exercises the ratio rule and
+    removeDuplicatedMatches."""
+    rng = np.random.default_rng(seed)
+    t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    src = rng.integers(0, max(nt // 2, 1), nq)
+    q = t[src].copy()
+    flips = rng.integers(0, 60, nq)
+    for i in range(nq):
+        pos = rng.choice(256, flips[i], replace=False)
+        np.bitwise_xor.at(q[i], pos >> 3, (1 << (pos & 7)).astype(np.uint8))
+    q[::7] = rng.integers(0, 256, (len(q[::7]), 32), dtype=np.uint8)
+    return q, t
+
+
+def _check_match_features(got, want, q, t):
+    """want = the reference's matchFeatures output.  The surviving trainIdx set is exact; which query survives on a
+    duplicated trainIdx is std::sort's choice in the reference (unstable) and the lowest query index in ours
+    (include/viorb.h: stable) - both must come from the pre-dedup candidates of that trainIdx."""
+    idx, dist = oracle.knn2(q, t)
+    cand = oracle.ratio_filter(idx, dist, 1.0, 1)
+    np.testing.assert_array_equal(got[:, 1], want[:, 1])
+    assert np.all(np.diff(want[:, 1]) > 0)
+    by_train = {}
+    for qi, ti, d in cand:
+        by_train.setdefault(int(ti), []).append((int(qi), int(d)))
+    n_dup = 0
+    for g, w in zip(got, want):
+        c = by_train[int(w[1])]
+        assert (int(w[0]), int(w[2])) in c and (int(g[0]), int(g[2])) in c
+        if len(c) == 1:
+            assert tuple(g) == tuple(w)
+        else:
+            n_dup += 1
+            assert int(g[0]) == min(x[0] for x in c)
+    return n_dup
+
+
+@needs_ref
+@pytest.mark.parametrize("seed,nq,nt", [(1, 900, 700), (2, 12, 40), (3, 300, 2)])
+def test_oracle_match_features_equals_reference_text(seed, nq, nt):
+    q, t = _match_features_case(seed, nq, nt)
+    want = ref.match_features(q, t, 1)
+    idx, dist = oracle.knn2(q, t)
+    got = oracle.dedup_by_train(oracle.ratio_filter(idx, dist, 1.0, 1))
+    n_dup = _check_match_features(got, want, q, t)
+    assert len(want) > 0 and (nq < 100 or n_dup > 0)
+    if nq <= 16:                      # std::sort is an insertion sort (stable) up to 16 elements: everything is exact
+        np.testing.assert_array_equal(got, want)
+
+
+def test_oracle_match_features_equals_committed_reference_fixture(golden_dir):
+    z = np.load(os.path.join(golden_dir, "refm_matchfeatures.npz"))
+    idx, dist = oracle.knn2(z["q"], z["t"])
+    got = oracle.dedup_by_train(oracle.ratio_filter(idx, dist, 1.0, 1))
+    assert _check_match_features(got, z["matches"], z["q"], z["t"]) > 0
+
+
+@pytest.mark.gpu
+def test_cuda_match_features_equals_committed_reference_fixture(golden_dir):
+    from vi_slam_b200 import matcher
+    z = np.load(os.path.join(golden_dir, "refm_matchfeatures.npz"))
+    m = matcher.match_features(z["q"], z["t"], method_index=2, lowe_method_dist_ratio=1.0)
+    got = np.stack([m["query_idx"], m["train_idx"], m["distance"]], 1).astype(np.int32)
+    assert _check_match_features(got, z["matches"], z["q"], z["t"]) > 0
 
 
 # --------------------------------------------------------------------------------------------- row a-10
