@@ -161,8 +161,8 @@ __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int 
 // FAST-9 + cell-local 3x3 NMS + per-cell ini/min threshold.  One CTA = one strip (up to
 // VIORB_FAST_STRIP_CELLS consecutive cells of one cell row) of one frame: per-CTA fixed costs and the
 // five barriers are amortised over ~8k pixels, and rows are loaded as long coalesced runs.
-//   phase 0  stage the cell region + 3-px halo in shared memory with aligned 32-bit loads
-//   phase A  opposite-pair pre-test per pixel -> warp-ballot compaction into a queue
+//   phase 0  stage the cell region + 3-px halo in shared memory with 16-byte cp.async
+//   phase A  opposite-pair pre-test per pixel -> queue of pixels that may be corners
 //   phase B  dense corner score (cornerScore<16>) on the queue -> 8-bit score tile
 //   phase C  strict 3x3 NMS inside the cell (outside = 0), survivors to shared
 //   phase D  keep score >= iniTh if any survivor reaches it, else all (>= minTh); append to the
@@ -224,14 +224,6 @@ __device__ __forceinline__ unsigned fast_score16x2(const uint8_t* pa, const uint
     return __vsub2(__vmaxs2(a, __vsub2(0u, b)), 0x00010001u);
 }
 
-// shared-memory layout of one k_fast CTA (all sizes from ExtractGeom::tileW/tileH = max region + 6)
-__host__ __device__ inline int fast_tile_pitch(int tileW) { return ((tileW + 19 + 8 + 15) >> 4) << 4; }   // bytes: alignment shift + region + halo + pad word, whole 16-byte chunks
-__host__ __device__ inline int fast_score_pitch(int tileW) { return (tileW - 4 + 3) & ~3; }             // region + ring
-__host__ __device__ inline size_t fast_smem_bytes(int tileW, int tileH) {
-    return (size_t)tileH * fast_tile_pitch(tileW) + (size_t)(tileH - 4) * fast_score_pitch(tileW) +
-           (size_t)2 * (tileW - 6) * (tileH - 6) + 32;      // queue (2 B / px); the survivors reuse the pixel tile
-}
-
 // bytes 0,1 (resp. 2,3) of w zero-extended into the two 16-bit lanes
 __device__ __forceinline__ unsigned lo16x2(unsigned w) { return __byte_perm(w, 0, 0x4140); }
 __device__ __forceinline__ unsigned hi16x2(unsigned w) { return __byte_perm(w, 0, 0x4342); }
@@ -251,12 +243,30 @@ __device__ __forceinline__ unsigned fast_pretest2(unsigned c, unsigned up, unsig
     return (xb | yd) & 0x40004000u;
 }
 
+// ---- k_fast: every pitch is a compile-time constant ---------------------------------------------------------------------
+// The host cuts strips so that a region is at most VIORB_FAST_MAXRW pixels wide (wCell < 60, so a strip always holds >= 4
+// cells); pixel tile and score tile share ONE pitch, VIORB_FAST_TP, so a queue entry is the linear offset py * TP + px and
+// addresses both tiles without decoding, and the 16 ring offsets of the score network are immediates.
+#ifndef VIORB_FAST_TP
+#define VIORB_FAST_TP 336
+#endif
+#define VIORB_FAST_MAXRW (VIORB_FAST_TP - 48)               // 19 alignment shift + 6 halo + word right of the halo + chunk rounding
+#ifndef VIORB_FAST_MAXAREA
+#define VIORB_FAST_MAXAREA 7168                             // the host shortens strips of tall cell rows to this many pixels
+#endif
+__host__ __device__ inline size_t fast_smem_bytes(int /*tileW*/, int tileH, int area) {
+    return (size_t)tileH * VIORB_FAST_TP + (size_t)(tileH - 4) * VIORB_FAST_TP +   // pixel tile (rh + 6 rows), score tile (rh + 2 rows)
+           (size_t)2 * area + 32;                                                   // queue (2 B / px); the survivors reuse the pixel tile
+}
+
 __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, FrameSrc fs, const CellDesc* __restrict__ cells,
                                                              uint32_t* __restrict__ cand, int* __restrict__ candCount,
                                                              int* __restrict__ status) {
+    constexpr int TP = VIORB_FAST_TP, TPW = TP >> 2;
     VIORB_DYN_SMEM(smem);
     __shared__ int qCount, sCount;
     __shared__ int hasIni[32];                               // per cell of the strip
+    __shared__ uint2 wordMask[VIORB_FAST_MAXRW / 4 + 4];
     const int tid = threadIdx.x, lane = tid & 31;
     const int f = blockIdx.y + g.frame0;
     const CellDesc c = cells[blockIdx.x];
@@ -265,90 +275,86 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
     int pitch;
     const uint8_t* img = level_ptr(g, fs, l, f, pitch);
     const int rw = c.x1 - c.x0, rh = c.y1 - c.y0, wCell = L.wCell, ncell = c.ncell;
-    const int TP = fast_tile_pitch(g.tileW), TPW = TP >> 2;
-    const int SP = fast_score_pitch(g.tileW);
     uint8_t* T = smem;
     uint8_t* S = T + g.tileH * TP;
-    uint16_t* Q = reinterpret_cast<uint16_t*>(S + (g.tileH - 4) * SP);          // entries: py << 9 | px
-    // NMS survivors (4 B per 2x2 block at most = 1 B per region pixel) overwrite the pixel tile, which is dead after the
-    // score phase: 43 KB instead of 53 KB of shared memory per CTA = 5 instead of 4 resident CTAs per SM
-    uint32_t* surv = reinterpret_cast<uint32_t*>(T);
+    uint16_t* Q = reinterpret_cast<uint16_t*>(S + (g.tileH - 4) * TP);          // entries: py * TP + px
+    uint32_t* surv = reinterpret_cast<uint32_t*>(T);        // NMS survivors overwrite the pixel tile, dead after the score phase
     if (tid == 0) { qCount = 0; sCount = 0; }
     if (tid < 32) hasIni[tid] = 0;
 
-    // phase 0: tile column 0 <-> image x = ax (16-byte aligned, at least one pad word left of the halo).
-    // Rows are copied global -> shared with 16-byte cp.async (LDGSTS): every thread has all its chunks in
-    // flight at once instead of a load -> store dependency per word.
+    // phase 0: tile column 0 <-> image x = ax (16-byte aligned, at least one pad word left of the halo).  The chunks of
+    // all rows form one flat index space (row = i / nC by the host's reciprocal): three 16-byte cp.async per thread.
     const int ox = c.x0 - 3, oy = c.y0 - 3;
     const int ax = ((ox & ~3) - 4) & ~15, shift = ox - ax;  // shift in [4,19]
-    const int nB = ((((shift + 3 + rw + 2) >> 2) + 2) << 2); // bytes per row incl. the word right of the halo
-    const int nC = (nB + 15) >> 4, nR = rh + 6;
+    if (tid < c.ng) {
+        // pixels of the first / last word of a region row that lie inside the region, as 0x4000-per-lane masks
+        // (x: px 0,1; y: px 2,3); every word between them is all ones
+        const int col0 = shift + 3, g0 = col0 >> 2, g1 = (col0 + rw - 1) >> 2;
+        const int s0 = col0 - 4 * g0, e1 = col0 + rw - 1 - 4 * g1;
+        uint2 m = make_uint2(0x40004000u, 0x40004000u);
+        if (tid == 0) { m.x &= (s0 <= 0 ? 0x4000u : 0u) | (s0 <= 1 ? 0x40000000u : 0u); m.y &= (s0 <= 2 ? 0x4000u : 0u) | 0x40000000u; }
+        if (tid == g1 - g0) { m.x &= 0x4000u | (e1 >= 1 ? 0x40000000u : 0u); m.y &= (e1 >= 2 ? 0x4000u : 0u) | (e1 >= 3 ? 0x40000000u : 0u); }
+        wordMask[tid] = m;
+    }
     {
-        const int tx = tid & 31, ty = tid >> 5;              // 32 chunks x 8 rows per pass, no divisions
+        const int nC = c.nC, nChunk = (rh + 6) * nC;
         const uint8_t* src = img + (size_t)oy * pitch + ax;
-        for (int r = ty; r < nR; r += VIORB_FAST_THREADS / 32) {
-            const uint8_t* srow = src + (size_t)r * pitch;
-            uint8_t* trow = T + r * TP;
-            for (int k = tx; k < nC; k += 32) {
-                if (ax + 16 * k + 16 <= pitch) {
-                    __pipeline_memcpy_async(trow + 16 * k, srow + 16 * k, 16);
-                } else {                                     // never read past the end of an image row
-                    for (int j = 0; j < 4; ++j)
-                        if (ax + 16 * k + 4 * j + 4 <= pitch) __pipeline_memcpy_async(trow + 16 * k + 4 * j, srow + 16 * k + 4 * j, 4);
-                }
+        for (int i = tid; i < nChunk; i += VIORB_FAST_THREADS) {
+            const int r = (int)(((unsigned)i * c.invNC) >> 20);
+            const int k16 = (i - r * nC) << 4;
+            const uint8_t* s = src + r * pitch + k16;
+            uint8_t* d = T + r * TP + k16;
+            if (ax + k16 + 16 <= pitch) {
+                __pipeline_memcpy_async(d, s, 16);
+            } else {                                         // never read past the end of an image row
+                for (int j = 0; j < 4; ++j)
+                    if (ax + k16 + 4 * j + 4 <= pitch) __pipeline_memcpy_async(d + 4 * j, s + 4 * j, 4);
             }
         }
         __pipeline_commit();
     }
-    for (int i = tid; i < (((rh + 2) * SP) >> 2); i += VIORB_FAST_THREADS) reinterpret_cast<uint32_t*>(S)[i] = 0;
+    for (int i = tid; i < (((rh + 2) * TP) >> 4); i += VIORB_FAST_THREADS) reinterpret_cast<uint4*>(S)[i] = make_uint4(0, 0, 0, 0);
     __pipeline_wait_prior(0);
     __syncthreads();
 
     const int th = g.minTh;
     const int col0 = shift + 3;                             // tile column of region pixel 0
     const uint8_t* T0 = T + 3 * TP + col0;                  // region pixel (0,0)
+    uint8_t* S0 = S + TP + 1;                               // its score
 
     // phase A: thread = aligned tile word (4 horizontally adjacent pixels) of the flattened region, packed 16x2
     // pre-test.  Pixels that may be corners go to the queue; its order is irrelevant, so a thread claims its
     // slots with one shared-memory atomic (MIO pipe) instead of a warp scan (the kernel is ALU-pipe bound).
     {
-        const int g0 = col0 >> 2, g1 = (col0 + rw - 1) >> 2;
+        const int g0 = col0 >> 2;
         const unsigned kc = (0x4000u - (unsigned)(th + 1)) * 0x10001u;                     // K - th - 1 in both lanes
-        // pixels of the first / last word that lie inside the region, as 0x4000-per-lane masks (a: px 0,1; b: px 2,3)
-        const int s0 = col0 - 4 * g0, e1 = col0 + rw - 1 - 4 * g1;
-        const unsigned firstA = (s0 <= 0 ? 0x4000u : 0u) | (s0 <= 1 ? 0x40000000u : 0u);
-        const unsigned firstB = (s0 <= 2 ? 0x4000u : 0u) | 0x40000000u;
-        const unsigned lastA = 0x4000u | (e1 >= 1 ? 0x40000000u : 0u);
-        const unsigned lastB = (e1 >= 2 ? 0x4000u : 0u) | (e1 >= 3 ? 0x40000000u : 0u);
-        const int ng = g1 - g0 + 1, total = ng * rh;
-        const unsigned ginv = (1u << 22) / (unsigned)ng + 1;     // i / ng = (i * ginv) >> 22, exact while i * ng < 2^22 (ng <= 130, rh <= 127)
-        {
-            for (int i = tid; i < total; i += VIORB_FAST_THREADS) {
-                const int py = (int)(((unsigned)i * ginv) >> 22);
-                const int gx = g0 + (i - py * ng);
-                const uint32_t* R = reinterpret_cast<const uint32_t*>(T + (py + 3) * TP) + gx;
-                const unsigned cw = R[0], wl = R[-1], wr = R[1];
-                const unsigned up = R[-3 * TPW], dn = R[3 * TPW];
-                const unsigned rt = __funnelshift_r(cw, wr, 24), lf = __funnelshift_r(wl, cw, 8);
-                const uint32_t* Rp = R + 2 * TPW;
-                const uint32_t* Rm = R - 2 * TPW;
-                const unsigned d22 = __funnelshift_r(Rp[0], Rp[1], 16), dm22 = __funnelshift_r(Rp[-1], Rp[0], 16);
-                const unsigned d2m2 = __funnelshift_r(Rm[0], Rm[1], 16), dm2m2 = __funnelshift_r(Rm[-1], Rm[0], 16);
-                unsigned a = fast_pretest2(lo16x2(cw), lo16x2(up), lo16x2(dn), lo16x2(lf), lo16x2(rt), lo16x2(d22),
-                                           lo16x2(dm2m2), lo16x2(d2m2), lo16x2(dm22), kc);
-                unsigned b = fast_pretest2(hi16x2(cw), hi16x2(up), hi16x2(dn), hi16x2(lf), hi16x2(rt), hi16x2(d22),
-                                           hi16x2(dm2m2), hi16x2(d2m2), hi16x2(dm22), kc);
-                if (gx == g0) { a &= firstA; b &= firstB; }
-                if (gx == g1) { a &= lastA; b &= lastB; }
-                const unsigned ab = a | (b >> 1);
-                if (ab) {
-                    int q = atomicAdd(&qCount, __popc(ab));
-                    const int e0 = (py << 9) + (gx * 4 - col0);       // valid pixels have e0 + j >= py << 9
-                    if (a & 0x4000u) Q[q++] = (uint16_t)e0;
-                    if (a & 0x40000000u) Q[q++] = (uint16_t)(e0 + 1);
-                    if (b & 0x4000u) Q[q++] = (uint16_t)(e0 + 2);
-                    if (b & 0x40000000u) Q[q++] = (uint16_t)(e0 + 3);
-                }
+        const int ng = c.ng, total = ng * rh;
+        const unsigned ginv = c.ginv;                            // i / ng = (i * ginv) >> 22, exact while i * ng < 2^22 (ng <= 74, rh <= 127)
+        const uint32_t* TW = reinterpret_cast<const uint32_t*>(T + 3 * TP) + g0;
+        for (int i = tid; i < total; i += VIORB_FAST_THREADS) {
+            const int py = (int)(((unsigned)i * ginv) >> 22);
+            const int gi = i - py * ng;                          // word of the row, 0 = g0
+            const uint32_t* R = TW + py * TPW + gi;
+            const unsigned cw = R[0], wl = R[-1], wr = R[1];
+            const unsigned up = R[-3 * TPW], dn = R[3 * TPW];
+            const unsigned rt = __funnelshift_r(cw, wr, 24), lf = __funnelshift_r(wl, cw, 8);
+            const unsigned d22 = __funnelshift_r(R[2 * TPW], R[2 * TPW + 1], 16), dm22 = __funnelshift_r(R[2 * TPW - 1], R[2 * TPW], 16);
+            const unsigned d2m2 = __funnelshift_r(R[-2 * TPW], R[-2 * TPW + 1], 16), dm2m2 = __funnelshift_r(R[-2 * TPW - 1], R[-2 * TPW], 16);
+            unsigned a = fast_pretest2(lo16x2(cw), lo16x2(up), lo16x2(dn), lo16x2(lf), lo16x2(rt), lo16x2(d22),
+                                       lo16x2(dm2m2), lo16x2(d2m2), lo16x2(dm22), kc);
+            unsigned b = fast_pretest2(hi16x2(cw), hi16x2(up), hi16x2(dn), hi16x2(lf), hi16x2(rt), hi16x2(d22),
+                                       hi16x2(dm2m2), hi16x2(d2m2), hi16x2(dm22), kc);
+            const uint2 wm = wordMask[gi];
+            a &= wm.x; b &= wm.y;
+            const unsigned ab = a | (b >> 1);
+            if (ab) {
+                const int q = atomicAdd(&qCount, __popc(ab));
+                const int e0 = py * TP + ((g0 + gi) * 4 - col0);  // valid pixels have e0 + j >= py * TP
+                const int f0 = (a >> 14) & 1, f1 = a >> 30, f2 = (b >> 14) & 1;
+                if (f0) Q[q] = (uint16_t)e0;
+                if (f1) Q[q + f0] = (uint16_t)(e0 + 1);
+                if (f2) Q[q + f0 + f1] = (uint16_t)(e0 + 2);
+                if (b >> 30) Q[q + f0 + f1 + f2] = (uint16_t)(e0 + 3);
             }
         }
     }
@@ -357,38 +363,55 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
 
     // phase B: dense corner score on the queue, two queued pixels per thread (s16x2 lanes)
     {
-        const int o[16] = {3 * TP, 3 * TP + 1, 2 * TP + 2, TP + 3, 3, -TP + 3, -2 * TP + 2, -3 * TP + 1,
-                           -3 * TP, -3 * TP - 1, -2 * TP - 2, -TP - 3, -3, TP - 3, 2 * TP - 2, 3 * TP - 1};
+        constexpr int o[16] = {3 * TP, 3 * TP + 1, 2 * TP + 2, TP + 3, 3, -TP + 3, -2 * TP + 2, -3 * TP + 1,
+                               -3 * TP, -3 * TP - 1, -2 * TP - 2, -TP - 3, -3, TP - 3, 2 * TP - 2, 3 * TP - 1};
         for (int i = 2 * tid; i < nq; i += 2 * VIORB_FAST_THREADS) {
             const int ea = Q[i], eb = Q[min(i + 1, nq - 1)];
-            const int pya = ea >> 9, pxa = ea & 511, pyb = eb >> 9, pxb = eb & 511;
-            const unsigned sc = fast_score16x2(T0 + pya * TP + pxa, T0 + pyb * TP + pxb, o);
+            const unsigned sc = fast_score16x2(T0 + ea, T0 + eb, o);
             const int sa = (int)(short)(sc & 0xFFFF), sb = (int)sc >> 16;
-            if (sa >= th) S[(pya + 1) * SP + pxa + 1] = (uint8_t)sa;
-            if (sb >= th) S[(pyb + 1) * SP + pxb + 1] = (uint8_t)sb;
+            if (sa >= th) S0[ea] = (uint8_t)sa;
+            if (sb >= th) S0[eb] = (uint8_t)sb;
         }
     }
     __syncthreads();
 
     // phase C: strict 3x3 NMS run densely over the queue (only queued pixels can hold a score).  Neighbours in
     // another cell do not count (cv::FAST ran per cell): rows outside the strip are the zero ring of S, columns
-    // across a cell boundary are masked here.
-    const unsigned cinv = (1u << 20) / (unsigned)wCell + 1;                       // px / wCell for px < 16384
-    for (int i = tid; i < nq; i += VIORB_FAST_THREADS) {
-        const int q = Q[i];
-        const int py = q >> 9, px = q & 511;
-        const uint8_t* s = S + (py + 1) * SP + px + 1;
-        const int v = s[0];
-        if (v == 0) continue;                                  // not a corner
-        const int cell = min((int)(((unsigned)px * cinv) >> 20), ncell - 1);
-        const int cl = px - cell * wCell;
-        const bool hasL = cl > 0, hasR = cl < wCell - 1;      // the strip's own ends fall on the zero ring
-        const int mc = max((int)s[-SP], (int)s[SP]);
-        const int ml = hasL ? __vimax3_s32(s[-SP - 1], s[-1], s[SP - 1]) : 0;
-        const int mr = hasR ? __vimax3_s32(s[-SP + 1], s[1], s[SP + 1]) : 0;
-        if (v > __vimax3_s32(mc, ml, mr)) {
-            if (v >= g.iniTh) hasIni[cell] = 1;
-            surv[atomicAdd(&sCount, 1)] = (uint32_t)(c.x0 + px - VIORB_MINB) | ((uint32_t)(c.y0 + py - VIORB_MINB) << 12) | ((uint32_t)v << 24);
+    // across a cell boundary are masked here.  A thread keeps its first two survivors in registers and appends them
+    // after the loop (10 % of the queue survives: the append, not the test, was the cost of this phase).
+    const unsigned cinv = L.cinv;                                                 // px / wCell = (px * cinv) >> 20 for px < 16384
+    {
+        // pending survivors as e | score << 16 (never 0: score >= minTh >= 1), turned into candidate words at the end
+        auto candidate = [&](uint32_t p) {
+            const int e = (int)(p & 0xFFFF), py = (int)((unsigned)e / (unsigned)TP), px = e - py * TP;
+            return (uint32_t)(c.x0 + px - VIORB_MINB) | ((uint32_t)(c.y0 + py - VIORB_MINB) << 12) | ((p >> 16) << 24);
+        };
+        uint32_t pend0 = 0, pend1 = 0;
+        for (int i = tid; i < nq; i += VIORB_FAST_THREADS) {
+            const int e = Q[i];
+            const uint8_t* s = S0 + e;
+            const int v = s[0];
+            if (v == 0) continue;                                  // not a corner
+            const int px = e - (int)((unsigned)e / (unsigned)TP) * TP;
+            const int cell = min((int)(((unsigned)px * cinv) >> 20), ncell - 1);
+            const int cl = px - cell * wCell;
+            const bool hasL = cl > 0, hasR = cl < wCell - 1;      // the strip's own ends fall on the zero ring
+            const int mc = max((int)s[-TP], (int)s[TP]);
+            const int ml = hasL ? __vimax3_s32(s[-TP - 1], s[-1], s[TP - 1]) : 0;
+            const int mr = hasR ? __vimax3_s32(s[-TP + 1], s[1], s[TP + 1]) : 0;
+            if (v > __vimax3_s32(mc, ml, mr)) {
+                if (v >= g.iniTh) hasIni[cell] = 1;
+                const uint32_t p = (uint32_t)e | ((uint32_t)v << 16);
+                if (pend1) surv[atomicAdd(&sCount, 1)] = candidate(p);   // third and later survivors of a thread: rare
+                else if (pend0) pend1 = p;
+                else pend0 = p;
+            }
+        }
+        const int np = (pend0 != 0) + (pend1 != 0);
+        if (np) {
+            const int q = atomicAdd(&sCount, np);
+            surv[q] = candidate(pend0);
+            if (pend1) surv[q + 1] = candidate(pend1);
         }
     }
     __syncthreads();

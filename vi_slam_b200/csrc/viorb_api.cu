@@ -281,7 +281,7 @@ int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
     ex->cells.clear();
     tabs = ResizeTabs();
     size_t off = 0;
-    int candOff = 0, keptOff = 0, maxRW = 1, maxRH = 1, maxNodes = 8, blurBase = 0;
+    int candOff = 0, keptOff = 0, maxRW = 1, maxRH = 1, maxArea = 1, maxNodes = 8, blurBase = 0;
     for (int l = 0; l < nl; ++l) {
         LevelGeom& L = g.lv[l];
         L.w = cv_round_f((float)W * ex->invScale[l]);           // fextractor.cpp:1139-1140
@@ -321,6 +321,7 @@ int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
         if (L.nCols > 0 && L.nRows > 0 && width > 0 && height > 0) {
             L.wCell = (int)std::ceil(width / L.nCols);
             L.hCell = (int)std::ceil(height / L.nRows);
+            L.cinv = (1u << 20) / (unsigned)L.wCell + 1;
             for (int i = 0; i < L.nRows; ++i) {
                 const float iniY = (float)(VIORB_MINB + i * L.hCell);
                 float maxY = iniY + L.hCell + 6;
@@ -342,20 +343,30 @@ int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
                     L.lastRow = std::max(L.lastRow, i);
                 }
                 // k_fast works on strips of consecutive cells of one cell row
-                const int per = std::max(1, std::min(VIORB_FAST_STRIP_CELLS, 500 / L.wCell));
+                const int per = std::max(1, std::min(std::min(VIORB_FAST_STRIP_CELLS, VIORB_FAST_MAXRW / L.wCell), VIORB_FAST_MAXAREA / (L.wCell * (y1 - y0))));
                 for (size_t j0 = 0; j0 < row.size(); j0 += per) {
                     const size_t j1 = std::min(row.size(), j0 + per);
                     CellDesc c;
                     c.level = (short)l; c.ncell = (short)(j1 - j0);
                     c.x0 = (short)row[j0].first; c.x1 = (short)row[j1 - 1].second;
                     c.y0 = (short)y0; c.y1 = (short)y1;
+                    {   // the constants k_fast derives from the strip (same expressions as in the kernel)
+                        const int rw = c.x1 - c.x0, ox = c.x0 - 3, ax = ((ox & ~3) - 4) & ~15, shift = ox - ax, col0 = shift + 3;
+                        const int nB = ((((shift + 3 + rw + 2) >> 2) + 2) << 2);
+                        const int ng = ((col0 + rw - 1) >> 2) - (col0 >> 2) + 1;
+                        c.nC = (short)((nB + 15) >> 4); c.ng = (short)ng; c.pad2[0] = c.pad2[1] = 0;
+                        c.invNC = (1u << 20) / (unsigned)c.nC + 1;
+                        c.ginv = (1u << 22) / (unsigned)ng + 1;
+                    }
                     ex->cells.push_back(c);
                     maxRW = std::max(maxRW, c.x1 - c.x0);
                     maxRH = std::max(maxRH, c.y1 - c.y0);
+                    maxArea = std::max(maxArea, (c.x1 - c.x0) * (c.y1 - c.y0));
                 }
             }
         } else {
             L.wCell = L.hCell = 1;
+            L.cinv = (1u << 20) + 1;
         }
         L.nCells = (int)ex->cells.size() - L.cellBase;
         // NMS leaves at most one corner per 2x2 block
@@ -388,11 +399,11 @@ int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
     g.tileH = maxRH + 6;
     g.maxNodes = maxNodes;
     g.arenaStride = off;
-    ex->fastSmem = fast_smem_bytes(g.tileW, g.tileH);
+    ex->fastSmem = fast_smem_bytes(g.tileW, g.tileH, maxArea);
     ex->octSmem = octree_smem_bytes(maxNodes, VIORB_OCT_LIGHT_PYR_CELLS);
     ex->octSmemDense = octree_smem_bytes(maxNodes, VIORB_OCT_PYR_CELLS);
     if (ex->octSmemDense > 220 * 1024) return fail(VIORB_E_ARG, "nfeatures too large for the quadtree's shared memory");
-    if (maxRW > 511 || maxRH > 127) return fail(VIORB_E_ARG, "FAST cell larger than supported");
+    if (maxRW > VIORB_FAST_MAXRW || maxRH > 127) return fail(VIORB_E_ARG, "FAST cell larger than supported");
     return VIORB_OK;
 }
 

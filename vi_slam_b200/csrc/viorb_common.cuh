@@ -30,6 +30,7 @@ struct LevelGeom {
     int off;               // byte offset inside one frame's pyramid / blur arena
     int maxBX, maxBY;      // w - 16, h - 16 (fextractor.cpp:766-767)
     int nCols, nRows, wCell, hCell, lastCol, lastRow;   // FAST cell grid (fextractor.cpp:775-778)
+    unsigned cinv;         // (1 << 20) / wCell + 1: strip pixel -> cell of the strip
     int cellBase, nCells;  // slice of the cell table
     int candOff, candCap;  // slice of one frame's candidate arena (entries)
     int nWant, nIni;       // DistributeOctTree N and root count
@@ -62,9 +63,13 @@ struct ExtractGeom {
 #ifndef VIORB_FAST_STRIP_CELLS
 #define VIORB_FAST_STRIP_CELLS 8
 #endif
-struct CellDesc {
+struct __align__(16) CellDesc {
     short level, ncell;
     short x0, y0, x1, y1;
+    short nC, ng;          // 16-byte chunks per staged tile row; aligned 4-pixel words per region row
+    unsigned invNC;        // (1 << 20) / nC + 1: chunk index -> tile row
+    unsigned ginv;         // (1 << 22) / (words per region row) + 1: word index -> region row
+    unsigned pad2[2];
 };
 
 // Where the images of a batch live.
