@@ -596,6 +596,22 @@ def run_ours(args, wl, rank, world, local_rank):
         cnt = np.array([exl.fetch(i)[1].shape[0] for i in range(0, min(chunk, B), max(1, chunk // 16))])
         stats = {"keypoints_per_frame": float(cnt.mean())}
 
+    # FAST survivors per image (the quadtree's input), over the 32 frame classes of the last extract call of the left handle
+    import ctypes as _C
+    nf = min(32, getattr(exl, "_last_n", 32))
+    ncand = 0
+    for fr in range(nf):
+        for lv in range(NLEVELS):
+            c = _C.c_int32()
+            if exl._lib.viorb_debug_candidates(exl._h, fr, lv, None, 0, _C.byref(c)) != 0:
+                nf = fr
+                break
+            ncand += c.value
+        else:
+            continue
+        break
+    stats["fast_candidates_per_frame"] = ncand / max(nf, 1)
+
     # ---- end to end through the host-buffer C ABI
     e2e = None
     if not args.no_e2e:
@@ -723,7 +739,9 @@ def run_ours(args, wl, rank, world, local_rank):
     mean = {k: v / K for k, v in stages.items()}           # ms per step (all handles summed)
     ext = {k: v for k, v in mean.items() if k in FExtractor.STAGES}
     dom = max(ext, key=ext.get)                            # the dominant kernel of the step is an extraction kernel
-    alg = {"fast": sum(px), "blur": 2 * sum(px), "resize": sum(px[:-1]) + sum(px[1:])}
+    # k_octree: every FAST survivor (4-byte word) read once, every kept keypoint (20-byte record) written once
+    alg = {"fast": sum(px), "blur": 2 * sum(px), "resize": sum(px[:-1]) + sum(px[1:]),
+           "octree": 4 * stats["fast_candidates_per_frame"] + 20 * stats["keypoints_per_frame"]}
     nimg = (2 if stereo else 1) * B
     calls = (2 if stereo else 1) * (-(-B // chunk))         # extract calls per step
     launches_per_step = calls * ((NLEVELS - 1) if dom == "resize" else 1)

@@ -15,7 +15,8 @@ def emu(oracle_mod):
 
 
 @pytest.mark.parametrize("w,h,nf,lap,seed", [(320, 240, 500, (0, 0), 1), (400, 200, 700, (100, 250), 2),
-                                             (640, 360, 3000, (0, 1000), 3), (131, 97, 300, (0, 0), 4), (258, 130, 400, (0, 0), 5)])
+                                             (640, 360, 3000, (0, 1000), 3), (131, 97, 300, (0, 0), 4), (258, 130, 400, (0, 0), 5),
+                                             (123, 91, 200, (0, 0), 6), (700, 96, 600, (0, 0), 7)])   # one 59-px cell column; strips of 8 cells, 2 cell rows
 def test_extract_stages(emu, w, h, nf, lap, seed):
     parity.check_extract(synthetic.make_frame(seed, w, h), nf, lap, lib_path=emu)
 
