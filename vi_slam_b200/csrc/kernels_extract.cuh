@@ -195,13 +195,27 @@ __device__ __forceinline__ int fast_score16(const uint8_t* p, const int* o) {
 }
 
 // cornerScore<16> of TWO pixels at once in s16x2 lanes (pixel A low, pixel B high): the 96 min/max of the
-// arc network are shared, the ring bytes are packed with one multiply-add (FMA pipe) per ring position.
-// Returns (scoreA & 0xFFFF) | scoreB << 16 (scores may be negative = not a corner).
+// arc network are shared.  Every lane carries its value + 256: centre - ring pixel + 256 lies in [1, 511], so ONE 32-bit
+// multiply-add per pixel forms both lanes' differences without a borrow between them (the packed subtraction
+// __vsub2 costs three ALU-pipe instructions on sm_100a, and that pipe bounds the kernel; the multiply-adds go to the
+// FMA pipe, the multipliers come from constant memory so that ptxas keeps them there).  min / max commute with the
+// bias.  Returns, per lane, score + 257 (a value below 257 + threshold = not a corner).
+#define VIORB_FAST_SCORE_BIAS 257
+#ifndef VIORB_EMU
+__constant__ int c_fastMul[2] = {-1, -65536};
+__device__ __forceinline__ unsigned fast_mad(unsigned a, int which, unsigned c) {
+    unsigned r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"((unsigned)c_fastMul[which]), "r"(c));
+    return r;
+}
+#else
+__device__ __forceinline__ unsigned fast_mad(unsigned a, int which, unsigned c) { return a * (which ? 0xFFFF0000u : 0xFFFFFFFFu) + c; }
+#endif
 __device__ __forceinline__ unsigned fast_score16x2(const uint8_t* pa, const uint8_t* pb, const int* o) {
-    const unsigned v = (unsigned)pa[0] + ((unsigned)pb[0] << 16);
+    const unsigned v = ((unsigned)pa[0] + ((unsigned)pb[0] << 16)) | 0x01000100u;         // centre + 256 per lane
     unsigned d[16];
 #pragma unroll
-    for (int k = 0; k < 16; ++k) d[k] = __vsub2(v, (unsigned)pb[o[k]] * 65536u + (unsigned)pa[o[k]]);
+    for (int k = 0; k < 16; ++k) d[k] = fast_mad((unsigned)pb[o[k]], 1, fast_mad((unsigned)pa[o[k]], 0, v));
     unsigned t[16], u[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
@@ -217,11 +231,12 @@ __device__ __forceinline__ unsigned fast_score16x2(const uint8_t* pa, const uint
     }
     unsigned a = __vimax3_s16x2(__vimax3_s16x2(m[0], m[1], m[2]), __vimax3_s16x2(m[3], m[4], m[5]), __vimax3_s16x2(m[6], m[7], m[8]));
     a = __vimax3_s16x2(a, __vimax3_s16x2(m[9], m[10], m[11]), __vimax3_s16x2(m[12], m[13], m[14]));
-    a = __vimax3_s16x2(a, m[15], 0xFF00FF00u);                                      // -256 per lane
+    a = __vimax3_s16x2(a, m[15], 0u);                                               // -256 (+ bias) per lane
     unsigned b = __vimin3_s16x2(__vimin3_s16x2(n[0], n[1], n[2]), __vimin3_s16x2(n[3], n[4], n[5]), __vimin3_s16x2(n[6], n[7], n[8]));
     b = __vimin3_s16x2(b, __vimin3_s16x2(n[9], n[10], n[11]), __vimin3_s16x2(n[12], n[13], n[14]));
-    b = __vimin3_s16x2(b, n[15], 0x01000100u);                                      // +256 per lane
-    return __vsub2(__vmaxs2(a, __vsub2(0u, b)), 0x00010001u);
+    b = __vimin3_s16x2(b, n[15], 0x02000200u);                                      // +256 (+ bias) per lane
+    // max(a, -b) - 1 without the bias = max(a + 256, 512 - (b + 256)) - 257; 512 - (b + 256) >= 0 in both lanes: plain subtraction
+    return __vmaxs2(a, 0x02000200u - b);
 }
 
 // bytes 0,1 (resp. 2,3) of w zero-extended into the two 16-bit lanes
@@ -368,7 +383,7 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
         for (int i = 2 * tid; i < nq; i += 2 * VIORB_FAST_THREADS) {
             const int ea = Q[i], eb = Q[min(i + 1, nq - 1)];
             const unsigned sc = fast_score16x2(T0 + ea, T0 + eb, o);
-            const int sa = (int)(short)(sc & 0xFFFF), sb = (int)sc >> 16;
+            const int sa = (int)(sc & 0xFFFF) - VIORB_FAST_SCORE_BIAS, sb = (int)(sc >> 16) - VIORB_FAST_SCORE_BIAS;
             if (sa >= th) S0[ea] = (uint8_t)sa;
             if (sb >= th) S0[eb] = (uint8_t)sb;
         }
