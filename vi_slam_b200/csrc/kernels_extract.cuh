@@ -22,6 +22,13 @@ __device__ __forceinline__ int reflect101_dev(int p, int n) {
     return p;
 }
 
+// reflect-101 of a position at most 3 outside [0, n): branch-free for n >= 4
+__device__ __forceinline__ int reflect101_near(int p, int n) {
+    if (n < 4) return reflect101_dev(p, n);
+    p = abs(p);
+    return min(p, 2 * (n - 1) - p);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Pyramid level l from level l-1.  One thread = 4 adjacent output pixels x VIORB_RS_ROWS rows: the
 // horizontal coefficients (11-bit, built on the host exactly like cv::resize does) are fetched once per
@@ -1194,15 +1201,16 @@ __global__ void __launch_bounds__(64) k_blur(ExtractGeom g, FrameSrc fs, BlurTil
     int pitch;
     const uint8_t* img = level_ptr(g, fs, l, f, pitch);
     uint8_t* dst = fs.blur + (size_t)f * g.arenaStride + L.off;
-    const int yEnd = min(y0 + VIORB_BLUR_TH, L.h);
+    const int Lw = L.w, Lh = L.h;                    // (L indexes kernel parameters by a run-time level: keep the loops off the constant bank)
+    const int yEnd = min(y0 + VIORB_BLUR_TH, Lh);
     const int nrows = yEnd - y0 + 6;
     const int NCH = VIORB_BLUR_SP / 16;              // 18 chunks per staged row
     for (int i = threadIdx.x; i < nrows * NCH; i += 64) {
         const int r = (i * 3641) >> 16, c = i - r * NCH;            // i / 18 for i < 2^13
         const int cx = X0 - 16 + 16 * c;
-        if (cx >= 0 && cx + 16 <= L.w) {
-            const int sy = reflect101_dev(y0 - 3 + r, L.h);
-            __pipeline_memcpy_async(tile + r * VIORB_BLUR_SP + 16 * c, img + (size_t)sy * pitch + cx, 16);
+        if (cx >= 0 && cx + 16 <= Lw) {
+            const int sy = reflect101_near(y0 - 3 + r, Lh);
+            __pipeline_memcpy_async(tile + r * VIORB_BLUR_SP + 16 * c, img + (unsigned)(sy * pitch + cx), 16);
         }
     }
     // Columns that no whole in-image chunk covers: the 3 reflected columns left of the image (first tile column) and
@@ -1210,23 +1218,22 @@ __global__ void __launch_bounds__(64) k_blur(ExtractGeom g, FrameSrc fs, BlurTil
     // pass: a lane-serial byte loop inside the chunk loop above made the whole warp wait ~300 instructions per chunk.
     {
         const int nL = X0 == 0 ? 3 : 0;
-        const int cR = max(L.w & ~15, X0 - 16), eR = min(L.w + 3, X0 + VIORB_BLUR_TW + 16);
+        const int cR = max(Lw & ~15, X0 - 16), eR = min(Lw + 3, X0 + VIORB_BLUR_TW + 16);
         const int nE = nL + max(eR - cR, 0);
         const int e = threadIdx.x & 31;
         if (e < nE) {
             const int colx = e < nL ? e - 3 : cR + (e - nL);
-            const int sx = reflect101_dev(colx, L.w);
-            for (int r = threadIdx.x >> 5; r < nrows; r += 2) {
-                const int sy = reflect101_dev(y0 - 3 + r, L.h);
-                tile[r * VIORB_BLUR_SP + (colx - X0 + 16)] = img[(size_t)sy * pitch + sx];
-            }
+            const uint8_t* scol = img + reflect101_near(colx, Lw);
+            uint8_t* tcol = tile + (colx - X0 + 16);
+            for (int r = threadIdx.x >> 5; r < nrows; r += 2)
+                tcol[r * VIORB_BLUR_SP] = scol[(unsigned)(reflect101_near(y0 - 3 + r, Lh) * pitch)];
         }
     }
     __pipeline_commit();
     __pipeline_wait_prior(0);
     __syncthreads();
     const int x0 = X0 + threadIdx.x * 4;
-    if (x0 >= L.w) return;
+    if (x0 >= Lw) return;
     const uint32_t* col = reinterpret_cast<const uint32_t*>(tile + 16 + threadIdx.x * 4);
     const int SPW = VIORB_BLUR_SP / 4;
     unsigned ring[7][4];
@@ -1264,7 +1271,7 @@ __global__ void __launch_bounds__(64) k_blur(ExtractGeom g, FrameSrc fs, BlurTil
 // separately (no FMA), round-half-even.  grid (ceil(outCap/8), B), block 256.
 // ---------------------------------------------------------------------------------------------
 #define VIORB_DESC_R 18                     // largest rounded sample offset: |(13,13)| = 18.4
-#define VIORB_DESC_PW 44                    // staged patch row: 37 bytes + alignment shift, in whole words (11: see i / 11 in k_describe)
+#define VIORB_DESC_PW 64                    // staged patch row: 37 bytes + alignment shift (<= 15) in four 16-byte chunks
 // round-half-even of |v| < 2^22 on the FMA pipe (F2I would go to the quarter-rate XU pipe): adding 1.5 * 2^23
 // leaves the integer in the low mantissa bits.  Same result as cvRound / lrintf.
 __device__ __forceinline__ int round_rn_magic(float v) {
@@ -1298,22 +1305,18 @@ __global__ void __launch_bounds__(256, VIORB_DESC_MINB) k_describe(ExtractGeom g
     }
     const KeptKp* kf = kept + (size_t)f * g.keptPerFrame;
     const int* s2k = slot2kept + (size_t)f * g.outCap;
-    const int NW = VIORB_DESC_PW / 4;
-    // stage the (2R+1)-row neighbourhood of keypoint k with aligned 4-byte asynchronous copies (the 512 samples would
-    // otherwise be 512 scattered byte requests to L1); returns the byte shift of the patch inside its first word
+    const int NCH = (2 * VIORB_DESC_R + 1) * (VIORB_DESC_PW / 16);
+    // stage the (2R+1)-row neighbourhood of keypoint k with aligned 16-byte asynchronous copies (the 512 samples would
+    // otherwise be 512 scattered byte requests to L1): 5 copies per lane.  A keypoint lies at least 19 pixels inside the
+    // level, so the rows exist; the last chunk of a row may run a few bytes into the next row of the level (never sampled).
     auto stage = [&](const KeptKp& k, uint8_t* P) {
         const LevelGeom& L = g.lv[k.score >> 16];
-        const uint8_t* img = fs.blur + (size_t)f * g.arenaStride + L.off;
-        const int xs = (k.x - VIORB_DESC_R) & ~3;
-        const uint8_t* src = img + (size_t)(k.y - VIORB_DESC_R) * L.pitch + xs;
         const int lp = L.pitch;
+        const uint8_t* src = fs.blur + (size_t)f * g.arenaStride + L.off + (size_t)((k.y - VIORB_DESC_R) * lp + ((k.x - VIORB_DESC_R) & ~15));
 #pragma unroll
-        for (int i0 = 0; i0 < (2 * VIORB_DESC_R + 1) * NW; i0 += 32) {
+        for (int i0 = 0; i0 < NCH; i0 += 32) {
             const int i = i0 + lane;
-            if (i < (2 * VIORB_DESC_R + 1) * NW) {
-                const int r = (i * 373) >> 12, c = i - r * NW;            // i / 11 (exact for i < 593; i < 407 here)
-                __pipeline_memcpy_async(P + 4 * i, src + (size_t)r * lp + 4 * c, 4);
-            }
+            if (i < NCH) __pipeline_memcpy_async(P + 16 * i, src + (unsigned)((i >> 2) * lp + 16 * (i & 3)), 16);
         }
         __pipeline_commit();
     };
@@ -1332,7 +1335,7 @@ __global__ void __launch_bounds__(256, VIORB_DESC_MINB) k_describe(ExtractGeom g
             __pipeline_wait_prior(0);
         }
         __syncwarp();
-        const int shift = (k.x - VIORB_DESC_R) & 3;
+        const int shift = (k.x - VIORB_DESC_R) & 15;
         const uint8_t* ctr = patch[wid][j & 1] + VIORB_DESC_R * VIORB_DESC_PW + VIORB_DESC_R + shift;
         const float a = k.c, b = k.s;
         int val = 0;
