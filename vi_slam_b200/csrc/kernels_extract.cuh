@@ -39,7 +39,10 @@ __device__ __forceinline__ int reflect101_near(int p, int n) {
 #ifndef VIORB_RS_ROWS
 #define VIORB_RS_ROWS 8
 #endif
-__global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int l, const int* __restrict__ xofs,
+#ifndef VIORB_RS_MINB
+#define VIORB_RS_MINB 6          // <= 40 registers (88 B of spills) keeps 6 CTAs per SM: 0.491 ms against 0.573 ms at the 59 registers of the unrolled rows
+#endif
+__global__ void __launch_bounds__(256, VIORB_RS_MINB) k_resize(ExtractGeom g, FrameSrc fs, int l, const int* __restrict__ xofs,
                                                 const short2* __restrict__ xalpha, const int* __restrict__ yofs,
                                                 const short2* __restrict__ ybeta) {
     const LevelGeom& L = g.lv[l];
@@ -97,7 +100,7 @@ __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int 
         int haveRow = -0x40000000;
         // h = (row sum) >> 4, the form the vertical pass consumes (each row sum is used by up to two output rows)
         auto hpass = [&](int sy, unsigned h[4]) {
-            const uint32_t* r = reinterpret_cast<const uint32_t*>(src + (size_t)sy * sp);
+            const uint32_t* r = reinterpret_cast<const uint32_t*>(src + (unsigned)(sy * sp));
             const unsigned a = __ldg(r + w0i), b = __ldg(r + w1i), c = __ldg(r + w2i);
 #pragma unroll
             for (int i = 0; i < 4; ++i)
@@ -105,10 +108,17 @@ __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int 
         };
         const int srcH1 = S.h - 1, opitch = L.pitch;
         uint8_t* d = dst + (size_t)dy0 * opitch + x4;
-        for (int r = 0; r < nrow; ++r) {
-            const int dy = dy0 + r;
-            const int sy = __ldg(yofs + L.yTab + dy);
-            const short2 bt = __ldg(ybeta + L.yTab + dy);
+        // the rows' source offsets and weights: the y tables are padded to whole groups of VIORB_RS_ROWS entries per level
+        static_assert(VIORB_RS_ROWS == 8, "two int4 loads per table");
+        const int4 syA = __ldg(reinterpret_cast<const int4*>(yofs + L.yTab + dy0)), syB = __ldg(reinterpret_cast<const int4*>(yofs + L.yTab + dy0) + 1);
+        const int4 btA = __ldg(reinterpret_cast<const int4*>(ybeta + L.yTab + dy0)), btB = __ldg(reinterpret_cast<const int4*>(ybeta + L.yTab + dy0) + 1);
+        const int syv[8] = {syA.x, syA.y, syA.z, syA.w, syB.x, syB.y, syB.z, syB.w};
+        const int btv[8] = {btA.x, btA.y, btA.z, btA.w, btB.x, btB.y, btB.z, btB.w};
+#pragma unroll
+        for (int r = 0; r < VIORB_RS_ROWS; ++r) {
+            if (r >= nrow) break;
+            const int sy = syv[r];
+            const int btr = btv[r];
             const int sy0 = min(max(sy, 0), srcH1), sy1 = min(max(sy + 1, 0), srcH1);
             if (haveRow == sy0) {
 #pragma unroll
@@ -119,7 +129,7 @@ __global__ void __launch_bounds__(256) k_resize(ExtractGeom g, FrameSrc fs, int 
             hpass(sy1, g1);
             haveRow = sy1;
             // (beta * h) >> 16 as the high half of (beta << 16) * h: beta in [0, 2048], h < 2^20, one IMAD.HI each
-            const unsigned B0 = (unsigned)(int)bt.x << 16, B1 = (unsigned)(int)bt.y << 16;
+            const unsigned B0 = (unsigned)btr << 16, B1 = (unsigned)btr & 0xFFFF0000u;
             uint32_t packed = 0;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
@@ -1029,6 +1039,9 @@ __device__ __forceinline__ void sincos_small(double x, double& sn, double& cs) {
     if ((n + 1) & 2) cs = -cs;
 }
 
+#ifndef VIORB_ORIENT_KPW
+#define VIORB_ORIENT_KPW 8                  // consecutive kept-arena slots handled by one warp
+#endif
 __global__ void __launch_bounds__(256) k_orient(ExtractGeom g, FrameSrc fs, const int* __restrict__ orientTab,
                                                 const uint8_t* __restrict__ slotLevel, KeptKp* __restrict__ kept,
                                                 const int* __restrict__ keptCount) {
@@ -1037,21 +1050,28 @@ __global__ void __launch_bounds__(256) k_orient(ExtractGeom g, FrameSrc fs, cons
     else (&wU[0][0])[threadIdx.x - 128] = orientTab[threadIdx.x];
     __syncthreads();
     const int lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int slot0 = (blockIdx.x * 8 + (threadIdx.x >> 5)) * VIORB_ORIENT_KPW;
     const int f = blockIdx.y + g.frame0;
-    if (slot >= g.keptPerFrame) return;
-    const int l = slotLevel[slot];                    // the level whose slice of the kept arena holds this slot
-    if (slot - g.lv[l].keptOff >= keptCount[f * g.nlevels + l]) return;
-    KeptKp* kp = kept + (size_t)f * g.keptPerFrame + slot;
-    int pitch;
-    const uint8_t* img = level_ptr(g, fs, l, f, pitch);
-    const int x = kp->x, y = kp->y;
-    int m10 = 0, m01 = 0;
-    {
+    if (slot0 >= g.keptPerFrame) return;
+    // The warp sums the moments of VIORB_ORIENT_KPW keypoints one after the other; lane j keeps keypoint j's pair, and the
+    // angle + sincos arithmetic (a third of the kernel when one lane did it per keypoint) runs once, on KPW lanes in parallel.
+    int my10 = 0, my01 = 0;
+    bool mine = false;
+    const int wc = lane & 7, rg = lane >> 3;
+#pragma unroll 1
+    for (int j = 0; j < VIORB_ORIENT_KPW; ++j) {
+        const int slot = slot0 + j;
+        if (slot >= g.keptPerFrame) break;
+        const int l = slotLevel[slot];                // the level whose slice of the kept arena holds this slot
+        if (slot - g.lv[l].keptOff >= keptCount[f * g.nlevels + l]) continue;
+        const KeptKp* kp = kept + (size_t)f * g.keptPerFrame + slot;
+        int pitch;
+        const uint8_t* img = level_ptr(g, fs, l, f, pitch);
+        const int x = kp->x, y = kp->y;
+        int m10 = 0, m01 = 0;
         // keypoints stay >= 19 px inside the level, so rows y - 15 .. y + 15 exist and none is the last one: the
         // aligned words around [x - 15, x + 15] never leave the image buffer.  pitch % 4 == 0: one shift for all rows.
-        const int wc = lane & 7, rg = lane >> 3;
-        const uint8_t* p = img + (size_t)(y - VIORB_HALF_PATCH) * pitch + (x - VIORB_HALF_PATCH);
+        const uint8_t* p = img + (unsigned)((y - VIORB_HALF_PATCH) * pitch + (x - VIORB_HALF_PATCH));
         const unsigned sh = ((unsigned)(uintptr_t)p & 3u) * 8u;
         const uint8_t* a = p - ((uintptr_t)p & 3) + 4 * wc;
         unsigned lo[8], hi[8];
@@ -1059,7 +1079,7 @@ __global__ void __launch_bounds__(256) k_orient(ExtractGeom g, FrameSrc fs, cons
         for (int i = 0; i < 8; ++i) {
             const int r = rg + 4 * i;
             if (r < 31) {
-                const uint32_t* q = reinterpret_cast<const uint32_t*>(a + (size_t)r * pitch);
+                const uint32_t* q = reinterpret_cast<const uint32_t*>(a + (unsigned)(r * pitch));
                 lo[i] = __ldg(q);
                 hi[i] = __ldg(q + 1);
             } else { lo[i] = hi[i] = 0; }
@@ -1075,11 +1095,13 @@ __global__ void __launch_bounds__(256) k_orient(ExtractGeom g, FrameSrc fs, cons
                 m01 += v * sumI;
             }
         }
+        m10 = __reduce_add_sync(0xffffffffu, m10);
+        m01 = __reduce_add_sync(0xffffffffu, m01);
+        if (lane == j) { my10 = m10; my01 = m01; mine = true; }
     }
-    m10 = __reduce_add_sync(0xffffffffu, m10);
-    m01 = __reduce_add_sync(0xffffffffu, m01);
-    if (lane == 0) {
-        const float ang = fast_atan2_deg((float)m01, (float)m10);
+    if (mine) {
+        KeptKp* kp = kept + (size_t)f * g.keptPerFrame + slot0 + lane;
+        const float ang = fast_atan2_deg((float)my01, (float)my10);
         const float factorPI = (float)(3.14159265358979323846 / 180.0);
         double sn, cs;
         sincos_small((double)__fmul_rn(ang, factorPI), sn, cs);

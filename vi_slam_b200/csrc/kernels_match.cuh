@@ -478,9 +478,12 @@ __global__ void __launch_bounds__(256, VIORB_REFINE_MINB) k_stereo_refine(Stereo
             const uint8_t* imL = level_ptr(g, fsL, lv, f, pl);
             const uint8_t* imR = level_ptr(g, fsR, lv, f, pr);
             const int cL = imL[(size_t)cv * pl + cu];
-            int cR[11], acc[11];
+            // |(a - cL) - (b - cR_k)| = |(a + cR_k - cL) - b|: one add and one VABSDIFF (absolute difference + accumulate) per
+            // (pixel, shift) instead of two subtractions, IABS, select and add
+            int tk[11];
+            unsigned acc[11];
 #pragma unroll
-            for (int k = 0; k < 11; ++k) { cR[k] = imR[(size_t)cv * pr + cr + k - 5]; acc[k] = 0; }
+            for (int k = 0; k < 11; ++k) { tk[k] = (int)imR[(unsigned)(cv * pr + cr + k - 5)] - cL; acc[k] = 0u; }
             // the four passes over the 121 patch pixels are unrolled so that all 48 byte loads of a lane are in flight
             // together (the kernel is load-latency bound)
 #pragma unroll
@@ -488,13 +491,14 @@ __global__ void __launch_bounds__(256, VIORB_REFINE_MINB) k_stereo_refine(Stereo
                 const int p = min(lane + 32 * it, 120);
                 const bool on = lane + 32 * it < 121;
                 const int dy = p / 11 - 5, dx = p % 11 - 5;
-                const int a = (int)imL[(size_t)(cv + dy) * pl + cu + dx] - cL;
-                const uint8_t* rr = imR + (size_t)(cv + dy) * pr + cr + dx - 5;
+                const int a = (int)imL[(unsigned)((cv + dy) * pl + cu + dx)];
+                const uint8_t* rr = imR + (unsigned)((cv + dy) * pr + cr + dx - 5);
+                int b[11];
 #pragma unroll
-                for (int k = 0; k < 11; ++k) {
-                    const int b = (int)rr[k] - cR[k];
-                    const int d = a - b;
-                    acc[k] += on ? (d < 0 ? -d : d) : 0;
+                for (int k = 0; k < 11; ++k) b[k] = (int)rr[k];
+                if (on) {
+#pragma unroll
+                    for (int k = 0; k < 11; ++k) acc[k] = __sad(a + tk[k], b[k], acc[k]);
                 }
             }
 #pragma unroll
@@ -502,7 +506,7 @@ __global__ void __launch_bounds__(256, VIORB_REFINE_MINB) k_stereo_refine(Stereo
             int bestS = 0x7fffffff, bestInc = 0;
 #pragma unroll
             for (int k = 0; k < 11; ++k)
-                if (acc[k] < bestS) { bestS = acc[k]; bestInc = k - 5; }
+                if ((int)acc[k] < bestS) { bestS = (int)acc[k]; bestInc = k - 5; }
             if (bestInc != -5 && bestInc != 5) {
                 float d1 = 0.f, d2 = 0.f, d3 = 0.f;
 #pragma unroll

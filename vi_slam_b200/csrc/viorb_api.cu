@@ -269,6 +269,8 @@ void build_resize_tables(int sw, int sh, int dw, int dh, ResizeTabs& t) {
         t.yofs.push_back(sy);
         t.ybeta.push_back(make_short2(sat_short((1.f - fy) * 2048), sat_short(fy * 2048)));
     }
+    // k_resize fetches the VIORB_RS_ROWS entries of a thread's rows with vector loads
+    while (t.yofs.size() % VIORB_RS_ROWS) { t.yofs.push_back(0); t.ybeta.push_back(make_short2(2048, 0)); }
 }
 
 int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
@@ -559,7 +561,7 @@ int run_pipeline(viorb_extractor* ex, int f0, int n, int lap0, int lap1) {
         }
     }
     if (tm) CU(cudaEventRecord(ex->evX[3], st));
-    VIORB_LAUNCH(k_orient, dim3((g.keptPerFrame + 7) / 8, n), dim3(256), 0, st, g, fs, ex->dOrientTab.p, ex->dSlotLevel.p, ex->dKept.p,
+    VIORB_LAUNCH(k_orient, dim3((g.keptPerFrame + 8 * VIORB_ORIENT_KPW - 1) / (8 * VIORB_ORIENT_KPW), n), dim3(256), 0, st, g, fs, ex->dOrientTab.p, ex->dSlotLevel.p, ex->dKept.p,
                  ex->dKeptCount.p);
     if (tm) CU(cudaEventRecord(ex->evX[4], st));
     VIORB_LAUNCH(k_emit, dim3(n), dim3(256), 0, st, g, ex->dKept.p, ex->dKeptCount.p, lap0, lap1, ex->dKps.p,
