@@ -450,7 +450,7 @@ __global__ void __launch_bounds__(256, VIORB_COARSE_MINB) k_stereo_coarse(Stereo
 // grid (ceil(outCap/8), nFrames), block 256.
 // ---------------------------------------------------------------------------------------------
 #ifndef VIORB_REFINE_MINB
-#define VIORB_REFINE_MINB 5      // <= 51 registers: 0.240 -> 0.218 ms against the unconstrained 64-register build (latency bound: occupancy pays)
+#define VIORB_REFINE_MINB 6      // <= 40 registers (36 B of spills): the kernel is a chain of dependent loads per keypoint, occupancy pays (0.197 -> 0.180 ms against 5 CTAs per SM; 8 CTAs at 32 registers: 0.199)
 #endif
 __global__ void __launch_bounds__(256, VIORB_REFINE_MINB) k_stereo_refine(StereoParams sp, ExtractGeom g, FrameSrc fsL, FrameSrc fsR,
                                                        const viorb_keypoint* __restrict__ kl, const int* __restrict__ nL,
