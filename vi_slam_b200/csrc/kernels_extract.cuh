@@ -191,26 +191,6 @@ __global__ void __launch_bounds__(256, VIORB_RS_MINB) k_resize(ExtractGeom g, Fr
 #define VIORB_FAST_THREADS 256
 #endif
 
-__device__ __forceinline__ int fast_score16(const uint8_t* p, const int* o) {
-    const int v = p[0];
-    int d[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) d[k] = v - (int)p[o[k]];
-    int t[16], u[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        t[k] = __vimin3_s32(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-        u[k] = __vimax3_s32(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-    }
-    int a = -256, b = 256;
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        a = max(a, __vimin3_s32(t[k], t[(k + 3) & 15], t[(k + 6) & 15]));
-        b = min(b, __vimax3_s32(u[k], u[(k + 3) & 15], u[(k + 6) & 15]));
-    }
-    return max(a, -b) - 1;
-}
-
 // cornerScore<16> of TWO pixels at once in s16x2 lanes (pixel A low, pixel B high): the 96 min/max of the
 // arc network are shared.  Every lane carries its value + 256: centre - ring pixel + 256 lies in [1, 511], so ONE 32-bit
 // multiply-add per pixel forms both lanes' differences without a borrow between them (the packed subtraction
@@ -286,7 +266,7 @@ __device__ __forceinline__ unsigned fast_pretest2(unsigned c, unsigned up, unsig
 #ifndef VIORB_FAST_MAXAREA
 #define VIORB_FAST_MAXAREA 7168                             // the host shortens strips of tall cell rows to this many pixels
 #endif
-__host__ __device__ inline size_t fast_smem_bytes(int /*tileW*/, int tileH, int area) {
+__host__ __device__ inline size_t fast_smem_bytes(int tileH, int area) {
     return (size_t)tileH * VIORB_FAST_TP + (size_t)(tileH - 4) * VIORB_FAST_TP +   // pixel tile (rh + 6 rows), score tile (rh + 2 rows)
            (size_t)2 * area + 32;                                                   // queue (2 B / px); the survivors reuse the pixel tile
 }

@@ -401,7 +401,7 @@ int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
     g.tileH = maxRH + 6;
     g.maxNodes = maxNodes;
     g.arenaStride = off;
-    ex->fastSmem = fast_smem_bytes(g.tileW, g.tileH, maxArea);
+    ex->fastSmem = fast_smem_bytes(g.tileH, maxArea);
     ex->octSmem = octree_smem_bytes(maxNodes, VIORB_OCT_LIGHT_PYR_CELLS);
     ex->octSmemDense = octree_smem_bytes(maxNodes, VIORB_OCT_PYR_CELLS);
     if (ex->octSmemDense > 220 * 1024) return fail(VIORB_E_ARG, "nfeatures too large for the quadtree's shared memory");

@@ -49,7 +49,7 @@ struct ExtractGeom {
     int totalCells;
     int candPerFrame, keptPerFrame;
     int outCap;            // per-frame output capacity (keypoints)
-    int tileW, tileH;      // FAST smem tile (max cell region + 6)
+    int tileW, tileH;      // widest / tallest FAST strip region + 6 (k_fast's tiles have tileH rows of VIORB_FAST_TP bytes)
     int maxNodes;          // octree node capacity in shared memory
     int frame0;            // first frame of the batch this launch works on (chunked host batches)
     size_t arenaStride;    // bytes per frame in the pyramid and blur arenas
