@@ -643,6 +643,7 @@ __device__ __forceinline__ void octree_body(const ExtractGeom& g, const uint32_t
                 pth = pth * 4 + q;
             }
             c = cell_idx(D0, r, pth);
+            kn[k] = (uint16_t)((r << (2 * D0)) + pth);          // the key's leaf cell (< PYR_CELLS): assign_keys finds its node from it
         }
         warp_add(pyr, c);
     }
@@ -663,7 +664,9 @@ __device__ __forceinline__ void octree_body(const ExtractGeom& g, const uint32_t
     int live = sh_live;
     bool careful = false;
     bool usePyr = true;
-    // (depth, root, path) -> node table over the pyramid's cells (-1 = split further), then every key walks down to its node
+    // (depth, root, path) -> node table over the pyramid's cells (-1 = split further), then every key finds its node among the
+    // ancestors of its leaf cell (recorded by the counting pass: ancestor at depth d = leaf >> 2 (D0 - d), no second walk over
+    // the midpoints and no second read of the key)
     auto assign_keys = [&](const OctBounds* /*B*/, const int* codes, int nLive) {
         for (int i = tid; i < pyrTotal; i += nth) pyr[i] = -1;
         __syncthreads();
@@ -673,17 +676,10 @@ __device__ __forceinline__ void octree_body(const ExtractGeom& g, const uint32_t
         }
         __syncthreads();
         for (int k = tid; k < n; k += nth) {
-            const uint32_t e = keys[k];
-            const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
-            const int r = min((int)__fdiv_rn((float)x, hX), nIni - 1);
-            const OctBounds b = sh_rootB[r];
-            int ulx = b.ulx, brx = b.brx, uly = b.uly, bry = b.bry, pth = 0, d = 0, t;
-            while ((t = pyr[cell_idx(d, r, pth)]) < 0 && d < D0) {
-                const int mx = ulx + ((brx - ulx + 1) >> 1), my = uly + ((bry - uly + 1) >> 1);
-                int q = 0;
-                if (x < mx) brx = mx; else { ulx = mx; q = 1; }
-                if (y < my) bry = my; else { uly = my; q += 2; }
-                pth = pth * 4 + q;
+            const int leaf = kn[k];
+            int d = 0, off = 0, t;
+            while ((t = pyr[off + (leaf >> (2 * (D0 - d)))]) < 0 && d < D0) {
+                off += nIni << (2 * d);
                 ++d;
             }
             if (t < 0) { atomicOr(status, 8); t = 0; }          // cannot happen: the leaves partition the keys
