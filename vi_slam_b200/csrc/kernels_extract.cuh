@@ -500,10 +500,12 @@ __global__ void __launch_bounds__(VIORB_FAST_THREADS) k_fast(ExtractGeom g, Fram
 
 struct OctBounds { short ulx, uly, brx, bry; };
 
-__host__ __device__ inline size_t octree_smem_bytes(int nc, int pyrCells) {
+// lutInts: the per-axis leaf tables of the counting pass (4 B per key column + 2 B per key row of the widest level, in ints)
+__host__ __device__ inline int octree_lut_ints(int nx, int ny) { return nx + (ny + 1) / 2 + 4; }
+__host__ __device__ inline size_t octree_smem_bytes(int nc, int pyrCells, int lutInts) {
     // bounds[2][nc] (8 B) + cnt[2][nc] + child[4 nc] + rank[nc] + aux0[nc] + aux1[nc] + newIdx[nc] + child2[4 nc] + code[2][nc]
     // + the count pyramid (VIORB_OCT_PYR_INTS)
-    return (size_t)nc * (16 + 8 + 16 + 4 + 4 + 4 + 4 + 16 + 8) + 64 + (size_t)(pyrCells * 4 / 3 + 8) * 4;
+    return (size_t)nc * (16 + 8 + 16 + 4 + 4 + 4 + 4 + 16 + 8) + 64 + (size_t)(pyrCells * 4 / 3 + 8 + lutInts) * 4;
 }
 
 // exclusive scan of a[0..m) in place by the whole CTA; returns the total (all threads).
@@ -625,25 +627,43 @@ __device__ __forceinline__ void octree_body(const ExtractGeom& g, const uint32_t
         sh_rootB[i] = b;
     }
     for (int i = tid; i < pyrTotal; i += nth) pyr[i] = 0;
+    // A key's leaf cell = (root << 2 D0) + path, two path bits per level: bit 0 from the x comparisons, bit 1 from the y
+    // comparisons of DivideNode (:474-475, :506-517).  The x bits (and the root) depend on x alone, the y bits on y alone (all
+    // roots span the full height), so the D0-level descent is done once per key COLUMN and once per key ROW into two tables,
+    // and the counting pass is two table reads and an OR per key.
+    uint32_t* lutX = reinterpret_cast<uint32_t*>(pyr + PYR_CELLS * 4 / 3 + 8);
+    const int nX = L.maxBX - VIORB_MINB, nY = L.maxBY - VIORB_MINB;
+    uint16_t* lutY = reinterpret_cast<uint16_t*>(lutX + nX);
+    __syncthreads();                                   // sh_rootB
+    for (int x = tid; x < nX; x += nth) {
+        const int r = min((int)__fdiv_rn((float)x, hX), nIni - 1);
+        int ul = sh_rootB[r].ulx, br = sh_rootB[r].brx, bits = 0;
+        for (int d = 0; d < D0; ++d) {
+            const int m = ul + ((br - ul + 1) >> 1);
+            bits <<= 2;
+            if (x < m) br = m; else { ul = m; bits |= 1; }
+        }
+        lutX[x] = (uint32_t)((r << (2 * D0)) | bits);
+    }
+    for (int y = tid; y < nY; y += nth) {
+        int ul = 0, br = nY, bits = 0;
+        for (int d = 0; d < D0; ++d) {
+            const int m = ul + ((br - ul + 1) >> 1);
+            bits <<= 2;
+            if (y < m) br = m; else { ul = m; bits |= 2; }
+        }
+        lutY[y] = (uint16_t)bits;
+    }
     __syncthreads();
+    const int offD0 = lvl_off(D0);
     for (int base = 0; base < n; base += nth) {
         const int k = base + tid;
         int c = -1;
         if (k < n) {
             const uint32_t e = keys[k];
-            const int x = e & 0xFFF, y = (e >> 12) & 0xFFF;
-            const int r = min((int)__fdiv_rn((float)x, hX), nIni - 1);
-            const OctBounds b = sh_rootB[r];
-            int ulx = b.ulx, brx = b.brx, uly = b.uly, bry = b.bry, pth = 0;
-            for (int d = 0; d < D0; ++d) {
-                const int mx = ulx + ((brx - ulx + 1) >> 1), my = uly + ((bry - uly + 1) >> 1);
-                int q = 0;
-                if (x < mx) brx = mx; else { ulx = mx; q = 1; }
-                if (y < my) bry = my; else { uly = my; q += 2; }
-                pth = pth * 4 + q;
-            }
-            c = cell_idx(D0, r, pth);
-            kn[k] = (uint16_t)((r << (2 * D0)) + pth);          // the key's leaf cell (< PYR_CELLS): assign_keys finds its node from it
+            const int leaf = (int)(lutX[e & 0xFFF] | lutY[(e >> 12) & 0xFFF]);
+            c = offD0 + leaf;
+            kn[k] = (uint16_t)leaf;                    // assign_keys finds the key's node from its leaf cell
         }
         warp_add(pyr, c);
     }

@@ -402,8 +402,9 @@ int build_geometry(viorb_extractor* ex, int W, int H, ResizeTabs& tabs) {
     g.maxNodes = maxNodes;
     g.arenaStride = off;
     ex->fastSmem = fast_smem_bytes(g.tileH, maxArea);
-    ex->octSmem = octree_smem_bytes(maxNodes, VIORB_OCT_LIGHT_PYR_CELLS);
-    ex->octSmemDense = octree_smem_bytes(maxNodes, VIORB_OCT_PYR_CELLS);
+    const int lutInts = octree_lut_ints(g.lv[0].maxBX - VIORB_MINB, g.lv[0].maxBY - VIORB_MINB);     // level 0 is the widest and tallest
+    ex->octSmem = octree_smem_bytes(maxNodes, VIORB_OCT_LIGHT_PYR_CELLS, lutInts);
+    ex->octSmemDense = octree_smem_bytes(maxNodes, VIORB_OCT_PYR_CELLS, lutInts);
     if (ex->octSmemDense > 220 * 1024) return fail(VIORB_E_ARG, "nfeatures too large for the quadtree's shared memory");
     if (maxRW > VIORB_FAST_MAXRW || maxRH > 127) return fail(VIORB_E_ARG, "FAST cell larger than supported");
     return VIORB_OK;
