@@ -21,6 +21,23 @@ def test_extract_stages(emu, w, h, nf, lap, seed):
     parity.check_extract(synthetic.make_frame(seed, w, h), nf, lap, lib_path=emu)
 
 
+@pytest.mark.parametrize("seed", range(8))
+def test_extract_random_geometries(emu, seed):
+    """Random image sizes, feature counts and frame classes: strip geometry of k_fast (cell width 30..59, clipped last cells),
+    quadtree root counts 1..4+ and the per-axis leaf tables, patches next to the 19-pixel border."""
+    rng = np.random.default_rng(100 + seed)
+    w, h = int(rng.integers(96, 460)), int(rng.integers(80, 300))
+    if seed % 3 == 2:
+        w, h = h, w + 40                                            # portrait: one quadtree root
+    nf = int(rng.integers(150, 1800))
+    img = synthetic.make_frame(200 + seed, w, h)
+    if seed % 4 == 1:
+        img = rng.integers(0, 256, (h, w), dtype=np.uint8)          # noise: the dense quadtree launch, long FAST queues
+    if seed % 4 == 3:
+        img = (img.astype(np.float32) * 0.1 + 90).astype(np.uint8)  # low texture: minThFAST cells
+    parity.check_extract(img, nf, (0, 0) if seed % 2 else (w // 4, w // 2), lib_path=emu)
+
+
 def test_extract_edge_cases(emu):
     from vi_slam_b200 import FExtractor
     ex = FExtractor(500, 1.2, 8, 20, 7, max_size=(320, 240), lib_path=emu)

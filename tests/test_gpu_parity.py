@@ -56,6 +56,22 @@ def test_extract_stages_vs_oracle(w, h, nf, lap, seed):
     print("descriptor rows differing from the oracle:", ndiff)
 
 
+@pytest.mark.parametrize("seed", range(8))
+def test_extract_random_geometries(seed):
+    """The random sizes / feature counts / frame classes of tests/test_emu_parity.py on the CUDA build."""
+    rng = np.random.default_rng(100 + seed)
+    w, h = int(rng.integers(96, 460)), int(rng.integers(80, 300))
+    if seed % 3 == 2:
+        w, h = h, w + 40
+    nf = int(rng.integers(150, 1800))
+    img = _syn().make_frame(200 + seed, w, h)
+    if seed % 4 == 1:
+        img = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    if seed % 4 == 3:
+        img = (img.astype(np.float32) * 0.1 + 90).astype(np.uint8)
+    parity.check_extract(img, nf, (0, 0) if seed % 2 else (w // 4, w // 2), max_desc_diff=2)
+
+
 def test_extract_many_seeds_counts_descriptor_differences():
     """Integer outputs exact on every frame; descriptor differences (cosf/sinf rounding) are counted."""
     from vi_slam_b200 import FExtractor
